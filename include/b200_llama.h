@@ -1,0 +1,222 @@
+/*
+ * b200_llama.h — C ABI of the B200-native (sm_100a) LLaMA decoder hot path.
+ *
+ * Every entry point replaces one `launch*` template of the reference
+ * (Mr-wang27/llm-inference, `src/kernels/*.h`); the reference file:line each one
+ * stands in for is cited above it. Plain pointers and sizes only: no C++ types,
+ * no torch types. The reference's TensorWrapper-based templates are re-created on
+ * top of this ABI by the header shim in `llm-inference_b200/include/src/kernels/`.
+ *
+ * Conventions
+ *  - `dtype`: B200_F32 (float) or B200_F16 (IEEE half). All arithmetic accumulates in fp32.
+ *  - all data pointers are DEVICE pointers unless the name ends in `_host`.
+ *  - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream, which is
+ *    what the reference launches on).
+ *  - return value: 0 on success; >0 is a cudaError_t from the launch; <0 is one of the
+ *    B200_E* argument errors. Nothing allocates; scratch is passed in and sized by the
+ *    matching *_workspace_bytes() query.
+ *  - there is no CPU fallback anywhere: without a CUDA device every call returns an error.
+ */
+#ifndef B200_LLAMA_H
+#define B200_LLAMA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_F32 0
+#define B200_F16 1
+
+#define B200_OK 0
+#define B200_EINVAL (-1)       /* bad shape / null pointer / misalignment */
+#define B200_EUNSUPPORTED (-2) /* shape outside what the kernel covers */
+#define B200_EWORKSPACE (-3)   /* workspace missing or too small */
+
+/* library identity; b200_abi_version() bumps when a signature changes */
+int b200_abi_version(void);
+const char* b200_build_info(void);
+/* number of kernel launches issued through this library since load (or last reset) */
+uint64_t b200_launch_count(void);
+void b200_launch_count_reset(void);
+
+/* ------------------------------------------------------------------------------------
+ * a1  launchRMSNorm            src/kernels/rmsnorm_kernel.cu:175 (decl rmsnorm_kernel.h:12-17)
+ * in place x <- x * rsqrt(mean(x^2)+eps) * gamma ; residual_out <- x (pre-norm) if non-NULL
+ * x, residual_out: [n_tokens, hidden]; gamma: [hidden]
+ * ------------------------------------------------------------------------------------ */
+int b200_rmsnorm(void* x, void* residual_out, const void* gamma, int n_tokens, int hidden,
+                 float eps, int dtype, void* stream);
+
+/* a5  launchFusedAddBiasResidualRMSNorm   src/kernels/fused_addresidual_norm.cu:193
+ * residual <- residual + out (+ bias) ; out <- RMSNorm(residual) * gamma.  bias may be NULL. */
+int b200_fused_add_bias_residual_rmsnorm(void* residual, void* out, const void* bias,
+                                         const void* gamma, int n_tokens, int hidden, float eps,
+                                         int dtype, void* stream);
+
+/* a7  launchAddResidual        src/kernels/add_residual.cu:58    out <- out + residual */
+int b200_add_residual(const void* residual, void* out, int n_tokens, int hidden, int dtype,
+                      void* stream);
+
+/* a6  launchAct (SwiGLU)       src/kernels/act_kernel.cu:57
+ * gate_up: [n_tokens, 2, inter] (gate block, then up block); out: [n_tokens, inter]
+ * out = gate/(1+exp(-gate)) * up */
+int b200_swiglu(const void* gate_up, void* out, int n_tokens, int inter, int dtype, void* stream);
+
+/* a3  launchRoPE               src/kernels/qkv_bias_and_RoPE.cu:410
+ * rotate-half RoPE, in place, on q and k of the newest token (position step-1).
+ * qkv: token-major [batch, head_num + 2*kv_head_num, head_size]. */
+int b200_rope_decode(void* qkv, int batch, int head_num, int kv_head_num, int head_size, int step,
+                     int rotary_dim, float rotary_base, int dtype, void* stream);
+
+/* a8  launchAddFusedQKVBiasTransposeAndRoPE   src/kernels/qkv_bias_and_RoPE.cu:248
+ * QKV [token_num, head_num+2*kv_head_num, head_size] (no padding) ->
+ * q [batch, head_num, seq_len, head_size], k,v [batch, kv_head_num, seq_len, head_size];
+ * optional bias [(head_num+2*kv_head_num)*head_size]; RoPE on q,k at
+ * history_len[b] + local token index; padded rows of q/k/v are left untouched. */
+int b200_qkv_bias_rope_transpose(void* q, void* k, void* v, const void* qkv, const void* bias,
+                                 const int* padding_offset, const int* history_len,
+                                 const int* input_len, int batch, int seq_len, int token_num,
+                                 int head_num, int kv_head_num, int head_size, int rotary_dim,
+                                 float rotary_base, int dtype, void* stream);
+
+/* a9  launchConcatKVCache      src/kernels/concat_past_kv.cu:103
+ * k_src,v_src [batch, kv_head_num, max_q_len, head_size] -> cache layer slice
+ * [batch, kv_head_num, max_seq_len, head_size] at row history_len[b]+t for t < cur_len[b].
+ * k_cache/v_cache point at the START of the whole cache; layer_offset is in elements. */
+int b200_concat_kv_cache(const void* k_src, const void* v_src, void* k_cache, void* v_cache,
+                         size_t layer_offset, const int* cur_query_len, const int* history_len,
+                         int batch, int kv_head_num, int max_q_len, int max_seq_len, int head_size,
+                         int dtype, void* stream);
+
+/* a10 launchRepeatKVCache      src/kernels/repeat_kv.cu:76
+ * cache layer slice -> dense [batch, head_num, max_k_len, head_size], head j <- j/(head_num/kv_head_num),
+ * rows < context_len[b] only (other rows untouched). */
+int b200_repeat_kv_cache(const void* k_cache, const void* v_cache, void* k_dst, void* v_dst,
+                         size_t layer_offset, const int* context_len, int batch, int head_num,
+                         int kv_head_num, int max_seq_len, int max_k_len, int head_size, int dtype,
+                         void* stream);
+
+/* a12 launchTransposeOutRemovePadding   src/kernels/fused_transpose_and_remv_pad.cu:51
+ * src [batch, head_num, seq_len, head_size] -> dst [token_num, head_num*head_size] */
+int b200_transpose_remove_padding(const void* src, void* dst, const int* padding_offset,
+                                  int token_num, int batch, int seq_len, int head_num,
+                                  int head_size, int dtype, void* stream);
+
+/* a13 launchCalPaddingoffset   src/kernels/cal_paddingoffset.cu:74   (int32, bit-exact)
+ * padding_offset [batch*max_q_len] (first sum(len) entries written), cum_seqlens [batch+1] */
+int b200_cal_padding_offset(int* padding_offset, int* cum_seqlens, const int* input_lens,
+                            int batch, int max_q_len, void* stream);
+
+/* a13 launchBuildCausalMasks   src/kernels/build_causal_mask.cu:50   (0/1 values, bit-exact)
+ * mask [batch, max_q_len, max_k_len]. history_visible=1: the unit test's CPU predicate
+ * (tests/unittests/test_casual_mask.cu:12-32: q<qlen && k<klen && k<=q+klen-qlen);
+ * history_visible=0: the GPU kernel's extra `k >= klen-qlen` clause (build_causal_mask.cu:29). */
+int b200_build_causal_mask(void* mask, const int* q_lens, const int* k_lens, int batch,
+                           int max_q_len, int max_k_len, int history_visible, int dtype,
+                           void* stream);
+
+/* a11 launchScaleMaskAndSoftmax   src/kernels/attn_softmax_kernel.cu:337
+ * score = softmax_row(scale*qk + (1-mask)*(-10000)), denominator + 1e-6; may run in place.
+ * qk/score [batch, head_num, q_len, k_len]; mask [batch, q_len, k_len]. */
+int b200_scale_mask_softmax(const void* qk, const void* mask, void* score, int batch, int head_num,
+                            int q_len, int k_len, float scale, int dtype, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * a2  launchLinearGemm         src/kernels/linear.cu:39  (cublasWrapper::Gemm cublas_utils.cc:32)
+ * y[n_tokens, N] = x[n_tokens, K] * op(W) (+ bias[N] if non-NULL)
+ *   trans_b = 1: W is [N, K] row-major (the layout of every engine call site)
+ *   trans_b = 0: W is [K, N] row-major (tests/unittests/test_linear.cu)
+ * Dispatch: n_tokens <= B200_GEMV_MAX_TOKENS and trans_b -> weight-streaming GEMV (bulk-async
+ * smem ring); fp16 with large n_tokens -> tcgen05/TMEM GEMM; everything else -> SIMT tiled GEMM.
+ * workspace may be NULL when b200_linear_workspace_bytes() returns 0.
+ * ------------------------------------------------------------------------------------ */
+#define B200_GEMV_MAX_TOKENS 8
+size_t b200_linear_workspace_bytes(int n_tokens, int N, int K, int trans_b, int dtype);
+int b200_linear(const void* x, const void* W, const void* bias, void* y, int n_tokens, int N, int K,
+                int trans_b, int dtype, void* workspace, size_t workspace_bytes, void* stream);
+
+/* Fused decode-time linears (engine path; the unfused reference sequence they replace is cited).
+ * All take W [N, K] row-major, n_tokens <= B200_GEMV_MAX_TOKENS.
+ *
+ * flags for b200_gemv_fused: */
+#define B200_GEMV_NORM 1u     /* prologue: x <- (x*inv_rms)*gamma in smem (x itself untouched)  */
+#define B200_GEMV_RESIDUAL 2u /* epilogue: y <- y_in + W x (y is read-modify-write)             */
+#define B200_GEMV_SWIGLU 4u   /* W = [2*N, K] (gate rows, then up rows); y[N] = silu(g)*u        */
+#define B200_GEMV_ROPE_KV 8u  /* W = qkv; epilogue rotates q,k (pos step-1), writes qkv to y and */
+                              /* k,v also straight into the KV cache row step-1                 */
+#define B200_GEMV_NORM_GFIRST 16u /* with NORM: (gamma*x)*inv_rms, the rounding order of        */
+                                  /* fused_addresidual_norm.cu:119-124 instead of rmsnorm's     */
+typedef struct b200_gemv_args {
+    const void* x;     /* [n_tokens, K]                                   */
+    const void* W;     /* [N(or 2N), K]                                   */
+    const void* bias;  /* [N] or NULL                                     */
+    void* y;           /* [n_tokens, N]                                   */
+    const void* gamma; /* [K], with B200_GEMV_NORM                        */
+    float eps;
+    int n_tokens, N, K;
+    unsigned flags;
+    /* B200_GEMV_ROPE_KV only: N = (head_num+2*kv_head_num)*head_size */
+    void* k_cache_layer; /* [batch, kv_head_num, max_seq_len, head_size] */
+    void* v_cache_layer;
+    int head_num, kv_head_num, head_size, max_seq_len, step, rotary_dim;
+    float rotary_base;
+    const int* step_dev; /* optional DEVICE int overriding `step` (CUDA-graph replay) */
+} b200_gemv_args;
+int b200_gemv_fused(const b200_gemv_args* args, int dtype, void* stream);
+
+/* launchLinearStridedBatchGemm  src/kernels/linear.cu:127 (cublas_utils.cc:75)
+ * C[b] = A[b] * op(B[b]) for b < batch_count; A [m,k] row-major; B [n,k] if trans_b else [k,n];
+ * C [m,n]; strides in elements (the reference's strideC defect D14 is not reproduced). */
+int b200_batched_gemm(const void* A, const void* B, void* C, int batch_count, int m, int n, int k,
+                      int trans_b, int dtype, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * a4  launchDecoderMaskedMHA   src/kernels/fused_decoder_self_attention.cu:317
+ * One new token per sequence. qkv [batch, head_num+2*kv_head_num, head_size] (token-major),
+ * caches point at the layer slice [batch, kv_head_num, max_seq_len, head_size].
+ * append_kv=1 (reference semantics): write k,v of the new token to row step-1, then attend over
+ * rows [0, step). append_kv=0: the row is already in the cache (fused QKV GEMV wrote it).
+ * out [batch, head_num*head_size]. softmax: max-subtracted, denominator + 1e-6 (:214).
+ * Split-KV: grid (batch*kv_head_num, n_splits); partials in workspace; combine kernel.
+ * ------------------------------------------------------------------------------------ */
+size_t b200_decode_attention_workspace_bytes(int batch, int head_num, int head_size, int step);
+int b200_decode_attention(const void* qkv, void* k_cache_layer, void* v_cache_layer, void* out,
+                          void* workspace, size_t workspace_bytes, int batch, int head_num,
+                          int kv_head_num, int head_size, int max_seq_len, int step, int append_kv,
+                          int dtype, void* stream);
+/* graph-replay form: `step_dev` (DEVICE int, may be NULL) overrides `step` at run time; the
+ * launch geometry is sized for `step` (an upper bound of *step_dev within the bucket). */
+int b200_decode_attention_ex(const void* qkv, void* k_cache_layer, void* v_cache_layer, void* out,
+                             void* workspace, size_t workspace_bytes, int batch, int head_num,
+                             int kv_head_num, int head_size, int max_seq_len, int step,
+                             const int* step_dev, int append_kv, int dtype, void* stream);
+
+/* Prefill attention without materialising scores / mask / repeated KV (replaces
+ * context_attention.cpp:136-161: RepeatKV + QK^T + ScaleMaskSoftmax + PV + transpose):
+ * q [batch, head_num, seq_len, head_size]; cache layer slice as above;
+ * out [token_num, head_num*head_size] (padding removed). Same -10000/1e-6 softmax contract. */
+int b200_context_attention(const void* q, const void* k_cache_layer, const void* v_cache_layer,
+                           void* out, const int* padding_offset, const int* input_len,
+                           const int* history_len, int batch, int seq_len, int token_num,
+                           int head_num, int kv_head_num, int head_size, int max_seq_len,
+                           int dtype, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * next-tier ops bracketing a decode step
+ * launchInputEmbedding   src/kernels/input_embedding.cu:30   out[t,:] = table[ids[t],:]
+ * greedy pick            src/kernels/topK.cu:147 (K=1 case): lowest index wins ties
+ * ------------------------------------------------------------------------------------ */
+int b200_embedding(const int* ids, const void* table, void* out, int n_tokens, int hidden,
+                   int vocab, int dtype, void* stream);
+int b200_argmax(const void* logits, int* out_ids, int batch, int vocab, int dtype, void* stream);
+/* top-K (K <= 8) values+ids per row, descending, ties -> lower index first */
+int b200_topk(const void* logits, int* out_ids, void* out_vals, int batch, int vocab, int k,
+              int dtype, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_LLAMA_H */

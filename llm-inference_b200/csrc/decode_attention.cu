@@ -1,0 +1,405 @@
+// Masked decode self-attention over the KV cache, split-KV (flash-decoding) form.
+// Replaces launchDecoderMaskedMHA (src/kernels/fused_decoder_self_attention.cu:80-291, 317-365):
+//   append k,v of the new token at row step-1; s_j = (q . K_j) * rsqrt(d), j < step;
+//   p = exp(s - max s) / (sum + 1e-6) (:203-221); out = sum_j p_j V_j (:272-287).
+// SURVEY defects D1-D6 resolved: kv head = q head / (h/hk), element-correct addressing, layer
+// slice includes kv_head_num, softmax over the full length, token-major qkv, fp16 implemented.
+//
+// HBM-bound: algorithmic bytes = 2*B*hk*step*d*sizeof(T). Layout of the work:
+//  * grid (B*hk, n_splits): one CTA streams one contiguous chunk of one kv head's keys/values
+//    and serves all G = h/hk query heads of that group from a single read (GQA reuse, so
+//    RepeatKV is never materialised);
+//  * a key row is PR 16-byte packets; PR lanes own one row, 32/PR rows per warp-wide load,
+//    kUnroll loads in flight per lane; dot products reduce with warp shuffles across the PR lanes;
+//  * every lane group runs its own online softmax (m, l, o[]) in fp32, merged by shuffles, then
+//    across warps through shared memory, then across splits by the combine kernel.
+#include "common.cuh"
+#include "launch_count.h"
+
+namespace b200 {
+
+constexpr int kAttnWarps = 4;
+constexpr int kUnroll = 4;
+
+struct AttnParams {
+    const void* qkv;  // [B, h+2hk, d]
+    void* k_cache;    // [B, hk, max_seq, d]
+    void* v_cache;
+    void* out;        // [B, h*d]
+    float* part_ml;   // [B, h, splits, 2]
+    float* part_o;    // [B, h, splits, d]
+    int batch, head_num, kv_head_num, head_size, max_seq_len, step;
+    const int* step_dev;
+    int append_kv;
+};
+
+// fp32 data keeps the accurate expf (1e-5 tolerance); half data uses the MUFU fast path
+template <typename T> __device__ __forceinline__ float fexp(float x);
+template <> __device__ __forceinline__ float fexp<float>(float x) { return expf(x); }
+template <> __device__ __forceinline__ float fexp<__half>(float x) { return __expf(x); }
+__device__ __forceinline__ float exp_guard(float m, float M) {
+    return (m == -INFINITY) ? 0.f : expf(m - M);
+}
+
+template <typename T, int G, int PR>
+__global__ void __launch_bounds__(kAttnWarps * 32)
+decode_attn_split_kernel(const AttnParams p) {
+    constexpr int E = DT<T>::kPer16B;
+    constexpr int KPI = 32 / PR;  // key rows per warp-wide load
+    constexpr int D = PR * E;     // head size
+    extern __shared__ float sm[];  // [kAttnWarps][G][2 + D]
+
+    pdl_wait();
+    const int step = p.step_dev ? *p.step_dev : p.step;
+    const int bh = blockIdx.x;
+    const int b = bh / p.kv_head_num, kvh = bh - b * p.kv_head_num;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int pi = lane % PR, ks = lane / PR;
+    const int qkv_heads = p.head_num + 2 * p.kv_head_num;
+    const T* tok = reinterpret_cast<const T*>(p.qkv) + (size_t)b * qkv_heads * D;
+    T* kc = reinterpret_cast<T*>(p.k_cache) + ((size_t)b * p.kv_head_num + kvh) * p.max_seq_len * D;
+    T* vc = reinterpret_cast<T*>(p.v_cache) + ((size_t)b * p.kv_head_num + kvh) * p.max_seq_len * D;
+
+    // keys of this split
+    const int splits = gridDim.y;
+    const int per = (step + splits - 1) / splits;
+    const int k0 = blockIdx.y * per;
+    const int k1 = min(step, k0 + per);
+
+    // append the new token's k,v (reference :170-172, :274-276) - only the CTA that will read it
+    if (p.append_kv && k0 <= step - 1 && step - 1 < k1) {
+        if (threadIdx.x < PR) {
+            st16(kc + (size_t)(step - 1) * D + threadIdx.x * E,
+                 ld16(tok + (size_t)(p.head_num + kvh) * D + threadIdx.x * E));
+        } else if (threadIdx.x >= 32 && threadIdx.x < 32 + PR) {
+            const int t = threadIdx.x - 32;
+            st16(vc + (size_t)(step - 1) * D + t * E,
+                 ld16(tok + (size_t)(p.head_num + p.kv_head_num + kvh) * D + t * E));
+        }
+        __syncthreads();
+    }
+
+    // q packets for the G heads of this kv group stay packed in T
+    Pack16 q[G];
+#pragma unroll
+    for (int g = 0; g < G; ++g) q[g] = ld16(tok + (size_t)(kvh * G + g) * D + pi * E);
+    const float scale = rsqrtf((float)D);
+
+    float m[G], l[G], o[G][E];
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+        m[g] = -INFINITY;
+        l[g] = 0.f;
+#pragma unroll
+        for (int e = 0; e < E; ++e) o[g][e] = 0.f;
+    }
+
+    // warp w takes key rows k0 + (it*kAttnWarps + w)*KPI*kUnroll + u*KPI + ks
+    for (int base = k0 + warp * KPI * kUnroll; base < k1; base += kAttnWarps * KPI * kUnroll) {
+        Pack16 kp[kUnroll], vp[kUnroll];
+        bool ok[kUnroll];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            const int key = base + u * KPI + ks;
+            ok[u] = key < k1;
+            if (ok[u]) kp[u] = ld16_stream(kc + (size_t)key * D + pi * E);
+        }
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            const int key = base + u * KPI + ks;
+            if (ok[u]) vp[u] = ld16_stream(vc + (size_t)key * D + pi * E);
+        }
+        float s[G][kUnroll];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+#pragma unroll
+            for (int g = 0; g < G; ++g) {
+                float d = ok[u] ? dot16<T>(kp[u], q[g], 0.f) : 0.f;
+#pragma unroll
+                for (int off = PR >> 1; off > 0; off >>= 1) d += __shfl_xor_sync(0xffffffffu, d, off);
+                s[g][u] = ok[u] ? d * scale : -INFINITY;
+            }
+        }
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+            float mn = m[g];
+#pragma unroll
+            for (int u = 0; u < kUnroll; ++u) mn = fmaxf(mn, s[g][u]);
+            if (mn != -INFINITY) {
+                const float corr = exp_guard(m[g], mn);
+                l[g] *= corr;
+#pragma unroll
+                for (int e = 0; e < E; ++e) o[g][e] *= corr;
+                m[g] = mn;
+#pragma unroll
+                for (int u = 0; u < kUnroll; ++u) {
+                    if (ok[u]) {
+                        const float pr = fexp<T>(s[g][u] - mn);
+                        l[g] += pr;
+                        float vf[E];
+                        Unpack<T>::get(vp[u], vf);
+#pragma unroll
+                        for (int e = 0; e < E; ++e) o[g][e] = fmaf(pr, vf[e], o[g][e]);
+                    }
+                }
+            }
+        }
+    }
+
+    // merge the KPI lane groups of the warp
+#pragma unroll
+    for (int off = PR; off < 32; off <<= 1) {
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+            const float mo = __shfl_xor_sync(0xffffffffu, m[g], off);
+            const float lo = __shfl_xor_sync(0xffffffffu, l[g], off);
+            const float M = fmaxf(m[g], mo);
+            const float a = exp_guard(m[g], M), bb = exp_guard(mo, M);
+            l[g] = l[g] * a + lo * bb;
+#pragma unroll
+            for (int e = 0; e < E; ++e) {
+                const float oo = __shfl_xor_sync(0xffffffffu, o[g][e], off);
+                o[g][e] = o[g][e] * a + oo * bb;
+            }
+            m[g] = M;
+        }
+    }
+    // across warps through shared memory
+    if (ks == 0) {
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+            float* dst = sm + ((size_t)warp * G + g) * (2 + D);
+            if (pi == 0) { dst[0] = m[g]; dst[1] = l[g]; }
+#pragma unroll
+            for (int e = 0; e < E; ++e) dst[2 + pi * E + e] = o[g][e];
+        }
+    }
+    __syncthreads();
+    pdl_launch_dependents();
+    for (int idx = threadIdx.x; idx < G * D; idx += blockDim.x) {
+        const int g = idx / D, e = idx - g * D;
+        float M = -INFINITY;
+#pragma unroll
+        for (int w = 0; w < kAttnWarps; ++w) M = fmaxf(M, sm[((size_t)w * G + g) * (2 + D)]);
+        float L = 0.f, O = 0.f;
+#pragma unroll
+        for (int w = 0; w < kAttnWarps; ++w) {
+            const float* src = sm + ((size_t)w * G + g) * (2 + D);
+            const float a = exp_guard(src[0], M);
+            L += src[1] * a;
+            O += src[2 + e] * a;
+        }
+        const int head = kvh * G + g;
+        if (splits == 1) {
+            reinterpret_cast<T*>(p.out)[((size_t)b * p.head_num + head) * D + e] =
+                DT<T>::from_f(O / (L + 1e-6f));
+        } else {
+            const size_t slot = ((size_t)b * p.head_num + head) * splits + blockIdx.y;
+            p.part_o[slot * D + e] = O;
+            if (e == 0) { p.part_ml[slot * 2] = M; p.part_ml[slot * 2 + 1] = L; }
+        }
+    }
+}
+
+// merge the per-split partials: grid B*h, one thread per output element
+template <typename T>
+__global__ void __launch_bounds__(128)
+decode_attn_combine_kernel(const float* __restrict__ part_ml, const float* __restrict__ part_o,
+                           T* __restrict__ out, int splits, int d) {
+    pdl_wait();
+    const size_t bh = blockIdx.x;
+    const float* ml = part_ml + bh * splits * 2;
+    float M = -INFINITY;
+    for (int s = 0; s < splits; ++s) M = fmaxf(M, ml[2 * s]);
+    float L = 0.f;
+    for (int s = 0; s < splits; ++s) L += ml[2 * s + 1] * exp_guard(ml[2 * s], M);
+    const float inv = 1.f / (L + 1e-6f);
+    pdl_launch_dependents();
+    for (int e = threadIdx.x; e < d; e += blockDim.x) {
+        float O = 0.f;
+        for (int s = 0; s < splits; ++s)
+            O += part_o[(bh * splits + s) * d + e] * exp_guard(ml[2 * s], M);
+        out[bh * d + e] = DT<T>::from_f(O * inv);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// generic path (any head size, e.g. the reference unit test's d = 4): one CTA per (b, head),
+// scores staged in a global fp32 scratch row. Not a performance path.
+// ------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(128)
+decode_attn_generic_kernel(const AttnParams p, float* __restrict__ scores) {
+    __shared__ float scratch[33];
+    pdl_wait();
+    const int step = p.step_dev ? *p.step_dev : p.step;
+    const int d = p.head_size;
+    const int b = blockIdx.x / p.head_num, head = blockIdx.x - b * p.head_num;
+    const int kvh = head / (p.head_num / p.kv_head_num);
+    const int qkv_heads = p.head_num + 2 * p.kv_head_num;
+    const T* tok = reinterpret_cast<const T*>(p.qkv) + (size_t)b * qkv_heads * d;
+    const T* q = tok + (size_t)head * d;
+    const T* knew = tok + (size_t)(p.head_num + kvh) * d;
+    const T* vnew = tok + (size_t)(p.head_num + p.kv_head_num + kvh) * d;
+    T* kc = reinterpret_cast<T*>(p.k_cache) + ((size_t)b * p.kv_head_num + kvh) * p.max_seq_len * d;
+    T* vc = reinterpret_cast<T*>(p.v_cache) + ((size_t)b * p.kv_head_num + kvh) * p.max_seq_len * d;
+    float* sc = scores + (size_t)blockIdx.x * p.max_seq_len;
+    const float scale = rsqrtf((float)d);
+    const bool use_new = p.append_kv != 0;
+
+    float mx = -INFINITY;
+    for (int j = threadIdx.x; j < step; j += blockDim.x) {
+        const T* kr = (use_new && j == step - 1) ? knew : kc + (size_t)j * d;
+        float acc = 0.f;
+        for (int e = 0; e < d; ++e) acc = fmaf(DT<T>::to_f(q[e]), DT<T>::to_f(kr[e]), acc);
+        acc *= scale;
+        sc[j] = acc;
+        mx = fmaxf(mx, acc);
+    }
+    mx = block_max(mx, scratch);
+    float sum = 0.f;
+    for (int j = threadIdx.x; j < step; j += blockDim.x) {
+        const float e = expf(sc[j] - mx);
+        sc[j] = e;
+        sum += e;
+    }
+    sum = block_sum(sum, scratch);  // barriers inside also publish sc[] to the whole CTA
+    const float inv = 1.f / (sum + 1e-6f);
+    for (int e = threadIdx.x; e < d; e += blockDim.x) {
+        float acc = 0.f;
+        for (int j = 0; j < step; ++j) {
+            const T* vr = (use_new && j == step - 1) ? vnew : vc + (size_t)j * d;
+            acc = fmaf(sc[j], DT<T>::to_f(vr[e]), acc);
+        }
+        reinterpret_cast<T*>(p.out)[((size_t)b * p.head_num + head) * d + e] = DT<T>::from_f(acc * inv);
+    }
+    // append after all reads of this CTA; only the first q head of the kv group writes
+    if (use_new && head % (p.head_num / p.kv_head_num) == 0) {
+        for (int e = threadIdx.x; e < d; e += blockDim.x) {
+            kc[(size_t)(step - 1) * d + e] = knew[e];
+            vc[(size_t)(step - 1) * d + e] = vnew[e];
+        }
+    }
+    pdl_launch_dependents();
+}
+
+// ------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------
+static int attn_pick_splits(int batch, int kv_head_num, int step) {
+    const int ctas = batch * kv_head_num;
+    const int target = 2 * sm_count();
+    int splits = (target + ctas - 1) / ctas;
+    const int max_by_len = (step + 63) / 64;  // keep >= 64 keys per split
+    if (splits > max_by_len) splits = max_by_len;
+    if (splits < 1) splits = 1;
+    if (splits > 64) splits = 64;
+    return splits;
+}
+
+static bool attn_fast_shape(int head_num, int kv_head_num, int head_size, int esz) {
+    const int G = head_num / kv_head_num;
+    const int row = head_size * esz;
+    const bool g_ok = G == 1 || G == 2 || G == 4 || G == 8;
+    const bool pr_ok = row == 128 || row == 256 || row == 512;
+    return g_ok && pr_ok && head_num % kv_head_num == 0;
+}
+
+template <typename T, int G, int PR>
+static cudaError_t attn_launch_split(const AttnParams& p, int splits, cudaStream_t s) {
+    constexpr int D = PR * DT<T>::kPer16B;
+    const size_t smem = (size_t)kAttnWarps * G * (2 + D) * sizeof(float);
+    return launch_k(decode_attn_split_kernel<T, G, PR>, dim3(p.batch * p.kv_head_num, splits),
+                    dim3(kAttnWarps * 32), smem, s, true, p);
+}
+
+template <typename T>
+static int attn_dispatch(const AttnParams& p, int splits, cudaStream_t s) {
+    const int G = p.head_num / p.kv_head_num;
+    const int PR = p.head_size * (int)sizeof(T) / 16;
+    cudaError_t e = cudaErrorInvalidValue;
+#define CASE(g, pr) \
+    if (G == g && PR == pr) e = attn_launch_split<T, g, pr>(p, splits, s);
+    CASE(1, 8) CASE(1, 16) CASE(1, 32) CASE(2, 8) CASE(2, 16) CASE(2, 32)
+    CASE(4, 8) CASE(4, 16) CASE(4, 32) CASE(8, 8) CASE(8, 16) CASE(8, 32)
+#undef CASE
+    count_launch();
+    if (e != cudaSuccess) return (int)e;
+    if (splits > 1) {
+        e = launch_k(decode_attn_combine_kernel<T>, dim3(p.batch * p.head_num), dim3(128), 0, s,
+                     true, (const float*)p.part_ml, (const float*)p.part_o, (T*)p.out, splits,
+                     p.head_size);
+        count_launch();
+    }
+    return (int)e;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" size_t b200_decode_attention_workspace_bytes(int batch, int head_num, int head_size,
+                                                        int step) {
+    if (batch <= 0 || head_num <= 0 || head_size <= 0 || step <= 0) return 0;
+    // split partials (worst case 64 splits) or the generic path's score rows (max_seq <= step
+    // is not known here, so the generic path sizes its rows by `step` rounded up by the caller:
+    // callers pass step = max_seq_len when they want one buffer for the whole generation).
+    const size_t part = (size_t)batch * head_num * 64 * (2 + (size_t)head_size) * sizeof(float);
+    const size_t generic = (size_t)batch * head_num * (size_t)step * sizeof(float);
+    return (part > generic ? part : generic) + 256;
+}
+
+extern "C" int b200_decode_attention_ex(const void* qkv, void* k_cache_layer, void* v_cache_layer,
+                                        void* out, void* workspace, size_t workspace_bytes,
+                                        int batch, int head_num, int kv_head_num, int head_size,
+                                        int max_seq_len, int step, const int* step_dev,
+                                        int append_kv, int dtype, void* stream) {
+    B200_RETURN_IF(!qkv || !k_cache_layer || !v_cache_layer || !out, B200_EINVAL);
+    B200_RETURN_IF(batch <= 0 || head_num <= 0 || kv_head_num <= 0 || head_size <= 0 ||
+                       max_seq_len <= 0 || head_num % kv_head_num != 0,
+                   B200_EINVAL);
+    B200_RETURN_IF(step < 1 || step > max_seq_len, B200_EINVAL);
+    B200_RETURN_IF(dtype != B200_F32 && dtype != B200_F16, B200_EINVAL);
+    cudaStream_t s = (cudaStream_t)stream;
+    const int esz = dtype == B200_F16 ? 2 : 4;
+    AttnParams p{};
+    p.qkv = qkv; p.k_cache = k_cache_layer; p.v_cache = v_cache_layer; p.out = out;
+    p.batch = batch; p.head_num = head_num; p.kv_head_num = kv_head_num; p.head_size = head_size;
+    p.max_seq_len = max_seq_len; p.step = step; p.step_dev = step_dev; p.append_kv = append_kv;
+    auto al = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15u) == 0; };
+    const bool fast = attn_fast_shape(head_num, kv_head_num, head_size, esz) && al(qkv) &&
+                      al(k_cache_layer) && al(v_cache_layer);
+    if (fast) {
+        const int splits = attn_pick_splits(batch, kv_head_num, step);
+        if (splits > 1) {
+            const size_t ml = (size_t)batch * head_num * splits * 2 * sizeof(float);
+            const size_t need = ((ml + 255) & ~(size_t)255) +
+                                (size_t)batch * head_num * splits * head_size * sizeof(float);
+            B200_RETURN_IF(!workspace || workspace_bytes < need, B200_EWORKSPACE);
+            p.part_ml = reinterpret_cast<float*>(workspace);
+            p.part_o = reinterpret_cast<float*>((char*)workspace + ((ml + 255) & ~(size_t)255));
+        }
+        return dtype == B200_F16 ? attn_dispatch<__half>(p, splits, s)
+                                 : attn_dispatch<float>(p, splits, s);
+    }
+    const size_t need = (size_t)batch * head_num * (size_t)max_seq_len * sizeof(float);
+    B200_RETURN_IF(!workspace || workspace_bytes < need, B200_EWORKSPACE);
+    cudaError_t e;
+    if (dtype == B200_F16)
+        e = launch_k(decode_attn_generic_kernel<__half>, dim3(batch * head_num), dim3(128), 0, s,
+                     true, p, (float*)workspace);
+    else
+        e = launch_k(decode_attn_generic_kernel<float>, dim3(batch * head_num), dim3(128), 0, s,
+                     true, p, (float*)workspace);
+    count_launch();
+    return (int)e;
+}
+
+extern "C" int b200_decode_attention(const void* qkv, void* k_cache_layer, void* v_cache_layer,
+                                     void* out, void* workspace, size_t workspace_bytes, int batch,
+                                     int head_num, int kv_head_num, int head_size, int max_seq_len,
+                                     int step, int append_kv, int dtype, void* stream) {
+    return b200_decode_attention_ex(qkv, k_cache_layer, v_cache_layer, out, workspace,
+                                    workspace_bytes, batch, head_num, kv_head_num, head_size,
+                                    max_seq_len, step, nullptr, append_kv, dtype, stream);
+}

@@ -1,0 +1,442 @@
+// Weight-streaming GEMV for the decode-time linears:  y[b, n] = sum_k x[b, k] * W[n, k].
+// Replaces cuBLAS GemmEx with n = batch (src/kernels/linear.cu:39-104, cublas_utils.cc:32-71)
+// at the call sites masked_self_attention.cpp:62,84 and ffn.cpp:72,88, and optionally fuses the
+// neighbouring bandwidth kernels of the decode layer (rmsnorm_kernel.cu:63, act_kernel.cu:18,
+// qkv_bias_and_RoPE.cu:323, the KV append of fused_decoder_self_attention.cu:170-172,274-276,
+// and the residual adds of fused_addresidual_norm.cu:62 / add_residual.cu:9).
+//
+// Structure (HBM-bound; algorithmic bytes = N*K*sizeof(T) + small vectors):
+//  * one persistent CTA per SM owns a contiguous, byte-balanced range of row-pair "units";
+//  * a producer warp streams those rows through a ring of 16 KB stages with 1-D bulk async
+//    copies (cp.async.bulk -> SASS UBLKCP, completion on an mbarrier); each stage holds
+//    8 units x 2 rows x 1 KB K-segment;
+//  * 8 consumer warps: warp w owns unit w of the stage, dots both rows against x held in
+//    shared memory (one x packet read serves two weight packets), fp32 accumulation
+//    (fma.rn.f32.f16 -> FHFMA for half), warp-shuffle reduce at the end of the row;
+//  * under programmatic dependent launch the producer starts streaming WEIGHTS before
+//    griddepcontrol.wait, so the HBM pipe stays busy across kernel boundaries; only the
+//    x load waits for the predecessor.
+#include "common.cuh"
+#include "launch_count.h"
+
+namespace b200 {
+
+constexpr int kGemvWarps = 8;                       // consumer warps == units per stage
+constexpr int kGemvThreads = (kGemvWarps + 1) * 32; // + producer warp
+constexpr int kSegBytes = 1024;                     // K-segment per row per stage
+constexpr int kStageBytes = kGemvWarps * 2 * kSegBytes;  // 16 KB
+constexpr int kMaxStages = 5;
+constexpr int kJ = kSegBytes / 16 / 32;  // 16B packets per lane per row-segment (=2)
+
+enum { kModePlain = 0, kModeResidual = 1, kModeSwiglu = 2, kModeRopeKV = 3 };
+
+struct GemvParams {
+    const void* x;
+    const void* W;
+    const void* bias;
+    void* y;
+    const void* gamma;
+    float eps;
+    int N;       // output features (for SWIGLU: inter size; W has 2N rows)
+    int K;
+    int units;   // row pairs to process
+    int stages;  // ring depth actually allocated
+    int nb;      // valid tokens (<= NB)
+    unsigned flags;  // B200_GEMV_NORM / _NORM_GFIRST (prologue, run-time)
+    // rope / kv
+    void* k_cache;
+    void* v_cache;
+    int head_num, kv_head_num, head_size, max_seq_len, step, rotary_dim;
+    float rotary_base;
+    const int* step_dev;
+};
+
+// unit -> (row_a, row_b); row_b < 0 means "no second row"
+template <int MODE>
+__device__ __forceinline__ void unit_rows(const GemvParams& p, int u, int& ra, int& rb) {
+    if (MODE == kModeSwiglu) {
+        ra = u;
+        rb = p.N + u;
+    } else if (MODE == kModeRopeKV) {
+        const int hd = p.head_size >> 1;
+        const int head = u / hd, i = u - head * hd;
+        ra = head * p.head_size + i;
+        rb = ra + hd;
+    } else {
+        ra = 2 * u;
+        rb = (2 * u + 1 < p.N) ? 2 * u + 1 : -1;
+    }
+}
+
+__device__ __forceinline__ void consumer_bar() {
+    asm volatile("bar.sync 1, %0;" ::"n"(kGemvWarps * 32) : "memory");
+}
+
+template <typename T, int NB, int MODE>
+__global__ void __launch_bounds__(kGemvThreads, 1) gemv_stream_kernel(const GemvParams p) {
+    constexpr int E = DT<T>::kPer16B;
+    constexpr int KSEG = kSegBytes / (int)sizeof(T);  // elements per segment
+    extern __shared__ __align__(128) unsigned char smem[];
+    unsigned char* ring = smem;
+    T* xs = reinterpret_cast<T*>(smem + (size_t)p.stages * kStageBytes);
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(
+        smem + (size_t)p.stages * kStageBytes + (((size_t)NB * p.K * sizeof(T) + 15) & ~(size_t)15));
+    uint64_t* empty_bar = full_bar + kMaxStages;
+    float* red = reinterpret_cast<float*>(empty_bar + kMaxStages);  // [NB][kGemvWarps] + [NB]
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nseg = (p.K + KSEG - 1) / KSEG;
+    // byte-balanced contiguous unit range of this CTA
+    const int u0 = (int)(((long long)p.units * blockIdx.x) / gridDim.x);
+    const int u1 = (int)(((long long)p.units * (blockIdx.x + 1)) / gridDim.x);
+    const int ngroups = (u1 - u0 + kGemvWarps - 1) / kGemvWarps;
+    const int total_stages = ngroups * nseg;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < p.stages; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], kGemvWarps);
+        }
+        mbar_fence_init();
+    }
+    __syncthreads();
+    pdl_launch_dependents();  // dependents only prefetch weights before their own wait
+
+    if (warp == kGemvWarps) {
+        // ===================== producer: one lane issues the bulk copies =====================
+        if (lane == 0) {
+            const unsigned char* Wb = reinterpret_cast<const unsigned char*>(p.W);
+            const size_t row_bytes = (size_t)p.K * sizeof(T);
+            for (int t = 0; t < total_stages; ++t) {
+                const int slot = t % p.stages;
+                if (t >= p.stages) mbar_wait(&empty_bar[slot], ((t / p.stages) - 1) & 1);
+                const int g = t / nseg, seg = t - g * nseg;
+                const int seg_elems = min(KSEG, p.K - seg * KSEG);
+                const uint32_t seg_bytes = (uint32_t)seg_elems * sizeof(T);
+                const int ubase = u0 + g * kGemvWarps;
+                const int nu = min(kGemvWarps, u1 - ubase);
+                // count the bytes first so the expect_tx precedes every complete_tx
+                uint32_t tx = 0;
+                for (int w = 0; w < nu; ++w) {
+                    int ra, rb;
+                    unit_rows<MODE>(p, ubase + w, ra, rb);
+                    tx += seg_bytes * (rb >= 0 ? 2u : 1u);
+                }
+                mbar_expect_tx(&full_bar[slot], tx);
+                unsigned char* dst = ring + (size_t)slot * kStageBytes;
+                const size_t koff = (size_t)seg * kSegBytes;
+                for (int w = 0; w < nu; ++w) {
+                    int ra, rb;
+                    unit_rows<MODE>(p, ubase + w, ra, rb);
+                    bulk_g2s(dst + (2 * w) * kSegBytes, Wb + (size_t)ra * row_bytes + koff, seg_bytes,
+                             &full_bar[slot]);
+                    if (rb >= 0)
+                        bulk_g2s(dst + (2 * w + 1) * kSegBytes, Wb + (size_t)rb * row_bytes + koff,
+                                 seg_bytes, &full_bar[slot]);
+                }
+            }
+        }
+        return;
+    }
+
+    // ========================= consumers =========================
+    // x (and the optional RMSNorm prologue) depend on the predecessor kernel.
+    pdl_wait();
+    {
+        const int pk = p.K / E;  // packets per token
+        const T* xg = reinterpret_cast<const T*>(p.x);
+        float ss[NB];
+#pragma unroll
+        for (int b = 0; b < NB; ++b) ss[b] = 0.f;
+        for (int i = threadIdx.x; i < pk; i += kGemvWarps * 32) {
+#pragma unroll
+            for (int b = 0; b < NB; ++b) {
+                if (b >= p.nb) break;
+                Pack16 v = ld16(xg + (size_t)b * p.K + (size_t)i * E);
+                st16(xs + (size_t)b * p.K + (size_t)i * E, v);
+                if (p.flags & B200_GEMV_NORM) {
+                    float f[E];
+                    Unpack<T>::get(v, f);
+#pragma unroll
+                    for (int e = 0; e < E; ++e) ss[b] = fmaf(f[e], f[e], ss[b]);
+                }
+            }
+        }
+        if (p.flags & B200_GEMV_NORM) {
+#pragma unroll
+            for (int b = 0; b < NB; ++b) {
+                const float s = warp_sum(ss[b]);
+                if (lane == 0) red[b * kGemvWarps + warp] = s;
+            }
+            consumer_bar();
+            if (threadIdx.x < NB) {
+                float s = 0.f;
+                for (int w = 0; w < kGemvWarps; ++w) s += red[threadIdx.x * kGemvWarps + w];
+                red[NB * kGemvWarps + threadIdx.x] = rsqrtf(s / (float)p.K + p.eps);
+            }
+            consumer_bar();
+            const T* gm = reinterpret_cast<const T*>(p.gamma);
+            const bool gfirst = (p.flags & B200_GEMV_NORM_GFIRST) != 0;
+            for (int i = threadIdx.x; i < pk; i += kGemvWarps * 32) {
+                float g[E];
+                Unpack<T>::get(ld16(gm + (size_t)i * E), g);
+#pragma unroll
+                for (int b = 0; b < NB; ++b) {
+                    if (b >= p.nb) break;
+                    const float inv = red[NB * kGemvWarps + b];
+                    float f[E];
+                    Unpack<T>::get(ld16(xs + (size_t)b * p.K + (size_t)i * E), f);
+#pragma unroll
+                    for (int e = 0; e < E; ++e)
+                        f[e] = gfirst ? (g[e] * f[e]) * inv
+                                                               : (f[e] * inv) * g[e];
+                    st16(xs + (size_t)b * p.K + (size_t)i * E, Unpack<T>::put(f));  // rounds to T
+                }
+            }
+        }
+        consumer_bar();
+    }
+
+    int step = p.step;
+    if (MODE == kModeRopeKV) {
+        if (p.step_dev) step = *p.step_dev;
+    }
+
+    float acc_a[NB], acc_b[NB];
+#pragma unroll
+    for (int b = 0; b < NB; ++b) acc_a[b] = acc_b[b] = 0.f;
+
+    for (int t = 0; t < total_stages; ++t) {
+        const int slot = t % p.stages;
+        const int g = t / nseg, seg = t - g * nseg;
+        const int unit = u0 + g * kGemvWarps + warp;
+        const bool active = unit < u1;
+        int ra = 0, rb = -1;
+        if (active) unit_rows<MODE>(p, unit, ra, rb);
+
+        mbar_wait(&full_bar[slot], (t / p.stages) & 1);
+        if (active) {
+            const int seg_pk = min(KSEG, p.K - seg * KSEG) / E;
+            const unsigned char* sa = ring + (size_t)slot * kStageBytes + (2 * warp) * kSegBytes;
+            const unsigned char* sb = sa + kSegBytes;
+            const T* xseg = xs + (size_t)seg * KSEG;
+#pragma unroll
+            for (int j = 0; j < kJ; ++j) {
+                const int pkt = lane + 32 * j;
+                if (pkt < seg_pk) {
+                    const Pack16 wa = ld16(sa + pkt * 16);
+                    Pack16 wb;
+                    if (rb >= 0) wb = ld16(sb + pkt * 16);
+#pragma unroll
+                    for (int b = 0; b < NB; ++b) {
+                        const Pack16 xv = ld16(xseg + (size_t)b * p.K + (size_t)pkt * E);
+                        acc_a[b] = dot16<T>(wa, xv, acc_a[b]);
+                        if (rb >= 0) acc_b[b] = dot16<T>(wb, xv, acc_b[b]);
+                    }
+                }
+            }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty_bar[slot]);
+
+        if (seg == nseg - 1 && active) {
+            // ---- end of the row pair: reduce + epilogue (lane 0 writes) ----
+#pragma unroll
+            for (int b = 0; b < NB; ++b) {
+                acc_a[b] = warp_sum(acc_a[b]);
+                acc_b[b] = warp_sum(acc_b[b]);
+            }
+            if (lane == 0) {
+                const T* bias = reinterpret_cast<const T*>(p.bias);
+                T* y = reinterpret_cast<T*>(p.y);
+                if (MODE == kModeSwiglu) {
+#pragma unroll
+                    for (int b = 0; b < NB; ++b) {
+                        if (b >= p.nb) break;
+                        float gv = acc_a[b], uv = acc_b[b];
+                        if (bias) { gv += DT<T>::to_f(bias[ra]); uv += DT<T>::to_f(bias[rb]); }
+                        gv = DT<T>::to_f(DT<T>::from_f(gv));  // the unfused path stores gate/up in T
+                        uv = DT<T>::to_f(DT<T>::from_f(uv));
+                        const float s = DT<T>::to_f(DT<T>::from_f(gv / (1.f + expf(-gv))));
+                        y[(size_t)b * p.N + ra] = DT<T>::from_f(s * uv);
+                    }
+                } else if (MODE == kModeRopeKV) {
+                    const int d = p.head_size, hd = d >> 1;
+                    const int head = ra / d, i = ra - head * d;
+                    const int qkv_heads = p.head_num + 2 * p.kv_head_num;
+                    float c = 1.f, s = 0.f;
+                    if (head < p.head_num + p.kv_head_num && i < (p.rotary_dim >> 1)) {
+                        const float ang = (float)(step - 1) /
+                                          powf(p.rotary_base, (float)(2 * i) / (float)p.rotary_dim);
+                        c = cosf(ang);
+                        s = sinf(ang);
+                    }
+#pragma unroll
+                    for (int b = 0; b < NB; ++b) {
+                        if (b >= p.nb) break;
+                        float av = acc_a[b], bv = acc_b[b];
+                        if (bias) { av += DT<T>::to_f(bias[ra]); bv += DT<T>::to_f(bias[rb]); }
+                        av = DT<T>::to_f(DT<T>::from_f(av));  // qkv_buf is stored in T before RoPE
+                        bv = DT<T>::to_f(DT<T>::from_f(bv));
+                        const T oa = DT<T>::from_f(c * av - s * bv);
+                        const T ob = DT<T>::from_f(c * bv + s * av);
+                        T* yt = y + (size_t)b * qkv_heads * d;
+                        yt[ra] = oa;
+                        yt[rb] = ob;
+                        if (head >= p.head_num) {
+                            const bool is_k = head < p.head_num + p.kv_head_num;
+                            const int kvh = is_k ? head - p.head_num : head - p.head_num - p.kv_head_num;
+                            T* cache = reinterpret_cast<T*>(is_k ? p.k_cache : p.v_cache);
+                            T* row = cache + (((size_t)b * p.kv_head_num + kvh) * p.max_seq_len +
+                                              (size_t)(step - 1)) * d;
+                            row[i] = oa;
+                            row[i + hd] = ob;
+                        }
+                    }
+                } else {
+#pragma unroll
+                    for (int b = 0; b < NB; ++b) {
+                        if (b >= p.nb) break;
+                        float av = acc_a[b], bv = acc_b[b];
+                        if (MODE == kModeResidual) {
+                            // unfused: linear output rounded to T, then T(out + bias + residual)
+                            av = DT<T>::to_f(DT<T>::from_f(av));
+                            bv = DT<T>::to_f(DT<T>::from_f(bv));
+                            if (bias) { av += DT<T>::to_f(bias[ra]); if (rb >= 0) bv += DT<T>::to_f(bias[rb]); }
+                            av += DT<T>::to_f(y[(size_t)b * p.N + ra]);
+                            if (rb >= 0) bv += DT<T>::to_f(y[(size_t)b * p.N + rb]);
+                        } else if (bias) {
+                            av += DT<T>::to_f(bias[ra]);
+                            if (rb >= 0) bv += DT<T>::to_f(bias[rb]);
+                        }
+                        y[(size_t)b * p.N + ra] = DT<T>::from_f(av);
+                        if (rb >= 0) y[(size_t)b * p.N + rb] = DT<T>::from_f(bv);
+                    }
+                }
+            }
+#pragma unroll
+            for (int b = 0; b < NB; ++b) acc_a[b] = acc_b[b] = 0.f;
+        }
+    }
+}
+
+
+// ------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------
+static size_t gemv_smem_bytes(int stages, int NB, int K, int esz) {
+    size_t x = (((size_t)NB * K * esz) + 15) & ~(size_t)15;
+    return (size_t)stages * kStageBytes + x + 2 * kMaxStages * sizeof(uint64_t) +
+           (size_t)(NB * kGemvWarps + NB) * sizeof(float) + 16;
+}
+
+static int gemv_pick_stages(int NB, int K, int esz) {
+    for (int st = kMaxStages; st >= 2; --st)
+        if (gemv_smem_bytes(st, NB, K, esz) <= 227 * 1024) return st;
+    return 0;
+}
+
+template <typename T, int NB, int MODE>
+static int gemv_launch_one(const GemvParams& p, size_t smem, int grid, cudaStream_t s) {
+    auto kern = gemv_stream_kernel<T, NB, MODE>;
+    static bool attr_set = false;  // per instantiation
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             227 * 1024);
+        if (e != cudaSuccess) return (int)e;
+        attr_set = true;
+    }
+    cudaError_t e = launch_k(kern, dim3(grid), dim3(kGemvThreads), smem, s, true, p);
+    count_launch();
+    return (int)e;
+}
+
+template <typename T, int MODE>
+static int gemv_dispatch_nb(GemvParams p, int n_tokens, cudaStream_t s) {
+    const int esz = (int)sizeof(T);
+    int NB = n_tokens <= 1 ? 1 : n_tokens <= 2 ? 2 : n_tokens <= 4 ? 4 : 8;
+    const int stages = gemv_pick_stages(NB, p.K, esz);
+    if (stages == 0) return B200_EUNSUPPORTED;
+    p.stages = stages;
+    p.nb = n_tokens;
+    const size_t smem = gemv_smem_bytes(stages, NB, p.K, esz);
+    int grid = sm_count();
+    const int groups = (p.units + kGemvWarps - 1) / kGemvWarps;
+    if (grid > groups) grid = groups;
+    if (grid < 1) grid = 1;
+    switch (NB) {
+        case 1: return gemv_launch_one<T, 1, MODE>(p, smem, grid, s);
+        case 2: return gemv_launch_one<T, 2, MODE>(p, smem, grid, s);
+        case 4: return gemv_launch_one<T, 4, MODE>(p, smem, grid, s);
+        default: return gemv_launch_one<T, 8, MODE>(p, smem, grid, s);
+    }
+}
+
+template <typename T>
+static int gemv_fused_impl(const b200_gemv_args* a, cudaStream_t s) {
+    constexpr int E = DT<T>::kPer16B;
+    B200_RETURN_IF(a->K % E != 0, B200_EUNSUPPORTED);
+    B200_RETURN_IF(a->n_tokens < 1 || a->n_tokens > B200_GEMV_MAX_TOKENS, B200_EUNSUPPORTED);
+    const unsigned epi = a->flags & (B200_GEMV_RESIDUAL | B200_GEMV_SWIGLU | B200_GEMV_ROPE_KV);
+    B200_RETURN_IF(epi & (epi - 1), B200_EINVAL);  // at most one epilogue mode
+    B200_RETURN_IF((a->flags & B200_GEMV_NORM) && !a->gamma, B200_EINVAL);
+    GemvParams p{};
+    p.x = a->x; p.W = a->W; p.bias = a->bias; p.y = a->y; p.gamma = a->gamma; p.eps = a->eps;
+    p.N = a->N; p.K = a->K;
+    p.flags = a->flags & (B200_GEMV_NORM | B200_GEMV_NORM_GFIRST);
+    p.k_cache = a->k_cache_layer; p.v_cache = a->v_cache_layer;
+    p.head_num = a->head_num; p.kv_head_num = a->kv_head_num; p.head_size = a->head_size;
+    p.max_seq_len = a->max_seq_len; p.step = a->step; p.rotary_dim = a->rotary_dim;
+    p.rotary_base = a->rotary_base; p.step_dev = a->step_dev;
+    if (epi == B200_GEMV_SWIGLU) {
+        p.units = a->N;
+        return gemv_dispatch_nb<T, kModeSwiglu>(p, a->n_tokens, s);
+    }
+    if (epi == B200_GEMV_ROPE_KV) {
+        B200_RETURN_IF(!a->k_cache_layer || !a->v_cache_layer, B200_EINVAL);
+        B200_RETURN_IF(a->head_size <= 0 || (a->head_size & 1) || a->head_num <= 0 ||
+                           a->kv_head_num <= 0 ||
+                           a->N != (a->head_num + 2 * a->kv_head_num) * a->head_size,
+                       B200_EINVAL);
+        B200_RETURN_IF(a->rotary_dim <= 0 || a->rotary_dim > a->head_size || (a->rotary_dim & 1),
+                       B200_EINVAL);
+        B200_RETURN_IF(!a->step_dev && (a->step < 1 || a->step > a->max_seq_len), B200_EINVAL);
+        p.units = a->N / 2;
+        return gemv_dispatch_nb<T, kModeRopeKV>(p, a->n_tokens, s);
+    }
+    p.units = (a->N + 1) / 2;
+    if (epi == B200_GEMV_RESIDUAL) return gemv_dispatch_nb<T, kModeResidual>(p, a->n_tokens, s);
+    return gemv_dispatch_nb<T, kModePlain>(p, a->n_tokens, s);
+}
+
+// used by b200_linear (linear.cu): plain GEMV, any n_tokens (tiled by B200_GEMV_MAX_TOKENS)
+int gemv_plain(const void* x, const void* W, const void* bias, void* y, int n_tokens, int N, int K,
+               int dtype, cudaStream_t s) {
+    const int esz = dtype == B200_F16 ? 2 : 4;
+    for (int t0 = 0; t0 < n_tokens; t0 += B200_GEMV_MAX_TOKENS) {
+        b200_gemv_args a{};
+        a.x = (const char*)x + (size_t)t0 * K * esz;
+        a.W = W;
+        a.bias = bias;
+        a.y = (char*)y + (size_t)t0 * N * esz;
+        a.n_tokens = (n_tokens - t0 < B200_GEMV_MAX_TOKENS) ? n_tokens - t0 : B200_GEMV_MAX_TOKENS;
+        a.N = N;
+        a.K = K;
+        int rc = dtype == B200_F16 ? gemv_fused_impl<__half>(&a, s) : gemv_fused_impl<float>(&a, s);
+        if (rc != 0) return rc;
+    }
+    return B200_OK;
+}
+
+}  // namespace b200
+
+extern "C" int b200_gemv_fused(const b200_gemv_args* args, int dtype, void* stream) {
+    B200_RETURN_IF(!args || !args->x || !args->W || !args->y, B200_EINVAL);
+    B200_RETURN_IF(args->N <= 0 || args->K <= 0, B200_EINVAL);
+    auto al = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; };
+    B200_RETURN_IF(!al(args->x) || !al(args->W) || !al(args->gamma), B200_EINVAL);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (dtype == B200_F32) return b200::gemv_fused_impl<float>(args, s);
+    if (dtype == B200_F16) return b200::gemv_fused_impl<__half>(args, s);
+    return B200_EINVAL;
+}
