@@ -1,0 +1,418 @@
+#!/usr/bin/env python
+"""bench.py — LLaMA-2-7B fp16 decode tok/s on B200 (BASELINE.json metric), one JSON line.
+
+    python bench.py --gpus N --steps K --warmup W [--workload cfg2|cfg4] [--impl reference]
+
+A "step" is one decode step of the whole model for the whole batch (one new token per sequence).
+Workloads (BASELINE.json configs):
+  cfg2 (default): LLaMA-2-7B fp16 random-init full model, batch 1 greedy decode at a 512-token
+        context. N GPUs = N independent requests (weights replicated, no communication): weak.
+  cfg4: batch 32 x KV length 4096, 32/N sequences per GPU (strong), no communication.
+`value`  : tokens/s with everything resident in HBM, CUDA events on the engine's stream, max over ranks.
+`e2e`    : same metric through the call a user of the reference makes per token
+           (b200_engine_decode_step_host: H2D token ids from pinned memory, the step, D2H ids).
+`roofline`: the dominant kernel (weight-streaming GEMV; 98% of the step's bytes at cfg2) timed
+           alone, back to back, on the model's own weights; achieved = algorithmic bytes / time.
+`cpu_baseline`: the CPU oracle port (oracle/llama_cpu.c) on a bounded sample, host cores stated.
+--impl reference: the reference's own CPU test functions (oracle/_ref, tests/unittests/*.cu)
+           composed into the decode step, on the host cores, same metric / config.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+L7B = dict(num_layers=32, head_num=32, kv_head_num=32, head_size=128, inter_size=11008, vocab_size=32000)
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=128)
+    ap.add_argument("--warmup", type=int, default=8)
+    ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg4"])
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--context", type=int, default=None)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def workload(args):
+    if args.workload == "cfg4":
+        return dict(name="LLaMA-2-7B fp16 decode, batch 32 x KV 4096 (configs[3])", batch=32,
+                    context=args.context or 4096, scaling="strong")
+    return dict(name="LLaMA-2-7B fp16 random-init full model, batch 1 greedy decode, 512-token context (configs[1])",
+                batch=1, context=args.context or 512, scaling="weak")
+
+
+# --------------------------------------------------------------------------------------------
+# clocks sampler (nvidia-smi during the timed region)
+# --------------------------------------------------------------------------------------------
+class Clocks:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.proc, self.lines, self.index = None, [], index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=lambda: [self.lines.append(l) for l in self.proc.stdout], daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for l in self.lines:
+            f = [x.strip() for x in l.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx = float(f[1])
+            except ValueError:
+                continue
+            for n, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# --------------------------------------------------------------------------------------------
+# CPU baselines
+# --------------------------------------------------------------------------------------------
+def _cheap_random(shape, scale, seed):
+    """fast deterministic pseudo-random fp32 fill (tiles a 1M-element block; content is irrelevant
+    to a timing run)"""
+    import numpy as np
+    n = int(np.prod(shape))
+    blk = (np.random.default_rng(seed).standard_normal(1 << 20).astype(np.float32) * scale)
+    return np.resize(blk, n).reshape(shape)
+
+
+def cpu_baseline_port(wl, budget_layers=2):
+    """oracle port (plain C, pthreads over all host cores): one decode step of `budget_layers`
+    LLaMA-2-7B-shaped layers + final norm + LM head at the workload's batch/context, scaled to 32."""
+    import numpy as np
+    from oracle import cpu, model as omodel
+    B, ctx = wl["batch"], wl["context"]
+    if B > 4:
+        B_s = 4      # bounded sample: 4 of the sequences, tokens/s scales with batch on the CPU too
+    else:
+        B_s = B
+    H, I, V = 4096, 11008, 32000
+    layers = [dict(attn_norm=np.ones(H, np.float32), qkv=_cheap_random((3 * H, H), 0.02, 1),
+                   o=_cheap_random((H, H), 0.02, 2), ffn_norm=np.ones(H, np.float32),
+                   gate_up=_cheap_random((2 * I, H), 0.02, 3), down=_cheap_random((H, I), 0.02, 4))
+              for _ in range(1)] * budget_layers
+    w = dict(layers=layers, embed=_cheap_random((V, H), 0.02, 5), final_norm=np.ones(H, np.float32),
+             lm_head=_cheap_random((V, H), 0.02, 6))
+    cfg = dict(L7B, num_layers=budget_layers)
+    om = omodel.OracleModel(w, cfg, B_s, ctx + 4, "fp32")
+    om.k[:] = 0.1
+    om.v[:] = 0.1
+    om.step = ctx
+    ids = np.zeros(B_s, np.int32)
+    t0 = time.perf_counter()
+    om.decode_step(ids)
+    t_all = time.perf_counter() - t0
+    # split the LM-head part out so only the layer part is scaled by 32/budget_layers
+    x = np.zeros((B_s, H), np.float32)
+    lg = np.zeros((B_s, V), np.float32)
+    t0 = time.perf_counter()
+    cpu.linear(x, w["lm_head"], lg, True)
+    t_head = time.perf_counter() - t0
+    t_step = (t_all - t_head) * (32 / budget_layers) + t_head
+    return {"value": round(B_s / t_step * (wl["batch"] / B_s), 4), "unit": "tok/s", "cores": cpu.num_threads(),
+            "kind": "port",
+            "sample": f"1 decode step, {budget_layers} of 32 LLaMA-2-7B fp32 layers + LM head, batch {B_s}, "
+                      f"context {ctx}, layer time scaled x{32 // budget_layers}"
+                      + (f", tokens/s scaled x{wl['batch'] // B_s} to batch {wl['batch']}" if B_s != wl["batch"] else "")
+                      + f" ({t_all:.2f} s measured)"}
+
+
+class RefCpu:
+    """The reference's own CPU test functions (tests/unittests/*.cu compiled into
+    oracle/_ref/libref.so) composed into a decode-layer sample. CPUlinear is a single-threaded
+    triple loop over W[K,N]; the output columns are sliced over all host cores (one slice per
+    thread, ctypes releases the GIL). Attention / RoPE use the oracle port: the reference's
+    CPUMaskedAttn / CPUfunc are unsound outside their toy shapes."""
+
+    def __init__(self):
+        self.lib = C.CDLL(os.path.join(ROOT, "oracle", "_ref", "libref.so"))
+
+    def linear_sliced(self, x, w_slices, outs):
+        ths = []
+        for ws, o in zip(w_slices, outs):
+            t = threading.Thread(target=self.lib.ref_cpu_linear,
+                                 args=(x.ctypes.data_as(C.c_void_p), ws.ctypes.data_as(C.c_void_p),
+                                       o.ctypes.data_as(C.c_void_p), x.shape[0], x.shape[1], ws.shape[1]))
+            t.start()
+            ths.append(t)
+        for t in ths:
+            t.join()
+
+
+def reference_arm(args, wl):
+    """--impl reference: one bounded sample per step = 1/FRAC of the linear work of one 7B layer
+    through the reference's CPUlinear (+ its CPU RMSNorm / SwiGLU in full), all host cores."""
+    import numpy as np
+    cores = os.cpu_count() or 1
+    H, I, V = 4096, 11008, 32000
+    B = min(wl["batch"], 4)
+    FRAC = 16
+    try:
+        ref = RefCpu()
+        kind = "reference"
+    except OSError:
+        ref, kind = None, "port"
+    from oracle import cpu
+    n_lin = (3 * H + H + 2 * I) // FRAC   # output columns with K = H
+    n_dn = H // FRAC                      # output columns with K = I
+    x = _cheap_random((B, H), 1.0, 1)
+    xa = _cheap_random((B, I), 1.0, 2)
+    per = max(1, n_lin // cores)
+    w1 = [_cheap_random((H, per), 0.02, 10 + i) for i in range(cores)]
+    o1 = [np.zeros((B, per), np.float32) for _ in range(cores)]
+    per2 = max(1, n_dn // cores)
+    w2 = [_cheap_random((I, per2), 0.02, 30 + i) for i in range(cores)]
+    o2 = [np.zeros((B, per2), np.float32) for _ in range(cores)]
+    g = np.ones(H, np.float32)
+    gu = _cheap_random((B, 2, I), 1.0, 3)
+    act = np.zeros((B, I), np.float32)
+    qkv = _cheap_random((B, 96, 128), 1.0, 4)
+    kc = _cheap_random((B, 32, wl["context"] + 1, 128), 0.1, 5)
+    vc = kc.copy()
+    att = np.zeros((B, H), np.float32)
+
+    def sample():
+        if ref:
+            for o in o1 + o2:
+                o[:] = 0   # CPUlinear accumulates into its output
+            xx = x.copy()
+            ref.lib.ref_cpu_rmsnorm(xx.ctypes.data_as(C.c_void_p), g.ctypes.data_as(C.c_void_p), C.c_float(1e-5), H, B)
+            ref.linear_sliced(x, w1, o1)
+            ref.lib.ref_cpu_swiglu(gu.ctypes.data_as(C.c_void_p), act.ctypes.data_as(C.c_void_p), B, I)
+            ref.linear_sliced(xa, w2, o2)
+        else:
+            for ws, o in zip(w1, o1):
+                cpu.linear(x, ws, o, False)
+            for ws, o in zip(w2, o2):
+                cpu.linear(xa, ws, o, False)
+        t0 = time.perf_counter()
+        cpu.decode_attention(qkv, kc, vc, att, 32, 32, wl["context"] + 1, True)
+        return time.perf_counter() - t0
+
+    for _ in range(max(1, min(args.warmup, 3))):
+        sample()
+    t_attn = 0.0
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        t_attn += sample()
+    t_total = time.perf_counter() - t0
+    t_sample = t_total / args.steps
+    t_attn /= args.steps
+    done_cols = per * cores + 0.0
+    lin_scale = (3 * H + H + 2 * I) / done_cols   # the sliced linears cover 1/FRAC (rounded) of a layer
+    t_layer = (t_sample - t_attn) * lin_scale + t_attn
+    t_step = 32 * t_layer * (1 + V * H / (32.0 * (3 * H * H + H * H + 2 * I * H + H * I)))  # + LM head share
+    value = wl["batch"] / t_step * 1.0 if B == wl["batch"] else (B / t_step) * (wl["batch"] / B)
+    out = {"impl": "reference", "metric": "decode_tokens_per_s", "value": round(value, 5), "unit": "tok/s",
+           "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+           "ms_per_step": round(t_step * 1e3 * (wl["batch"] / B if B != wl["batch"] else 1), 3), "higher_is_better": True,
+           "scaling": wl["scaling"], "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "config": {"workload": wl["name"], "batch": wl["batch"], "context": wl["context"]},
+           "cpu_baseline": {"value": round(value, 5), "unit": "tok/s", "cores": cores, "kind": kind,
+                            "sample": f"per step: 1/{FRAC} of one 7B layer's linear columns through the reference's "
+                                      f"CPUlinear (tests/unittests/test_linear.cu:13) sliced over {cores} threads, its CPU "
+                                      f"RMSNorm + SwiGLU in full, decode attention via the oracle port at context "
+                                      f"{wl['context']}, batch {B}; scaled to 32 layers + LM head"},
+           "e2e": {"value": round(value, 5), "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+           "gpu_launches": 0}
+    print(json.dumps(out))
+
+
+# --------------------------------------------------------------------------------------------
+# the B200 arm
+# --------------------------------------------------------------------------------------------
+def main():
+    args = parse()
+    wl = workload(args)
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        if rank == 0:
+            reference_arm(args, wl)
+        return
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from __graft_entry__ import load_package
+    pkg = load_package()
+    E, capi, ops = pkg.engine, pkg.capi, pkg.ops
+    if not torch.cuda.is_available():
+        raise SystemExit("[b200][ERROR] bench.py needs a CUDA device: there is no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- shard the requests: independent sequences, no data-path collective
+    if wl["scaling"] == "weak":
+        B_local, B_total = wl["batch"], wl["batch"] * world
+    else:
+        assert wl["batch"] % world == 0
+        B_local, B_total = wl["batch"] // world, wl["batch"]
+    ctx, K, W = wl["context"], args.steps, args.warmup
+    W = max(W, 3)
+    max_seq = ctx + 2 * (W + K) + 8
+    eng = E.Engine(B_local, max_seq, dtype=capi.F16, **L7B)
+    eng.init_random(seed=1234 + rank, std=0.02)
+    eng.fill_kv_random(ctx, seed=7 + rank, amp=0.5)   # context already in the cache (prefill is not the metric)
+    stream = torch.cuda.ExternalStream(eng.stream)
+    ids0 = np.random.default_rng(7 + rank).integers(0, 32000, B_local).astype(np.int32)
+
+    # ---- device-resident timed region
+    eng.decode_step_host(ids0)
+    for _ in range(W - 1):
+        eng.decode_step()
+    barrier()
+    clocks = Clocks(local_rank)
+    if rank == 0:
+        clocks.start()
+    capi.lib().b200_launch_count_reset()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with torch.cuda.stream(stream):
+        ev0.record()
+        for _ in range(K):
+            eng.decode_step()
+        ev1.record()
+    barrier()
+    launches = int(capi.lib().b200_launch_count())
+    ms = ev0.elapsed_time(ev1)
+    clk = clocks.stop() if rank == 0 else None
+
+    # ---- end to end: host ids in, host ids out, every step
+    ids = eng.decode_step_host(None)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(K):
+        ids = eng.decode_step_host(ids)
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+
+    t = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max, e2e_ms_max = float(t[0]), float(t[1])
+
+    # ---- roofline of the dominant kernel, alone, on the model's own weights (rank 0)
+    roof = None
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        H, I, V = 4096, 11008, 32000
+        nb = min(B_local, 8)
+        x_h = torch.randn(nb, H, device="cuda").half() * 0.1
+        x_i = torch.randn(nb, I, device="cuda").half() * 0.1
+        y_qkv = torch.zeros(nb, 3 * H, device="cuda").half()
+        y_h = torch.zeros(nb, H, device="cuda").half()
+        y_i = torch.zeros(nb, I, device="cuda").half()
+        gam = torch.ones(H, device="cuda").half()
+        kc, vc = eng.kv_caches()
+        step_dev = torch.tensor([5], dtype=torch.int32, device="cuda")
+        reps = 2
+        tot_bytes, n_launch = 0, 0
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        for timed in (False, True):
+            if timed:
+                torch.cuda.synchronize()
+                s0.record()
+            for _ in range(reps):
+                for l in range(32):   # 32 layers x 4 GEMVs: 12.9 GB per pass, far beyond the 126 MB L2
+                    ops.gemv_fused(x_h, eng.weight_view(E.W_QKV, l), y_qkv, capi.GEMV_NORM | capi.GEMV_ROPE_KV,
+                                   gamma=gam, eps=1e-5, k_cache_layer=kc[l][:nb], v_cache_layer=vc[l][:nb],
+                                   head_num=32, kv_head_num=32, head_size=128, rotary_dim=128, step_dev=step_dev)
+                    ops.gemv_fused(x_h, eng.weight_view(E.W_O, l), y_h, capi.GEMV_RESIDUAL)
+                    ops.gemv_fused(x_h, eng.weight_view(E.W_GATE_UP, l), y_i,
+                                   capi.GEMV_NORM | capi.GEMV_NORM_GFIRST | capi.GEMV_SWIGLU, gamma=gam, eps=1e-5)
+                    ops.gemv_fused(x_i, eng.weight_view(E.W_DOWN, l), y_h, capi.GEMV_RESIDUAL)
+                    if timed:
+                        tot_bytes += 2 * (3 * H * H + H * H + 2 * I * H + H * I)
+                        n_launch += 4
+            if timed:
+                s1.record()
+        torch.cuda.synchronize()
+        g_ms = s0.elapsed_time(s1)
+        achieved = tot_bytes / (g_ms * 1e-3) / 1e9
+        roof = {"bound": "hbm", "kernel": "gemv_stream_kernel", "achieved": round(achieved, 1), "peak": peak,
+                "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": None,
+                "per_launch_us": round(g_ms * 1e3 / n_launch, 2), "per_launch_MB": round(tot_bytes / n_launch / 1e6, 2),
+                "peak_source": "MEASURED_PEAKS.json hbm_gbs (burst copy)" if peaks else "fallback 6650 GB/s",
+                "note": "traffic: see profiles/ (ncu dram__bytes per launch)"}
+
+    tok_s = B_total * K / (ms_max * 1e-3)
+    e2e_tok_s = B_total * K / (e2e_ms_max * 1e-3)
+    step_bytes = eng.weight_bytes - 2 * 32000 * 4096 + 0 + B_local * 2 * 32 * 4096 * 2 * (ctx + W + K // 2)
+    out = None
+    if rank == 0:
+        out = {"metric": "decode_tokens_per_s", "value": round(tok_s, 2), "unit": "tok/s", "n_gpus": world,
+               "steps": K, "warmup": W, "ms_per_step": round(ms_max / K, 4), "higher_is_better": True,
+               "scaling": wl["scaling"], "vs_baseline": None, "dtype": "f16", "data": "synthetic",
+               "config": {"workload": wl["name"], "batch_total": B_total, "batch_per_gpu": B_local, "context": ctx,
+                          "weights": "random-init N(0,0.02^2) fp16, 13.2 GB per GPU", "accumulate": "fp32",
+                          "l2": "inputs larger than L2 (13.2 GB of weights streamed per step vs 126 MB L2)",
+                          "parallelism": f"dp{world} (independent requests, no collective)"},
+               "e2e": {"value": round(e2e_tok_s, 2), "unit": "tok/s", "h2d_bytes_per_step": 4 * B_local,
+                       "d2h_bytes_per_step": 4 * B_local, "ms_per_step": round(e2e_ms_max / K, 4)},
+               "gpu_launches": launches, "launches_per_step": eng.launches_per_step,
+               "step_hbm": {"algorithmic_GB_per_step": round(step_bytes / 1e9, 3),
+                            "achieved_GBps": round(step_bytes / (ms_max / K * 1e-3) / 1e9, 1)},
+               "roofline": roof, "clocks": clk}
+        if not args.no_cpu_baseline:
+            try:
+                out["cpu_baseline"] = cpu_baseline_port(wl)
+            except Exception as ex:   # the baseline must never take the GPU number down with it
+                out["cpu_baseline"] = {"value": None, "unit": "tok/s", "cores": os.cpu_count(), "kind": "port",
+                                       "sample": f"failed: {ex}"}
+        print(json.dumps(out))
+    eng.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

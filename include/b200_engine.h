@@ -1,0 +1,127 @@
+/*
+ * b200_engine.h — C ABI of the decode-step driver built on b200_llama.h.
+ *
+ * Stands in for the reference's per-token path:
+ *   Llama<T>::continueTokenGen            src/models/llama/llama.cpp:319-361
+ *   LlamaSelfDecoder<T>::forward          src/layers/decoder/self_decoder.cpp:24-85
+ *   LLaMASelfAttentionLayer<T>::Forward   src/layers/attention/masked_self_attention.cpp:55-92
+ *   LLaMAFFNLayer<T>::forward             src/layers/ffn/ffn.cpp:53-93
+ *   Llama<T>::LMHeadAndTopKSample         src/models/llama/llama.cpp:215-271 (greedy: top-1)
+ * with the per-call Malloc/Free and cudaDeviceSynchronize calls of those files replaced by a
+ * persistent arena (src/memory change), stream-ordered launches and CUDA-graph replay.
+ *
+ * Memory layout (one cudaMalloc each, 256-byte aligned sub-allocations):
+ *   weights arena : per layer [attn_norm γ | qkv W[(h+2hk)d, H] | o W[H, hd] | ffn_norm γ |
+ *                   gate_up W[2I, H] (gate rows first) | down W[H, I]], then embedding [V,H],
+ *                   final norm γ, lm_head W[V,H]  — all row-major [N,K] (the reference's
+ *                   trans_b=true layout), which is exactly what the GEMV's bulk copies and the
+ *                   GEMM's TMA maps read; no repacking.
+ *   KV cache      : K and V each [layers, batch, kv_heads, max_seq_len, head_size]
+ *                   (reference llama.cpp:77-78,102-103), 64-bit indexed.
+ *   activations   : hidden [B,H], qkv [B,(h+2hk)d], attn [B,hd], act [B,I] (fused) or
+ *                   gate_up [B,2,I] (unfused), logits [B,V], token ids, device-side step.
+ *
+ * Tensor parallelism (config 5): tp_size ranks each hold h/tp query heads, hk/tp kv heads and
+ * I/tp FFN columns; o_proj and down_proj produce partial sums that the caller-provided
+ * allreduce hook sums after each (the only two collective sites).
+ */
+#ifndef B200_ENGINE_H
+#define B200_ENGINE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct b200_engine b200_engine;
+
+typedef struct b200_model_config {
+    int num_layers;
+    int head_num;     /* GLOBAL query heads  */
+    int kv_head_num;  /* GLOBAL kv heads     */
+    int head_size;
+    int inter_size;   /* GLOBAL FFN width    */
+    int vocab_size;
+    int max_seq_len;
+    int max_batch;
+    float rms_eps;
+    int rotary_dim;
+    float rotary_base;
+    int dtype;        /* B200_F32 / B200_F16 */
+    int tp_size;      /* 1 = no tensor parallelism */
+    int tp_rank;
+} b200_model_config;
+
+/* weight slots for b200_engine_set_weight / get_weight (layer ignored for the last three) */
+enum {
+    B200_W_ATTN_NORM = 0,
+    B200_W_QKV = 1,
+    B200_W_O = 2,
+    B200_W_FFN_NORM = 3,
+    B200_W_GATE_UP = 4,
+    B200_W_DOWN = 5,
+    B200_W_EMBED = 6,
+    B200_W_FINAL_NORM = 7,
+    B200_W_LM_HEAD = 8
+};
+
+/* mode flags for b200_engine_set_mode */
+#define B200_ENGINE_FUSED 1u   /* fused GEMV prologues/epilogues (default)                    */
+#define B200_ENGINE_GRAPH 2u   /* CUDA-graph replay of the whole step (default)               */
+/* without FUSED the engine issues the reference's kernel sequence one launch* at a time
+ * (rmsnorm, linear, rope, masked MHA, linear, fused add+norm, linear, act, linear, add) */
+
+/* allreduce hook: sum `count` elements of `buf` (dtype as the model) in place across the
+ * tensor-parallel group, enqueued on `stream`. NULL when tp_size == 1. */
+typedef int (*b200_allreduce_fn)(void* buf, size_t count, int dtype, void* stream, void* user);
+
+b200_engine* b200_engine_create(const b200_model_config* cfg, int batch);
+void b200_engine_destroy(b200_engine* e);
+const char* b200_engine_last_error(void);
+
+size_t b200_engine_weight_bytes(const b200_engine* e);      /* this rank's weights         */
+size_t b200_engine_kv_bytes(const b200_engine* e);          /* K + V cache                 */
+size_t b200_engine_weight_elems(const b200_engine* e, int slot);
+int b200_engine_set_mode(b200_engine* e, unsigned flags);
+int b200_engine_set_allreduce(b200_engine* e, b200_allreduce_fn fn, void* user);
+void* b200_engine_stream(b200_engine* e);
+
+/* weights: deterministic N(0, std^2) fill on the device (norm weights 1 + N(0,std^2)), or
+ * explicit upload/download of one tensor (host pointers, element type = model dtype) */
+int b200_engine_init_random(b200_engine* e, uint64_t seed, float std);
+int b200_engine_set_weight(b200_engine* e, int slot, int layer, const void* host_src, size_t bytes);
+int b200_engine_get_weight(b200_engine* e, int slot, int layer, void* host_dst, size_t bytes);
+
+/* KV cache: fill rows [0, len) of every layer with U(-amp, amp) (bench configs that start from a
+ * given context length) and set the step so the next decoded token sits at position `len`. */
+int b200_engine_fill_kv_random(b200_engine* e, int len, uint64_t seed, float amp);
+int b200_engine_reset(b200_engine* e);            /* step <- 0 (cache contents kept)          */
+int b200_engine_get_step(const b200_engine* e);   /* tokens already in the cache              */
+
+/* One decode step for the whole batch, all on the engine's stream, no host sync:
+ *   ids_in (device int32 [batch], NULL = use the ids produced by the previous step)
+ *   -> embedding -> layers -> final norm -> LM head -> argmax -> ids_out (device, inside engine)
+ * The new token's K/V land at row `step`, then step <- step + 1. */
+int b200_engine_decode_step(b200_engine* e, const int* ids_in_dev);
+/* The call a user of the reference makes per token (llama.cpp:443 H2D id, :266 D2H id):
+ * host ids in (pinned or pageable), one decode step, host ids out; synchronises. */
+int b200_engine_decode_step_host(b200_engine* e, const int* ids_in_host, int* ids_out_host);
+
+/* device pointers into the engine (valid until destroy): logits [batch, vocab], ids [batch],
+ * hidden [batch, H], caches; for parity tests and the bench. */
+void* b200_engine_logits(b200_engine* e);
+int* b200_engine_ids_out(b200_engine* e);
+void* b200_engine_hidden(b200_engine* e);
+void* b200_engine_k_cache(b200_engine* e);
+void* b200_engine_v_cache(b200_engine* e);
+/* device pointer of one weight tensor (bench: per-kernel roofline runs on the real weights) */
+void* b200_engine_weight_ptr(b200_engine* e, int slot, int layer);
+/* kernel launches one decode step issues (graph nodes or stream launches) */
+int b200_engine_launches_per_step(const b200_engine* e);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_ENGINE_H */

@@ -110,6 +110,18 @@ __device__ __forceinline__ float dot16<__half>(const Pack16& a, const Pack16& b,
 }
 
 // ---------------------------------------------------------------------------
+// RoPE angle: pos / base^(2i/rot_dim) (reference qkv_bias_and_RoPE.cu:29-36). The power is
+// evaluated in double and rounded once, so it is the correctly rounded float power on every
+// implementation (device powf is only ~2 ulp, which at position 4095 already moves the angle by
+// 1e-3 rad). The fp32 division and cosf/sinf then see bit-identical angles as the CPU oracle.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ float rope_angle(int pair, int rot_dim, float base, float pos) {
+    const float ex = (float)(2 * pair) / (float)rot_dim;
+    const float den = (float)pow((double)base, (double)ex);
+    return pos / den;
+}
+
+// ---------------------------------------------------------------------------
 // reductions
 // ---------------------------------------------------------------------------
 __device__ __forceinline__ float warp_sum(float v) {

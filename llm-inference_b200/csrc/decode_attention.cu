@@ -297,6 +297,10 @@ static int attn_pick_splits(int batch, int kv_head_num, int step) {
     return splits;
 }
 
+int attn_pick_splits_public(int batch, int kv_head_num, int step) {
+    return attn_pick_splits(batch, kv_head_num, step);
+}
+
 static bool attn_fast_shape(int head_num, int kv_head_num, int head_size, int esz) {
     const int G = head_num / kv_head_num;
     const int row = head_size * esz;

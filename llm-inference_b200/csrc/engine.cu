@@ -1,0 +1,522 @@
+// Decode-step driver (C ABI in include/b200_engine.h).
+// Host-side order of operations follows the reference's per-token path —
+// llama.cpp:319-361 (continueTokenGen), self_decoder.cpp:53-85 (layer loop),
+// masked_self_attention.cpp:55-92, ffn.cpp:53-93, llama.cpp:215-271 (LM head + top-1) —
+// with its per-call Malloc/Free + cudaDeviceSynchronize replaced by one arena, one stream and
+// CUDA-graph replay (one graph per split-KV geometry; `step` lives in device memory so the same
+// graph serves every position of its bucket).
+#include <map>
+#include <string>
+#include <vector>
+
+#include "b200_engine.h"
+#include "common.cuh"
+#include "launch_count.h"
+
+namespace b200 {
+
+static thread_local std::string g_err;
+static int fail(const std::string& m, int code = B200_EINVAL) {
+    g_err = m;
+    return code;
+}
+#define CU(call)                                                                            \
+    do {                                                                                    \
+        cudaError_t e_ = (call);                                                            \
+        if (e_ != cudaSuccess)                                                              \
+            return fail(std::string(#call) + ": " + cudaGetErrorString(e_), (int)e_);       \
+    } while (0)
+#define RC(call)                                                        \
+    do {                                                                \
+        int rc_ = (call);                                               \
+        if (rc_ != 0) return fail(std::string(#call) + " failed", rc_); \
+    } while (0)
+
+struct LayerW {
+    void *attn_norm, *qkv, *o, *ffn_norm, *gate_up, *down;
+};
+
+}  // namespace b200
+
+using namespace b200;
+
+struct b200_engine {
+    b200_model_config cfg;
+    int batch;
+    size_t esz;
+    // per-rank shapes
+    int h, hk, d, H, I, V, qkv_n;
+    // memory
+    char* arena = nullptr;
+    size_t arena_bytes = 0;
+    std::vector<LayerW> layers;
+    void *embed = nullptr, *final_norm = nullptr, *lm_head = nullptr;
+    char *k_cache = nullptr, *v_cache = nullptr;
+    size_t kv_bytes_each = 0, layer_kv_elems = 0;
+    char* act_arena = nullptr;
+    void *hidden, *residual, *qkv, *attn, *act, *gate_up, *logits, *partial;
+    int *ids_cur, *ids_next, *step_dev;
+    void* attn_ws;
+    size_t attn_ws_bytes;
+    int* pinned_ids = nullptr;
+    // control
+    cudaStream_t stream = nullptr;
+    unsigned mode = B200_ENGINE_FUSED | B200_ENGINE_GRAPH;
+    b200_allreduce_fn allreduce = nullptr;
+    void* allreduce_user = nullptr;
+    int step = 0;  // host mirror of *step_dev: tokens already in the cache
+    std::map<int, cudaGraphExec_t> graphs;  // key: split-KV count
+    int launches_per_step = 0;
+};
+
+namespace b200 {
+
+static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+static size_t slot_elems(const b200_engine* e, int slot) {
+    switch (slot) {
+        case B200_W_ATTN_NORM: case B200_W_FFN_NORM: case B200_W_FINAL_NORM: return (size_t)e->H;
+        case B200_W_QKV: return (size_t)e->qkv_n * e->H;
+        case B200_W_O: return (size_t)e->H * e->h * e->d;
+        case B200_W_GATE_UP: return (size_t)2 * e->I * e->H;
+        case B200_W_DOWN: return (size_t)e->H * e->I;
+        case B200_W_EMBED: case B200_W_LM_HEAD: return (size_t)e->V * e->H;
+    }
+    return 0;
+}
+
+static void* slot_ptr(b200_engine* e, int slot, int layer) {
+    if (slot <= B200_W_DOWN) {
+        if (layer < 0 || layer >= (int)e->layers.size()) return nullptr;
+        LayerW& w = e->layers[layer];
+        switch (slot) {
+            case B200_W_ATTN_NORM: return w.attn_norm;
+            case B200_W_QKV: return w.qkv;
+            case B200_W_O: return w.o;
+            case B200_W_FFN_NORM: return w.ffn_norm;
+            case B200_W_GATE_UP: return w.gate_up;
+            case B200_W_DOWN: return w.down;
+        }
+    }
+    if (slot == B200_W_EMBED) return e->embed;
+    if (slot == B200_W_FINAL_NORM) return e->final_norm;
+    if (slot == B200_W_LM_HEAD) return e->lm_head;
+    return nullptr;
+}
+
+// counter-based normal / uniform fill (splitmix64 hash -> Box-Muller); value = mean + std*n
+template <typename T>
+__global__ void fill_normal_kernel(T* p, size_t n, uint64_t seed, float mean, float std) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+         i += (size_t)gridDim.x * blockDim.x) {
+        uint64_t z = seed + 0x9E3779B97F4A7C15ull * (i + 1);
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+        z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+        z ^= z >> 31;
+        const float u1 = ((uint32_t)(z >> 40) + 1.0f) * (1.0f / 16777217.0f);
+        const float u2 = (uint32_t)((z >> 8) & 0xffffff) * (1.0f / 16777216.0f);
+        const float nrm = sqrtf(-2.f * logf(u1)) * cospif(2.f * u2);
+        p[i] = DT<T>::from_f(mean + std * nrm);
+    }
+}
+template <typename T>
+__global__ void fill_uniform_rows_kernel(T* cache, size_t rows_total, int max_seq, int len, int d,
+                                         uint64_t seed, float amp) {
+    // cache viewed as [rows_total = layers*B*hk][max_seq][d]; fill rows t < len
+    const size_t n = rows_total * (size_t)len * d;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+         i += (size_t)gridDim.x * blockDim.x) {
+        const size_t r = i / ((size_t)len * d);
+        const size_t rem = i - r * (size_t)len * d;
+        uint64_t z = seed + 0x9E3779B97F4A7C15ull * (i + 1);
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+        z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+        z ^= z >> 31;
+        const float u = (uint32_t)(z >> 40) * (1.0f / 16777216.0f);
+        cache[r * (size_t)max_seq * d + rem] = DT<T>::from_f(amp * (2.f * u - 1.f));
+    }
+}
+
+__global__ void advance_kernel(int* ids_cur, const int* ids_next, int* step, int batch) {
+    pdl_wait();
+    if (threadIdx.x < batch) ids_cur[threadIdx.x] = ids_next[threadIdx.x];
+    if (threadIdx.x == 0) *step += 1;
+}
+
+}  // namespace b200
+
+extern "C" const char* b200_engine_last_error(void) { return g_err.c_str(); }
+
+extern "C" b200_engine* b200_engine_create(const b200_model_config* c, int batch) {
+    if (!c || batch < 1 || batch > c->max_batch) { fail("bad config / batch"); return nullptr; }
+    if (c->tp_size < 1 || c->head_num % c->tp_size || c->kv_head_num % c->tp_size ||
+        c->inter_size % c->tp_size || c->head_num % c->kv_head_num) {
+        fail("heads / inter size not divisible by tp_size");
+        return nullptr;
+    }
+    if (c->dtype != B200_F32 && c->dtype != B200_F16) { fail("dtype"); return nullptr; }
+    if (batch > 1024) { fail("batch > 1024"); return nullptr; }
+    b200_engine* e = new b200_engine();
+    e->cfg = *c;
+    e->batch = batch;
+    e->esz = c->dtype == B200_F16 ? 2 : 4;
+    e->h = c->head_num / c->tp_size;
+    e->hk = c->kv_head_num / c->tp_size;
+    e->d = c->head_size;
+    e->H = c->head_num * c->head_size;
+    e->I = c->inter_size / c->tp_size;
+    e->V = c->vocab_size;
+    e->qkv_n = (e->h + 2 * e->hk) * e->d;
+    const size_t es = e->esz;
+    auto fail_free = [&](const char* what, cudaError_t err) {
+        fail(std::string(what) + ": " + cudaGetErrorString(err), (int)err);
+        b200_engine_destroy(e);
+        return (b200_engine*)nullptr;
+    };
+    // ---- weights arena
+    size_t off = 0;
+    std::vector<size_t> offs;
+    auto take = [&](size_t elems) { size_t o = off; off += align256(elems * es); return o; };
+    struct LO { size_t an, qkv, o, fn, gu, dn; };
+    std::vector<LO> lo(c->num_layers);
+    for (int l = 0; l < c->num_layers; ++l) {
+        lo[l].an = take(slot_elems(e, B200_W_ATTN_NORM));
+        lo[l].qkv = take(slot_elems(e, B200_W_QKV));
+        lo[l].o = take(slot_elems(e, B200_W_O));
+        lo[l].fn = take(slot_elems(e, B200_W_FFN_NORM));
+        lo[l].gu = take(slot_elems(e, B200_W_GATE_UP));
+        lo[l].dn = take(slot_elems(e, B200_W_DOWN));
+    }
+    const size_t o_embed = take(slot_elems(e, B200_W_EMBED));
+    const size_t o_fnorm = take(slot_elems(e, B200_W_FINAL_NORM));
+    const size_t o_head = take(slot_elems(e, B200_W_LM_HEAD));
+    e->arena_bytes = off;
+    cudaError_t err = cudaMalloc(&e->arena, off);
+    if (err != cudaSuccess) return fail_free("cudaMalloc(weights)", err);
+    e->layers.resize(c->num_layers);
+    for (int l = 0; l < c->num_layers; ++l)
+        e->layers[l] = {e->arena + lo[l].an, e->arena + lo[l].qkv, e->arena + lo[l].o,
+                        e->arena + lo[l].fn, e->arena + lo[l].gu, e->arena + lo[l].dn};
+    e->embed = e->arena + o_embed;
+    e->final_norm = e->arena + o_fnorm;
+    e->lm_head = e->arena + o_head;
+    // ---- KV cache [layers, B, hk, max_seq, d] x2, 64-bit sizes (reference D21)
+    e->layer_kv_elems = (size_t)batch * e->hk * c->max_seq_len * e->d;
+    e->kv_bytes_each = e->layer_kv_elems * c->num_layers * es;
+    if ((err = cudaMalloc(&e->k_cache, e->kv_bytes_each)) != cudaSuccess) return fail_free("cudaMalloc(K)", err);
+    if ((err = cudaMalloc(&e->v_cache, e->kv_bytes_each)) != cudaSuccess) return fail_free("cudaMalloc(V)", err);
+    cudaMemset(e->k_cache, 0, e->kv_bytes_each);
+    cudaMemset(e->v_cache, 0, e->kv_bytes_each);
+    // ---- activations
+    e->attn_ws_bytes = b200_decode_attention_workspace_bytes(batch, e->h, e->d, c->max_seq_len);
+    off = 0;
+    const size_t B = batch;
+    const size_t o_hidden = take(B * e->H), o_resid = take(B * e->H), o_qkv = take(B * e->qkv_n),
+                 o_attn = take(B * e->h * e->d), o_act = take(B * e->I),
+                 o_gu = take(B * 2 * e->I), o_logits = take(B * e->V), o_part = take(B * e->H);
+    const size_t o_ids = off; off += align256(2 * B * sizeof(int) + sizeof(int) + 64);
+    const size_t o_ws = off; off += align256(e->attn_ws_bytes);
+    if ((err = cudaMalloc(&e->act_arena, off)) != cudaSuccess) return fail_free("cudaMalloc(act)", err);
+    cudaMemset(e->act_arena, 0, off);
+    char* a = e->act_arena;
+    e->hidden = a + o_hidden; e->residual = a + o_resid; e->qkv = a + o_qkv; e->attn = a + o_attn;
+    e->act = a + o_act; e->gate_up = a + o_gu; e->logits = a + o_logits; e->partial = a + o_part;
+    e->ids_cur = (int*)(a + o_ids); e->ids_next = e->ids_cur + B; e->step_dev = e->ids_next + B;
+    e->attn_ws = a + o_ws;
+    if ((err = cudaMallocHost(&e->pinned_ids, 2 * B * sizeof(int))) != cudaSuccess) return fail_free("cudaMallocHost", err);
+    if ((err = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking)) != cudaSuccess) return fail_free("stream", err);
+    const int ref_step0 = 1;  // reference `step` of the first token (tokens in cache + 1)
+    cudaMemcpy(e->step_dev, &ref_step0, sizeof(int), cudaMemcpyHostToDevice);
+    cudaDeviceSynchronize();
+    return e;
+}
+
+extern "C" void b200_engine_destroy(b200_engine* e) {
+    if (!e) return;
+    for (auto& kv : e->graphs) cudaGraphExecDestroy(kv.second);
+    if (e->stream) cudaStreamDestroy(e->stream);
+    if (e->pinned_ids) cudaFreeHost(e->pinned_ids);
+    cudaFree(e->arena);
+    cudaFree(e->k_cache);
+    cudaFree(e->v_cache);
+    cudaFree(e->act_arena);
+    delete e;
+}
+
+// ------------------------------------------------------------------------------------------
+// accessors / weights
+// ------------------------------------------------------------------------------------------
+extern "C" size_t b200_engine_weight_bytes(const b200_engine* e) { return e ? e->arena_bytes : 0; }
+extern "C" size_t b200_engine_kv_bytes(const b200_engine* e) { return e ? 2 * e->kv_bytes_each : 0; }
+extern "C" size_t b200_engine_weight_elems(const b200_engine* e, int slot) { return e ? slot_elems(e, slot) : 0; }
+extern "C" void* b200_engine_stream(b200_engine* e) { return e ? (void*)e->stream : nullptr; }
+extern "C" void* b200_engine_logits(b200_engine* e) { return e->logits; }
+extern "C" int* b200_engine_ids_out(b200_engine* e) { return e->ids_next; }
+extern "C" void* b200_engine_hidden(b200_engine* e) { return e->hidden; }
+extern "C" void* b200_engine_k_cache(b200_engine* e) { return e->k_cache; }
+extern "C" void* b200_engine_v_cache(b200_engine* e) { return e->v_cache; }
+extern "C" int b200_engine_get_step(const b200_engine* e) { return e->step; }
+extern "C" void* b200_engine_weight_ptr(b200_engine* e, int slot, int layer) { return e ? slot_ptr(e, slot, layer) : nullptr; }
+extern "C" int b200_engine_launches_per_step(const b200_engine* e) { return e->launches_per_step; }
+
+static void drop_graphs(b200_engine* e) {
+    for (auto& kv : e->graphs) cudaGraphExecDestroy(kv.second);
+    e->graphs.clear();
+}
+
+extern "C" int b200_engine_set_mode(b200_engine* e, unsigned flags) {
+    if (!e) return B200_EINVAL;
+    cudaStreamSynchronize(e->stream);
+    drop_graphs(e);
+    e->mode = flags;
+    return B200_OK;
+}
+extern "C" int b200_engine_set_allreduce(b200_engine* e, b200_allreduce_fn fn, void* user) {
+    if (!e) return B200_EINVAL;
+    drop_graphs(e);
+    e->allreduce = fn;
+    e->allreduce_user = user;
+    return B200_OK;
+}
+
+static int set_step(b200_engine* e, int n) {
+    e->step = n;
+    const int ref_step = n + 1;  // reference `step`: tokens in the cache including the new one
+    CU(cudaMemcpyAsync(e->step_dev, &ref_step, sizeof(int), cudaMemcpyHostToDevice, e->stream));
+    CU(cudaStreamSynchronize(e->stream));
+    return B200_OK;
+}
+
+extern "C" int b200_engine_reset(b200_engine* e) { return e ? set_step(e, 0) : B200_EINVAL; }
+
+template <typename T>
+static void fill_normal(void* p, size_t n, uint64_t seed, float mean, float std, cudaStream_t s) {
+    size_t blocks = (n + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    fill_normal_kernel<T><<<(unsigned)blocks, 256, 0, s>>>((T*)p, n, seed, mean, std);
+}
+
+extern "C" int b200_engine_init_random(b200_engine* e, uint64_t seed, float std) {
+    if (!e) return B200_EINVAL;
+    uint64_t k = seed * 1000003ull;
+    auto fill = [&](void* p, int slot, float mean) {
+        const size_t n = slot_elems(e, slot);
+        if (e->cfg.dtype == B200_F16) fill_normal<__half>(p, n, ++k, mean, std, e->stream);
+        else fill_normal<float>(p, n, ++k, mean, std, e->stream);
+    };
+    for (auto& w : e->layers) {
+        fill(w.attn_norm, B200_W_ATTN_NORM, 1.f);
+        fill(w.qkv, B200_W_QKV, 0.f);
+        fill(w.o, B200_W_O, 0.f);
+        fill(w.ffn_norm, B200_W_FFN_NORM, 1.f);
+        fill(w.gate_up, B200_W_GATE_UP, 0.f);
+        fill(w.down, B200_W_DOWN, 0.f);
+    }
+    fill(e->embed, B200_W_EMBED, 0.f);
+    fill(e->final_norm, B200_W_FINAL_NORM, 1.f);
+    fill(e->lm_head, B200_W_LM_HEAD, 0.f);
+    CU(cudaStreamSynchronize(e->stream));
+    CU(cudaGetLastError());
+    return B200_OK;
+}
+
+extern "C" int b200_engine_set_weight(b200_engine* e, int slot, int layer, const void* src, size_t bytes) {
+    if (!e || !src) return B200_EINVAL;
+    void* p = slot_ptr(e, slot, layer);
+    if (!p || bytes != slot_elems(e, slot) * e->esz) return fail("set_weight: bad slot / size");
+    CU(cudaMemcpy(p, src, bytes, cudaMemcpyHostToDevice));
+    return B200_OK;
+}
+extern "C" int b200_engine_get_weight(b200_engine* e, int slot, int layer, void* dst, size_t bytes) {
+    if (!e || !dst) return B200_EINVAL;
+    void* p = slot_ptr(e, slot, layer);
+    if (!p || bytes != slot_elems(e, slot) * e->esz) return fail("get_weight: bad slot / size");
+    CU(cudaMemcpy(dst, p, bytes, cudaMemcpyDeviceToHost));
+    return B200_OK;
+}
+
+extern "C" int b200_engine_fill_kv_random(b200_engine* e, int len, uint64_t seed, float amp) {
+    if (!e || len < 0 || len >= e->cfg.max_seq_len) return fail("fill_kv: len out of range");
+    const size_t rows = (size_t)e->cfg.num_layers * e->batch * e->hk;
+    if (len > 0) {
+        const size_t n = rows * (size_t)len * e->d;
+        size_t blocks = (n + 255) / 256;
+        if (blocks > 148 * 32) blocks = 148 * 32;
+        if (e->cfg.dtype == B200_F16) {
+            fill_uniform_rows_kernel<__half><<<(unsigned)blocks, 256, 0, e->stream>>>(
+                (__half*)e->k_cache, rows, e->cfg.max_seq_len, len, e->d, seed * 2 + 1, amp);
+            fill_uniform_rows_kernel<__half><<<(unsigned)blocks, 256, 0, e->stream>>>(
+                (__half*)e->v_cache, rows, e->cfg.max_seq_len, len, e->d, seed * 2 + 2, amp);
+        } else {
+            fill_uniform_rows_kernel<float><<<(unsigned)blocks, 256, 0, e->stream>>>(
+                (float*)e->k_cache, rows, e->cfg.max_seq_len, len, e->d, seed * 2 + 1, amp);
+            fill_uniform_rows_kernel<float><<<(unsigned)blocks, 256, 0, e->stream>>>(
+                (float*)e->v_cache, rows, e->cfg.max_seq_len, len, e->d, seed * 2 + 2, amp);
+        }
+        CU(cudaGetLastError());
+    }
+    return set_step(e, len);
+}
+
+// ------------------------------------------------------------------------------------------
+// one decode step
+// ------------------------------------------------------------------------------------------
+namespace b200 {
+int attn_pick_splits_public(int batch, int kv_head_num, int step);  // decode_attention.cu
+}
+
+static int gemv(b200_engine* e, const void* x, const void* W, void* y, int N, int K, unsigned flags,
+                const void* gamma = nullptr, int layer = -1) {
+    b200_gemv_args a{};
+    a.x = x; a.W = W; a.y = y; a.gamma = gamma; a.eps = e->cfg.rms_eps;
+    a.n_tokens = e->batch; a.N = N; a.K = K; a.flags = flags;
+    if (flags & B200_GEMV_ROPE_KV) {
+        a.k_cache_layer = e->k_cache + (size_t)layer * e->layer_kv_elems * e->esz;
+        a.v_cache_layer = e->v_cache + (size_t)layer * e->layer_kv_elems * e->esz;
+        a.head_num = e->h; a.kv_head_num = e->hk; a.head_size = e->d;
+        a.max_seq_len = e->cfg.max_seq_len; a.step = e->step + 1;
+        a.rotary_dim = e->cfg.rotary_dim; a.rotary_base = e->cfg.rotary_base;
+        a.step_dev = e->step_dev;
+    }
+    // batches above the GEMV tile are walked in tiles of B200_GEMV_MAX_TOKENS
+    const int B = e->batch;
+    for (int t0 = 0; t0 < B; t0 += B200_GEMV_MAX_TOKENS) {
+        b200_gemv_args t = a;
+        const int nt = (B - t0 < B200_GEMV_MAX_TOKENS) ? B - t0 : B200_GEMV_MAX_TOKENS;
+        t.n_tokens = nt;
+        t.x = (const char*)x + (size_t)t0 * K * e->esz;
+        t.y = (char*)y + (size_t)t0 * N * e->esz;
+        if (flags & B200_GEMV_ROPE_KV) {
+            const size_t per_seq = (size_t)e->hk * e->cfg.max_seq_len * e->d * e->esz;
+            t.k_cache_layer = (char*)a.k_cache_layer + (size_t)t0 * per_seq;
+            t.v_cache_layer = (char*)a.v_cache_layer + (size_t)t0 * per_seq;
+        }
+        int rc = b200_gemv_fused(&t, e->cfg.dtype, e->stream);
+        if (rc != 0) return rc;
+    }
+    return 0;
+}
+
+static int tp_allreduce_add(b200_engine* e) {
+    // partial [B,H] -> sum over ranks -> hidden += partial
+    if (e->allreduce) RC(e->allreduce(e->partial, (size_t)e->batch * e->H, e->cfg.dtype, e->stream, e->allreduce_user));
+    RC(b200_add_residual(e->partial, e->hidden, e->batch, e->H, e->cfg.dtype, e->stream));
+    return 0;
+}
+
+static int enqueue_step(b200_engine* e) {
+    const int dt = e->cfg.dtype, B = e->batch, H = e->H;
+    const int ref_step = e->step + 1;
+    cudaStream_t s = e->stream;
+    const bool tp = e->cfg.tp_size > 1;
+    RC(b200_embedding(e->ids_cur, e->embed, e->hidden, B, H, e->V, dt, s));
+    for (int l = 0; l < e->cfg.num_layers; ++l) {
+        LayerW& w = e->layers[l];
+        void* kc = e->k_cache + (size_t)l * e->layer_kv_elems * e->esz;
+        void* vc = e->v_cache + (size_t)l * e->layer_kv_elems * e->esz;
+        if (e->mode & B200_ENGINE_FUSED) {
+            RC(gemv(e, e->hidden, w.qkv, e->qkv, e->qkv_n, H, B200_GEMV_NORM | B200_GEMV_ROPE_KV, w.attn_norm, l));
+            RC(b200_decode_attention_ex(e->qkv, kc, vc, e->attn, e->attn_ws, e->attn_ws_bytes, B, e->h, e->hk,
+                                        e->d, e->cfg.max_seq_len, ref_step, e->step_dev, 0, dt, s));
+            if (!tp) {
+                RC(gemv(e, e->attn, w.o, e->hidden, H, e->h * e->d, B200_GEMV_RESIDUAL));
+            } else {
+                RC(gemv(e, e->attn, w.o, e->partial, H, e->h * e->d, 0));
+                RC(tp_allreduce_add(e));
+            }
+            RC(gemv(e, e->hidden, w.gate_up, e->act, e->I, H,
+                    B200_GEMV_NORM | B200_GEMV_NORM_GFIRST | B200_GEMV_SWIGLU, w.ffn_norm));
+            if (!tp) {
+                RC(gemv(e, e->act, w.down, e->hidden, H, e->I, B200_GEMV_RESIDUAL));
+            } else {
+                RC(gemv(e, e->act, w.down, e->partial, H, e->I, 0));
+                RC(tp_allreduce_add(e));
+            }
+        } else {
+            // the reference's launch sequence, one kernel per launch* (self_decoder.cpp:53-85)
+            RC(b200_rmsnorm(e->hidden, e->residual, w.attn_norm, B, H, e->cfg.rms_eps, dt, s));
+            RC(b200_linear(e->hidden, w.qkv, nullptr, e->qkv, B, e->qkv_n, H, 1, dt, nullptr, 0, s));
+            RC(b200_rope_decode(e->qkv, B, e->h, e->hk, e->d, ref_step, e->cfg.rotary_dim, e->cfg.rotary_base, dt, s));
+            RC(b200_decode_attention(e->qkv, kc, vc, e->attn, e->attn_ws, e->attn_ws_bytes, B, e->h, e->hk, e->d,
+                                     e->cfg.max_seq_len, ref_step, 1, dt, s));
+            RC(b200_linear(e->attn, w.o, nullptr, e->hidden, B, H, e->h * e->d, 1, dt, nullptr, 0, s));
+            if (tp && e->allreduce) RC(e->allreduce(e->hidden, (size_t)B * H, dt, s, e->allreduce_user));
+            RC(b200_fused_add_bias_residual_rmsnorm(e->residual, e->hidden, nullptr, w.ffn_norm, B, H, e->cfg.rms_eps, dt, s));
+            RC(b200_linear(e->hidden, w.gate_up, nullptr, e->gate_up, B, 2 * e->I, H, 1, dt, nullptr, 0, s));
+            RC(b200_swiglu(e->gate_up, e->act, B, e->I, dt, s));
+            RC(b200_linear(e->act, w.down, nullptr, e->hidden, B, H, e->I, 1, dt, nullptr, 0, s));
+            if (tp && e->allreduce) RC(e->allreduce(e->hidden, (size_t)B * H, dt, s, e->allreduce_user));
+            RC(b200_add_residual(e->residual, e->hidden, B, H, dt, s));
+        }
+    }
+    if (e->mode & B200_ENGINE_FUSED) {
+        RC(gemv(e, e->hidden, e->lm_head, e->logits, e->V, H, B200_GEMV_NORM, e->final_norm));
+    } else {
+        // llama.cpp:341 normalises decoder_output in place; we do it on a copy so that
+        // b200_engine_hidden() shows the decoder output in both modes
+        CU(cudaMemcpyAsync(e->partial, e->hidden, (size_t)B * H * e->esz, cudaMemcpyDeviceToDevice, s));
+        RC(b200_rmsnorm(e->partial, nullptr, e->final_norm, B, H, e->cfg.rms_eps, dt, s));
+        RC(b200_linear(e->partial, e->lm_head, nullptr, e->logits, B, e->V, H, 1, dt, nullptr, 0, s));
+    }
+    RC(b200_argmax(e->logits, e->ids_next, B, e->V, dt, s));
+    CU(launch_k(advance_kernel, dim3(1), dim3(1024), 0, s, true, e->ids_cur, (const int*)e->ids_next, e->step_dev, B));
+    count_launch();
+    return 0;
+}
+
+static int run_step(b200_engine* e) {
+    if (e->step + 1 > e->cfg.max_seq_len) return fail("KV cache full (step == max_seq_len)");
+    const bool use_graph = (e->mode & B200_ENGINE_GRAPH) && (e->mode & B200_ENGINE_FUSED);
+    if (!use_graph) {
+        const uint64_t before = b200_launch_count();
+        RC(enqueue_step(e));
+        e->launches_per_step = (int)(b200_launch_count() - before);
+        e->step += 1;
+        return 0;
+    }
+    const int key = attn_pick_splits_public(e->batch, e->hk, e->step + 1);
+    auto it = e->graphs.find(key);
+    if (it == e->graphs.end()) {
+        const uint64_t before = b200_launch_count();
+        cudaGraph_t g = nullptr;
+        CU(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
+        int rc = enqueue_step(e);
+        cudaError_t ce = cudaStreamEndCapture(e->stream, &g);
+        if (rc != 0) { if (g) cudaGraphDestroy(g); return rc; }
+        if (ce != cudaSuccess) return fail(std::string("graph capture: ") + cudaGetErrorString(ce), (int)ce);
+        cudaGraphExec_t ge = nullptr;
+        ce = cudaGraphInstantiate(&ge, g, 0);
+        cudaGraphDestroy(g);
+        if (ce != cudaSuccess) return fail(std::string("graph instantiate: ") + cudaGetErrorString(ce), (int)ce);
+        e->launches_per_step = (int)(b200_launch_count() - before);
+        // the capture itself launched nothing: take its count back, replays are counted below
+        it = e->graphs.emplace(key, ge).first;
+    } else {
+        count_launch((uint64_t)e->launches_per_step);
+    }
+    CU(cudaGraphLaunch(it->second, e->stream));
+    e->step += 1;
+    return 0;
+}
+
+extern "C" int b200_engine_decode_step(b200_engine* e, const int* ids_in_dev) {
+    if (!e) return B200_EINVAL;
+    if (ids_in_dev)
+        CU(cudaMemcpyAsync(e->ids_cur, ids_in_dev, sizeof(int) * e->batch, cudaMemcpyDeviceToDevice, e->stream));
+    return run_step(e);
+}
+
+extern "C" int b200_engine_decode_step_host(b200_engine* e, const int* ids_in_host, int* ids_out_host) {
+    if (!e || !ids_out_host) return B200_EINVAL;
+    const size_t nb = sizeof(int) * e->batch;
+    if (ids_in_host) {
+        memcpy(e->pinned_ids, ids_in_host, nb);
+        CU(cudaMemcpyAsync(e->ids_cur, e->pinned_ids, nb, cudaMemcpyHostToDevice, e->stream));
+    }
+    int rc = run_step(e);
+    if (rc != 0) return rc;
+    CU(cudaMemcpyAsync(e->pinned_ids + e->batch, e->ids_next, nb, cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaStreamSynchronize(e->stream));
+    memcpy(ids_out_host, e->pinned_ids + e->batch, nb);
+    return 0;
+}

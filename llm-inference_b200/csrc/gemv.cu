@@ -266,8 +266,7 @@ __global__ void __launch_bounds__(kGemvThreads, 1) gemv_stream_kernel(const Gemv
                     const int qkv_heads = p.head_num + 2 * p.kv_head_num;
                     float c = 1.f, s = 0.f;
                     if (head < p.head_num + p.kv_head_num && i < (p.rotary_dim >> 1)) {
-                        const float ang = (float)(step - 1) /
-                                          powf(p.rotary_base, (float)(2 * i) / (float)p.rotary_dim);
+                        const float ang = rope_angle(i, p.rotary_dim, p.rotary_base, (float)(step - 1));
                         c = cosf(ang);
                         s = sinf(ang);
                     }
@@ -355,8 +354,28 @@ template <typename T, int MODE>
 static int gemv_dispatch_nb(GemvParams p, int n_tokens, cudaStream_t s) {
     const int esz = (int)sizeof(T);
     int NB = n_tokens <= 1 ? 1 : n_tokens <= 2 ? 2 : n_tokens <= 4 ? 4 : 8;
-    const int stages = gemv_pick_stages(NB, p.K, esz);
-    if (stages == 0) return B200_EUNSUPPORTED;
+    int stages = gemv_pick_stages(NB, p.K, esz);
+    if (stages == 0) {
+        // x does not fit in shared memory next to the ring: run the tokens in smaller tiles
+        // (the weights are streamed once per tile). Token tiles are independent in every mode.
+        if (NB == 1) return B200_EUNSUPPORTED;
+        const int half = NB / 2;
+        const int y_stride = (MODE == kModeRopeKV) ? p.N : p.N;  // y is [tokens, N] in all modes
+        for (int t0 = 0; t0 < n_tokens; t0 += half) {
+            GemvParams q = p;
+            q.x = (const char*)p.x + (size_t)t0 * p.K * esz;
+            q.y = (char*)p.y + (size_t)t0 * y_stride * esz;
+            if (MODE == kModeRopeKV) {
+                const size_t per_seq = (size_t)p.kv_head_num * p.max_seq_len * p.head_size * esz;
+                q.k_cache = (char*)p.k_cache + (size_t)t0 * per_seq;
+                q.v_cache = (char*)p.v_cache + (size_t)t0 * per_seq;
+            }
+            const int nt = (n_tokens - t0 < half) ? n_tokens - t0 : half;
+            int rc = gemv_dispatch_nb<T, MODE>(q, nt, s);
+            if (rc != 0) return rc;
+        }
+        return B200_OK;
+    }
     p.stages = stages;
     p.nb = n_tokens;
     const size_t smem = gemv_smem_bytes(stages, NB, p.K, esz);

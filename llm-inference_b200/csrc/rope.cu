@@ -11,7 +11,7 @@
 namespace b200 {
 
 __device__ __forceinline__ float2 rope_cos_sin(int pair, int rot_dim, float base, float pos) {
-    const float ang = pos / powf(base, (float)(2 * pair) / (float)rot_dim);
+    const float ang = rope_angle(pair, rot_dim, base, pos);
     return make_float2(cosf(ang), sinf(ang));
 }
 

@@ -1,0 +1,220 @@
+"""ctypes front end of include/b200_engine.h (the decode-step driver). Plumbing only."""
+import ctypes as C
+
+import numpy as np
+
+from . import capi
+
+W_ATTN_NORM, W_QKV, W_O, W_FFN_NORM, W_GATE_UP, W_DOWN, W_EMBED, W_FINAL_NORM, W_LM_HEAD = range(9)
+LAYER_SLOTS = (W_ATTN_NORM, W_QKV, W_O, W_FFN_NORM, W_GATE_UP, W_DOWN)
+MODE_FUSED, MODE_GRAPH = 1, 2
+
+
+class ModelConfig(C.Structure):
+    _fields_ = [("num_layers", C.c_int), ("head_num", C.c_int), ("kv_head_num", C.c_int),
+                ("head_size", C.c_int), ("inter_size", C.c_int), ("vocab_size", C.c_int),
+                ("max_seq_len", C.c_int), ("max_batch", C.c_int), ("rms_eps", C.c_float),
+                ("rotary_dim", C.c_int), ("rotary_base", C.c_float), ("dtype", C.c_int),
+                ("tp_size", C.c_int), ("tp_rank", C.c_int)]
+
+
+ALLREDUCE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_void_p)
+
+_vp, _i = C.c_void_p, C.c_int
+ENGINE_PROTOTYPES = {
+    "b200_engine_create": (_vp, [C.POINTER(ModelConfig), _i]),
+    "b200_engine_destroy": (None, [_vp]),
+    "b200_engine_last_error": (C.c_char_p, []),
+    "b200_engine_weight_bytes": (C.c_size_t, [_vp]),
+    "b200_engine_kv_bytes": (C.c_size_t, [_vp]),
+    "b200_engine_weight_elems": (C.c_size_t, [_vp, _i]),
+    "b200_engine_set_mode": (_i, [_vp, C.c_uint]),
+    "b200_engine_set_allreduce": (_i, [_vp, ALLREDUCE_FN, _vp]),
+    "b200_engine_stream": (_vp, [_vp]),
+    "b200_engine_init_random": (_i, [_vp, C.c_uint64, C.c_float]),
+    "b200_engine_set_weight": (_i, [_vp, _i, _i, _vp, C.c_size_t]),
+    "b200_engine_get_weight": (_i, [_vp, _i, _i, _vp, C.c_size_t]),
+    "b200_engine_fill_kv_random": (_i, [_vp, _i, C.c_uint64, C.c_float]),
+    "b200_engine_reset": (_i, [_vp]),
+    "b200_engine_get_step": (_i, [_vp]),
+    "b200_engine_decode_step": (_i, [_vp, _vp]),
+    "b200_engine_decode_step_host": (_i, [_vp, _vp, _vp]),
+    "b200_engine_logits": (_vp, [_vp]),
+    "b200_engine_ids_out": (_vp, [_vp]),
+    "b200_engine_hidden": (_vp, [_vp]),
+    "b200_engine_k_cache": (_vp, [_vp]),
+    "b200_engine_v_cache": (_vp, [_vp]),
+    "b200_engine_launches_per_step": (_i, [_vp]),
+    "b200_engine_weight_ptr": (_vp, [_vp, _i, _i]),
+}
+
+_bound = False
+
+
+def _lib():
+    global _bound
+    lib = capi.lib()
+    if not _bound:
+        for name, (res, args) in ENGINE_PROTOTYPES.items():
+            fn = getattr(lib, name)
+            fn.restype, fn.argtypes = res, args
+        _bound = True
+    return lib
+
+
+LLAMA2_7B = dict(num_layers=32, head_num=32, kv_head_num=32, head_size=128, inter_size=11008,
+                 vocab_size=32000)
+LLAMA2_70B = dict(num_layers=80, head_num=64, kv_head_num=8, head_size=128, inter_size=28672,
+                  vocab_size=32000)
+
+
+class Engine:
+    """Owns one b200_engine on the current CUDA device."""
+
+    def __init__(self, batch, max_seq_len, dtype=capi.F16, rms_eps=1e-5, rotary_base=10000.0,
+                 rotary_dim=None, tp_size=1, tp_rank=0, **shape):
+        cfg = ModelConfig()
+        for k, v in shape.items():
+            setattr(cfg, k, v)
+        cfg.max_seq_len, cfg.max_batch = max_seq_len, batch
+        cfg.rms_eps, cfg.rotary_base = rms_eps, rotary_base
+        cfg.rotary_dim = rotary_dim if rotary_dim is not None else cfg.head_size
+        cfg.dtype, cfg.tp_size, cfg.tp_rank = dtype, tp_size, tp_rank
+        self.cfg, self.batch, self.dtype = cfg, batch, dtype
+        self.np_dtype = np.float16 if dtype == capi.F16 else np.float32
+        self.lib = _lib()
+        self.h = self.lib.b200_engine_create(C.byref(cfg), batch)
+        if not self.h:
+            raise RuntimeError("[b200][ERROR] engine_create: " + self.lib.b200_engine_last_error().decode())
+        self._cb = None
+
+    def close(self):
+        if self.h:
+            self.lib.b200_engine_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc, what):
+        if rc != 0:
+            raise RuntimeError(f"[b200][ERROR] {what}: rc={rc} {self.lib.b200_engine_last_error().decode()}")
+
+    # ---- properties
+    @property
+    def weight_bytes(self):
+        return self.lib.b200_engine_weight_bytes(self.h)
+
+    @property
+    def kv_bytes(self):
+        return self.lib.b200_engine_kv_bytes(self.h)
+
+    @property
+    def step(self):
+        return self.lib.b200_engine_get_step(self.h)
+
+    @property
+    def launches_per_step(self):
+        return self.lib.b200_engine_launches_per_step(self.h)
+
+    @property
+    def stream(self):
+        return self.lib.b200_engine_stream(self.h)
+
+    # ---- control
+    def set_mode(self, fused=True, graph=True):
+        self._ck(self.lib.b200_engine_set_mode(self.h, (MODE_FUSED if fused else 0) | (MODE_GRAPH if graph else 0)),
+                 "set_mode")
+
+    def set_allreduce(self, pyfunc):
+        """pyfunc(buf_ptr:int, count:int, dtype:int, stream_ptr:int) -> int"""
+        self._cb = ALLREDUCE_FN(lambda buf, n, dt, st, user: int(pyfunc(buf, n, dt, st) or 0))
+        self._ck(self.lib.b200_engine_set_allreduce(self.h, self._cb, None), "set_allreduce")
+
+    def init_random(self, seed=1234, std=0.02):
+        self._ck(self.lib.b200_engine_init_random(self.h, seed, std), "init_random")
+
+    def weight_shape(self, slot):
+        c = self.cfg
+        tp = c.tp_size
+        H, h, hk, d, I, V = c.head_num * c.head_size, c.head_num // tp, c.kv_head_num // tp, c.head_size, c.inter_size // tp, c.vocab_size
+        return {W_ATTN_NORM: (H,), W_FFN_NORM: (H,), W_FINAL_NORM: (H,), W_QKV: ((h + 2 * hk) * d, H),
+                W_O: (H, h * d), W_GATE_UP: (2 * I, H), W_DOWN: (H, I), W_EMBED: (V, H), W_LM_HEAD: (V, H)}[slot]
+
+    def set_weight(self, slot, layer, array):
+        a = np.ascontiguousarray(array, dtype=self.np_dtype)
+        assert a.shape == self.weight_shape(slot), (a.shape, self.weight_shape(slot))
+        self._ck(self.lib.b200_engine_set_weight(self.h, slot, layer, a.ctypes.data_as(C.c_void_p), a.nbytes), "set_weight")
+
+    def get_weight(self, slot, layer=0):
+        a = np.empty(self.weight_shape(slot), self.np_dtype)
+        self._ck(self.lib.b200_engine_get_weight(self.h, slot, layer, a.ctypes.data_as(C.c_void_p), a.nbytes), "get_weight")
+        return a
+
+    def fill_kv_random(self, length, seed=7, amp=0.5):
+        self._ck(self.lib.b200_engine_fill_kv_random(self.h, length, seed, amp), "fill_kv_random")
+
+    def reset(self):
+        self._ck(self.lib.b200_engine_reset(self.h), "reset")
+
+    # ---- stepping
+    def decode_step(self, ids_dev_ptr=None):
+        self._ck(self.lib.b200_engine_decode_step(self.h, ids_dev_ptr), "decode_step")
+
+    def decode_step_host(self, ids_in):
+        """numpy int32 [batch] (or None to continue from the previous output) -> numpy int32 [batch]"""
+        out = np.empty(self.batch, np.int32)
+        inp = None
+        if ids_in is not None:
+            ids_in = np.ascontiguousarray(ids_in, dtype=np.int32)
+            inp = ids_in.ctypes.data_as(C.c_void_p)
+        self._ck(self.lib.b200_engine_decode_step_host(self.h, inp, out.ctypes.data_as(C.c_void_p)), "decode_step_host")
+        return out
+
+    def _view(self, ptr, shape, torch_dtype):
+        """zero-copy torch view of engine-owned device memory (tests / bench only)"""
+        import torch
+        n = int(np.prod(shape))
+        itemsize = torch.tensor([], dtype=torch_dtype).element_size()
+
+        class _Mem:
+            pass
+        m = _Mem()
+        m.__cuda_array_interface__ = {"shape": (n * itemsize,), "typestr": "|u1", "data": (int(ptr), False), "version": 2}
+        return torch.as_tensor(m, device="cuda").view(torch_dtype).view(*shape)
+
+    def logits(self):
+        import torch
+        td = torch.float16 if self.dtype == capi.F16 else torch.float32
+        return self._view(self.lib.b200_engine_logits(self.h), (self.batch, self.cfg.vocab_size), td)
+
+    def hidden(self):
+        import torch
+        td = torch.float16 if self.dtype == capi.F16 else torch.float32
+        return self._view(self.lib.b200_engine_hidden(self.h), (self.batch, self.cfg.head_num * self.cfg.head_size), td)
+
+    def weight_view(self, slot, layer=0):
+        """torch view of one weight tensor in the engine's arena"""
+        import torch
+        td = torch.float16 if self.dtype == capi.F16 else torch.float32
+        return self._view(self.lib.b200_engine_weight_ptr(self.h, slot, layer), self.weight_shape(slot), td)
+
+    def kv_caches(self):
+        """torch views [layers, batch, kv_heads(local), max_seq, d] of K and V"""
+        import torch
+        td = torch.float16 if self.dtype == capi.F16 else torch.float32
+        c = self.cfg
+        shape = (c.num_layers, self.batch, c.kv_head_num // c.tp_size, c.max_seq_len, c.head_size)
+        return (self._view(self.lib.b200_engine_k_cache(self.h), shape, td),
+                self._view(self.lib.b200_engine_v_cache(self.h), shape, td))
+
+    def ids_out(self):
+        import torch
+        return self._view(self.lib.b200_engine_ids_out(self.h), (self.batch,), torch.int32)
+
+    def sync(self):
+        import torch
+        torch.cuda.synchronize()
