@@ -164,8 +164,12 @@ typedef struct b200_gemv_args {
     int head_num, kv_head_num, head_size, max_seq_len, step, rotary_dim;
     float rotary_base;
     const int* step_dev; /* optional DEVICE int overriding `step` (CUDA-graph replay) */
+    const float* rope_den; /* optional DEVICE table [rotary_dim/2] of base^(2i/rotary_dim) from     */
+                           /* b200_rope_table(); NULL = computed in the kernel                   */
 } b200_gemv_args;
 int b200_gemv_fused(const b200_gemv_args* args, int dtype, void* stream);
+/* fills den[i] = base^(2i/rotary_dim), i < rotary_dim/2 (correctly rounded; see common.cuh) */
+int b200_rope_table(float* den, int rotary_dim, float rotary_base, void* stream);
 
 /* launchLinearStridedBatchGemm  src/kernels/linear.cu:127 (cublas_utils.cc:75)
  * C[b] = A[b] * op(B[b]) for b < batch_count; A [m,k] row-major; B [n,k] if trans_b else [k,n];

@@ -19,7 +19,7 @@ class GemvArgs(C.Structure):
         ("k_cache_layer", C.c_void_p), ("v_cache_layer", C.c_void_p),
         ("head_num", C.c_int), ("kv_head_num", C.c_int), ("head_size", C.c_int),
         ("max_seq_len", C.c_int), ("step", C.c_int), ("rotary_dim", C.c_int),
-        ("rotary_base", C.c_float), ("step_dev", C.c_void_p),
+        ("rotary_base", C.c_float), ("step_dev", C.c_void_p), ("rope_den", C.c_void_p),
     ]
 
 
@@ -49,6 +49,7 @@ PROTOTYPES = {
     "b200_linear_workspace_bytes": (_sz, [_i, _i, _i, _i, _i]),
     "b200_linear": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp, _sz, _vp]),
     "b200_gemv_fused": (_i, [C.POINTER(GemvArgs), _i, _vp]),
+    "b200_rope_table": (_i, [_vp, _i, _f, _vp]),
     "b200_batched_gemm": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "b200_decode_attention_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "b200_decode_attention": (_i, [_vp, _vp, _vp, _vp, _vp, _sz] + [_i] * 8 + [_vp]),

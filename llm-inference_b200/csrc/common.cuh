@@ -5,6 +5,8 @@
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <mutex>
+#include <unordered_set>
 
 #include "b200_llama.h"
 
@@ -235,10 +237,23 @@ inline bool pdl_enabled() {
     return v == 1;
 }
 
+// Every kernel of the decode path asks for the maximum shared-memory carveout: an SM keeps one
+// carveout configuration at a time, so kernels with different preferences cannot be co-resident
+// and a PDL-launched successor would have to wait for the SM to drain.
+inline void prefer_max_smem_carveout(const void* func) {
+    static std::mutex mu;
+    static std::unordered_set<const void*> done;
+    std::lock_guard<std::mutex> g(mu);
+    if (done.insert(func).second)
+        cudaFuncSetAttribute(func, cudaFuncAttributePreferredSharedMemoryCarveout,
+                             cudaSharedmemCarveoutMaxShared);
+}
+
 // launch with optional programmatic-stream-serialization attribute
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
                             cudaStream_t stream, bool pdl, Args... args) {
+    prefer_max_smem_carveout(reinterpret_cast<const void*>(kernel));
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = grid;
     cfg.blockDim = block;

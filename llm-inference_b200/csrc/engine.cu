@@ -56,6 +56,7 @@ struct b200_engine {
     char* act_arena = nullptr;
     void *hidden, *residual, *qkv, *attn, *act, *gate_up, *logits, *partial;
     int *ids_cur, *ids_next, *step_dev;
+    float* rope_den;
     void* attn_ws;
     size_t attn_ws_bytes;
     int* pinned_ids = nullptr;
@@ -215,6 +216,7 @@ extern "C" b200_engine* b200_engine_create(const b200_model_config* c, int batch
                  o_attn = take(B * e->h * e->d), o_act = take(B * e->I),
                  o_gu = take(B * 2 * e->I), o_logits = take(B * e->V), o_part = take(B * e->H);
     const size_t o_ids = off; off += align256(2 * B * sizeof(int) + sizeof(int) + 64);
+    const size_t o_den = off; off += align256((size_t)c->rotary_dim / 2 * sizeof(float) + 64);
     const size_t o_ws = off; off += align256(e->attn_ws_bytes);
     if ((err = cudaMalloc(&e->act_arena, off)) != cudaSuccess) return fail_free("cudaMalloc(act)", err);
     cudaMemset(e->act_arena, 0, off);
@@ -223,6 +225,8 @@ extern "C" b200_engine* b200_engine_create(const b200_model_config* c, int batch
     e->act = a + o_act; e->gate_up = a + o_gu; e->logits = a + o_logits; e->partial = a + o_part;
     e->ids_cur = (int*)(a + o_ids); e->ids_next = e->ids_cur + B; e->step_dev = e->ids_next + B;
     e->attn_ws = a + o_ws;
+    e->rope_den = (float*)(a + o_den);
+    b200_rope_table(e->rope_den, c->rotary_dim, c->rotary_base, nullptr);
     if ((err = cudaMallocHost(&e->pinned_ids, 2 * B * sizeof(int))) != cudaSuccess) return fail_free("cudaMallocHost", err);
     if ((err = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking)) != cudaSuccess) return fail_free("stream", err);
     const int ref_step0 = 1;  // reference `step` of the first token (tokens in cache + 1)
@@ -377,6 +381,7 @@ static int gemv(b200_engine* e, const void* x, const void* W, void* y, int N, in
         a.max_seq_len = e->cfg.max_seq_len; a.step = e->step + 1;
         a.rotary_dim = e->cfg.rotary_dim; a.rotary_base = e->cfg.rotary_base;
         a.step_dev = e->step_dev;
+        a.rope_den = e->rope_den;
     }
     // batches above the GEMV tile are walked in tiles of B200_GEMV_MAX_TOKENS
     const int B = e->batch;

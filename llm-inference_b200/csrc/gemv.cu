@@ -7,9 +7,9 @@
 //
 // Structure (HBM-bound; algorithmic bytes = N*K*sizeof(T) + small vectors):
 //  * one persistent CTA per SM owns a contiguous, byte-balanced range of row-pair "units";
-//  * a producer warp streams those rows through a ring of 16 KB stages with 1-D bulk async
+//  * a producer warp streams those rows through a ring of 32 KB stages with 1-D bulk async
 //    copies (cp.async.bulk -> SASS UBLKCP, completion on an mbarrier); each stage holds
-//    8 units x 2 rows x 1 KB K-segment;
+//    8 units x 2 rows x 2 KB K-segment;
 //  * 8 consumer warps: warp w owns unit w of the stage, dots both rows against x held in
 //    shared memory (one x packet read serves two weight packets), fp32 accumulation
 //    (fma.rn.f32.f16 -> FHFMA for half), warp-shuffle reduce at the end of the row;
@@ -23,10 +23,10 @@ namespace b200 {
 
 constexpr int kGemvWarps = 8;                       // consumer warps == units per stage
 constexpr int kGemvThreads = (kGemvWarps + 1) * 32; // + producer warp
-constexpr int kSegBytes = 1024;                     // K-segment per row per stage
-constexpr int kStageBytes = kGemvWarps * 2 * kSegBytes;  // 16 KB
-constexpr int kMaxStages = 5;
-constexpr int kJ = kSegBytes / 16 / 32;  // 16B packets per lane per row-segment (=2)
+constexpr int kSegBytes = 2048;                     // K-segment per row per stage
+constexpr int kStageBytes = kGemvWarps * 2 * kSegBytes;  // 32 KB
+constexpr int kMaxStages = 4;
+constexpr int kJ = kSegBytes / 16 / 32;  // 16B packets per lane per row-segment (=4)
 
 enum { kModePlain = 0, kModeResidual = 1, kModeSwiglu = 2, kModeRopeKV = 3 };
 
@@ -49,6 +49,7 @@ struct GemvParams {
     int head_num, kv_head_num, head_size, max_seq_len, step, rotary_dim;
     float rotary_base;
     const int* step_dev;
+    const float* rope_den;
 };
 
 // unit -> (row_a, row_b); row_b < 0 means "no second row"
@@ -86,14 +87,14 @@ __global__ void __launch_bounds__(kGemvThreads, 1) gemv_stream_kernel(const Gemv
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int nseg = (p.K + KSEG - 1) / KSEG;
+    const int nstages = p.stages;
     // byte-balanced contiguous unit range of this CTA
     const int u0 = (int)(((long long)p.units * blockIdx.x) / gridDim.x);
     const int u1 = (int)(((long long)p.units * (blockIdx.x + 1)) / gridDim.x);
     const int ngroups = (u1 - u0 + kGemvWarps - 1) / kGemvWarps;
-    const int total_stages = ngroups * nseg;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < p.stages; ++s) {
+        for (int s = 0; s < nstages; ++s) {
             mbar_init(&full_bar[s], 1);
             mbar_init(&empty_bar[s], kGemvWarps);
         }
@@ -103,36 +104,40 @@ __global__ void __launch_bounds__(kGemvThreads, 1) gemv_stream_kernel(const Gemv
     pdl_launch_dependents();  // dependents only prefetch weights before their own wait
 
     if (warp == kGemvWarps) {
-        // ===================== producer: one lane issues the bulk copies =====================
-        if (lane == 0) {
-            const unsigned char* Wb = reinterpret_cast<const unsigned char*>(p.W);
-            const size_t row_bytes = (size_t)p.K * sizeof(T);
-            for (int t = 0; t < total_stages; ++t) {
-                const int slot = t % p.stages;
-                if (t >= p.stages) mbar_wait(&empty_bar[slot], ((t / p.stages) - 1) & 1);
-                const int g = t / nseg, seg = t - g * nseg;
-                const int seg_elems = min(KSEG, p.K - seg * KSEG);
-                const uint32_t seg_bytes = (uint32_t)seg_elems * sizeof(T);
-                const int ubase = u0 + g * kGemvWarps;
-                const int nu = min(kGemvWarps, u1 - ubase);
-                // count the bytes first so the expect_tx precedes every complete_tx
-                uint32_t tx = 0;
-                for (int w = 0; w < nu; ++w) {
-                    int ra, rb;
-                    unit_rows<MODE>(p, ubase + w, ra, rb);
-                    tx += seg_bytes * (rb >= 0 ? 2u : 1u);
-                }
-                mbar_expect_tx(&full_bar[slot], tx);
-                unsigned char* dst = ring + (size_t)slot * kStageBytes;
-                const size_t koff = (size_t)seg * kSegBytes;
-                for (int w = 0; w < nu; ++w) {
-                    int ra, rb;
-                    unit_rows<MODE>(p, ubase + w, ra, rb);
-                    bulk_g2s(dst + (2 * w) * kSegBytes, Wb + (size_t)ra * row_bytes + koff, seg_bytes,
+        // ============ producer warp: lane l streams row (l&1) of unit (l>>1) of each group ============
+        // 16 lanes issue their bulk copies in parallel; lane 0 also arms the barrier. The
+        // expect_tx may land after some complete_tx of the same phase: the phase cannot finish
+        // before the single arrival that expect_tx carries.
+        const unsigned char* Wb = reinterpret_cast<const unsigned char*>(p.W);
+        const size_t row_bytes = (size_t)p.K * sizeof(T);
+        const int last_seg_bytes = (p.K - (nseg - 1) * KSEG) * (int)sizeof(T);
+        int slot = 0;
+        uint32_t phase = 0;  // parity to wait for on empty_bar once the ring has wrapped
+        bool wrapped = false;
+        for (int g = 0; g < ngroups; ++g) {
+            const int ubase = u0 + g * kGemvWarps;
+            const int nu = min(kGemvWarps, u1 - ubase);
+            // this lane's source row for the whole group
+            const unsigned char* src = nullptr;
+            if (lane < 2 * nu) {
+                int ra, rb;
+                unit_rows<MODE>(p, ubase + (lane >> 1), ra, rb);
+                const int r = (lane & 1) ? rb : ra;
+                if (r >= 0) src = Wb + (size_t)r * row_bytes;
+            }
+            const uint32_t rows_here = __popc(__ballot_sync(0xffffffffu, src != nullptr));
+            unsigned char* dst_lane = ring + (size_t)lane * kSegBytes;
+            for (int seg = 0; seg < nseg; ++seg) {
+                if (wrapped) mbar_wait(&empty_bar[slot], phase);
+                const uint32_t seg_bytes = (seg == nseg - 1) ? (uint32_t)last_seg_bytes : (uint32_t)kSegBytes;
+                if (lane == 0) mbar_expect_tx(&full_bar[slot], seg_bytes * rows_here);
+                if (src)
+                    bulk_g2s(dst_lane + (size_t)slot * kStageBytes, src + (size_t)seg * kSegBytes, seg_bytes,
                              &full_bar[slot]);
-                    if (rb >= 0)
-                        bulk_g2s(dst + (2 * w + 1) * kSegBytes, Wb + (size_t)rb * row_bytes + koff,
-                                 seg_bytes, &full_bar[slot]);
+                if (++slot == nstages) {
+                    slot = 0;
+                    if (wrapped) phase ^= 1;
+                    wrapped = true;
                 }
             }
         }
@@ -206,38 +211,49 @@ __global__ void __launch_bounds__(kGemvThreads, 1) gemv_stream_kernel(const Gemv
 #pragma unroll
     for (int b = 0; b < NB; ++b) acc_a[b] = acc_b[b] = 0.f;
 
-    for (int t = 0; t < total_stages; ++t) {
-        const int slot = t % p.stages;
-        const int g = t / nseg, seg = t - g * nseg;
-        const int unit = u0 + g * kGemvWarps + warp;
-        const bool active = unit < u1;
-        int ra = 0, rb = -1;
-        if (active) unit_rows<MODE>(p, unit, ra, rb);
-
-        mbar_wait(&full_bar[slot], (t / p.stages) & 1);
+    const int last_seg_pk = (p.K - (nseg - 1) * KSEG) / E;
+    int slot = 0;
+    uint32_t full_phase = 0;
+    for (int g = 0; g < ngroups; ++g) {
+      const int unit = u0 + g * kGemvWarps + warp;
+      const bool active = unit < u1;
+      int ra = 0, rb = -1;
+      if (active) unit_rows<MODE>(p, unit, ra, rb);
+      for (int seg = 0; seg < nseg; ++seg) {
+        mbar_wait(&full_bar[slot], full_phase);
         if (active) {
-            const int seg_pk = min(KSEG, p.K - seg * KSEG) / E;
+            const int seg_pk = (seg == nseg - 1) ? last_seg_pk : KSEG / E;
             const unsigned char* sa = ring + (size_t)slot * kStageBytes + (2 * warp) * kSegBytes;
             const unsigned char* sb = sa + kSegBytes;
             const T* xseg = xs + (size_t)seg * KSEG;
+            Pack16 wa[kJ], wb[kJ];
 #pragma unroll
             for (int j = 0; j < kJ; ++j) {
                 const int pkt = lane + 32 * j;
                 if (pkt < seg_pk) {
-                    const Pack16 wa = ld16(sa + pkt * 16);
-                    Pack16 wb;
-                    if (rb >= 0) wb = ld16(sb + pkt * 16);
+                    wa[j] = ld16(sa + pkt * 16);
+                    if (rb >= 0) wb[j] = ld16(sb + pkt * 16);
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < kJ; ++j) {
+                const int pkt = lane + 32 * j;
+                if (pkt < seg_pk) {
 #pragma unroll
                     for (int b = 0; b < NB; ++b) {
                         const Pack16 xv = ld16(xseg + (size_t)b * p.K + (size_t)pkt * E);
-                        acc_a[b] = dot16<T>(wa, xv, acc_a[b]);
-                        if (rb >= 0) acc_b[b] = dot16<T>(wb, xv, acc_b[b]);
+                        acc_a[b] = dot16<T>(wa[j], xv, acc_a[b]);
+                        if (rb >= 0) acc_b[b] = dot16<T>(wb[j], xv, acc_b[b]);
                     }
                 }
             }
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(&empty_bar[slot]);
+        if (++slot == nstages) {
+            slot = 0;
+            full_phase ^= 1;
+        }
 
         if (seg == nseg - 1 && active) {
             // ---- end of the row pair: reduce + epilogue (lane 0 writes) ----
@@ -266,7 +282,8 @@ __global__ void __launch_bounds__(kGemvThreads, 1) gemv_stream_kernel(const Gemv
                     const int qkv_heads = p.head_num + 2 * p.kv_head_num;
                     float c = 1.f, s = 0.f;
                     if (head < p.head_num + p.kv_head_num && i < (p.rotary_dim >> 1)) {
-                        const float ang = rope_angle(i, p.rotary_dim, p.rotary_base, (float)(step - 1));
+                        const float ang = p.rope_den ? (float)(step - 1) / p.rope_den[i]
+                                                     : rope_angle(i, p.rotary_dim, p.rotary_base, (float)(step - 1));
                         c = cosf(ang);
                         s = sinf(ang);
                     }
@@ -316,6 +333,7 @@ __global__ void __launch_bounds__(kGemvThreads, 1) gemv_stream_kernel(const Gemv
 #pragma unroll
             for (int b = 0; b < NB; ++b) acc_a[b] = acc_b[b] = 0.f;
         }
+      }
     }
 }
 
@@ -329,8 +347,19 @@ static size_t gemv_smem_bytes(int stages, int NB, int K, int esz) {
            (size_t)(NB * kGemvWarps + NB) * sizeof(float) + 16;
 }
 
+static int gemv_max_stages() {
+    static int v = 0;
+    if (v == 0) {
+        const char* e = getenv("B200_GEMV_STAGES");
+        v = e ? atoi(e) : 3;  // 3 x 32 KB: two GEMV kernels fit one SM, so PDL prefetch can overlap
+        if (v < 2) v = 2;
+        if (v > kMaxStages) v = kMaxStages;
+    }
+    return v;
+}
+
 static int gemv_pick_stages(int NB, int K, int esz) {
-    for (int st = kMaxStages; st >= 2; --st)
+    for (int st = gemv_max_stages(); st >= 2; --st)
         if (gemv_smem_bytes(st, NB, K, esz) <= 227 * 1024) return st;
     return 0;
 }
@@ -406,7 +435,7 @@ static int gemv_fused_impl(const b200_gemv_args* a, cudaStream_t s) {
     p.k_cache = a->k_cache_layer; p.v_cache = a->v_cache_layer;
     p.head_num = a->head_num; p.kv_head_num = a->kv_head_num; p.head_size = a->head_size;
     p.max_seq_len = a->max_seq_len; p.step = a->step; p.rotary_dim = a->rotary_dim;
-    p.rotary_base = a->rotary_base; p.step_dev = a->step_dev;
+    p.rotary_base = a->rotary_base; p.step_dev = a->step_dev; p.rope_den = a->rope_den;
     if (epi == B200_GEMV_SWIGLU) {
         p.units = a->N;
         return gemv_dispatch_nb<T, kModeSwiglu>(p, a->n_tokens, s);
@@ -448,6 +477,18 @@ int gemv_plain(const void* x, const void* W, const void* bias, void* y, int n_to
 }
 
 }  // namespace b200
+
+__global__ void rope_table_kernel(float* den, int rot_dim, float base) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < rot_dim / 2) den[i] = (float)pow((double)base, (double)((float)(2 * i) / (float)rot_dim));
+}
+
+extern "C" int b200_rope_table(float* den, int rotary_dim, float rotary_base, void* stream) {
+    B200_RETURN_IF(!den || rotary_dim <= 0 || (rotary_dim & 1), B200_EINVAL);
+    rope_table_kernel<<<(rotary_dim / 2 + 63) / 64, 64, 0, (cudaStream_t)stream>>>(den, rotary_dim, rotary_base);
+    b200::count_launch();
+    return (int)cudaGetLastError();
+}
 
 extern "C" int b200_gemv_fused(const b200_gemv_args* args, int dtype, void* stream) {
     B200_RETURN_IF(!args || !args->x || !args->W || !args->y, B200_EINVAL);

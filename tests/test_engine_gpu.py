@@ -61,26 +61,40 @@ def test_small_model_teacher_forced(pkg, kind, mode):
 
 
 def test_modes_agree_and_graph_replays(pkg):
-    """fused+graph, fused and unfused produce the same logits (fp16 storage rounding is applied at
-    the same points), and graph replay over many steps keeps tracking the device-side step."""
+    """Graph replay is bit-identical to stream launches over 150 free-running greedy steps (several
+    split-KV buckets -> several graphs, device-side step keeps tracking), and the fused path agrees
+    with the unfused reference launch sequence when both are fed the same tokens."""
     E = pkg.engine
     B, max_seq = 3, 200
     outs = {}
-    for mode in ("fused_graph", "fused", "unfused"):
+    for mode in ("fused_graph", "fused"):
         eng = E.Engine(B, max_seq, dtype=pkg.F16, **SMALL)
         eng.init_random(seed=9, std=0.05)
-        eng.set_mode(fused=mode != "unfused", graph=mode == "fused_graph")
+        eng.set_mode(fused=True, graph=mode == "fused_graph")
         ids = np.array([1, 2, 3], np.int32)
         toks = []
-        for s in range(150):          # crosses several split-KV buckets -> several graphs
+        for s in range(150):
             ids = eng.decode_step_host(ids if s == 0 else None)
             toks.append(ids.copy())
         outs[mode] = (np.stack(toks), eng.logits().float().cpu().numpy().copy(), eng.launches_per_step)
         eng.close()
+    assert np.array_equal(outs["fused"][0], outs["fused_graph"][0]), "graph replay changed the tokens"
     assert rel_err(outs["fused"][1], outs["fused_graph"][1]) == 0.0, "graph replay must be bit-identical"
-    assert np.array_equal(outs["fused"][0], outs["fused_graph"][0])
-    assert rel_err(outs["fused_graph"][1], outs["unfused"][1]) <= 2e-2
-    assert outs["fused_graph"][2] < outs["unfused"][2], "fusion must cut the launches per step"
+    # fused vs unfused on the trajectory the fused engine produced (teacher forcing)
+    traj = outs["fused_graph"][0]
+    eng = E.Engine(B, max_seq, dtype=pkg.F16, **SMALL)
+    eng.init_random(seed=9, std=0.05)
+    eng.set_mode(fused=False, graph=False)
+    ids = np.array([1, 2, 3], np.int32)
+    same = 0
+    for s in range(150):
+        out = eng.decode_step_host(ids)
+        same += int(np.array_equal(out, traj[s]))
+        ids = traj[s]
+    assert_close(eng.logits().float().cpu().numpy(), outs["fused_graph"][1], "fp16", "fused vs unfused logits")
+    assert same >= 140, f"fused and unfused greedy picks agree on only {same}/150 steps"
+    assert outs["fused_graph"][2] < eng.launches_per_step, "fusion must cut the launches per step"
+    eng.close()
 
 
 def test_config0_single_7b_layer_fp32(pkg):
