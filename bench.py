@@ -353,35 +353,47 @@ def main():
         gam = torch.ones(H, device="cuda").half()
         kc, vc = eng.kv_caches()
         step_dev = torch.tensor([5], dtype=torch.int32, device="cuda")
-        reps = 2
-        tot_bytes, n_launch = 0, 0
-        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        for timed in (False, True):
-            if timed:
-                torch.cuda.synchronize()
-                s0.record()
+        # the 128 GEMVs of one pass are captured in a CUDA graph (as in the engine) so that the
+        # timing is the device's, not the Python/ctypes launch path's (~35 us per call)
+        layer_bytes = 2 * (3 * H * H + H * H + 2 * I * H + H * I)
+
+        def one_pass():
+            for l in range(32):   # 32 layers x 4 GEMVs: 12.9 GB per pass, far beyond the 126 MB L2
+                ops.gemv_fused(x_h, eng.weight_view(E.W_QKV, l), y_qkv, capi.GEMV_NORM | capi.GEMV_ROPE_KV,
+                               gamma=gam, eps=1e-5, k_cache_layer=kc[l][:nb], v_cache_layer=vc[l][:nb],
+                               head_num=32, kv_head_num=32, head_size=128, rotary_dim=128, step_dev=step_dev)
+                ops.gemv_fused(x_h, eng.weight_view(E.W_O, l), y_h, capi.GEMV_RESIDUAL)
+                ops.gemv_fused(x_h, eng.weight_view(E.W_GATE_UP, l), y_i,
+                               capi.GEMV_NORM | capi.GEMV_NORM_GFIRST | capi.GEMV_SWIGLU, gamma=gam, eps=1e-5)
+                ops.gemv_fused(x_i, eng.weight_view(E.W_DOWN, l), y_h, capi.GEMV_RESIDUAL)
+
+        side = torch.cuda.Stream()
+        with torch.cuda.stream(side):
+            one_pass()                       # warm-up (also sets the func attributes outside capture)
+            torch.cuda.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph, stream=side):
+                one_pass()
+            reps = 4
+            graph.replay()
+            s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s0.record()
             for _ in range(reps):
-                for l in range(32):   # 32 layers x 4 GEMVs: 12.9 GB per pass, far beyond the 126 MB L2
-                    ops.gemv_fused(x_h, eng.weight_view(E.W_QKV, l), y_qkv, capi.GEMV_NORM | capi.GEMV_ROPE_KV,
-                                   gamma=gam, eps=1e-5, k_cache_layer=kc[l][:nb], v_cache_layer=vc[l][:nb],
-                                   head_num=32, kv_head_num=32, head_size=128, rotary_dim=128, step_dev=step_dev)
-                    ops.gemv_fused(x_h, eng.weight_view(E.W_O, l), y_h, capi.GEMV_RESIDUAL)
-                    ops.gemv_fused(x_h, eng.weight_view(E.W_GATE_UP, l), y_i,
-                                   capi.GEMV_NORM | capi.GEMV_NORM_GFIRST | capi.GEMV_SWIGLU, gamma=gam, eps=1e-5)
-                    ops.gemv_fused(x_i, eng.weight_view(E.W_DOWN, l), y_h, capi.GEMV_RESIDUAL)
-                    if timed:
-                        tot_bytes += 2 * (3 * H * H + H * H + 2 * I * H + H * I)
-                        n_launch += 4
-            if timed:
-                s1.record()
+                graph.replay()
+            s1.record()
         torch.cuda.synchronize()
+        tot_bytes, n_launch = reps * 32 * layer_bytes, reps * 128
         g_ms = s0.elapsed_time(s1)
         achieved = tot_bytes / (g_ms * 1e-3) / 1e9
         roof = {"bound": "hbm", "kernel": "gemv_stream_kernel", "achieved": round(achieved, 1), "peak": peak,
-                "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": None,
+                "unit": "GB/s", "frac": round(achieved / peak, 4),
+                # dram__bytes_read+write per launch, mean of the four GEMVs of a layer, from the committed
+                # `ncu --set full` capture (profiles/r01_gemv_full.md): 101.2 MB read + 2.6 MB written
+                "traffic": 103.8e6, "traffic_unit": "bytes/launch (ncu, profiles/r01_gemv_full.md)",
                 "per_launch_us": round(g_ms * 1e3 / n_launch, 2), "per_launch_MB": round(tot_bytes / n_launch / 1e6, 2),
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (burst copy)" if peaks else "fallback 6650 GB/s",
-                "note": "traffic: see profiles/ (ncu dram__bytes per launch)"}
+                "algorithmic_bytes_per_launch": round(tot_bytes / n_launch),
+                "note": "128 GEMVs of one token (32 layers x qkv/o/gate_up/down) replayed as a CUDA graph, back to back"}
 
     tok_s = B_total * K / (ms_max * 1e-3)
     e2e_tok_s = B_total * K / (e2e_ms_max * 1e-3)
