@@ -2,7 +2,7 @@
  * b200_llama.h — C ABI of the B200-native (sm_100a) LLaMA decoder hot path.
  *
  * Every entry point replaces one `launch*` template of the reference
- * (Mr-wang27/llm-inference, `src/kernels/*.h`); the reference file:line each one
+ * (Mr-wang27/llm-inference, the headers under `src/kernels`); the reference file:line each one
  * stands in for is cited above it. Plain pointers and sizes only: no C++ types,
  * no torch types. The reference's TensorWrapper-based templates are re-created on
  * top of this ABI by the header shim in `llm-inference_b200/include/src/kernels/`.

@@ -42,3 +42,5 @@ public:
     LLaMAattentionWeights<T> self_attn_weight;
     LLaMAFFNWeights<T> ffn_weight;
 };
+
+#include "src/weights/llama/layer_weights_impl.h"
