@@ -43,8 +43,9 @@ def ints(vals):
     return torch.tensor(vals, dtype=torch.int32, device="cuda")
 
 
-@pytest.mark.parametrize("nt,h", [(64, 4096), (3, 4096), (1, 8192)])
+@pytest.mark.parametrize("nt,h", [(64, 4096), (3, 4096), (1, 2048)])
 def test_rmsnorm_vs_reference_kernel(ref, ops, nt, h):
+    # the reference launches H/4 threads per block (rmsnorm_kernel.cu:187): H <= 4096 only
     x, g = rnd((nt, h), 1), rnd((h,), 2, 0.5, 1.5)
     want, scratch = x.clone(), torch.zeros_like(x)
     assert ref.ref_gpu_rmsnorm_f32(P(want), P(scratch), P(g), nt, h, C.c_float(1e-5)) == 0
