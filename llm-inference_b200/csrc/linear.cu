@@ -15,7 +15,8 @@ int gemv_plain(const void* x, const void* W, const void* bias, void* y, int n_to
                int dtype, cudaStream_t s);
 // tcgen05 path (gemm_tcgen05.cu); returns B200_EUNSUPPORTED when the shape does not fit
 int gemm_tcgen05_f16(const void* x, const void* W, const void* bias, void* y, int M, int N, int K,
-                     cudaStream_t s);
+                     void* workspace, size_t workspace_bytes, cudaStream_t s);
+size_t gemm_tcgen05_workspace_bytes(int M, int N, int K);
 
 constexpr int BM = 64, BN = 64, BK = 16;
 
@@ -111,13 +112,16 @@ static int gemm_simt(const void* A, const void* B, const void* bias, void* C, in
 
 using namespace b200;
 
-extern "C" size_t b200_linear_workspace_bytes(int, int, int, int, int) { return 0; }
+// split-K partials of the tcgen05 weight-streaming mode (fp16, 8 < n_tokens <= 256); 0 otherwise.
+// Without a workspace the call still succeeds (single-split schedule, less SM coverage).
+extern "C" size_t b200_linear_workspace_bytes(int n_tokens, int N, int K, int trans_b, int dtype) {
+    if (!trans_b || dtype != B200_F16) return 0;
+    return gemm_tcgen05_workspace_bytes(n_tokens, N, K);
+}
 
 extern "C" int b200_linear(const void* x, const void* W, const void* bias, void* y, int n_tokens,
                            int N, int K, int trans_b, int dtype, void* workspace,
                            size_t workspace_bytes, void* stream) {
-    (void)workspace;
-    (void)workspace_bytes;
     B200_RETURN_IF(!x || !W || !y || n_tokens < 0 || N <= 0 || K <= 0, B200_EINVAL);
     B200_RETURN_IF(dtype != B200_F32 && dtype != B200_F16, B200_EINVAL);
     if (n_tokens == 0) return B200_OK;
@@ -129,7 +133,7 @@ extern "C" int b200_linear(const void* x, const void* W, const void* bias, void*
         if (rc != B200_EUNSUPPORTED) return rc;
     }
     if (trans_b && dtype == B200_F16) {
-        int rc = gemm_tcgen05_f16(x, W, bias, y, n_tokens, N, K, s);
+        int rc = gemm_tcgen05_f16(x, W, bias, y, n_tokens, N, K, workspace, workspace_bytes, s);
         if (rc != B200_EUNSUPPORTED) return rc;
     }
     if (dtype == B200_F16)

@@ -161,9 +161,11 @@ def launchLinearGemm(inp, weight, output, trans_a=False, trans_b=False, bias=Non
     wn = weight.shape[0] if trans_b else weight.shape[1]
     if wk != k or wn != n:
         raise RuntimeError("[b200][ERROR] 2nd dim of input MUST = 1st dim of weight Assertion fail")
-    _check(capi.lib().b200_linear(_p(inp), _p(weight), _p(bias), _p(output), m, n, k,
-                                  1 if trans_b else 0, _dt(inp), None, 0, _stream()),
-           "launchLinearGemm")
+    lib = capi.lib()
+    nbytes = lib.b200_linear_workspace_bytes(m, n, k, 1 if trans_b else 0, _dt(inp))
+    ws = _workspace(inp.device, nbytes, "linear") if nbytes else None
+    _check(lib.b200_linear(_p(inp), _p(weight), _p(bias), _p(output), m, n, k, 1 if trans_b else 0,
+                           _dt(inp), _p(ws), nbytes, _stream()), "launchLinearGemm")
 
 
 def launchLinearStridedBatchGemm(input1, input2, output, trans_a=False, trans_b=False):
@@ -181,15 +183,19 @@ def launchLinearStridedBatchGemm(input1, input2, output, trans_a=False, trans_b=
            "launchLinearStridedBatchGemm")
 
 
-_attn_ws = {}
+_ws = {}
+
+
+def _workspace(device, nbytes, what):
+    ws = _ws.get((device, what))
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=device)
+        _ws[(device, what)] = ws
+    return ws
 
 
 def _attn_workspace(device, nbytes):
-    ws = _attn_ws.get(device)
-    if ws is None or ws.numel() < nbytes:
-        ws = torch.empty(nbytes, dtype=torch.uint8, device=device)
-        _attn_ws[device] = ws
-    return ws
+    return _workspace(device, nbytes, "attn")
 
 
 def launchDecoderMaskedMHA(qkv_buf, layer_id, k_cache, v_cache, step, mha_output, append_kv=True,

@@ -1,0 +1,78 @@
+"""tcgen05 / TMEM GEMM behind launchLinearGemm for fp16 with more than 8 token rows
+(csrc/gemm_tcgen05.cu): the swapped weight-streaming mode (9..256 tokens, split-K) and the normal
+prefill mode (> 256 tokens), LLaMA-7B / 70B-TP shaped and ragged sizes, against the CPU oracle's
+linear (fp32 accumulate) on the same fp16-rounded inputs. Tolerance 2e-2 (fp16, north_star);
+observed errors are ~1e-3 (output rounding)."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import assert_close, rel_err
+from oracle import cpu
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ops(pkg):
+    assert torch.cuda.is_available()
+    return pkg.ops
+
+
+def case(ops, m, n, k, seed, bias=False):
+    rng = np.random.default_rng(seed)
+    x = rng.uniform(-1, 1, (m, k)).astype(np.float16)
+    w = (rng.standard_normal((n, k)) * 0.05).astype(np.float16)
+    b = (rng.standard_normal(n) * 0.5).astype(np.float16) if bias else None
+    want = np.zeros((m, n), np.float32)
+    cpu.linear(x.astype(np.float32), w.astype(np.float32), want, True, None if b is None else b.astype(np.float32))
+    y = torch.full((m, n), float("nan"), dtype=torch.float16, device="cuda")
+    ops.launchLinearGemm(torch.from_numpy(x).cuda(), torch.from_numpy(w).cuda(), y, trans_b=True,
+                         bias=None if b is None else torch.from_numpy(b).cuda())
+    torch.cuda.synchronize()
+    return y.float().cpu().numpy(), want
+
+
+@pytest.mark.parametrize("m,n,k", [(32, 4096, 4096), (9, 12288, 4096), (16, 4096, 11008), (32, 22016, 4096),
+                                   (64, 1024, 512), (100, 384, 1000), (128, 4096, 1024), (200, 520, 264),
+                                   (256, 2048, 2048), (33, 136, 72), (17, 8, 64)])
+def test_swapped_weight_streaming_mode(ops, m, n, k):
+    got, want = case(ops, m, n, k, m * 7 + n)
+    assert_close(got, want, "fp16", f"tcgen05 swapped {m}x{n}x{k}")
+    assert rel_err(got, want) < 4e-3
+
+
+@pytest.mark.parametrize("m,n,k", [(257, 256, 64), (512, 4096, 4096), (1000, 520, 264), (2048, 12288, 4096),
+                                   (384, 96, 128), (300, 40, 2048), (4096, 4096, 11008)])
+def test_normal_prefill_mode(ops, m, n, k):
+    got, want = case(ops, m, n, k, m + n * 3)
+    assert_close(got, want, "fp16", f"tcgen05 normal {m}x{n}x{k}")
+    assert rel_err(got, want) < 4e-3
+
+
+@pytest.mark.parametrize("m", [24, 700])
+def test_bias_epilogue(ops, m):
+    got, want = case(ops, m, 1024, 512, 5, bias=True)
+    assert_close(got, want, "fp16", "tcgen05 + bias")
+
+
+def test_linearity_at_full_size(ops):
+    # size-independent property at the cfg3 shape (8192 x 12288 x 4096): W(x1 + x2) == W x1 + W x2
+    # up to fp16 output rounding; a wrong tile / swizzle / accumulate flag breaks it grossly
+    m, n, k = 8192, 12288, 4096
+    g = torch.Generator(device="cuda").manual_seed(1)
+    x1 = (torch.rand(m, k, device="cuda", generator=g) - 0.5).half()
+    x2 = (torch.rand(m, k, device="cuda", generator=g) - 0.5).half()
+    w = (torch.randn(n, k, device="cuda", generator=g) * 0.02).half()
+    xs = (x1.float() + x2.float()).half()
+    y1, y2, ys = (torch.empty(m, n, dtype=torch.float16, device="cuda") for _ in range(3))
+    ops.launchLinearGemm(x1, w, y1, trans_b=True)
+    ops.launchLinearGemm(x2, w, y2, trans_b=True)
+    ops.launchLinearGemm(xs, w, ys, trans_b=True)
+    err = (ys.float() - (y1.float() + y2.float())).abs().max().item() / ys.float().abs().max().item()
+    assert err < 1e-2, err
+    # and a sampled exact check against fp32 math on 64 random rows
+    rows = torch.randint(0, m, (64,), device="cuda")
+    ref = x1[rows].float() @ w.float().t()
+    e2 = (y1[rows].float() - ref).abs().max().item() / ref.abs().max().item()
+    assert e2 < 4e-3, e2
