@@ -70,6 +70,10 @@ int b200_swiglu(const void* gate_up, void* out, int n_tokens, int inter, int dty
  * qkv: token-major [batch, head_num + 2*kv_head_num, head_size]. */
 int b200_rope_decode(void* qkv, int batch, int head_num, int kv_head_num, int head_size, int step,
                      int rotary_dim, float rotary_base, int dtype, void* stream);
+/* graph-replay form: `step_dev` (DEVICE int, may be NULL) overrides `step` at run time */
+int b200_rope_decode_ex(void* qkv, int batch, int head_num, int kv_head_num, int head_size, int step,
+                        const int* step_dev, int rotary_dim, float rotary_base, int dtype,
+                        void* stream);
 
 /* a8  launchAddFusedQKVBiasTransposeAndRoPE   src/kernels/qkv_bias_and_RoPE.cu:248
  * QKV [token_num, head_num+2*kv_head_num, head_size] (no padding) ->

@@ -39,6 +39,7 @@ PROTOTYPES = {
     "b200_add_residual": (_i, [_vp, _vp, _i, _i, _i, _vp]),
     "b200_swiglu": (_i, [_vp, _vp, _i, _i, _i, _vp]),
     "b200_rope_decode": (_i, [_vp, _i, _i, _i, _i, _i, _i, _f, _i, _vp]),
+    "b200_rope_decode_ex": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _i, _f, _i, _vp]),
     "b200_qkv_bias_rope_transpose": (_i, [_vp] * 8 + [_i] * 7 + [_f, _i, _vp]),
     "b200_concat_kv_cache": (_i, [_vp, _vp, _vp, _vp, _sz, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "b200_repeat_kv_cache": (_i, [_vp, _vp, _vp, _vp, _sz, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),

@@ -59,6 +59,8 @@ struct b200_engine {
     float* rope_den;
     void* attn_ws;
     size_t attn_ws_bytes;
+    void* lin_ws;          // split-K partials of the tcgen05 weight-streaming linears (batch > 8)
+    size_t lin_ws_bytes;
     int* pinned_ids = nullptr;
     // control
     cudaStream_t stream = nullptr;
@@ -218,6 +220,15 @@ extern "C" b200_engine* b200_engine_create(const b200_model_config* c, int batch
     const size_t o_ids = off; off += align256(2 * B * sizeof(int) + sizeof(int) + 64);
     const size_t o_den = off; off += align256((size_t)c->rotary_dim / 2 * sizeof(float) + 64);
     const size_t o_ws = off; off += align256(e->attn_ws_bytes);
+    e->lin_ws_bytes = 0;
+    {
+        const int shapes[5][2] = {{e->qkv_n, e->H}, {e->H, e->h * e->d}, {2 * e->I, e->H}, {e->H, e->I}, {e->V, e->H}};
+        for (auto& sh : shapes) {
+            const size_t w = b200_linear_workspace_bytes(batch, sh[0], sh[1], 1, c->dtype);
+            if (w > e->lin_ws_bytes) e->lin_ws_bytes = w;
+        }
+    }
+    const size_t o_lws = off; off += align256(e->lin_ws_bytes + 256);
     if ((err = cudaMalloc(&e->act_arena, off)) != cudaSuccess) return fail_free("cudaMalloc(act)", err);
     cudaMemset(e->act_arena, 0, off);
     char* a = e->act_arena;
@@ -225,6 +236,7 @@ extern "C" b200_engine* b200_engine_create(const b200_model_config* c, int batch
     e->act = a + o_act; e->gate_up = a + o_gu; e->logits = a + o_logits; e->partial = a + o_part;
     e->ids_cur = (int*)(a + o_ids); e->ids_next = e->ids_cur + B; e->step_dev = e->ids_next + B;
     e->attn_ws = a + o_ws;
+    e->lin_ws = a + o_lws;
     e->rope_den = (float*)(a + o_den);
     b200_rope_table(e->rope_den, c->rotary_dim, c->rotary_base, nullptr);
     if ((err = cudaMallocHost(&e->pinned_ids, 2 * B * sizeof(int))) != cudaSuccess) return fail_free("cudaMallocHost", err);
@@ -414,12 +426,19 @@ static int enqueue_step(b200_engine* e) {
     const int ref_step = e->step + 1;
     cudaStream_t s = e->stream;
     const bool tp = e->cfg.tp_size > 1;
+    // fused GEMV path: batches that fit the GEMV tile. Larger batches run the reference's launch
+    // sequence with the linears on the tcgen05 weight-streaming GEMM (weights are read once per
+    // step instead of once per 8-token tile).
+    const bool fused = (e->mode & B200_ENGINE_FUSED) && B <= B200_GEMV_MAX_TOKENS;
+    auto linear = [&](const void* x, const void* W, void* y, int N, int K) {
+        return b200_linear(x, W, nullptr, y, B, N, K, 1, dt, e->lin_ws, e->lin_ws_bytes, s);
+    };
     RC(b200_embedding(e->ids_cur, e->embed, e->hidden, B, H, e->V, dt, s));
     for (int l = 0; l < e->cfg.num_layers; ++l) {
         LayerW& w = e->layers[l];
         void* kc = e->k_cache + (size_t)l * e->layer_kv_elems * e->esz;
         void* vc = e->v_cache + (size_t)l * e->layer_kv_elems * e->esz;
-        if (e->mode & B200_ENGINE_FUSED) {
+        if (fused) {
             RC(gemv(e, e->hidden, w.qkv, e->qkv, e->qkv_n, H, B200_GEMV_NORM | B200_GEMV_ROPE_KV, w.attn_norm, l));
             RC(b200_decode_attention_ex(e->qkv, kc, vc, e->attn, e->attn_ws, e->attn_ws_bytes, B, e->h, e->hk,
                                         e->d, e->cfg.max_seq_len, ref_step, e->step_dev, 0, dt, s));
@@ -440,28 +459,29 @@ static int enqueue_step(b200_engine* e) {
         } else {
             // the reference's launch sequence, one kernel per launch* (self_decoder.cpp:53-85)
             RC(b200_rmsnorm(e->hidden, e->residual, w.attn_norm, B, H, e->cfg.rms_eps, dt, s));
-            RC(b200_linear(e->hidden, w.qkv, nullptr, e->qkv, B, e->qkv_n, H, 1, dt, nullptr, 0, s));
-            RC(b200_rope_decode(e->qkv, B, e->h, e->hk, e->d, ref_step, e->cfg.rotary_dim, e->cfg.rotary_base, dt, s));
-            RC(b200_decode_attention(e->qkv, kc, vc, e->attn, e->attn_ws, e->attn_ws_bytes, B, e->h, e->hk, e->d,
-                                     e->cfg.max_seq_len, ref_step, 1, dt, s));
-            RC(b200_linear(e->attn, w.o, nullptr, e->hidden, B, H, e->h * e->d, 1, dt, nullptr, 0, s));
+            RC(linear(e->hidden, w.qkv, e->qkv, e->qkv_n, H));
+            RC(b200_rope_decode_ex(e->qkv, B, e->h, e->hk, e->d, ref_step, e->step_dev, e->cfg.rotary_dim,
+                                   e->cfg.rotary_base, dt, s));
+            RC(b200_decode_attention_ex(e->qkv, kc, vc, e->attn, e->attn_ws, e->attn_ws_bytes, B, e->h, e->hk, e->d,
+                                        e->cfg.max_seq_len, ref_step, e->step_dev, 1, dt, s));
+            RC(linear(e->attn, w.o, e->hidden, H, e->h * e->d));
             if (tp && e->allreduce) RC(e->allreduce(e->hidden, (size_t)B * H, dt, s, e->allreduce_user));
             RC(b200_fused_add_bias_residual_rmsnorm(e->residual, e->hidden, nullptr, w.ffn_norm, B, H, e->cfg.rms_eps, dt, s));
-            RC(b200_linear(e->hidden, w.gate_up, nullptr, e->gate_up, B, 2 * e->I, H, 1, dt, nullptr, 0, s));
+            RC(linear(e->hidden, w.gate_up, e->gate_up, 2 * e->I, H));
             RC(b200_swiglu(e->gate_up, e->act, B, e->I, dt, s));
-            RC(b200_linear(e->act, w.down, nullptr, e->hidden, B, H, e->I, 1, dt, nullptr, 0, s));
+            RC(linear(e->act, w.down, e->hidden, H, e->I));
             if (tp && e->allreduce) RC(e->allreduce(e->hidden, (size_t)B * H, dt, s, e->allreduce_user));
             RC(b200_add_residual(e->residual, e->hidden, B, H, dt, s));
         }
     }
-    if (e->mode & B200_ENGINE_FUSED) {
+    if (fused) {
         RC(gemv(e, e->hidden, e->lm_head, e->logits, e->V, H, B200_GEMV_NORM, e->final_norm));
     } else {
         // llama.cpp:341 normalises decoder_output in place; we do it on a copy so that
         // b200_engine_hidden() shows the decoder output in both modes
         CU(cudaMemcpyAsync(e->partial, e->hidden, (size_t)B * H * e->esz, cudaMemcpyDeviceToDevice, s));
         RC(b200_rmsnorm(e->partial, nullptr, e->final_norm, B, H, e->cfg.rms_eps, dt, s));
-        RC(b200_linear(e->partial, e->lm_head, nullptr, e->logits, B, e->V, H, 1, dt, nullptr, 0, s));
+        RC(linear(e->partial, e->lm_head, e->logits, e->V, H));
     }
     RC(b200_argmax(e->logits, e->ids_next, B, e->V, dt, s));
     CU(launch_k(advance_kernel, dim3(1), dim3(1024), 0, s, true, e->ids_cur, (const int*)e->ids_next, e->step_dev, B));
@@ -471,7 +491,7 @@ static int enqueue_step(b200_engine* e) {
 
 static int run_step(b200_engine* e) {
     if (e->step + 1 > e->cfg.max_seq_len) return fail("KV cache full (step == max_seq_len)");
-    const bool use_graph = (e->mode & B200_ENGINE_GRAPH) && (e->mode & B200_ENGINE_FUSED);
+    const bool use_graph = (e->mode & B200_ENGINE_GRAPH) != 0;
     if (!use_graph) {
         const uint64_t before = b200_launch_count();
         RC(enqueue_step(e));

@@ -20,9 +20,12 @@ __device__ __forceinline__ float2 rope_cos_sin(int pair, int rot_dim, float base
 template <typename T>
 __global__ void __launch_bounds__(256)
 rope_decode_kernel(T* __restrict__ qkv, int head_num, int kv_head_num, int head_size, int pos,
-                   int rot_dim, float base) {
+                   const int* __restrict__ step_dev, int rot_dim, float base) {
     extern __shared__ float2 cs[];  // [rot_dim/2]
     const int half_rot = rot_dim >> 1;
+    // step_dev (CUDA-graph replay) is only ever written by the LAST kernel of the previous step,
+    // which has fully completed before any kernel of this step starts, so it may be read early
+    if (step_dev) pos = *step_dev - 1;
     for (int i = threadIdx.x; i < half_rot; i += blockDim.x)
         cs[i] = rope_cos_sin(i, rot_dim, base, (float)pos);
     pdl_wait();
@@ -121,10 +124,10 @@ qkv_rope_transpose_kernel(T* __restrict__ q, T* __restrict__ k, T* __restrict__ 
 
 template <typename T>
 static int rope_decode_impl(void* qkv, int batch, int head_num, int kv_head_num, int head_size,
-                            int step, int rot_dim, float base, cudaStream_t s) {
+                            int step, const int* step_dev, int rot_dim, float base, cudaStream_t s) {
     cudaError_t e = launch_k(rope_decode_kernel<T>, dim3(batch), dim3(256),
                              (size_t)(rot_dim / 2) * sizeof(float2), s, true, (T*)qkv, head_num,
-                             kv_head_num, head_size, step - 1, rot_dim, base);
+                             kv_head_num, head_size, step - 1, step_dev, rot_dim, base);
     count_launch();
     return (int)e;
 }
@@ -152,9 +155,9 @@ static int qkv_rope_impl(void* q, void* k, void* v, const void* qkv, const void*
 
 }  // namespace b200
 
-extern "C" int b200_rope_decode(void* qkv, int batch, int head_num, int kv_head_num, int head_size,
-                                int step, int rotary_dim, float rotary_base, int dtype,
-                                void* stream) {
+extern "C" int b200_rope_decode_ex(void* qkv, int batch, int head_num, int kv_head_num,
+                                   int head_size, int step, const int* step_dev, int rotary_dim,
+                                   float rotary_base, int dtype, void* stream) {
     B200_RETURN_IF(!qkv || batch < 0 || head_num <= 0 || kv_head_num <= 0 || head_size <= 0,
                    B200_EINVAL);
     B200_RETURN_IF(step < 1 || rotary_dim <= 0 || rotary_dim > head_size || (rotary_dim & 1) ||
@@ -164,11 +167,18 @@ extern "C" int b200_rope_decode(void* qkv, int batch, int head_num, int kv_head_
     cudaStream_t s = (cudaStream_t)stream;
     if (dtype == B200_F32)
         return b200::rope_decode_impl<float>(qkv, batch, head_num, kv_head_num, head_size, step,
-                                             rotary_dim, rotary_base, s);
+                                             step_dev, rotary_dim, rotary_base, s);
     if (dtype == B200_F16)
         return b200::rope_decode_impl<__half>(qkv, batch, head_num, kv_head_num, head_size, step,
-                                              rotary_dim, rotary_base, s);
+                                              step_dev, rotary_dim, rotary_base, s);
     return B200_EINVAL;
+}
+
+extern "C" int b200_rope_decode(void* qkv, int batch, int head_num, int kv_head_num, int head_size,
+                                int step, int rotary_dim, float rotary_base, int dtype,
+                                void* stream) {
+    return b200_rope_decode_ex(qkv, batch, head_num, kv_head_num, head_size, step, nullptr,
+                               rotary_dim, rotary_base, dtype, stream);
 }
 
 extern "C" int b200_qkv_bias_rope_transpose(void* q, void* k, void* v, const void* qkv,
