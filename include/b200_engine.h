@@ -70,6 +70,8 @@ enum {
 /* mode flags for b200_engine_set_mode */
 #define B200_ENGINE_FUSED 1u   /* fused GEMV prologues/epilogues (default)                    */
 #define B200_ENGINE_GRAPH 2u   /* CUDA-graph replay of the whole step (default)               */
+#define B200_ENGINE_PERSISTENT 4u /* with FUSED: ONE persistent cooperative kernel per step     */
+                                  /* (fp16, batch <= 4, tp_size 1; default where it applies)   */
 /* without FUSED the engine issues the reference's kernel sequence one launch* at a time
  * (rmsnorm, linear, rope, masked MHA, linear, fused add+norm, linear, act, linear, add) */
 

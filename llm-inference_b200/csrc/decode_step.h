@@ -1,0 +1,69 @@
+// Program of the persistent whole-step decode kernel (decode_step.cu), built by the engine.
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <vector>
+
+namespace b200 {
+
+enum { kOpGemv = 0, kOpAttn = 1, kOpFinal = 2 };
+enum { kEpiPlain = 0, kEpiResidual = 1, kEpiSwiglu = 2, kEpiRopeKV = 3 };
+enum { kXPlain = 0, kXEmbed = 1, kXCombine = 2 };
+
+struct StepOp {
+    int type;        // kOp*
+    int epi;         // kEpi* (gemv)
+    int xsrc;        // kX*   (gemv)
+    int norm;        // 0 none, 1 (x*inv)*gamma, 2 (gamma*x)*inv   (gemv prologue)
+    int N, K, units;
+    const void* W;
+    const void* x;
+    void* y;
+    const void* gamma;
+    void* k_cache;   // layer slice [B, hk, max_seq, d] (RoPE/KV epilogue, attention)
+    void* v_cache;
+};
+
+struct StepParams {
+    const StepOp* ops;
+    int n_ops;
+    int nb;               // sequences
+    int head_num, kv_head_num, head_size, max_seq_len, rotary_dim;
+    float eps;
+    const float* rope_den;
+    int* step_dev;        // reference `step` of the token being decoded (tokens in cache + 1)
+    int* ids_cur;
+    int* ids_next;
+    const void* embed;
+    int vocab, hidden;
+    void* hidden_buf;     // [B, H] residual stream
+    void* qkv;            // [B, h+2hk, d]
+    void* attn;           // [B, h*d]  (splits == 1 only)
+    void* logits;         // [B, V]
+    float* part_ml;       // [B, h, splits, 2]
+    float* part_o;        // [B, h, splits, d]
+    int splits;
+    unsigned* sync;       // [0] arrival counter (monotonic), [1] base of the current launch, [2] error flag
+    int stages;
+    size_t xs_bytes;
+};
+
+struct StepProgram {
+    StepParams params{};
+    StepOp* ops_dev = nullptr;
+    unsigned* sync_dev = nullptr;
+    void* attn_ws = nullptr;   // split-KV partials (sized by b200_decode_attention_workspace_bytes)
+    size_t smem = 0;
+    int nb_t = 0, g = 0, grid = 0;
+};
+
+
+// nullptr when the configuration is outside what the persistent kernel covers (fp16, batch <= 4,
+// head_size 128, h/hk in {1, 2, 4, 8}, cooperative launch available)
+StepProgram* step_program_create(const std::vector<StepOp>& ops, StepParams params, int batch, int head_num,
+                                 int kv_head_num, int head_size, int k_max, void* attn_ws);
+// `step` = reference step of the token being decoded (tokens already cached + 1)
+int step_program_launch(const StepProgram* sp, int step, cudaStream_t s);
+void step_program_destroy(StepProgram* sp);
+
+}  // namespace b200

@@ -5,12 +5,14 @@
 // with its per-call Malloc/Free + cudaDeviceSynchronize replaced by one arena, one stream and
 // CUDA-graph replay (one graph per split-KV geometry; `step` lives in device memory so the same
 // graph serves every position of its bucket).
+#include <algorithm>
 #include <map>
 #include <string>
 #include <vector>
 
 #include "b200_engine.h"
 #include "common.cuh"
+#include "decode_step.h"
 #include "launch_count.h"
 
 namespace b200 {
@@ -64,11 +66,12 @@ struct b200_engine {
     int* pinned_ids = nullptr;
     // control
     cudaStream_t stream = nullptr;
-    unsigned mode = B200_ENGINE_FUSED | B200_ENGINE_GRAPH;
+    unsigned mode = B200_ENGINE_FUSED | B200_ENGINE_GRAPH | B200_ENGINE_PERSISTENT;
     b200_allreduce_fn allreduce = nullptr;
     void* allreduce_user = nullptr;
     int step = 0;  // host mirror of *step_dev: tokens already in the cache
     std::map<int, cudaGraphExec_t> graphs;  // key: split-KV count
+    b200::StepProgram* program = nullptr;   // persistent whole-step kernel (fp16, batch <= 4, tp 1)
     int launches_per_step = 0;
 };
 
@@ -147,6 +150,40 @@ __global__ void advance_kernel(int* ids_cur, const int* ids_next, int* step, int
 }
 
 }  // namespace b200
+
+// The program of the persistent whole-step kernel: the same op order as enqueue_step()'s fused
+// branch, one entry per GEMV / attention phase.
+static void build_program(b200_engine* e) {
+    const b200_model_config& c = e->cfg;
+    if (c.dtype != B200_F16 || c.tp_size != 1 || e->batch > 4) return;
+    std::vector<StepOp> ops;
+    const int H = e->H;
+    for (int l = 0; l < c.num_layers; ++l) {
+        LayerW& w = e->layers[l];
+        void* kc = e->k_cache + (size_t)l * e->layer_kv_elems * e->esz;
+        void* vc = e->v_cache + (size_t)l * e->layer_kv_elems * e->esz;
+        StepOp qkv{kOpGemv, kEpiRopeKV, l == 0 ? kXEmbed : kXPlain, 1, e->qkv_n, H, e->qkv_n / 2,
+                   w.qkv, e->hidden, e->qkv, w.attn_norm, kc, vc};
+        StepOp att{kOpAttn, 0, 0, 0, 0, 0, 0, nullptr, nullptr, nullptr, nullptr, kc, vc};
+        StepOp o{kOpGemv, kEpiResidual, kXCombine, 0, H, e->h * e->d, (H + 1) / 2,
+                 w.o, e->attn, e->hidden, nullptr, nullptr, nullptr};
+        StepOp gu{kOpGemv, kEpiSwiglu, kXPlain, 2, e->I, H, e->I, w.gate_up, e->hidden, e->act, w.ffn_norm, nullptr, nullptr};
+        StepOp dn{kOpGemv, kEpiResidual, kXPlain, 0, H, e->I, (H + 1) / 2, w.down, e->act, e->hidden, nullptr, nullptr, nullptr};
+        ops.push_back(qkv); ops.push_back(att); ops.push_back(o); ops.push_back(gu); ops.push_back(dn);
+    }
+    StepOp head{kOpGemv, kEpiPlain, c.num_layers == 0 ? kXEmbed : kXPlain, 1, e->V, H, (e->V + 1) / 2,
+                e->lm_head, e->hidden, e->logits, e->final_norm, nullptr, nullptr};
+    StepOp fin{kOpFinal, 0, 0, 0, 0, 0, 0, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    ops.push_back(head); ops.push_back(fin);
+    StepParams p{};
+    p.head_num = e->h; p.kv_head_num = e->hk; p.head_size = e->d; p.max_seq_len = c.max_seq_len;
+    p.rotary_dim = c.rotary_dim; p.eps = c.rms_eps; p.rope_den = e->rope_den;
+    p.step_dev = e->step_dev; p.ids_cur = e->ids_cur; p.ids_next = e->ids_next;
+    p.embed = e->embed; p.vocab = e->V; p.hidden = H;
+    p.hidden_buf = e->hidden; p.qkv = e->qkv; p.attn = e->attn; p.logits = e->logits;
+    const int k_max = std::max(std::max(H, e->I), e->h * e->d);
+    e->program = step_program_create(ops, p, e->batch, e->h, e->hk, e->d, k_max, e->attn_ws);
+}
 
 extern "C" const char* b200_engine_last_error(void) { return g_err.c_str(); }
 
@@ -244,12 +281,14 @@ extern "C" b200_engine* b200_engine_create(const b200_model_config* c, int batch
     const int ref_step0 = 1;  // reference `step` of the first token (tokens in cache + 1)
     cudaMemcpy(e->step_dev, &ref_step0, sizeof(int), cudaMemcpyHostToDevice);
     cudaDeviceSynchronize();
+    build_program(e);
     return e;
 }
 
 extern "C" void b200_engine_destroy(b200_engine* e) {
     if (!e) return;
     for (auto& kv : e->graphs) cudaGraphExecDestroy(kv.second);
+    b200::step_program_destroy(e->program);
     if (e->stream) cudaStreamDestroy(e->stream);
     if (e->pinned_ids) cudaFreeHost(e->pinned_ids);
     cudaFree(e->arena);
@@ -491,6 +530,12 @@ static int enqueue_step(b200_engine* e) {
 
 static int run_step(b200_engine* e) {
     if (e->step + 1 > e->cfg.max_seq_len) return fail("KV cache full (step == max_seq_len)");
+    if (e->program && (e->mode & B200_ENGINE_FUSED) && (e->mode & B200_ENGINE_PERSISTENT)) {
+        RC(step_program_launch(e->program, e->step + 1, e->stream));
+        e->launches_per_step = 1;
+        e->step += 1;
+        return 0;
+    }
     const bool use_graph = (e->mode & B200_ENGINE_GRAPH) != 0;
     if (!use_graph) {
         const uint64_t before = b200_launch_count();

@@ -7,7 +7,7 @@ from . import capi
 
 W_ATTN_NORM, W_QKV, W_O, W_FFN_NORM, W_GATE_UP, W_DOWN, W_EMBED, W_FINAL_NORM, W_LM_HEAD = range(9)
 LAYER_SLOTS = (W_ATTN_NORM, W_QKV, W_O, W_FFN_NORM, W_GATE_UP, W_DOWN)
-MODE_FUSED, MODE_GRAPH = 1, 2
+MODE_FUSED, MODE_GRAPH, MODE_PERSISTENT = 1, 2, 4
 
 
 class ModelConfig(C.Structure):
@@ -125,9 +125,11 @@ class Engine:
         return self.lib.b200_engine_stream(self.h)
 
     # ---- control
-    def set_mode(self, fused=True, graph=True):
-        self._ck(self.lib.b200_engine_set_mode(self.h, (MODE_FUSED if fused else 0) | (MODE_GRAPH if graph else 0)),
-                 "set_mode")
+    def set_mode(self, fused=True, graph=True, persistent=False):
+        """A fresh engine runs the persistent whole-step kernel where it applies (fp16, batch <= 4);
+        an explicit set_mode() selects the multi-kernel paths unless persistent=True."""
+        flags = (MODE_FUSED if fused else 0) | (MODE_GRAPH if graph else 0) | (MODE_PERSISTENT if persistent else 0)
+        self._ck(self.lib.b200_engine_set_mode(self.h, flags), "set_mode")
 
     def set_allreduce(self, pyfunc):
         """pyfunc(buf_ptr:int, count:int, dtype:int, stream_ptr:int) -> int"""

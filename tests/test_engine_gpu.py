@@ -27,13 +27,15 @@ def download_weights(E, eng, n_layers):
 
 
 @pytest.mark.parametrize("kind", ["fp32", "fp16"])
-@pytest.mark.parametrize("mode", ["fused_graph", "fused", "unfused"])
+@pytest.mark.parametrize("mode", ["persistent", "fused_graph", "fused", "unfused"])
 def test_small_model_teacher_forced(pkg, kind, mode):
+    if mode == "persistent" and kind == "fp32":
+        pytest.skip("the persistent whole-step kernel is fp16 only (fp32 runs the multi-kernel path)")
     E = pkg.engine
     B, max_seq, steps = 2, 32, 8
     eng = E.Engine(B, max_seq, dtype=pkg.F16 if kind == "fp16" else pkg.F32, **SMALL)
     eng.init_random(seed=5, std=0.05)
-    eng.set_mode(fused=mode != "unfused", graph=mode == "fused_graph")
+    eng.set_mode(fused=mode != "unfused", graph=mode in ("fused_graph", "persistent"), persistent=mode == "persistent")
     ora = omodel.OracleModel(download_weights(E, eng, SMALL["num_layers"]), SMALL, B, max_seq, kind)
     rng = np.random.default_rng(0)
     ids = rng.integers(0, SMALL["vocab_size"], B).astype(np.int32)
@@ -53,6 +55,8 @@ def test_small_model_teacher_forced(pkg, kind, mode):
                 agree += int(got_ids[b] == want_ids[b])
         ids = want_ids   # teacher forcing: both sides continue from the oracle's token
     assert eng.step == steps
+    if mode == "persistent":
+        assert eng.launches_per_step == 1, "the persistent path must be ONE launch per step"
     assert agree == total and total > 0, f"greedy ids differ: {agree}/{total}"
     kc, vc = eng.kv_caches()
     assert_close(kc[:, :, :, :steps].float().cpu().numpy(), ora.k[:, :, :, :steps], kind, "K cache")
@@ -149,4 +153,43 @@ def test_batched_decode_uses_tcgen05_linears(pkg, B, graph):
     assert pkg.capi.lib().b200_launch_count() > before
     kc, vc = eng.kv_caches()
     assert_close(kc[:, :, :, ctx:ctx + steps].float().cpu().numpy(), ora.k[:, :, :, ctx:ctx + steps], "fp16", "K rows")
+    eng.close()
+
+
+@pytest.mark.parametrize("B,ctx", [(1, 0), (1, 300), (3, 130), (4, 64), (2, 1000)])
+def test_persistent_step_kernel_vs_oracle_with_context(pkg, B, ctx):
+    """The persistent whole-step kernel (ONE cooperative launch per token) teacher-forced against
+    the CPU oracle from a pre-filled KV cache, so that several split-KV geometries (1..4+ splits,
+    merged in the o_proj prologue), the device-side step and the grid barriers are exercised."""
+    E = pkg.engine
+    max_seq, steps = ctx + 16, 6
+    eng = E.Engine(B, max_seq, dtype=pkg.F16, **SMALL)   # fresh engine: persistent path is the default
+    eng.init_random(seed=33, std=0.05)
+    if ctx:
+        eng.fill_kv_random(ctx, seed=5, amp=0.5)
+    ora = omodel.OracleModel(download_weights(E, eng, SMALL["num_layers"]), SMALL, B, max_seq, "fp16")
+    kc, vc = eng.kv_caches()
+    ora.k[:] = kc.float().cpu().numpy()
+    ora.v[:] = vc.float().cpu().numpy()
+    ora.step = ctx
+    ids = np.random.default_rng(2).integers(0, SMALL["vocab_size"], B).astype(np.int32)
+    agree = total = 0
+    for s in range(steps):
+        got_ids = eng.decode_step_host(ids)
+        want_logits, want_ids = ora.decode_step(ids)
+        got_logits = eng.logits().float().cpu().numpy()
+        assert_close(got_logits, want_logits, "fp16", f"logits step {s} (B={B}, ctx={ctx})")
+        srt = np.sort(want_logits, axis=1)
+        band = 4 * 2e-2 * np.max(np.abs(want_logits))
+        for b in range(B):
+            if srt[b, -1] - srt[b, -2] > band:
+                total += 1
+                agree += int(got_ids[b] == want_ids[b])
+        ids = want_ids
+    assert eng.launches_per_step == 1
+    assert eng.step == ctx + steps
+    assert agree == total
+    kc, vc = eng.kv_caches()
+    assert_close(kc[:, :, :, ctx:ctx + steps].float().cpu().numpy(), ora.k[:, :, :, ctx:ctx + steps], "fp16", "K rows")
+    assert_close(vc[:, :, :, ctx:ctx + steps].float().cpu().numpy(), ora.v[:, :, :, ctx:ctx + steps], "fp16", "V rows")
     eng.close()
