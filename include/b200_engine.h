@@ -122,6 +122,10 @@ void* b200_engine_v_cache(b200_engine* e);
 void* b200_engine_weight_ptr(b200_engine* e, int slot, int layer);
 /* kernel launches one decode step issues (graph nodes or stream launches) */
 int b200_engine_launches_per_step(const b200_engine* e);
+/* debug (B200_STEP_TRACE=1 at create time): per-op %globaltimer stamps of CTA 0 of the persistent
+ * kernel's most recent launch: [2*i] = op i finished, [2*i+1] = barrier after op i passed. Returns
+ * the number of entries written (0 when tracing is off or the persistent path is not in use). */
+int b200_engine_step_trace(b200_engine* e, unsigned long long* host_dst, int max_entries);
 
 #ifdef __cplusplus
 }

@@ -29,6 +29,7 @@ constexpr int kStepConsumers = kStepWarps * 32;
 constexpr int kSegB = 2048;                           // K-segment bytes per row per stage
 constexpr int kStageB = kStepWarps * 2 * kSegB;       // 32 KB: 8 row pairs
 constexpr int kStepMaxStages = 6;
+constexpr int kStepScratchBytes = 6 * 1024;            // split-KV merge weights: nb*h*(splits+1) floats
 constexpr int kJS = kSegB / 16 / 32;                  // 16-byte packets per lane per segment
 
 // ------------------------------------------------------------------------------------------
@@ -42,6 +43,14 @@ __device__ __forceinline__ Pack16 ld16_cg(const void* p) {
                  : "=r"(r.w[0]), "=r"(r.w[1]), "=r"(r.w[2]), "=r"(r.w[3])
                  : "l"(p)
                  : "memory");
+    return r;
+}
+// non-volatile variant: the compiler may hoist / batch these (barriers carry memory clobbers, so
+// they never move across a grid barrier)
+__device__ __forceinline__ Pack16 ld16_cg_nv(const void* p) {
+    const uint4 v = __ldcg(reinterpret_cast<const uint4*>(p));
+    Pack16 r;
+    r.w[0] = v.x; r.w[1] = v.y; r.w[2] = v.z; r.w[3] = v.w;
     return r;
 }
 __device__ __forceinline__ float ldf_cg(const float* p) {
@@ -71,10 +80,9 @@ __device__ __forceinline__ void consumers_sync() {
 // grid-wide barrier among the consumer threads of all CTAs (all CTAs are co-resident: cooperative
 // launch). `target` = arrivals expected so far. A 2 s timeout turns a would-be hang into a trap.
 __device__ __forceinline__ void grid_barrier(unsigned* sync, unsigned target) {
-    consumers_sync();
+    consumers_sync();   // every consumer's writes of this op are ordered before thread 0's release
     if (threadIdx.x == 0) {
-        __threadfence();
-        atomicAdd(&sync[0], 1u);
+        asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(sync) : "memory");
         const unsigned long long t0 = global_timer_ns();
         while ((int)(ld_acquire_u32(&sync[0]) - target) < 0) {
             if (global_timer_ns() - t0 > 2000000000ull) {
@@ -82,7 +90,6 @@ __device__ __forceinline__ void grid_barrier(unsigned* sync, unsigned target) {
                 __trap();
             }
         }
-        __threadfence();
     }
     consumers_sync();
 }
@@ -121,53 +128,161 @@ __device__ __forceinline__ void op_rows_rt(const StepOp& op, int head_size, int 
     else op_unit_rows<kEpiPlain>(op, head_size, u, ra, rb);
 }
 
+// bulk L2 prefetch (no smem destination, no completion tracking): size % 16 == 0
+__device__ __forceinline__ void bulk_prefetch_l2(const void* gsrc, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gsrc), "r"(bytes) : "memory");
+}
+
+// this CTA's slice of one GEMV op, as the producer / prefetcher see it
+struct OpSlice {
+    const unsigned char* W;
+    int epi, N, K, u0, u1, ngroups;
+};
+__device__ __forceinline__ bool load_slice(const StepOp* ops, int oi, OpSlice& sl) {
+    if (ops[oi].type != kOpGemv) return false;
+    sl.W = reinterpret_cast<const unsigned char*>(ops[oi].W);
+    sl.epi = ops[oi].epi; sl.N = ops[oi].N; sl.K = ops[oi].K;
+    const int units = ops[oi].units;
+    sl.u0 = (int)(((long long)units * blockIdx.x) / gridDim.x);
+    sl.u1 = (int)(((long long)units * (blockIdx.x + 1)) / gridDim.x);
+    sl.ngroups = (sl.u1 - sl.u0 + kStepWarps - 1) / kStepWarps;
+    return true;
+}
+// source row of this lane (lane l -> row (l & 1) of unit (l >> 1)) in group g; nullptr if none
+__device__ __forceinline__ const unsigned char* slice_lane_row(const OpSlice& sl, int g, int lane, int head_size) {
+    const int ubase = sl.u0 + g * kStepWarps;
+    const int nu = min(kStepWarps, sl.u1 - ubase);
+    if (lane >= 2 * nu) return nullptr;
+    const int u = ubase + (lane >> 1);
+    int ra, rb;
+    if (sl.epi == kEpiSwiglu) { ra = u; rb = sl.N + u; }
+    else if (sl.epi == kEpiRopeKV) {
+        const int hd = head_size >> 1;
+        const int head = u / hd, i = u - head * hd;
+        ra = head * head_size + i;
+        rb = ra + hd;
+    } else { ra = 2 * u; rb = (2 * u + 1 < sl.N) ? 2 * u + 1 : -1; }
+    const int r = (lane & 1) ? rb : ra;
+    return r >= 0 ? sl.W + (size_t)r * ((size_t)sl.K * 2) : nullptr;
+}
+
+// position of a producer cursor in the step's sequence of ring stages: (op, row group, K segment)
+struct Cursor {
+    OpSlice sl;
+    const unsigned char* src;   // this lane's source row in the current group (nullptr: lane idle)
+    int oi, g, seg, nseg;
+    uint32_t rows_here, last_seg_bytes;
+    bool valid;
+};
+__device__ __forceinline__ void cursor_seek(Cursor& c, const StepOp* ops, int n_ops, int lane, int head_size) {
+    // first GEMV op at or after c.oi that has rows for this CTA
+    c.valid = false;
+    while (c.oi < n_ops) {
+        if (load_slice(ops, c.oi, c.sl) && c.sl.ngroups > 0) {
+            constexpr int KSEG = kSegB / 2;
+            c.nseg = (c.sl.K + KSEG - 1) / KSEG;
+            c.last_seg_bytes = (uint32_t)(c.sl.K - (c.nseg - 1) * KSEG) * 2u;
+            c.g = 0;
+            c.seg = 0;
+            c.src = slice_lane_row(c.sl, 0, lane, head_size);
+            c.rows_here = __popc(__ballot_sync(0xffffffffu, c.src != nullptr));
+            c.valid = true;
+            return;
+        }
+        ++c.oi;
+    }
+}
+__device__ __forceinline__ void cursor_next(Cursor& c, const StepOp* ops, int n_ops, int lane, int head_size) {
+    if (++c.seg < c.nseg) return;
+    c.seg = 0;
+    if (++c.g < c.sl.ngroups) {
+        c.src = slice_lane_row(c.sl, c.g, lane, head_size);
+        c.rows_here = __popc(__ballot_sync(0xffffffffu, c.src != nullptr));
+        return;
+    }
+    ++c.oi;
+    cursor_seek(c, ops, n_ops, lane, head_size);
+}
+__device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
+    uint32_t done;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(done)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return done != 0;
+}
+
+// Producer warp. The ring cursor issues bulk copies global -> smem stage as the consumers free
+// slots. While the consumers sit at a grid barrier / in a prologue the ring fills up and HBM
+// would go idle (the ring covers ~4 us of stall chip-wide); the producer notices this state -
+// it cannot get an empty slot AND the stage it issued last has already landed - and only then
+// runs a second cursor ahead of the ring with cp.async.bulk.prefetch.L2 (UBLKPF), up to
+// `pf_max` stages, so HBM keeps streaming into L2 and the ring catches up from L2 afterwards.
+// (Prefetching ahead unconditionally was measured slower: 2.88 -> 3.3 ms per step.)
 __device__ __noinline__ void step_producer(const StepParams& p, Ring rg, int lane) {
-    bool wrapped = false;
-    for (int oi = 0; oi < p.n_ops; ++oi) {
-        const StepOp& op = p.ops[oi];
-        if (op.type != kOpGemv) continue;
-        const int KSEG = kSegB / 2;
-        const int nseg = (op.K + KSEG - 1) / KSEG;
-        const unsigned char* Wb = reinterpret_cast<const unsigned char*>(op.W);
-        const size_t row_bytes = (size_t)op.K * 2;
-        const uint32_t last_seg_bytes = (uint32_t)(op.K - (nseg - 1) * KSEG) * 2u;
-        const int u0 = (int)(((long long)op.units * blockIdx.x) / gridDim.x);
-        const int u1 = (int)(((long long)op.units * (blockIdx.x + 1)) / gridDim.x);
-        const int ngroups = (u1 - u0 + kStepWarps - 1) / kStepWarps;
-        for (int g = 0; g < ngroups; ++g) {
-            const int ubase = u0 + g * kStepWarps;
-            const int nu = min(kStepWarps, u1 - ubase);
-            const unsigned char* src = nullptr;
-            if (lane < 2 * nu) {
-                int ra, rb;
-                op_rows_rt(op, p.head_size, ubase + (lane >> 1), ra, rb);
-                const int r = (lane & 1) ? rb : ra;
-                if (r >= 0) src = Wb + (size_t)r * row_bytes;
-            }
-            const uint32_t rows_here = __popc(__ballot_sync(0xffffffffu, src != nullptr));
-            unsigned char* dst_lane = rg.base + (size_t)lane * kSegB;
-            for (int seg = 0; seg < nseg; ++seg) {
-                if (wrapped) mbar_wait(&rg.empty[rg.slot], rg.phase);
-                const uint32_t seg_bytes = (seg == nseg - 1) ? last_seg_bytes : (uint32_t)kSegB;
-                if (lane == 0) mbar_expect_tx(&rg.full[rg.slot], seg_bytes * rows_here);
-                if (src)
-                    bulk_g2s(dst_lane + (size_t)rg.slot * kStageB, src + (size_t)seg * kSegB, seg_bytes,
-                             &rg.full[rg.slot]);
-                if (++rg.slot == rg.stages) {
-                    rg.slot = 0;
-                    if (wrapped) rg.phase ^= 1;
-                    wrapped = true;
+    unsigned char* const r_base = rg.base;
+    uint64_t* const r_full = rg.full;
+    uint64_t* const r_empty = rg.empty;
+    const int r_stages = rg.stages;
+    const int n_ops = p.n_ops, head_size = p.head_size;
+    const StepOp* ops = p.ops;
+    const int pf_max = (int)(p.l2_ahead_bytes / kStageB);
+
+    int slot = 0, pass = 0;   // pass = number of times the ring has wrapped
+    unsigned long long pf_issued = 0;
+    Cursor rc{}, pc{};
+    int lead = 0;             // stages the prefetch cursor is ahead of the ring cursor
+    rc.oi = 0;
+    cursor_seek(rc, ops, n_ops, lane, head_size);
+    while (rc.valid) {
+        if (pass > 0) {
+            const uint32_t eparity = (uint32_t)(pass - 1) & 1u;
+            if (pf_max > 0) {
+                // stage issued last: slot-1 of this pass, or the last slot of the previous pass
+                const int lslot = slot ? slot - 1 : r_stages - 1;
+                const uint32_t lparity = (uint32_t)(slot ? pass : pass - 1) & 1u;
+                while (!mbar_test(&r_empty[slot], eparity)) {
+                    if (lead < pf_max && mbar_test(&r_full[lslot], lparity)) {
+                        if (lead == 0) pc = rc;
+                        if (!pc.valid) { lead = pf_max; continue; }
+                        const uint32_t bytes = (pc.seg == pc.nseg - 1) ? pc.last_seg_bytes : (uint32_t)kSegB;
+                        if (pc.src) bulk_prefetch_l2(pc.src + (size_t)pc.seg * kSegB, bytes);
+                        cursor_next(pc, ops, n_ops, lane, head_size);
+                        ++lead;
+                        ++pf_issued;
+                    } else {
+                        __nanosleep(64);   // leave the issue slots to the consumer warps
+                    }
                 }
+            } else {
+                mbar_wait(&r_empty[slot], eparity);
             }
         }
+        const uint32_t seg_bytes = (rc.seg == rc.nseg - 1) ? rc.last_seg_bytes : (uint32_t)kSegB;
+        if (lane == 0) mbar_expect_tx(&r_full[slot], seg_bytes * rc.rows_here);
+        if (rc.src)
+            bulk_g2s(r_base + (size_t)slot * kStageB + (size_t)lane * kSegB, rc.src + (size_t)rc.seg * kSegB,
+                     seg_bytes, &r_full[slot]);
+        cursor_next(rc, ops, n_ops, lane, head_size);
+        if (lead > 0) --lead;
+        if (++slot == r_stages) {
+            slot = 0;
+            ++pass;
+        }
     }
+    if (p.trace && blockIdx.x == 0 && lane == 0) p.trace[4 * n_ops] = pf_issued;
 }
 
 // ------------------------------------------------------------------------------------------
 // consumers: x staging (+ RMSNorm / embedding / split-KV combine prologues)
 // ------------------------------------------------------------------------------------------
 template <int NB>
-__device__ __noinline__ void stage_x(const StepOp& op, const StepParams& p, __half* xs, float* red) {
+__device__ __noinline__ void stage_x(const StepOp& op, const StepParams& p, __half* xs, float* red, float* scratch) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int K = op.K, pk = K / 8;
     float ss[NB];
@@ -176,22 +291,61 @@ __device__ __noinline__ void stage_x(const StepOp& op, const StepParams& p, __ha
 
     if (op.xsrc == kXCombine && p.splits > 1) {
         // x = softmax-merged split-KV partials, rounded to fp16 (the unfused path stores the
-        // attention output in T before o_proj): fused_decoder_self_attention.cu:203-221,272-287
+        // attention output in T before o_proj): fused_decoder_self_attention.cu:203-221,272-287.
+        // Pass 1: one thread per (sequence, head) turns the split maxima / sums into merge weights;
+        // pass 2: one thread per output element, loads of the S partial rows are independent.
         const int d = p.head_size, S = p.splits;
-        const int total = p.nb * p.head_num * d;   // == nb * K
-        for (int idx = tid; idx < total; idx += kStepConsumers) {
-            const int bh = idx / d, e = idx - bh * d;
-            const float* ml = p.part_ml + (size_t)bh * S * 2;
+        const int nbh = p.nb * p.head_num;
+        float* wtab = scratch;            // [nbh][S] merge weights
+        float* inv_tab = scratch + nbh * S;   // [nbh]
+        for (int bh = tid; bh < nbh; bh += kStepConsumers) {
+            const float2* ml = reinterpret_cast<const float2*>(p.part_ml) + (size_t)bh * S;   // (m, l) pairs
             float M = -INFINITY;
-            for (int s = 0; s < S; ++s) M = fmaxf(M, ldf_cg(ml + 2 * s));
-            float L = 0.f, O = 0.f;
-            for (int s = 0; s < S; ++s) {
-                const float m = ldf_cg(ml + 2 * s);
-                const float a = (m == -INFINITY) ? 0.f : expf(m - M);
-                L += ldf_cg(ml + 2 * s + 1) * a;
-                O += ldf_cg(p.part_o + ((size_t)bh * S + s) * d + e) * a;
+            for (int s0 = 0; s0 < S; s0 += 4) {   // 4 independent L2 loads in flight
+                float2 v[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) v[u] = (s0 + u < S) ? __ldcg(ml + s0 + u) : make_float2(-INFINITY, 0.f);
+#pragma unroll
+                for (int u = 0; u < 4; ++u) M = fmaxf(M, v[u].x);
             }
-            xs[idx] = __float2half_rn(O * (1.f / (L + 1e-6f)));
+            float L = 0.f;
+            for (int s0 = 0; s0 < S; s0 += 4) {
+                float2 v[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) v[u] = (s0 + u < S) ? __ldcg(ml + s0 + u) : make_float2(-INFINITY, 0.f);
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    if (s0 + u < S) {
+                        const float a = (v[u].x == -INFINITY) ? 0.f : expf(v[u].x - M);
+                        wtab[bh * S + s0 + u] = a;
+                        L += v[u].y * a;
+                    }
+                }
+            }
+            inv_tab[bh] = 1.f / (L + 1e-6f);
+        }
+        consumers_sync();
+        // one thread per 4 consecutive output elements; the S partial rows are independent loads
+        const int d4 = d / 4, total4 = nbh * d4;
+        for (int idx = tid; idx < total4; idx += kStepConsumers) {
+            const int bh = idx / d4, e4 = idx - bh * d4;
+            const float4* po = reinterpret_cast<const float4*>(p.part_o + (size_t)bh * S * d) + e4;
+            float4 O = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int s0 = 0; s0 < S; s0 += 4) {
+                float4 v[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    v[u] = (s0 + u < S) ? __ldcg(po + (size_t)(s0 + u) * d4) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const float w = (s0 + u < S) ? wtab[bh * S + s0 + u] : 0.f;
+                    O.x += v[u].x * w; O.y += v[u].y * w; O.z += v[u].z * w; O.w += v[u].w * w;
+                }
+            }
+            const float inv = inv_tab[bh];
+            __half2* dst = reinterpret_cast<__half2*>(xs + (size_t)idx * 4);
+            dst[0] = __floats2half2_rn(O.x * inv, O.y * inv);
+            dst[1] = __floats2half2_rn(O.z * inv, O.w * inv);
         }
         consumers_sync();
         return;
@@ -209,16 +363,27 @@ __device__ __noinline__ void stage_x(const StepOp& op, const StepParams& p, __ha
             // with a single split the attention op has already written the merged fp16 output
             xg = reinterpret_cast<const __half*>(op.xsrc == kXCombine ? p.attn : op.x) + (size_t)b * K;
         }
-        for (int i = tid; i < pk; i += kStepConsumers) {
-            const Pack16 v = ld16_cg(xg + (size_t)i * 8);
-            st16(xs + (size_t)b * K + (size_t)i * 8, v);
-            if (op.xsrc == kXEmbed && blockIdx.x == 0)   // the residual stream starts as the embedding
-                st16(reinterpret_cast<__half*>(p.hidden_buf) + (size_t)b * K + (size_t)i * 8, v);
-            if (op.norm) {
-                float f[8];
-                Unpack<__half>::get(v, f);
+        for (int i0 = tid; i0 < pk; i0 += 4 * kStepConsumers) {
+            Pack16 v4[4];
 #pragma unroll
-                for (int e = 0; e < 8; ++e) ss[b] = fmaf(f[e], f[e], ss[b]);
+            for (int u = 0; u < 4; ++u) {   // four independent L2 loads in flight per thread
+                const int i = i0 + u * kStepConsumers;
+                if (i < pk) v4[u] = ld16_cg_nv(xg + (size_t)i * 8);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int i = i0 + u * kStepConsumers;
+                if (i >= pk) break;
+                const Pack16 v = v4[u];
+                st16(xs + (size_t)b * K + (size_t)i * 8, v);
+                if (op.xsrc == kXEmbed && blockIdx.x == 0)   // the residual stream starts as the embedding
+                    st16(reinterpret_cast<__half*>(p.hidden_buf) + (size_t)b * K + (size_t)i * 8, v);
+                if (op.norm) {
+                    float f[8];
+                    Unpack<__half>::get(v, f);
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) ss[b] = fmaf(f[e], f[e], ss[b]);
+                }
             }
         }
     }
@@ -259,61 +424,79 @@ __device__ __noinline__ void stage_x(const StepOp& op, const StepParams& p, __ha
 // consumers: one GEMV op. Warp w owns row pair w of every ring stage; two rows share each x packet.
 // Epilogues are those of gemv.cu (same rounding points as the unfused launch sequence).
 // ------------------------------------------------------------------------------------------
-template <int NB, int EPI>
-__device__ __noinline__ void gemv_consume(const StepOp& op, const StepParams& p, Ring& rg, const __half* xs, int step) {
+template <int NB>
+__device__ __forceinline__ uint32_t gemv_consume(const StepOp& op, const StepParams& p, unsigned char* const r_base,
+                                                 uint64_t* const r_full, uint64_t* const r_empty, const int r_stages,
+                                                 uint32_t state, const __half* xs, const int step) {
     constexpr int KSEG = kSegB / 2;
+    // everything the loops need sits in registers: with ~220 KB of shared memory in use there is
+    // no L1 left, so any local-memory access (spill, indexed array) would be an L2 round trip
+    int slot = (int)(state & 0xffu);
+    uint32_t phase = state >> 8;
+    const int epi = op.epi;
+    const int nb = p.nb, N = op.N, K = op.K, units = op.units, head_size = p.head_size;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int K = op.K;
     const int nseg = (K + KSEG - 1) / KSEG;
     const int last_seg_pk = (K - (nseg - 1) * KSEG) / 8;
-    const int u0 = (int)(((long long)op.units * blockIdx.x) / gridDim.x);
-    const int u1 = (int)(((long long)op.units * (blockIdx.x + 1)) / gridDim.x);
+    const int u0 = (int)(((long long)units * blockIdx.x) / gridDim.x);
+    const int u1 = (int)(((long long)units * (blockIdx.x + 1)) / gridDim.x);
     const int ngroups = (u1 - u0 + kStepWarps - 1) / kStepWarps;
-    __half* y = reinterpret_cast<__half*>(op.y);
-
-    float acc_a[NB], acc_b[NB];
-#pragma unroll
-    for (int b = 0; b < NB; ++b) acc_a[b] = acc_b[b] = 0.f;
+    __half* const y = reinterpret_cast<__half*>(op.y);
 
     for (int g = 0; g < ngroups; ++g) {
         const int unit = u0 + g * kStepWarps + warp;
         const bool active = unit < u1;
         int ra = 0, rb = -1;
-        if (active) op_unit_rows<EPI>(op, p.head_size, unit, ra, rb);
+        if (active) {
+            if (epi == kEpiSwiglu) { ra = unit; rb = N + unit; }
+            else if (epi == kEpiRopeKV) {
+                const int hd = head_size >> 1;
+                const int head = unit / hd, i = unit - head * hd;
+                ra = head * head_size + i;
+                rb = ra + hd;
+            } else { ra = 2 * unit; rb = (2 * unit + 1 < N) ? 2 * unit + 1 : -1; }
+        }
+        // residual epilogue: fetch the old y values now, their L2 latency hides behind the row
+        float ya[NB], yb[NB];
+#pragma unroll
+        for (int b = 0; b < NB; ++b) {
+            ya[b] = yb[b] = 0.f;
+            if (epi == kEpiResidual && active && lane == 0 && b < nb) {
+                ya[b] = __half2float(__ldcg(y + (size_t)b * N + ra));
+                if (rb >= 0) yb[b] = __half2float(__ldcg(y + (size_t)b * N + rb));
+            }
+        }
+        float acc_a[NB], acc_b[NB];
+#pragma unroll
+        for (int b = 0; b < NB; ++b) acc_a[b] = acc_b[b] = 0.f;
+
         for (int seg = 0; seg < nseg; ++seg) {
-            mbar_wait(&rg.full[rg.slot], rg.phase);
-            if (active) {
+            mbar_wait(&r_full[slot], phase);
+            if (active && !(p.debug_flags & 1)) {
                 const int seg_pk = (seg == nseg - 1) ? last_seg_pk : KSEG / 8;
-                const unsigned char* sa = rg.base + (size_t)rg.slot * kStageB + (2 * warp) * kSegB;
-                const unsigned char* sb = sa + kSegB;
+                const unsigned char* sa = r_base + (size_t)slot * kStageB + (2 * warp) * kSegB;
+                const unsigned char* sb = sa + kSegB;   // row b's slot (stale data when rb < 0: result unused)
                 const __half* xseg = xs + (size_t)seg * KSEG;
-                Pack16 wa[kJS], wb[kJS];
 #pragma unroll
                 for (int j = 0; j < kJS; ++j) {
                     const int pkt = lane + 32 * j;
                     if (pkt < seg_pk) {
-                        wa[j] = ld16(sa + pkt * 16);
-                        if (rb >= 0) wb[j] = ld16(sb + pkt * 16);
-                    }
-                }
-#pragma unroll
-                for (int j = 0; j < kJS; ++j) {
-                    const int pkt = lane + 32 * j;
-                    if (pkt < seg_pk) {
+                        const Pack16 wa = ld16(sa + pkt * 16);
+                        const Pack16 wb = ld16(sb + pkt * 16);
 #pragma unroll
                         for (int b = 0; b < NB; ++b) {
                             const Pack16 xv = ld16(xseg + (size_t)b * K + (size_t)pkt * 8);
-                            acc_a[b] = dot16<__half>(wa[j], xv, acc_a[b]);
-                            if (rb >= 0) acc_b[b] = dot16<__half>(wb[j], xv, acc_b[b]);
+                            acc_a[b] = dot16<__half>(wa, xv, acc_a[b]);
+                            acc_b[b] = dot16<__half>(wb, xv, acc_b[b]);
                         }
                     }
                 }
             }
             __syncwarp();
-            if (lane == 0) mbar_arrive(&rg.empty[rg.slot]);
-            if (++rg.slot == rg.stages) {
-                rg.slot = 0;
-                rg.phase ^= 1;
+            if (lane == 0) mbar_arrive(&r_empty[slot]);
+            if (++slot == r_stages) {
+                slot = 0;
+                phase ^= 1;
             }
         }
         if (active) {
@@ -324,61 +507,63 @@ __device__ __noinline__ void gemv_consume(const StepOp& op, const StepParams& p,
             }
             if (lane == 0) {
                 auto rnd = [](float v) { return __half2float(__float2half_rn(v)); };
-                if (EPI == kEpiSwiglu) {
+                if (epi == kEpiSwiglu) {
 #pragma unroll
                     for (int b = 0; b < NB; ++b) {
-                        if (b >= p.nb) break;
-                        const float gv = rnd(acc_a[b]), uv = rnd(acc_b[b]);   // gate/up are stored in T unfused
-                        const float s = rnd(gv / (1.f + expf(-gv)));
-                        y[(size_t)b * op.N + ra] = __float2half_rn(s * uv);
+                        if (b < nb) {
+                            const float gv = rnd(acc_a[b]), uv = rnd(acc_b[b]);   // gate/up are stored in T unfused
+                            const float sg = rnd(gv / (1.f + expf(-gv)));
+                            y[(size_t)b * N + ra] = __float2half_rn(sg * uv);
+                        }
                     }
-                } else if (EPI == kEpiRopeKV) {
-                    const int d = p.head_size, hd = d >> 1;
+                } else if (epi == kEpiRopeKV) {
+                    const int d = head_size, hd = d >> 1;
                     const int head = ra / d, i = ra - head * d;
                     const int qkv_heads = p.head_num + 2 * p.kv_head_num;
-                    float c = 1.f, s = 0.f;
+                    float c = 1.f, sn = 0.f;
                     if (head < p.head_num + p.kv_head_num && i < (p.rotary_dim >> 1)) {
                         const float ang = (float)(step - 1) / p.rope_den[i];
                         c = cosf(ang);
-                        s = sinf(ang);
+                        sn = sinf(ang);
                     }
 #pragma unroll
                     for (int b = 0; b < NB; ++b) {
-                        if (b >= p.nb) break;
-                        const float av = rnd(acc_a[b]), bv = rnd(acc_b[b]);   // qkv_buf is stored in T before RoPE
-                        const __half oa = __float2half_rn(c * av - s * bv);
-                        const __half ob = __float2half_rn(c * bv + s * av);
-                        __half* yt = y + (size_t)b * qkv_heads * d;
-                        yt[ra] = oa;
-                        yt[rb] = ob;
-                        if (head >= p.head_num) {
-                            const bool is_k = head < p.head_num + p.kv_head_num;
-                            const int kvh = is_k ? head - p.head_num : head - p.head_num - p.kv_head_num;
-                            __half* cache = reinterpret_cast<__half*>(is_k ? op.k_cache : op.v_cache);
-                            __half* row = cache + (((size_t)b * p.kv_head_num + kvh) * p.max_seq_len +
-                                                   (size_t)(step - 1)) * d;
-                            row[i] = oa;
-                            row[i + hd] = ob;
+                        if (b < nb) {
+                            const float av = rnd(acc_a[b]), bv = rnd(acc_b[b]);   // qkv_buf is stored in T before RoPE
+                            const __half oa = __float2half_rn(c * av - sn * bv);
+                            const __half ob = __float2half_rn(c * bv + sn * av);
+                            __half* yt = y + (size_t)b * qkv_heads * d;
+                            yt[ra] = oa;
+                            yt[rb] = ob;
+                            if (head >= p.head_num) {
+                                const bool is_k = head < p.head_num + p.kv_head_num;
+                                const int kvh = is_k ? head - p.head_num : head - p.head_num - p.kv_head_num;
+                                __half* cache = reinterpret_cast<__half*>(is_k ? op.k_cache : op.v_cache);
+                                __half* row = cache + (((size_t)b * p.kv_head_num + kvh) * p.max_seq_len +
+                                                       (size_t)(step - 1)) * d;
+                                row[i] = oa;
+                                row[i + hd] = ob;
+                            }
                         }
                     }
                 } else {
 #pragma unroll
                     for (int b = 0; b < NB; ++b) {
-                        if (b >= p.nb) break;
-                        float av = acc_a[b], bv = acc_b[b];
-                        if (EPI == kEpiResidual) {   // linear output rounded to T, then T(out + residual)
-                            av = rnd(av) + __half2float(ldh_cg(y + (size_t)b * op.N + ra));
-                            if (rb >= 0) bv = rnd(bv) + __half2float(ldh_cg(y + (size_t)b * op.N + rb));
+                        if (b < nb) {
+                            float av = acc_a[b], bv = acc_b[b];
+                            if (epi == kEpiResidual) {   // linear output rounded to T, then T(out + residual)
+                                av = rnd(av) + ya[b];
+                                bv = rnd(bv) + yb[b];
+                            }
+                            y[(size_t)b * N + ra] = __float2half_rn(av);
+                            if (rb >= 0) y[(size_t)b * N + rb] = __float2half_rn(bv);
                         }
-                        y[(size_t)b * op.N + ra] = __float2half_rn(av);
-                        if (rb >= 0) y[(size_t)b * op.N + rb] = __float2half_rn(bv);
                     }
                 }
             }
-#pragma unroll
-            for (int b = 0; b < NB; ++b) acc_a[b] = acc_b[b] = 0.f;
         }
     }
+    return (uint32_t)slot | (phase << 8);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -527,10 +712,29 @@ __device__ __noinline__ void final_consume(const StepParams& p, float* sv, int* 
         const __half* row = reinterpret_cast<const __half*>(p.logits) + (size_t)b * p.vocab;
         float bv = -INFINITY;
         int bi = 0x7fffffff;
-        for (int j = threadIdx.x; j < p.vocab; j += kStepConsumers) {
-            const float v = __half2float(ldh_cg(row + j));
+        auto take = [&](float v, int j) {
             if (v > bv || (v == bv && j < bi)) { bv = v; bi = j; }
+        };
+        const bool vec = (p.vocab & 7) == 0;
+        const int npk = vec ? p.vocab / 8 : 0;
+        for (int i0 = threadIdx.x; i0 < npk; i0 += 4 * kStepConsumers) {
+            Pack16 v4[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int i = i0 + u * kStepConsumers;
+                if (i < npk) v4[u] = ld16_cg_nv(row + (size_t)i * 8);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int i = i0 + u * kStepConsumers;
+                if (i >= npk) break;
+                float f[8];
+                Unpack<__half>::get(v4[u], f);
+#pragma unroll
+                for (int e = 0; e < 8; ++e) take(f[e], i * 8 + e);
+            }
         }
+        for (int j = npk * 8 + threadIdx.x; j < p.vocab; j += kStepConsumers) take(__half2float(ldh_cg(row + j)), j);
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
@@ -554,17 +758,24 @@ __device__ __noinline__ void final_consume(const StepParams& p, float* sv, int* 
 // the kernel
 // ------------------------------------------------------------------------------------------
 template <int NB, int G>
-__global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const StepParams p) {
+__global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const __grid_constant__ StepParams gp) {
     extern __shared__ __align__(128) unsigned char smem[];
+    // parameters and the consumers' current op live in shared memory: with ~214 KB of smem in use
+    // the L1 is too small to hold per-thread local copies, and every mbarrier wait (a compiler
+    // memory barrier) would otherwise re-fetch them from L2
+    __shared__ StepParams p;
+    __shared__ StepOp op;
     unsigned char* ring = smem;
-    __half* xs = reinterpret_cast<__half*>(smem + (size_t)p.stages * kStageB);
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + (size_t)p.stages * kStageB + p.xs_bytes);
+    __half* xs = reinterpret_cast<__half*>(smem + (size_t)gp.stages * kStageB);
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + (size_t)gp.stages * kStageB + gp.xs_bytes);
     uint64_t* empty_bar = full_bar + kStepMaxStages;
-    float* red = reinterpret_cast<float*>(empty_bar + kStepMaxStages);   // [NB*8 + NB] floats, also argmax scratch
+    float* red = reinterpret_cast<float*>(empty_bar + kStepMaxStages);   // [NB*8 + NB + 32] floats, also argmax scratch
+    float* scratch = red + (NB * kStepWarps + NB + 32);                  // split-KV merge weights
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x == 0) {
-        for (int s = 0; s < p.stages; ++s) {
+        p = gp;
+        for (int s = 0; s < gp.stages; ++s) {
             mbar_init(&full_bar[s], 1);
             mbar_init(&empty_bar[s], kStepWarps);
         }
@@ -572,45 +783,56 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const Step
     }
     __syncthreads();
 
-    Ring rg{ring, full_bar, empty_bar, p.stages, 0, 0};
+    Ring rg{ring, full_bar, empty_bar, gp.stages, 0, 0};
     if (warp == kStepWarps) {
         step_producer(p, rg, lane);
         return;
     }
 
     // ---- consumers
-    const int step = *p.step_dev;
-    const unsigned base = p.sync[1];
+    const int step = *gp.step_dev;
+    const unsigned base = gp.sync[1];
+    const int n_ops = gp.n_ops;
     unsigned epoch = 0;
-    for (int oi = 0; oi < p.n_ops; ++oi) {
-        const StepOp& op = p.ops[oi];
-        if (op.type == kOpGemv) {
-            stage_x<NB>(op, p, xs, red);
-            switch (op.epi) {
-                case kEpiResidual: gemv_consume<NB, kEpiResidual>(op, p, rg, xs, step); break;
-                case kEpiSwiglu: gemv_consume<NB, kEpiSwiglu>(op, p, rg, xs, step); break;
-                case kEpiRopeKV: gemv_consume<NB, kEpiRopeKV>(op, p, rg, xs, step); break;
-                default: gemv_consume<NB, kEpiPlain>(op, p, rg, xs, step); break;
+    uint32_t ring_state = 0;   // slot | phase << 8
+    for (int oi = 0; oi < n_ops; ++oi) {
+        if (threadIdx.x == 0) op = gp.ops[oi];
+        consumers_sync();
+        const int type = op.type;
+        if (type == kOpGemv) {
+            stage_x<NB>(op, p, xs, red, scratch);
+            if (gp.trace && blockIdx.x == 0 && threadIdx.x == 0) {
+                gp.trace[2 * n_ops + oi] = global_timer_ns();
+                int sl = (int)(ring_state & 0xffu), landed = 0;   // ring stages already landed when the GEMV starts
+                uint32_t ph = ring_state >> 8;
+                for (int i = 0; i < gp.stages; ++i) {
+                    landed += mbar_test(&full_bar[sl], ph) ? 1 : 0;
+                    if (++sl == gp.stages) { sl = 0; ph ^= 1; }
+                }
+                gp.trace[3 * n_ops + oi] = (unsigned long long)landed;
             }
-        } else if (op.type == kOpAttn) {
+            ring_state = gemv_consume<NB>(op, p, ring, full_bar, empty_bar, gp.stages, ring_state, xs, step);
+        } else if (type == kOpAttn) {
             attn_consume<G>(op, p, reinterpret_cast<float*>(xs), step);
         } else {
             final_consume(p, red, reinterpret_cast<int*>(red + 16));
         }
-        if (oi + 1 < p.n_ops) {
+        if (gp.trace && blockIdx.x == 0 && threadIdx.x == 0) gp.trace[2 * oi] = global_timer_ns();
+        if (oi + 1 < n_ops) {
             ++epoch;
-            grid_barrier(p.sync, base + epoch * gridDim.x);
+            grid_barrier(gp.sync, base + epoch * gridDim.x);
         }
+        if (gp.trace && blockIdx.x == 0 && threadIdx.x == 0) gp.trace[2 * oi + 1] = global_timer_ns();
     }
     // last op done by this CTA: the final arrival advances the launch base and the step
     consumers_sync();
     if (threadIdx.x == 0) {
         __threadfence();
         const unsigned total = (epoch + 1) * gridDim.x;
-        const unsigned prev = atomicAdd(&p.sync[0], 1u);
+        const unsigned prev = atomicAdd(&gp.sync[0], 1u);
         if (prev + 1 == base + total) {   // every CTA has finished its final op
-            p.sync[1] = base + total;
-            *p.step_dev = step + 1;
+            gp.sync[1] = base + total;
+            *gp.step_dev = step + 1;
         }
     }
 }
@@ -620,7 +842,7 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const Step
 // ------------------------------------------------------------------------------------------
 static size_t step_smem(int stages, size_t xs_bytes, int nb_t) {
     return (size_t)stages * kStageB + xs_bytes + 2 * kStepMaxStages * sizeof(uint64_t) +
-           (size_t)(nb_t * kStepWarps + nb_t + 32) * sizeof(float) + 64;
+           (size_t)(nb_t * kStepWarps + nb_t + 32) * sizeof(float) + kStepScratchBytes + 64;
 }
 
 template <int NB, int G>
@@ -628,7 +850,7 @@ static cudaError_t step_launch_t(const StepProgram& sp, cudaStream_t s) {
     auto kern = decode_step_kernel<NB, G>;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024);   // static smem holds params + op
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
@@ -671,8 +893,17 @@ int step_program_launch(const StepProgram* sp, int step, cudaStream_t s) {
     return (int)e;
 }
 
+int step_program_trace(const StepProgram* sp, unsigned long long* host_dst, int max_entries) {
+    if (!sp || !sp->params.trace) return 0;
+    int n = 4 * sp->params.n_ops + 1;
+    if (n > max_entries) n = max_entries;
+    cudaMemcpy(host_dst, sp->params.trace, (size_t)n * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+    return n;
+}
+
 void step_program_destroy(StepProgram* sp) {
     if (!sp) return;
+    cudaFree(sp->params.trace);
     cudaFree(sp->ops_dev);
     cudaFree(sp->sync_dev);
     delete sp;
@@ -691,7 +922,7 @@ StepProgram* step_program_create(const std::vector<StepOp>& ops, StepParams para
     const size_t attn_bytes = ((size_t)kStepWarps * G * (2 + 128) * sizeof(float) + 127) & ~(size_t)127;
     if (xs_bytes < attn_bytes) xs_bytes = attn_bytes;
     int stages = kStepMaxStages;
-    while (stages >= 2 && step_smem(stages, xs_bytes, nb_t) > 227 * 1024) --stages;
+    while (stages >= 2 && step_smem(stages, xs_bytes, nb_t) > 227 * 1024 - 1024) --stages;   // 1 KB: static smem
     if (stages < 2) return nullptr;
     int dev = 0, coop = 0;
     cudaGetDevice(&dev);
@@ -717,6 +948,18 @@ StepProgram* step_program_create(const std::vector<StepOp>& ops, StepParams para
     sp->params.sync = sp->sync_dev;
     sp->params.stages = stages;
     sp->params.xs_bytes = xs_bytes;
+    {
+        const char* a = getenv("B200_STEP_L2_AHEAD_KB");
+        sp->params.l2_ahead_bytes = (long long)(a ? atoi(a) : 0) * 1024;
+    }
+    {
+        const char* d = getenv("B200_STEP_DEBUG");
+        sp->params.debug_flags = d ? atoi(d) : 0;
+    }
+    {
+        const char* t = getenv("B200_STEP_TRACE");
+        if (t && t[0] == '1') cudaMalloc(&sp->params.trace, (4 * ops.size() + 1) * sizeof(unsigned long long));
+    }
     return sp;
 }
 

@@ -46,6 +46,9 @@ struct StepParams {
     unsigned* sync;       // [0] arrival counter (monotonic), [1] base of the current launch, [2] error flag
     int stages;
     size_t xs_bytes;
+    long long l2_ahead_bytes;    // per-CTA distance of the L2 prefetch cursor in front of the smem ring (0 = off)
+    int debug_flags;             // experiments only (B200_STEP_DEBUG): 1 = consumers skip the dot products
+    unsigned long long* trace;   // optional [2*n_ops] %globaltimer stamps of CTA 0 (op done, barrier passed)
 };
 
 struct StepProgram {
@@ -65,5 +68,7 @@ StepProgram* step_program_create(const std::vector<StepOp>& ops, StepParams para
 // `step` = reference step of the token being decoded (tokens already cached + 1)
 int step_program_launch(const StepProgram* sp, int step, cudaStream_t s);
 void step_program_destroy(StepProgram* sp);
+// debug: per-op timestamps of CTA 0 from the most recent launch (enabled by B200_STEP_TRACE=1)
+int step_program_trace(const StepProgram* sp, unsigned long long* host_dst, int max_entries);
 
 }  // namespace b200

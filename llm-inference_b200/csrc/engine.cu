@@ -313,6 +313,11 @@ extern "C" void* b200_engine_v_cache(b200_engine* e) { return e->v_cache; }
 extern "C" int b200_engine_get_step(const b200_engine* e) { return e->step; }
 extern "C" void* b200_engine_weight_ptr(b200_engine* e, int slot, int layer) { return e ? slot_ptr(e, slot, layer) : nullptr; }
 extern "C" int b200_engine_launches_per_step(const b200_engine* e) { return e->launches_per_step; }
+extern "C" int b200_engine_step_trace(b200_engine* e, unsigned long long* host_dst, int max_entries) {
+    if (!e || !e->program) return 0;
+    cudaStreamSynchronize(e->stream);
+    return step_program_trace(e->program, host_dst, max_entries);
+}
 
 static void drop_graphs(b200_engine* e) {
     for (auto& kv : e->graphs) cudaGraphExecDestroy(kv.second);

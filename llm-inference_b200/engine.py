@@ -45,6 +45,7 @@ ENGINE_PROTOTYPES = {
     "b200_engine_k_cache": (_vp, [_vp]),
     "b200_engine_v_cache": (_vp, [_vp]),
     "b200_engine_launches_per_step": (_i, [_vp]),
+    "b200_engine_step_trace": (_i, [_vp, _vp, _i]),
     "b200_engine_weight_ptr": (_vp, [_vp, _i, _i]),
 }
 
@@ -125,6 +126,17 @@ class Engine:
         return self.lib.b200_engine_stream(self.h)
 
     # ---- control
+    def step_trace(self):
+        """numpy uint64 [n_ops, 4]: %globaltimer stamps (op done, barrier passed, x staged) + ring stages landed at GEMV start, or None"""
+        buf = np.zeros(4096, np.uint64)
+        n = self.lib.b200_engine_step_trace(self.h, buf.ctypes.data_as(C.c_void_p), buf.size)
+        if not n:
+            return None
+        k = n // 4
+        self.prefetch_stages = int(buf[4 * k]) if n > 4 * k else 0
+        return np.concatenate([buf[:2 * k].reshape(k, 2), buf[2 * k:3 * k].reshape(k, 1),
+                               buf[3 * k:4 * k].reshape(k, 1)], axis=1)
+
     def set_mode(self, fused=True, graph=True, persistent=False):
         """A fresh engine runs the persistent whole-step kernel where it applies (fp16, batch <= 4);
         an explicit set_mode() selects the multi-kernel paths unless persistent=True."""

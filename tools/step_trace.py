@@ -1,0 +1,45 @@
+#!/usr/bin/env python
+"""Per-op timing of the persistent whole-step kernel (B200_STEP_TRACE=1): CTA 0's %globaltimer
+stamps after each op and after each grid barrier, averaged per op kind over the 32 layers."""
+import os
+import sys
+
+import numpy as np
+
+os.environ["B200_STEP_TRACE"] = "1"
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from __graft_entry__ import load_package  # noqa: E402
+
+pkg = load_package()
+E, capi = pkg.engine, pkg.capi
+L7B = dict(num_layers=32, head_num=32, kv_head_num=32, head_size=128, inter_size=11008, vocab_size=32000)
+B = int(sys.argv[1]) if len(sys.argv) > 1 else 1
+ctx = int(sys.argv[2]) if len(sys.argv) > 2 else 512
+eng = E.Engine(B, ctx + 64, dtype=capi.F16, **L7B)
+eng.init_random(seed=1, std=0.02)
+eng.fill_kv_random(ctx, seed=2, amp=0.5)
+ids = np.zeros(B, np.int32)
+for _ in range(5):
+    ids = eng.decode_step_host(ids)
+t = eng.step_trace().astype(np.int64)
+names = ["qkv", "attn", "o", "gate_up", "down"]
+start = t[0, 0]
+print("kernel start -> first op done: n/a; total ns:", t[-1, 0] - (t[0, 0]), "ops:", len(t))
+prev = None
+acc = {}
+for i in range(len(t)):
+    kind = names[i % 5] if i < 160 else ("lm_head" if i == 160 else "final")
+    op_ns = t[i, 0] - (t[i - 1, 1] if i else t[i, 0])
+    bar_ns = t[i, 1] - t[i, 0]
+    x_ns = (t[i, 2] - t[i - 1, 1]) if (i and t[i, 2] > 0) else 0
+    a = acc.setdefault(kind, [0, 0, 0, 0, 0])
+    a[4] += t[i, 3]
+    a[0] += op_ns
+    a[1] += bar_ns
+    a[2] += 1
+    a[3] += x_ns
+for k, (o, b, n, x, ld) in acc.items():
+    print(f"{k:8s} n={n:3d} op avg {o / n / 1e3:8.2f} us (x staging {x / n / 1e3:6.2f} us, ring stages landed at start "
+          f"{ld / n:4.1f})   barrier wait avg {b / n / 1e3:8.2f} us")
+print("L2 prefetch stages issued by CTA 0:", eng.prefetch_stages)
+print("first rows:", (t[:12] - start).tolist())
