@@ -10,22 +10,9 @@
 // separately, every phase pays launch + ramp + tail and the weight prefetch of the next kernel is
 // capped by what two co-resident CTAs can hold. Here one CTA per SM stays resident (cooperative
 // launch), a producer warp streams the WHOLE step's weights through one deep smem ring with 1-D
-// bulk copies (cp.async.bulk, UBLKCP) and never waits for a phase boundary, and the 7 consumer
+// bulk copies (cp.async.bulk, UBLKCP) and never waits for a phase boundary, and the 8 consumer
 // warps walk a small program of ops separated by grid barriers; while consumers wait at a
 // barrier the ring (up to ~190 KB per SM, ~28 MB chip-wide) keeps HBM busy.
-//
-// Exchange between ops without grid barriers: every activation that crosses CTAs (hidden, qkv,
-// SwiGLU output, split-KV partials) is written as a FLAGGED word - fp16 value | 16-bit tag in one
-// 32-bit store, fp32 value | 32-bit tag in one 64-bit store - and the consumer's prologue simply
-// polls the words it needs until they carry the tag of the producing op of THIS launch
-// (tag = launch_seq * n_ops + op index + 1). Value and flag travel in one naturally atomic word,
-// so no fence and no separate arrive/poll round trip is needed: the stall between two dependent
-// ops drops from ~5-6 us (release fence + atomic + acquire poll + op fetch + x load) to about one
-// L2 round trip, short enough for the ring to cover. A buffer written by op i+1 may alias one read
-// by op i-1's prologue: a CTA can only finish the prologue of op i+1 after every CTA with work in
-// op i has produced its outputs, i.e. has long left the prologue of op i (CTAs without rows in an
-// op skip its prologue). The only grid barrier left is the one in front of the greedy pick, which
-// scans all logits.
 //
 // HBM-bound: algorithmic bytes per step = all weights once + KV cache rows [0, step) once.
 #include <vector>
@@ -36,22 +23,14 @@
 
 namespace b200 {
 
-constexpr int kStepWarps = 7;                         // consumer warps (7 + producer = 256 threads: 255 registers each)
+constexpr int kStepWarps = 8;                         // consumer warps
 constexpr int kStepThreads = (kStepWarps + 1) * 32;   // + producer warp
 constexpr int kStepConsumers = kStepWarps * 32;
-// One ring stage = one 4 KB K-segment of ONE row per consumer warp (7 bulk copies of 4 KB). The two
-// rows of a warp's pair travel in consecutive stages. Copy size matters: the per-SM bulk-copy
-// engine costs ~27 ns per copy + bytes / 124 GB/s (tools/stream_bench.cu), so 2 KB copies cap an SM
-// at 47.8 GB/s - below its share of HBM (48.4 GB/s of 7.16 TB/s) - while 4 KB copies allow 69 GB/s.
-constexpr int kSegB = 4096;                           // K-segment bytes per row per stage
-constexpr int kStageB = kStepWarps * kSegB;           // 28 KB: one row segment per consumer warp
-constexpr int kStepMaxStages = 7;
+constexpr int kSegB = 2048;                           // K-segment bytes per row per stage
+constexpr int kStageB = kStepWarps * 2 * kSegB;       // 32 KB: 8 row pairs
+constexpr int kStepMaxStages = 6;
 constexpr int kStepScratchBytes = 6 * 1024;            // split-KV merge weights: nb*h*(splits+1) floats
-constexpr int kJS = kSegB / 16 / 32;
-#ifndef B200_POLL_NS
-#define B200_POLL_NS 400
-#endif
-constexpr unsigned kPollBackoffNs = B200_POLL_NS;                  // 16-byte packets per lane per segment
+constexpr int kJS = kSegB / 16 / 32;                  // 16-byte packets per lane per segment
 
 // ------------------------------------------------------------------------------------------
 // small device helpers
@@ -98,84 +77,14 @@ __device__ __forceinline__ void consumers_sync() {
     asm volatile("bar.sync 1, %0;" ::"n"(kStepConsumers) : "memory");
 }
 
-// ---- flagged exchange words ---------------------------------------------------------------
-__device__ __forceinline__ void ll16_store(unsigned* p, __half v, uint32_t tag) {
-    const uint32_t w = (uint32_t)__half_as_ushort(v) | (tag << 16);
-    asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(w) : "memory");
-}
-__device__ __forceinline__ void ll32_store(unsigned long long* p, float v, uint32_t tag) {
-    const unsigned long long w = (unsigned long long)__float_as_uint(v) | ((unsigned long long)tag << 32);
-    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(w) : "memory");
-}
-__device__ __forceinline__ uint32_t ll_load_u32(const unsigned* p) {
-    uint32_t v;
-    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ uint4 ll_load_4x32(const unsigned* p) {   // 4 fp16 words, 16-byte aligned
-    uint4 v;
-    asm volatile("ld.relaxed.gpu.global.v4.u32 {%0,%1,%2,%3}, [%4];"
-                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
-                 : "l"(p)
-                 : "memory");
-    return v;
-}
-__device__ __forceinline__ unsigned long long ll_load_u64(const unsigned long long* p) {
-    unsigned long long v;
-    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ ulonglong2 ll_load_2x64(const unsigned long long* p) {   // 2 fp32 words
-    ulonglong2 v;
-    asm volatile("ld.relaxed.gpu.global.v2.u64 {%0,%1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ bool ll16_ok(const uint4& v, uint32_t t16) {
-    return ((v.x >> 16) == t16) & ((v.y >> 16) == t16) & ((v.z >> 16) == t16) & ((v.w >> 16) == t16);
-}
-__device__ __forceinline__ bool ll32_ok(const ulonglong2& v, uint32_t t32) {
-    return ((uint32_t)(v.x >> 32) == t32) & ((uint32_t)(v.y >> 32) == t32);
-}
-// four fp16 payloads of a flagged quad as two packed half2 words
-__device__ __forceinline__ uint2 ll16_halves(const uint4& v) {
-    return make_uint2((v.x & 0xffffu) | (v.y << 16), (v.z & 0xffffu) | (v.w << 16));
-}
-// a producer that never shows up must not hang the GPU: ~2 s of polling ends in a trap
-struct SpinGuard {
-    unsigned n = 0;
-    __device__ __forceinline__ void tick(unsigned* sync) {
-        __nanosleep(kPollBackoffNs);   // keep the pollers of 148 CTAs from swamping the L2 slices that hold x
-        if (++n > (1u << 21)) {
-            atomicExch(&sync[2], 2u);
-            __trap();
-        }
-    }
-};
-__device__ __forceinline__ uint4 ll16_wait(const unsigned* p, uint32_t t16, unsigned* sync) {
-    uint4 v = ll_load_4x32(p);
-    SpinGuard g;
-    while (!ll16_ok(v, t16)) {
-        g.tick(sync);
-        v = ll_load_4x32(p);
-    }
-    return v;
-}
-__device__ __forceinline__ ulonglong2 ll32_wait(const unsigned long long* p, uint32_t t32, unsigned* sync) {
-    ulonglong2 v = ll_load_2x64(p);
-    SpinGuard g;
-    while (!ll32_ok(v, t32)) {
-        g.tick(sync);
-        v = ll_load_2x64(p);
-    }
-    return v;
-}
-
 // grid-wide barrier among the consumer threads of all CTAs (all CTAs are co-resident: cooperative
 // launch). `target` = arrivals expected so far. A 2 s timeout turns a would-be hang into a trap.
-__device__ __forceinline__ void grid_barrier(unsigned* sync, unsigned target) {
+__device__ __forceinline__ void grid_barrier_arrive(unsigned* sync) {
     consumers_sync();   // every consumer's writes of this op are ordered before thread 0's release
+    if (threadIdx.x == 0) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(sync) : "memory");
+}
+__device__ __forceinline__ void grid_barrier_wait(unsigned* sync, unsigned target) {
     if (threadIdx.x == 0) {
-        asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(sync) : "memory");
         const unsigned long long t0 = global_timer_ns();
         while ((int)(ld_acquire_u32(&sync[0]) - target) < 0) {
             if (global_timer_ns() - t0 > 2000000000ull) {
@@ -222,27 +131,8 @@ __device__ __forceinline__ void op_rows_rt(const StepOp& op, int head_size, int 
 }
 
 // bulk L2 prefetch (no smem destination, no completion tracking): size % 16 == 0
-__device__ __forceinline__ void bulk_prefetch_l2(const void* gsrc, uint32_t bytes, uint64_t policy) {
-    asm volatile("cp.async.bulk.prefetch.L2.global.L2::cache_hint [%0], %1, %2;" ::"l"(gsrc), "r"(bytes), "l"(policy)
-                 : "memory");
-}
-__device__ __forceinline__ void bulk_g2s_hint(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar,
-                                              uint64_t policy) {
-    asm volatile(
-        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::
-            "r"(smem_u32(smem_dst)),
-        "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
-        : "memory");
-}
-__device__ __forceinline__ uint64_t l2_policy_evict_first() {
-    uint64_t pol;
-    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
-    return pol;
-}
-__device__ __forceinline__ uint64_t l2_policy_evict_last() {
-    uint64_t pol;
-    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
-    return pol;
+__device__ __forceinline__ void bulk_prefetch_l2(const void* gsrc, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gsrc), "r"(bytes) : "memory");
 }
 
 // this CTA's slice of one GEMV op, as the producer / prefetcher see it
@@ -260,13 +150,12 @@ __device__ __forceinline__ bool load_slice(const StepOp* ops, int oi, OpSlice& s
     sl.ngroups = (sl.u1 - sl.u0 + kStepWarps - 1) / kStepWarps;
     return true;
 }
-// source row of this lane (lane l < 7 -> row `which` (0: a, 1: b) of unit l) in group g; nullptr if none
-__device__ __forceinline__ const unsigned char* slice_lane_row(const OpSlice& sl, int g, int which, int lane,
-                                                               int head_size) {
+// source row of this lane (lane l -> row (l & 1) of unit (l >> 1)) in group g; nullptr if none
+__device__ __forceinline__ const unsigned char* slice_lane_row(const OpSlice& sl, int g, int lane, int head_size) {
     const int ubase = sl.u0 + g * kStepWarps;
     const int nu = min(kStepWarps, sl.u1 - ubase);
-    if (lane >= nu) return nullptr;
-    const int u = ubase + lane;
+    if (lane >= 2 * nu) return nullptr;
+    const int u = ubase + (lane >> 1);
     int ra, rb;
     if (sl.epi == kEpiSwiglu) { ra = u; rb = sl.N + u; }
     else if (sl.epi == kEpiRopeKV) {
@@ -275,25 +164,18 @@ __device__ __forceinline__ const unsigned char* slice_lane_row(const OpSlice& sl
         ra = head * head_size + i;
         rb = ra + hd;
     } else { ra = 2 * u; rb = (2 * u + 1 < sl.N) ? 2 * u + 1 : -1; }
-    const int r = which ? rb : ra;
+    const int r = (lane & 1) ? rb : ra;
     return r >= 0 ? sl.W + (size_t)r * ((size_t)sl.K * 2) : nullptr;
 }
 
-// position of a producer cursor in the step's sequence of ring stages: (op, row group, K segment, row a/b)
+// position of a producer cursor in the step's sequence of ring stages: (op, row group, K segment)
 struct Cursor {
     OpSlice sl;
-    const unsigned char* src_a;   // this lane's source rows in the current group (nullptr: lane idle)
-    const unsigned char* src_b;
-    int oi, g, seg, which, nseg;
-    uint32_t rows_a, rows_b, last_seg_bytes;
+    const unsigned char* src;   // this lane's source row in the current group (nullptr: lane idle)
+    int oi, g, seg, nseg;
+    uint32_t rows_here, last_seg_bytes;
     bool valid;
 };
-__device__ __forceinline__ void cursor_group(Cursor& c, int lane, int head_size) {
-    c.src_a = slice_lane_row(c.sl, c.g, 0, lane, head_size);
-    c.src_b = slice_lane_row(c.sl, c.g, 1, lane, head_size);
-    c.rows_a = __popc(__ballot_sync(0xffffffffu, c.src_a != nullptr));
-    c.rows_b = __popc(__ballot_sync(0xffffffffu, c.src_b != nullptr));
-}
 __device__ __forceinline__ void cursor_seek(Cursor& c, const StepOp* ops, int n_ops, int lane, int head_size) {
     // first GEMV op at or after c.oi that has rows for this CTA
     c.valid = false;
@@ -304,8 +186,8 @@ __device__ __forceinline__ void cursor_seek(Cursor& c, const StepOp* ops, int n_
             c.last_seg_bytes = (uint32_t)(c.sl.K - (c.nseg - 1) * KSEG) * 2u;
             c.g = 0;
             c.seg = 0;
-            c.which = 0;
-            cursor_group(c, lane, head_size);
+            c.src = slice_lane_row(c.sl, 0, lane, head_size);
+            c.rows_here = __popc(__ballot_sync(0xffffffffu, c.src != nullptr));
             c.valid = true;
             return;
         }
@@ -313,12 +195,11 @@ __device__ __forceinline__ void cursor_seek(Cursor& c, const StepOp* ops, int n_
     }
 }
 __device__ __forceinline__ void cursor_next(Cursor& c, const StepOp* ops, int n_ops, int lane, int head_size) {
-    if (c.which == 0) { c.which = 1; return; }
-    c.which = 0;
     if (++c.seg < c.nseg) return;
     c.seg = 0;
     if (++c.g < c.sl.ngroups) {
-        cursor_group(c, lane, head_size);
+        c.src = slice_lane_row(c.sl, c.g, lane, head_size);
+        c.rows_here = __popc(__ballot_sync(0xffffffffu, c.src != nullptr));
         return;
     }
     ++c.oi;
@@ -353,10 +234,6 @@ __device__ __noinline__ void step_producer(const StepParams& p, Ring rg, int lan
     const int n_ops = p.n_ops, head_size = p.head_size;
     const StepOp* ops = p.ops;
     const int pf_max = (int)(p.l2_ahead_bytes / kStageB);
-    // weights are read once per step: the demand copies mark their lines evict-first so that the
-    // lines the prefetch cursor parked in L2 (evict-last) survive until the ring picks them up
-    const uint64_t pol_stream = l2_policy_evict_first(), pol_keep = l2_policy_evict_last();
-    const bool hints = (p.debug_flags & 2) != 0;
 
     int slot = 0, pass = 0;   // pass = number of times the ring has wrapped
     unsigned long long pf_issued = 0;
@@ -375,9 +252,8 @@ __device__ __noinline__ void step_producer(const StepParams& p, Ring rg, int lan
                     if (lead < pf_max && mbar_test(&r_full[lslot], lparity)) {
                         if (lead == 0) pc = rc;
                         if (!pc.valid) { lead = pf_max; continue; }
-                        // one prefetch per row (at its first segment): few, large engine operations
-                        const unsigned char* psrc = pc.which ? pc.src_b : pc.src_a;
-                        if (psrc && pc.seg == 0) bulk_prefetch_l2(psrc, (uint32_t)pc.sl.K * 2u, pol_keep);
+                        const uint32_t bytes = (pc.seg == pc.nseg - 1) ? pc.last_seg_bytes : (uint32_t)kSegB;
+                        if (pc.src) bulk_prefetch_l2(pc.src + (size_t)pc.seg * kSegB, bytes);
                         cursor_next(pc, ops, n_ops, lane, head_size);
                         ++lead;
                         ++pf_issued;
@@ -390,16 +266,10 @@ __device__ __noinline__ void step_producer(const StepParams& p, Ring rg, int lan
             }
         }
         const uint32_t seg_bytes = (rc.seg == rc.nseg - 1) ? rc.last_seg_bytes : (uint32_t)kSegB;
-        const unsigned char* rsrc = rc.which ? rc.src_b : rc.src_a;
-        if (lane == 0) mbar_expect_tx(&r_full[slot], seg_bytes * (rc.which ? rc.rows_b : rc.rows_a));
-        if (rsrc) {
-            if (hints)
-                bulk_g2s_hint(r_base + (size_t)slot * kStageB + (size_t)lane * kSegB, rsrc + (size_t)rc.seg * kSegB,
-                              seg_bytes, &r_full[slot], pol_stream);
-            else
-                bulk_g2s(r_base + (size_t)slot * kStageB + (size_t)lane * kSegB, rsrc + (size_t)rc.seg * kSegB,
-                         seg_bytes, &r_full[slot]);
-        }
+        if (lane == 0) mbar_expect_tx(&r_full[slot], seg_bytes * rc.rows_here);
+        if (rc.src)
+            bulk_g2s(r_base + (size_t)slot * kStageB + (size_t)lane * kSegB, rc.src + (size_t)rc.seg * kSegB,
+                     seg_bytes, &r_full[slot]);
         cursor_next(rc, ops, n_ops, lane, head_size);
         if (lead > 0) --lead;
         if (++slot == r_stages) {
@@ -414,17 +284,77 @@ __device__ __noinline__ void step_producer(const StepParams& p, Ring rg, int lan
 // consumers: x staging (+ RMSNorm / embedding / split-KV combine prologues)
 // ------------------------------------------------------------------------------------------
 template <int NB>
-__device__ __noinline__ void stage_x(const StepOp& op, const StepParams& p, __half* xs, float* red, float* scratch,
-                                     uint32_t tag_base) {
+__device__ __noinline__ void stage_x(const StepOp& op, const StepParams& p, __half* xs, float* red, float* scratch) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int K = op.K, pk = K / 8;
-    const uint32_t xtag = tag_base + (uint32_t)op.xop + 1u;   // tag of the op that produced x
     float ss[NB];
 #pragma unroll
     for (int b = 0; b < NB; ++b) ss[b] = 0.f;
 
+    if (op.xsrc == kXCombine && p.splits > 1) {
+        // x = softmax-merged split-KV partials, rounded to fp16 (the unfused path stores the
+        // attention output in T before o_proj): fused_decoder_self_attention.cu:203-221,272-287.
+        // Pass 1: one thread per (sequence, head) turns the split maxima / sums into merge weights;
+        // pass 2: one thread per output element, loads of the S partial rows are independent.
+        const int d = p.head_size, S = p.splits;
+        const int nbh = p.nb * p.head_num;
+        float* wtab = scratch;            // [nbh][S] merge weights
+        float* inv_tab = scratch + nbh * S;   // [nbh]
+        for (int bh = tid; bh < nbh; bh += kStepConsumers) {
+            const float2* ml = reinterpret_cast<const float2*>(p.part_ml) + (size_t)bh * S;   // (m, l) pairs
+            float M = -INFINITY;
+            for (int s0 = 0; s0 < S; s0 += 4) {   // 4 independent L2 loads in flight
+                float2 v[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) v[u] = (s0 + u < S) ? __ldcg(ml + s0 + u) : make_float2(-INFINITY, 0.f);
+#pragma unroll
+                for (int u = 0; u < 4; ++u) M = fmaxf(M, v[u].x);
+            }
+            float L = 0.f;
+            for (int s0 = 0; s0 < S; s0 += 4) {
+                float2 v[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) v[u] = (s0 + u < S) ? __ldcg(ml + s0 + u) : make_float2(-INFINITY, 0.f);
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    if (s0 + u < S) {
+                        const float a = (v[u].x == -INFINITY) ? 0.f : expf(v[u].x - M);
+                        wtab[bh * S + s0 + u] = a;
+                        L += v[u].y * a;
+                    }
+                }
+            }
+            inv_tab[bh] = 1.f / (L + 1e-6f);
+        }
+        consumers_sync();
+        // one thread per 4 consecutive output elements; the S partial rows are independent loads
+        const int d4 = d / 4, total4 = nbh * d4;
+        for (int idx = tid; idx < total4; idx += kStepConsumers) {
+            const int bh = idx / d4, e4 = idx - bh * d4;
+            const float4* po = reinterpret_cast<const float4*>(p.part_o + (size_t)bh * S * d) + e4;
+            float4 O = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int s0 = 0; s0 < S; s0 += 4) {
+                float4 v[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    v[u] = (s0 + u < S) ? __ldcg(po + (size_t)(s0 + u) * d4) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const float w = (s0 + u < S) ? wtab[bh * S + s0 + u] : 0.f;
+                    O.x += v[u].x * w; O.y += v[u].y * w; O.z += v[u].z * w; O.w += v[u].w * w;
+                }
+            }
+            const float inv = inv_tab[bh];
+            __half2* dst = reinterpret_cast<__half2*>(xs + (size_t)idx * 4);
+            dst[0] = __floats2half2_rn(O.x * inv, O.y * inv);
+            dst[1] = __floats2half2_rn(O.z * inv, O.w * inv);
+        }
+        consumers_sync();
+        return;
+    }
+
     // gamma packets of this thread, fetched while x is still in flight
-    constexpr int GP = 4;
+    constexpr int GP = 2;
     Pack16 gpk[GP];
     const __half* gm = reinterpret_cast<const __half*>(op.gamma);
     if (op.norm) {
@@ -438,64 +368,35 @@ __device__ __noinline__ void stage_x(const StepOp& op, const StepParams& p, __ha
 #pragma unroll
     for (int b = 0; b < NB; ++b) {
         if (b >= p.nb) break;
+        const __half* xg;
         if (op.xsrc == kXEmbed) {
             int id = p.ids_cur[b];
             id = id < 0 ? 0 : (id >= p.vocab ? p.vocab - 1 : id);
-            const __half* xg = reinterpret_cast<const __half*>(p.embed) + (size_t)id * K;
-            for (int i0 = tid; i0 < pk; i0 += 4 * kStepConsumers) {
-                Pack16 v4[4];
-#pragma unroll
-                for (int u = 0; u < 4; ++u) {   // four independent loads in flight per thread
-                    const int i = i0 + u * kStepConsumers;
-                    if (i < pk) v4[u] = ld16(xg + (size_t)i * 8);
-                }
-#pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    const int i = i0 + u * kStepConsumers;
-                    if (i >= pk) break;
-                    st16(xs + (size_t)b * K + (size_t)i * 8, v4[u]);
-                    if (op.norm) {
-                        float f[8];
-                        Unpack<__half>::get(v4[u], f);
-#pragma unroll
-                        for (int e = 0; e < 8; ++e) ss[b] = fmaf(f[e], f[e], ss[b]);
-                    }
-                }
-            }
+            xg = reinterpret_cast<const __half*>(p.embed) + (size_t)id * K;
         } else {
-            // flagged words of the producing op: all of this thread's quads in flight, then re-poll
-            // only the ones that have not arrived yet
-            constexpr int UN = 16;
-            const unsigned* xg = (op.xbuf == kBufAct ? p.ll_act : op.xbuf == kBufAttn ? p.ll_attn : p.ll_hidden) + (size_t)b * K;
-            const uint32_t t16 = xtag & 0xffffu;
-            const int nq = K / 4;
-            for (int q0 = tid; q0 < nq; q0 += UN * kStepConsumers) {
-                uint4 v[UN];
+            // with a single split the attention op has already written the merged fp16 output
+            xg = reinterpret_cast<const __half*>(op.xsrc == kXCombine ? p.attn : op.x) + (size_t)b * K;
+        }
+        for (int i0 = tid; i0 < pk; i0 += 4 * kStepConsumers) {
+            Pack16 v4[4];
 #pragma unroll
-                for (int u = 0; u < UN; ++u) {
-                    const int q = q0 + u * kStepConsumers;
-                    if (q < nq) v[u] = ll_load_4x32(xg + (size_t)q * 4);
-                }
+            for (int u = 0; u < 4; ++u) {   // four independent L2 loads in flight per thread
+                const int i = i0 + u * kStepConsumers;
+                if (i < pk) v4[u] = ld16_cg_nv(xg + (size_t)i * 8);
+            }
 #pragma unroll
-                for (int u = 0; u < UN; ++u) {
-                    const int q = q0 + u * kStepConsumers;
-                    if (q < nq) {
-                        SpinGuard g;
-                        while (!ll16_ok(v[u], t16)) {
-                            g.tick(p.sync);
-                            v[u] = ll_load_4x32(xg + (size_t)q * 4);
-                        }
-                        const uint2 h = ll16_halves(v[u]);
-                        *reinterpret_cast<uint2*>(xs + (size_t)b * K + (size_t)q * 4) = h;
-                        if (op.norm) {
-                            const float2 f0 = __half22float2(*reinterpret_cast<const __half2*>(&h.x));
-                            const float2 f1 = __half22float2(*reinterpret_cast<const __half2*>(&h.y));
-                            ss[b] = fmaf(f0.x, f0.x, ss[b]);
-                            ss[b] = fmaf(f0.y, f0.y, ss[b]);
-                            ss[b] = fmaf(f1.x, f1.x, ss[b]);
-                            ss[b] = fmaf(f1.y, f1.y, ss[b]);
-                        }
-                    }
+            for (int u = 0; u < 4; ++u) {
+                const int i = i0 + u * kStepConsumers;
+                if (i >= pk) break;
+                const Pack16 v = v4[u];
+                st16(xs + (size_t)b * K + (size_t)i * 8, v);
+                if (op.xsrc == kXEmbed && blockIdx.x == 0)   // the residual stream starts as the embedding
+                    st16(reinterpret_cast<__half*>(p.hidden_buf) + (size_t)b * K + (size_t)i * 8, v);
+                if (op.norm) {
+                    float f[8];
+                    Unpack<__half>::get(v, f);
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) ss[b] = fmaf(f[e], f[e], ss[b]);
                 }
             }
         }
@@ -506,35 +407,25 @@ __device__ __noinline__ void stage_x(const StepOp& op, const StepParams& p, __ha
             const float s = warp_sum(ss[b]);
             if (lane == 0) red[b * kStepWarps + warp] = s;
         }
-        consumers_sync();   // also: every x element is in xs
-        float inv[NB];
-#pragma unroll
-        for (int b = 0; b < NB; ++b) {
+        consumers_sync();
+        if (tid < NB) {
             float s = 0.f;
-#pragma unroll
-            for (int w = 0; w < kStepWarps; ++w) s += red[b * kStepWarps + w];
-            inv[b] = rsqrtf(s / (float)K + p.eps);
+            for (int w = 0; w < kStepWarps; ++w) s += red[tid * kStepWarps + w];
+            red[NB * kStepWarps + tid] = rsqrtf(s / (float)K + p.eps);
         }
+        consumers_sync();
         const bool gfirst = op.norm == 2;
         for (int i = tid, j = 0; i < pk; i += kStepConsumers, ++j) {
             float g[8];
-            Pack16 gp;
-            if (j < GP) {
-                gp = gpk[0];
-#pragma unroll
-                for (int jj = 1; jj < GP; ++jj)
-                    if (j == jj) gp = gpk[jj];
-            } else {
-                gp = ld16(gm + (size_t)i * 8);
-            }
-            Unpack<__half>::get(gp, g);
+            Unpack<__half>::get(j == 0 ? gpk[0] : (j == 1 ? gpk[1] : ld16(gm + (size_t)i * 8)), g);
 #pragma unroll
             for (int b = 0; b < NB; ++b) {
                 if (b >= p.nb) break;
+                const float inv = red[NB * kStepWarps + b];
                 float f[8];
                 Unpack<__half>::get(ld16(xs + (size_t)b * K + (size_t)i * 8), f);
 #pragma unroll
-                for (int e = 0; e < 8; ++e) f[e] = gfirst ? (g[e] * f[e]) * inv[b] : (f[e] * inv[b]) * g[e];
+                for (int e = 0; e < 8; ++e) f[e] = gfirst ? (g[e] * f[e]) * inv : (f[e] * inv) * g[e];
                 st16(xs + (size_t)b * K + (size_t)i * 8, Unpack<__half>::put(f));
             }
         }
@@ -547,10 +438,9 @@ __device__ __noinline__ void stage_x(const StepOp& op, const StepParams& p, __ha
 // Epilogues are those of gemv.cu (same rounding points as the unfused launch sequence).
 // ------------------------------------------------------------------------------------------
 template <int NB>
-__device__ __noinline__ uint32_t gemv_consume(const StepOp& op, const StepParams& p, unsigned char* const r_base,
+__device__ __forceinline__ uint32_t gemv_consume(const StepOp& op, const StepParams& p, unsigned char* const r_base,
                                                  uint64_t* const r_full, uint64_t* const r_empty, const int r_stages,
-                                                 uint32_t state, const __half* xs, const int step,
-                                                 const uint32_t tag_base, const int oi) {
+                                                 uint32_t state, const __half* xs, const int step) {
     constexpr int KSEG = kSegB / 2;
     // everything the loops need sits in registers: with ~220 KB of shared memory in use there is
     // no L1 left, so any local-memory access (spill, indexed array) would be an L2 round trip
@@ -564,12 +454,7 @@ __device__ __noinline__ uint32_t gemv_consume(const StepOp& op, const StepParams
     const int u0 = (int)(((long long)units * blockIdx.x) / gridDim.x);
     const int u1 = (int)(((long long)units * (blockIdx.x + 1)) / gridDim.x);
     const int ngroups = (u1 - u0 + kStepWarps - 1) / kStepWarps;
-    __half* const y = reinterpret_cast<__half*>(op.y);   // plain copy (logits, hidden) or nullptr
-    unsigned* const yll = op.ybuf == kBufHidden ? p.ll_hidden : op.ybuf == kBufQkv ? p.ll_qkv : p.ll_act;
-    const uint32_t ytag = (tag_base + (uint32_t)oi + 1u) & 0xffffu;
-    const int rop = op.rop;
-    const bool skip_math = (p.debug_flags & 1) != 0;   // experiments only
-    const uint32_t rtag = (tag_base + (uint32_t)rop + 1u) & 0xffffu;
+    __half* const y = reinterpret_cast<__half*>(op.y);
 
     for (int g = 0; g < ngroups; ++g) {
         const int unit = u0 + g * kStepWarps + warp;
@@ -584,23 +469,14 @@ __device__ __noinline__ uint32_t gemv_consume(const StepOp& op, const StepParams
                 rb = ra + hd;
             } else { ra = 2 * unit; rb = (2 * unit + 1 < N) ? 2 * unit + 1 : -1; }
         }
-        // residual epilogue: fetch the old y words now (flagged words of op `rop`, or the embedding
-        // row for the first layer), their L2 latency hides behind the row; tags are checked at use
-        uint32_t ya[NB], yb[NB];
+        // residual epilogue: fetch the old y values now, their L2 latency hides behind the row
+        float ya[NB], yb[NB];
 #pragma unroll
         for (int b = 0; b < NB; ++b) {
-            ya[b] = yb[b] = 0u;
+            ya[b] = yb[b] = 0.f;
             if (epi == kEpiResidual && active && lane == 0 && b < nb) {
-                if (rop < 0) {
-                    int id = p.ids_cur[b];
-                    id = id < 0 ? 0 : (id >= p.vocab ? p.vocab - 1 : id);
-                    const __half* er = reinterpret_cast<const __half*>(p.embed) + (size_t)id * N;
-                    ya[b] = (uint32_t)__half_as_ushort(er[ra]) | (rtag << 16);
-                    if (rb >= 0) yb[b] = (uint32_t)__half_as_ushort(er[rb]) | (rtag << 16);
-                } else {
-                    ya[b] = ll_load_u32(yll + (size_t)b * N + ra);
-                    if (rb >= 0) yb[b] = ll_load_u32(yll + (size_t)b * N + rb);
-                }
+                ya[b] = __half2float(__ldcg(y + (size_t)b * N + ra));
+                if (rb >= 0) yb[b] = __half2float(__ldcg(y + (size_t)b * N + rb));
             }
         }
         float acc_a[NB], acc_b[NB];
@@ -608,65 +484,32 @@ __device__ __noinline__ uint32_t gemv_consume(const StepOp& op, const StepParams
         for (int b = 0; b < NB; ++b) acc_a[b] = acc_b[b] = 0.f;
 
         for (int seg = 0; seg < nseg; ++seg) {
-            const int seg_pk = (seg == nseg - 1) ? last_seg_pk : KSEG / 8;
-            const bool full_seg = seg_pk == KSEG / 8;
-            const __half* xseg = xs + (size_t)seg * KSEG;
-            Pack16 xr[kJS];   // NB == 1: the x packets of this segment serve row a and then row b
+            mbar_wait(&r_full[slot], phase);
+            if (active && !(p.debug_flags & 1)) {
+                const int seg_pk = (seg == nseg - 1) ? last_seg_pk : KSEG / 8;
+                const unsigned char* sa = r_base + (size_t)slot * kStageB + (2 * warp) * kSegB;
+                const unsigned char* sb = sa + kSegB;   // row b's slot (stale data when rb < 0: result unused)
+                const __half* xseg = xs + (size_t)seg * KSEG;
 #pragma unroll
-            for (int which = 0; which < 2; ++which) {
-                mbar_wait(&r_full[slot], phase);
-                if (active && (which == 0 || rb >= 0) && !skip_math) {
-                    const unsigned char* sw = r_base + (size_t)slot * kStageB + (size_t)warp * kSegB;
-                    if (full_seg) {
-                        // all loads first, then four independent FMA chains per row
-                        Pack16 wv[kJS];
+                for (int j = 0; j < kJS; ++j) {
+                    const int pkt = lane + 32 * j;
+                    if (pkt < seg_pk) {
+                        const Pack16 wa = ld16(sa + pkt * 16);
+                        const Pack16 wb = ld16(sb + pkt * 16);
 #pragma unroll
-                        for (int j = 0; j < kJS; ++j) wv[j] = ld16(sw + (lane + 32 * j) * 16);
-                        if (NB == 1) {
-                            if (which == 0) {
-#pragma unroll
-                                for (int j = 0; j < kJS; ++j) xr[j] = ld16(xseg + (size_t)(lane + 32 * j) * 8);
-                            }
-                            float c[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-                            for (int j = 0; j < kJS; ++j) c[j & 3] = dot16<__half>(wv[j], xr[j], c[j & 3]);
-                            const float sum = (c[0] + c[1]) + (c[2] + c[3]);
-                            if (which == 0) acc_a[0] += sum;
-                            else acc_b[0] += sum;
-                        } else {
-#pragma unroll
-                            for (int b = 0; b < NB; ++b) {
-                                float c[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-                                for (int j = 0; j < kJS; ++j)
-                                    c[j & 3] = dot16<__half>(wv[j], ld16(xseg + (size_t)b * K + (size_t)(lane + 32 * j) * 8), c[j & 3]);
-                                const float sum = (c[0] + c[1]) + (c[2] + c[3]);
-                                if (which == 0) acc_a[b] += sum;
-                                else acc_b[b] += sum;
-                            }
-                        }
-                    } else {
-#pragma unroll
-                        for (int j = 0; j < kJS; ++j) {
-                            const int pkt = lane + 32 * j;
-                            if (pkt < seg_pk) {
-                                const Pack16 wv = ld16(sw + pkt * 16);
-#pragma unroll
-                                for (int b = 0; b < NB; ++b) {
-                                    const Pack16 xv = ld16(xseg + (size_t)b * K + (size_t)pkt * 8);
-                                    if (which == 0) acc_a[b] = dot16<__half>(wv, xv, acc_a[b]);
-                                    else acc_b[b] = dot16<__half>(wv, xv, acc_b[b]);
-                                }
-                            }
+                        for (int b = 0; b < NB; ++b) {
+                            const Pack16 xv = ld16(xseg + (size_t)b * K + (size_t)pkt * 8);
+                            acc_a[b] = dot16<__half>(wa, xv, acc_a[b]);
+                            acc_b[b] = dot16<__half>(wb, xv, acc_b[b]);
                         }
                     }
                 }
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&r_empty[slot]);
-                if (++slot == r_stages) {
-                    slot = 0;
-                    phase ^= 1;
-                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&r_empty[slot]);
+            if (++slot == r_stages) {
+                slot = 0;
+                phase ^= 1;
             }
         }
         if (active) {
@@ -683,7 +526,7 @@ __device__ __noinline__ uint32_t gemv_consume(const StepOp& op, const StepParams
                         if (b < nb) {
                             const float gv = rnd(acc_a[b]), uv = rnd(acc_b[b]);   // gate/up are stored in T unfused
                             const float sg = rnd(gv / (1.f + expf(-gv)));
-                            ll16_store(yll + (size_t)b * N + ra, __float2half_rn(sg * uv), ytag);
+                            y[(size_t)b * N + ra] = __float2half_rn(sg * uv);
                         }
                     }
                 } else if (epi == kEpiRopeKV) {
@@ -702,9 +545,9 @@ __device__ __noinline__ uint32_t gemv_consume(const StepOp& op, const StepParams
                             const float av = rnd(acc_a[b]), bv = rnd(acc_b[b]);   // qkv_buf is stored in T before RoPE
                             const __half oa = __float2half_rn(c * av - sn * bv);
                             const __half ob = __float2half_rn(c * bv + sn * av);
-                            unsigned* yt = yll + (size_t)b * qkv_heads * d;
-                            ll16_store(yt + ra, oa, ytag);
-                            ll16_store(yt + rb, ob, ytag);
+                            __half* yt = y + (size_t)b * qkv_heads * d;
+                            yt[ra] = oa;
+                            yt[rb] = ob;
                             if (head >= p.head_num) {
                                 const bool is_k = head < p.head_num + p.kv_head_num;
                                 const int kvh = is_k ? head - p.head_num : head - p.head_num - p.kv_head_num;
@@ -722,20 +565,11 @@ __device__ __noinline__ uint32_t gemv_consume(const StepOp& op, const StepParams
                         if (b < nb) {
                             float av = acc_a[b], bv = acc_b[b];
                             if (epi == kEpiResidual) {   // linear output rounded to T, then T(out + residual)
-                                SpinGuard sg;
-                                while ((ya[b] >> 16) != rtag) { sg.tick(p.sync); ya[b] = ll_load_u32(yll + (size_t)b * N + ra); }
-                                av = rnd(av) + __half2float(__ushort_as_half((unsigned short)(ya[b] & 0xffffu)));
-                                ll16_store(yll + (size_t)b * N + ra, __float2half_rn(av), ytag);
-                                if (rb >= 0) {
-                                    while ((yb[b] >> 16) != rtag) { sg.tick(p.sync); yb[b] = ll_load_u32(yll + (size_t)b * N + rb); }
-                                    bv = rnd(bv) + __half2float(__ushort_as_half((unsigned short)(yb[b] & 0xffffu)));
-                                    ll16_store(yll + (size_t)b * N + rb, __float2half_rn(bv), ytag);
-                                }
+                                av = rnd(av) + ya[b];
+                                bv = rnd(bv) + yb[b];
                             }
-                            if (y) {
-                                y[(size_t)b * N + ra] = __float2half_rn(av);
-                                if (rb >= 0) y[(size_t)b * N + rb] = __float2half_rn(bv);
-                            }
+                            y[(size_t)b * N + ra] = __float2half_rn(av);
+                            if (rb >= 0) y[(size_t)b * N + rb] = __float2half_rn(bv);
                         }
                     }
                 }
@@ -746,15 +580,37 @@ __device__ __noinline__ uint32_t gemv_consume(const StepOp& op, const StepParams
 }
 
 // ------------------------------------------------------------------------------------------
-// consumers: split-KV decode attention (decode_attention.cu's kernel restated for the consumer warps inside
+// consumers: split-KV decode attention (decode_attention.cu's kernel restated for 8 warps inside
 // the persistent kernel). Work item = (sequence, kv head, split); head_size 128 (16 packets / row).
 // The new token's k,v were written to cache row step-1 by the qkv op's epilogue.
 // ------------------------------------------------------------------------------------------
 __device__ __forceinline__ float exp_guard_s(float m, float M) { return (m == -INFINITY) ? 0.f : expf(m - M); }
 
+// L2 prefetch of the cache rows [k0, min(k1, step-1)) of this CTA's first attention item (one
+// prefetch per 128-byte line); the newest row is written by the qkv op of this step and is not touched
 template <int G>
-__device__ __noinline__ void attn_consume(const StepOp& op, const StepParams& p, float* sm, int step,
-                                          uint32_t tag_in, uint32_t tag_out) {
+__device__ __forceinline__ void attn_prefetch(const StepOp& op, const StepParams& p, int step) {
+    constexpr int D = 128;
+    const int splits = p.splits;
+    const int items = p.nb * p.kv_head_num * splits;
+    const int item = blockIdx.x;
+    if (item >= items) return;
+    const int per = (step + splits - 1) / splits;
+    const int split = item % splits, bh = item / splits;
+    const int b = bh / p.kv_head_num, kvh = bh - b * p.kv_head_num;
+    const __half* kc = reinterpret_cast<const __half*>(op.k_cache) + ((size_t)b * p.kv_head_num + kvh) * p.max_seq_len * D;
+    const __half* vc = reinterpret_cast<const __half*>(op.v_cache) + ((size_t)b * p.kv_head_num + kvh) * p.max_seq_len * D;
+    const int k0 = split * per, kend = min(min(step, k0 + per), step - 1);
+    const int lines = (kend - k0) * (D * 2 / 128);
+    for (int i = threadIdx.x; i < 2 * lines; i += kStepConsumers) {
+        const __half* base = (i < lines ? kc : vc) + (size_t)k0 * D;
+        const int li = i < lines ? i : i - lines;
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(base + (size_t)li * 64));
+    }
+}
+
+template <int G>
+__device__ __noinline__ void attn_consume(const StepOp& op, const StepParams& p, float* sm, int step) {
     constexpr int PR = 16, E = 8, D = 128, KPI = 2, UN = 4;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int pi = lane % PR, ks = lane / PR;
@@ -763,45 +619,18 @@ __device__ __noinline__ void attn_consume(const StepOp& op, const StepParams& p,
     const int qkv_heads = p.head_num + 2 * p.kv_head_num;
     const float scale = rsqrtf((float)D);
     const int per = (step + splits - 1) / splits;
-    // smem: merge area [consumer warps][G][2 + D] floats, then the new token's q (G heads), k, v in fp16
-    __half* tokh = reinterpret_cast<__half*>(sm + (((size_t)kStepWarps * G * (2 + D) + 3) & ~(size_t)3));   // 16-byte aligned
-    const uint32_t t16 = tag_in & 0xffffu;
 
     for (int item = blockIdx.x; item < items; item += gridDim.x) {
         const int split = item % splits, bh = item / splits;
         const int b = bh / p.kv_head_num, kvh = bh - b * p.kv_head_num;
+        const __half* tok = reinterpret_cast<const __half*>(p.qkv) + (size_t)b * qkv_heads * D;
         const __half* kc = reinterpret_cast<const __half*>(op.k_cache) + ((size_t)b * p.kv_head_num + kvh) * p.max_seq_len * D;
         const __half* vc = reinterpret_cast<const __half*>(op.v_cache) + ((size_t)b * p.kv_head_num + kvh) * p.max_seq_len * D;
         const int k0 = split * per, k1 = min(step, k0 + per);
 
-        // the cache rows of this item do not depend on this step: pull them into L2 while the qkv op
-        // is still finishing elsewhere (one prefetch per 128-byte line)
-        {
-            const int kend = min(k1, step - 1);
-            const int lines = (kend - k0) * (D * 2 / 128);
-            for (int i = threadIdx.x; i < 2 * lines; i += kStepConsumers) {
-                const __half* base = (i < lines ? kc : vc) + (size_t)k0 * D;
-                const int li = i < lines ? i : i - lines;
-                asm volatile("prefetch.global.L2 [%0];" ::"l"(base + (size_t)li * 64));
-            }
-        }
-        // the new token's q / k / v come from the qkv op of this launch (flagged words); its cache
-        // row was written by the same epilogue but carries no flag, so it is not read here
-        {
-            const unsigned* tok = p.ll_qkv + (size_t)b * qkv_heads * D;
-            for (int i = threadIdx.x; i < (G + 2) * (D / 4); i += kStepConsumers) {
-                const int which = i / (D / 4), e4 = i - which * (D / 4);
-                const int head = which < G ? kvh * G + which
-                                           : (which == G ? p.head_num + kvh : p.head_num + p.kv_head_num + kvh);
-                const uint4 v = ll16_wait(tok + (size_t)head * D + e4 * 4, t16, p.sync);
-                *reinterpret_cast<uint2*>(tokh + (size_t)which * D + e4 * 4) = ll16_halves(v);
-            }
-        }
-        consumers_sync();
-
         Pack16 q[G];
 #pragma unroll
-        for (int g = 0; g < G; ++g) q[g] = ld16(tokh + (size_t)g * D + pi * E);
+        for (int g = 0; g < G; ++g) q[g] = ld16_cg(tok + (size_t)(kvh * G + g) * D + pi * E);
         float m[G], l[G], o[G][E];
 #pragma unroll
         for (int g = 0; g < G; ++g) {
@@ -817,12 +646,12 @@ __device__ __noinline__ void attn_consume(const StepOp& op, const StepParams& p,
             for (int u = 0; u < UN; ++u) {
                 const int key = base + u * KPI + ks;
                 ok[u] = key < k1;
-                if (ok[u]) kp[u] = (key == step - 1) ? ld16(tokh + (size_t)G * D + pi * E) : ld16_cg_nv(kc + (size_t)key * D + pi * E);
+                if (ok[u]) kp[u] = ld16_cg(kc + (size_t)key * D + pi * E);
             }
 #pragma unroll
             for (int u = 0; u < UN; ++u) {
                 const int key = base + u * KPI + ks;
-                if (ok[u]) vp[u] = (key == step - 1) ? ld16(tokh + (size_t)(G + 1) * D + pi * E) : ld16_cg_nv(vc + (size_t)key * D + pi * E);
+                if (ok[u]) vp[u] = ld16_cg(vc + (size_t)key * D + pi * E);
             }
             float s[G][UN];
 #pragma unroll
@@ -899,70 +728,13 @@ __device__ __noinline__ void attn_consume(const StepOp& op, const StepParams& p,
                 O += src[2 + e] * a;
             }
             const int head = kvh * G + g;
-            if (splits == 1) {   // the attention output itself, rounded to T as the unfused path stores it
-                ll16_store(p.ll_attn + ((size_t)b * p.head_num + head) * D + e, __float2half_rn(O / (L + 1e-6f)),
-                           tag_out & 0xffffu);
+            if (splits == 1) {
+                reinterpret_cast<__half*>(p.attn)[((size_t)b * p.head_num + head) * D + e] =
+                    __float2half_rn(O / (L + 1e-6f));
             } else {
                 const size_t slot = ((size_t)b * p.head_num + head) * splits + split;
-                ll32_store(p.ll_po + slot * D + e, O, tag_out);
-                if (e == 0) {
-                    ll32_store(p.ll_pml + slot * 2, M, tag_out);
-                    ll32_store(p.ll_pml + slot * 2 + 1, L, tag_out);
-                }
-            }
-        }
-        if (splits > 1) {
-            // the CTA that finishes the last split of a (sequence, kv head) merges the splits
-            // (fused_decoder_self_attention.cu:203-221,272-287 as one online-softmax pass) and
-            // publishes the fp16 attention output; everybody else moves on
-            int* flag = reinterpret_cast<int*>(sm);
-            consumers_sync();   // merge area reads done (flag aliases it), partial stores issued
-            if (threadIdx.x == 0) {
-                unsigned* cnt = p.attn_cnt + (size_t)b * p.kv_head_num + kvh;
-                const unsigned old = atomicAdd(cnt, 1u);
-                int last = old == (unsigned)(splits - 1);
-                if (last) last += (int)(atomicExch(cnt, 0u) & 0u);   // reset performed before anything below is issued
-                *flag = last;
-            }
-            consumers_sync();
-            const bool last = *flag != 0;
-            if (last) {
-                for (int idx = threadIdx.x; idx < G * D; idx += kStepConsumers) {
-                    const int g = idx / D, e = idx - g * D;
-                    const int head = kvh * G + g;
-                    const size_t slot0 = ((size_t)b * p.head_num + head) * splits;
-                    float M = -INFINITY, L = 0.f, O = 0.f;
-                    for (int s0 = 0; s0 < splits; s0 += 4) {
-                        ulonglong2 ml[4];
-                        unsigned long long ov[4];
-#pragma unroll
-                        for (int u = 0; u < 4; ++u) {
-                            if (s0 + u < splits) {
-                                ml[u] = ll_load_2x64(p.ll_pml + (slot0 + s0 + u) * 2);
-                                ov[u] = ll_load_u64(p.ll_po + (slot0 + s0 + u) * D + e);
-                            }
-                        }
-#pragma unroll
-                        for (int u = 0; u < 4; ++u) {
-                            if (s0 + u < splits) {
-                                SpinGuard sg;
-                                while (!ll32_ok(ml[u], tag_out)) { sg.tick(p.sync); ml[u] = ll_load_2x64(p.ll_pml + (slot0 + s0 + u) * 2); }
-                                while ((uint32_t)(ov[u] >> 32) != tag_out) { sg.tick(p.sync); ov[u] = ll_load_u64(p.ll_po + (slot0 + s0 + u) * D + e); }
-                                const float ms = __uint_as_float((uint32_t)ml[u].x), ls = __uint_as_float((uint32_t)ml[u].y);
-                                const float os = __uint_as_float((uint32_t)ov[u]);
-                                const float Mn = fmaxf(M, ms);
-                                if (Mn != -INFINITY) {
-                                    const float a = exp_guard_s(M, Mn), c = exp_guard_s(ms, Mn);
-                                    L = L * a + ls * c;
-                                    O = O * a + os * c;
-                                    M = Mn;
-                                }
-                            }
-                        }
-                    }
-                    ll16_store(p.ll_attn + ((size_t)b * p.head_num + head) * D + e, __float2half_rn(O / (L + 1e-6f)),
-                               tag_out & 0xffffu);
-                }
+                p.part_o[slot * D + e] = O;
+                if (e == 0) { p.part_ml[slot * 2] = M; p.part_ml[slot * 2 + 1] = L; }
             }
         }
         consumers_sync();   // sm is reused by the next item
@@ -1028,7 +800,7 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const __gr
     // the L1 is too small to hold per-thread local copies, and every mbarrier wait (a compiler
     // memory barrier) would otherwise re-fetch them from L2
     __shared__ StepParams p;
-    __shared__ StepOp opbuf[2];   // current op / next op (fetched while the current one runs)
+    __shared__ __align__(16) StepOp opbuf[2];   // current op / next op (fetched while the current one runs)
     unsigned char* ring = smem;
     __half* xs = reinterpret_cast<__half*>(smem + (size_t)gp.stages * kStageB);
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + (size_t)gp.stages * kStageB + gp.xs_bytes);
@@ -1057,65 +829,60 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const __gr
     const int step = *gp.step_dev;
     const unsigned base = gp.sync[1];
     const int n_ops = gp.n_ops;
-    const uint32_t tag_base = gp.sync[3] * (uint32_t)n_ops;   // launch sequence number * ops per launch
     unsigned epoch = 0;
     uint32_t ring_state = 0;   // slot | phase << 8
     if (threadIdx.x == 0) opbuf[0] = gp.ops[0];
+    consumers_sync();
     for (int oi = 0; oi < n_ops; ++oi) {
-        consumers_sync();   // opbuf[oi & 1] is complete; everybody has left op oi-1 (its buffer may be refilled)
         const StepOp& op = opbuf[oi & 1];
-        if (threadIdx.x == 0 && oi + 1 < n_ops) opbuf[(oi + 1) & 1] = gp.ops[oi + 1];
+        // the next op's descriptor travels while this op runs (its L2 round trip used to sit between
+        // the grid barrier and the prologue); the barrier's first sync publishes it to the CTA
+        static_assert(sizeof(StepOp) % 16 == 0, "StepOp is copied in 16-byte cp.async pieces");
+        if (threadIdx.x < sizeof(StepOp) / 16 && oi + 1 < n_ops)
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(smem_u32(&opbuf[(oi + 1) & 1]) + 16u * threadIdx.x),
+                         "l"(reinterpret_cast<const char*>(gp.ops + oi + 1) + 16 * threadIdx.x)
+                         : "memory");
+        asm volatile("cp.async.commit_group;" ::: "memory");
         const int type = op.type;
         if (type == kOpGemv) {
-            // this CTA's rows (same split as the producer's): without rows, no prologue either
-            const int u0 = (int)(((long long)op.units * blockIdx.x) / gridDim.x);
-            const int u1 = (int)(((long long)op.units * (blockIdx.x + 1)) / gridDim.x);
-            if (u1 > u0) {
-                stage_x<NB>(op, p, xs, red, scratch, tag_base);
-                if (gp.trace && blockIdx.x == 0 && threadIdx.x == 0) {
-                    gp.trace[2 * n_ops + oi] = global_timer_ns();
-                    int sl = (int)(ring_state & 0xffu), landed = 0;   // ring stages already landed when the GEMV starts
-                    uint32_t ph = ring_state >> 8;
-                    for (int i = 0; i < gp.stages; ++i) {
-                        landed += mbar_test(&full_bar[sl], ph) ? 1 : 0;
-                        if (++sl == gp.stages) { sl = 0; ph ^= 1; }
-                    }
-                    gp.trace[3 * n_ops + oi] = (unsigned long long)landed;
+            stage_x<NB>(op, p, xs, red, scratch);
+            if (gp.trace && blockIdx.x == 0 && threadIdx.x == 0) {
+                gp.trace[2 * n_ops + oi] = global_timer_ns();
+                int sl = (int)(ring_state & 0xffu), landed = 0;   // ring stages already landed when the GEMV starts
+                uint32_t ph = ring_state >> 8;
+                for (int i = 0; i < gp.stages; ++i) {
+                    landed += mbar_test(&full_bar[sl], ph) ? 1 : 0;
+                    if (++sl == gp.stages) { sl = 0; ph ^= 1; }
                 }
-                ring_state = gemv_consume<NB>(op, p, ring, full_bar, empty_bar, gp.stages, ring_state, xs, step,
-                                              tag_base, oi);
+                gp.trace[3 * n_ops + oi] = (unsigned long long)landed;
             }
+            ring_state = gemv_consume<NB>(op, p, ring, full_bar, empty_bar, gp.stages, ring_state, xs, step);
         } else if (type == kOpAttn) {
-            attn_consume<G>(op, p, reinterpret_cast<float*>(xs), step, tag_base + (uint32_t)op.xop + 1u,
-                            tag_base + (uint32_t)oi + 1u);
+            attn_consume<G>(op, p, reinterpret_cast<float*>(xs), step);
         } else {
-            // the greedy pick scans every logit: the one grid barrier of the step
-            ++epoch;
-            grid_barrier(gp.sync, base + epoch * gridDim.x);
             final_consume(p, red, reinterpret_cast<int*>(red + 16));
         }
-        if (gp.trace && threadIdx.x == 0) {   // every CTA: when it finished op oi (+ its SM id, once)
-            unsigned long long* mine = gp.trace + (4 * n_ops + 1) + (size_t)blockIdx.x * (n_ops + 1);
-            mine[oi] = global_timer_ns();
-            if (oi == 0) {
-                unsigned smid;
-                asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
-                mine[n_ops] = smid;
-            }
+        if (gp.trace && blockIdx.x == 0 && threadIdx.x == 0) gp.trace[2 * oi] = global_timer_ns();
+        if (oi + 1 < n_ops) {
+            ++epoch;
+            asm volatile("cp.async.wait_group 0;" ::: "memory");   // the next op's descriptor has landed
+            grid_barrier_arrive(gp.sync);
+            // while the other CTAs arrive: warm L2 with what the next op reads first and that does not
+            // depend on this step (the KV rows of this CTA's attention item)
+            const StepOp& nop = opbuf[(oi + 1) & 1];
+            if (nop.type == kOpAttn) attn_prefetch<G>(nop, p, step);
+            grid_barrier_wait(gp.sync, base + epoch * gridDim.x);
         }
-        if (gp.trace && blockIdx.x == 0 && threadIdx.x == 0) {
-            gp.trace[2 * oi] = global_timer_ns();
-            gp.trace[2 * oi + 1] = gp.trace[2 * oi];
-        }
+        if (gp.trace && blockIdx.x == 0 && threadIdx.x == 0) gp.trace[2 * oi + 1] = global_timer_ns();
     }
-    // last op done by this CTA: the final arrival advances the launch base, the tag sequence and the step
+    // last op done by this CTA: the final arrival advances the launch base and the step
+    consumers_sync();
     if (threadIdx.x == 0) {
         __threadfence();
         const unsigned total = (epoch + 1) * gridDim.x;
         const unsigned prev = atomicAdd(&gp.sync[0], 1u);
         if (prev + 1 == base + total) {   // every CTA has finished its final op
             gp.sync[1] = base + total;
-            gp.sync[3] = gp.sync[3] + 1u;
             *gp.step_dev = step + 1;
         }
     }
@@ -1165,6 +932,9 @@ int step_program_launch(const StepProgram* sp, int step, cudaStream_t s) {
     StepProgram local = *sp;
     const int splits = step_pick_splits(local.params.nb, local.params.kv_head_num, step);
     local.params.splits = splits;
+    const size_t ml = (size_t)local.params.nb * local.params.head_num * splits * 2 * sizeof(float);
+    local.params.part_ml = reinterpret_cast<float*>(local.attn_ws);
+    local.params.part_o = reinterpret_cast<float*>((char*)local.attn_ws + ((ml + 255) & ~(size_t)255));
     cudaError_t e = cudaErrorInvalidValue;
 #define STEP_CASE(NB_, G_) if (local.nb_t == NB_ && local.g == G_) e = step_launch_t<NB_, G_>(local, s);
     STEP_CASE(1, 1) STEP_CASE(2, 1) STEP_CASE(4, 1) STEP_CASE(1, 2) STEP_CASE(2, 2) STEP_CASE(4, 2)
@@ -1176,7 +946,7 @@ int step_program_launch(const StepProgram* sp, int step, cudaStream_t s) {
 
 int step_program_trace(const StepProgram* sp, unsigned long long* host_dst, int max_entries) {
     if (!sp || !sp->params.trace) return 0;
-    int n = 4 * sp->params.n_ops + 1 + sp->grid * (sp->params.n_ops + 1);
+    int n = 4 * sp->params.n_ops + 1;
     if (n > max_entries) n = max_entries;
     cudaMemcpy(host_dst, sp->params.trace, (size_t)n * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
     return n;
@@ -1185,15 +955,14 @@ int step_program_trace(const StepProgram* sp, unsigned long long* host_dst, int 
 void step_program_destroy(StepProgram* sp) {
     if (!sp) return;
     cudaFree(sp->params.trace);
-    cudaFree(sp->ll_arena);
     cudaFree(sp->ops_dev);
     cudaFree(sp->sync_dev);
     delete sp;
 }
 
 // returns nullptr when the configuration is outside what the persistent kernel covers
-StepProgram* step_program_create(const std::vector<StepOp>& ops_in, StepParams params, int batch, int head_num,
-                                 int kv_head_num, int head_size, int k_max) {
+StepProgram* step_program_create(const std::vector<StepOp>& ops, StepParams params, int batch, int head_num,
+                                 int kv_head_num, int head_size, int k_max, void* attn_ws) {
     const int G = head_num / kv_head_num;
     if (batch > 4 || head_size != 128 || (G != 1 && G != 2 && G != 4 && G != 8) || head_num % kv_head_num) return nullptr;
     static int disabled = -1;
@@ -1201,40 +970,15 @@ StepProgram* step_program_create(const std::vector<StepOp>& ops_in, StepParams p
     if (disabled) return nullptr;
     const int nb_t = batch <= 1 ? 1 : batch <= 2 ? 2 : 4;
     size_t xs_bytes = ((size_t)nb_t * k_max * 2 + 127) & ~(size_t)127;
-    const size_t attn_bytes =
-        ((size_t)kStepWarps * G * (2 + 128) * sizeof(float) + 16 + (size_t)(G + 2) * 128 * 2 + 127) & ~(size_t)127;
+    const size_t attn_bytes = ((size_t)kStepWarps * G * (2 + 128) * sizeof(float) + 127) & ~(size_t)127;
     if (xs_bytes < attn_bytes) xs_bytes = attn_bytes;
     int stages = kStepMaxStages;
-    if (const char* e = getenv("B200_STEP_STAGES")) { const int v = atoi(e); if (v >= 2 && v < stages) stages = v; }   // experiments
     while (stages >= 2 && step_smem(stages, xs_bytes, nb_t) > 227 * 1024 - 1024) --stages;   // 1 KB: static smem
     if (stages < 2) return nullptr;
     int dev = 0, coop = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
     if (!coop) return nullptr;
-    // who produced what: the tag a prologue waits for is that of the last op that wrote its buffer
-    std::vector<StepOp> ops = ops_in;
-    {
-        int last[8];
-        for (int& v : last) v = -1;
-        for (size_t i = 0; i < ops.size(); ++i) {
-            StepOp& o = ops[i];
-            o.xop = -1;
-            o.rop = -1;
-            if (o.type == kOpGemv) {
-                if (o.xsrc != kXEmbed) {
-                    o.xop = last[o.xbuf];
-                    if (o.xop < 0) return nullptr;   // reads a buffer nothing has written
-                }
-                if (o.epi == kEpiResidual) o.rop = last[o.ybuf];   // -1: first layer, residual = embedding row
-                last[o.ybuf] = (int)i;
-            } else if (o.type == kOpAttn) {
-                o.xop = last[kBufQkv];
-                if (o.xop < 0) return nullptr;
-                last[kBufAttn] = (int)i;
-            }
-        }
-    }
     StepProgram* sp = new StepProgram();
     sp->nb_t = nb_t;
     sp->g = G;
@@ -1248,30 +992,7 @@ StepProgram* step_program_create(const std::vector<StepOp>& ops_in, StepParams p
     cudaMemcpy(sp->ops_dev, ops.data(), ops.size() * sizeof(StepOp), cudaMemcpyHostToDevice);
     cudaMemset(sp->sync_dev, 0, 64);
     sp->params = params;
-    {   // flagged exchange buffers
-        const size_t qkv_n = (size_t)(head_num + 2 * kv_head_num) * head_size;
-        const size_t n_hidden = (size_t)batch * params.hidden, n_qkv = (size_t)batch * qkv_n,
-                     n_act = (size_t)batch * k_max;
-        const size_t n_ml = (size_t)batch * head_num * 64 * 2, n_po = (size_t)batch * head_num * 64 * head_size;
-        auto up = [](size_t b) { return (b + 255) & ~(size_t)255; };
-        const size_t n_attn = (size_t)batch * head_num * head_size, n_cnt = (size_t)batch * kv_head_num;
-        const size_t o_h = 0, o_q = o_h + up(n_hidden * 4), o_a = o_q + up(n_qkv * 4), o_at = o_a + up(n_act * 4),
-                     o_cn = o_at + up(n_attn * 4), o_ml = o_cn + up(n_cnt * 4), o_po = o_ml + up(n_ml * 8),
-                     total = o_po + up(n_po * 8);
-        if (cudaMalloc(&sp->ll_arena, total) != cudaSuccess) {
-            step_program_destroy(sp);
-            return nullptr;
-        }
-        cudaMemset(sp->ll_arena, 0, total);
-        char* a = reinterpret_cast<char*>(sp->ll_arena);
-        sp->params.ll_hidden = reinterpret_cast<unsigned*>(a + o_h);
-        sp->params.ll_qkv = reinterpret_cast<unsigned*>(a + o_q);
-        sp->params.ll_act = reinterpret_cast<unsigned*>(a + o_a);
-        sp->params.ll_attn = reinterpret_cast<unsigned*>(a + o_at);
-        sp->params.attn_cnt = reinterpret_cast<unsigned*>(a + o_cn);
-        sp->params.ll_pml = reinterpret_cast<unsigned long long*>(a + o_ml);
-        sp->params.ll_po = reinterpret_cast<unsigned long long*>(a + o_po);
-    }
+    sp->attn_ws = attn_ws;
     sp->params.ops = sp->ops_dev;
     sp->params.n_ops = (int)ops.size();
     sp->params.nb = batch;
@@ -1288,7 +1009,7 @@ StepProgram* step_program_create(const std::vector<StepOp>& ops_in, StepParams p
     }
     {
         const char* t = getenv("B200_STEP_TRACE");
-        if (t && t[0] == '1') cudaMalloc(&sp->params.trace, (4 * ops.size() + 1 + (size_t)sp->grid * (ops.size() + 1)) * sizeof(unsigned long long));
+        if (t && t[0] == '1') cudaMalloc(&sp->params.trace, (4 * ops.size() + 1) * sizeof(unsigned long long));
     }
     return sp;
 }

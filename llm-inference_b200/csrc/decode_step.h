@@ -8,9 +8,7 @@ namespace b200 {
 
 enum { kOpGemv = 0, kOpAttn = 1, kOpFinal = 2 };
 enum { kEpiPlain = 0, kEpiResidual = 1, kEpiSwiglu = 2, kEpiRopeKV = 3 };
-enum { kXPlain = 0, kXEmbed = 1 };
-// exchange buffers between ops (flagged words, see decode_step.cu): where a GEMV reads x / writes y
-enum { kBufNone = 0, kBufHidden = 1, kBufQkv = 2, kBufAct = 3, kBufLogits = 4, kBufAttn = 5 };
+enum { kXPlain = 0, kXEmbed = 1, kXCombine = 2 };
 
 struct StepOp {
     int type;        // kOp*
@@ -24,10 +22,6 @@ struct StepOp {
     const void* gamma;
     void* k_cache;   // layer slice [B, hk, max_seq, d] (RoPE/KV epilogue, attention)
     void* v_cache;
-    int xbuf, ybuf;  // kBuf*: exchange buffer x is read from / y is written to
-    // filled by step_program_create:
-    int xop;         // index of the op that produced x (its tag is what the prologue waits for)
-    int rop;         // residual epilogue: op that produced the old y (-1: the embedding row)
 };
 
 struct StepParams {
@@ -44,18 +38,12 @@ struct StepParams {
     int vocab, hidden;
     void* hidden_buf;     // [B, H] residual stream
     void* qkv;            // [B, h+2hk, d]
+    void* attn;           // [B, h*d]  (splits == 1 only)
     void* logits;         // [B, V]
+    float* part_ml;       // [B, h, splits, 2]
+    float* part_o;        // [B, h, splits, d]
     int splits;
-    // flagged exchange buffers (value + tag in one naturally atomic word)
-    unsigned* ll_hidden;              // [B, H]        fp16 | tag16 << 16
-    unsigned* ll_qkv;                 // [B, (h+2hk)d]
-    unsigned* ll_act;                 // [B, I]
-    unsigned* ll_attn;                // [B, h*d]      merged attention output
-    unsigned* attn_cnt;               // [B, hk]       split arrivals (reset by the merging CTA)
-    unsigned long long* ll_pml;       // [B, h, splits, 2]  fp32 | tag32 << 32
-    unsigned long long* ll_po;        // [B, h, splits, d]
-    unsigned* sync;       // [0] arrival counter (monotonic), [1] base of the current launch, [2] error flag,
-                          // [3] launch sequence number (tags)
+    unsigned* sync;       // [0] arrival counter (monotonic), [1] base of the current launch, [2] error flag
     int stages;
     size_t xs_bytes;
     long long l2_ahead_bytes;    // per-CTA distance of the L2 prefetch cursor in front of the smem ring (0 = off)
@@ -67,7 +55,7 @@ struct StepProgram {
     StepParams params{};
     StepOp* ops_dev = nullptr;
     unsigned* sync_dev = nullptr;
-    void* ll_arena = nullptr;  // the flagged exchange buffers
+    void* attn_ws = nullptr;   // split-KV partials (sized by b200_decode_attention_workspace_bytes)
     size_t smem = 0;
     int nb_t = 0, g = 0, grid = 0;
 };
@@ -76,7 +64,7 @@ struct StepProgram {
 // nullptr when the configuration is outside what the persistent kernel covers (fp16, batch <= 4,
 // head_size 128, h/hk in {1, 2, 4, 8}, cooperative launch available)
 StepProgram* step_program_create(const std::vector<StepOp>& ops, StepParams params, int batch, int head_num,
-                                 int kv_head_num, int head_size, int k_max);
+                                 int kv_head_num, int head_size, int k_max, void* attn_ws);
 // `step` = reference step of the token being decoded (tokens already cached + 1)
 int step_program_launch(const StepProgram* sp, int step, cudaStream_t s);
 void step_program_destroy(StepProgram* sp);

@@ -163,28 +163,26 @@ static void build_program(b200_engine* e) {
         void* kc = e->k_cache + (size_t)l * e->layer_kv_elems * e->esz;
         void* vc = e->v_cache + (size_t)l * e->layer_kv_elems * e->esz;
         StepOp qkv{kOpGemv, kEpiRopeKV, l == 0 ? kXEmbed : kXPlain, 1, e->qkv_n, H, e->qkv_n / 2,
-                   w.qkv, nullptr, nullptr, w.attn_norm, kc, vc, kBufHidden, kBufQkv, -1, -1};
-        StepOp att{kOpAttn, 0, 0, 0, 0, 0, 0, nullptr, nullptr, nullptr, nullptr, kc, vc, kBufQkv, kBufAttn, -1, -1};
-        StepOp o{kOpGemv, kEpiResidual, kXPlain, 0, H, e->h * e->d, (H + 1) / 2,
-                 w.o, nullptr, e->hidden, nullptr, nullptr, nullptr, kBufAttn, kBufHidden, -1, -1};
-        StepOp gu{kOpGemv, kEpiSwiglu, kXPlain, 2, e->I, H, e->I, w.gate_up, nullptr, nullptr, w.ffn_norm,
-                  nullptr, nullptr, kBufHidden, kBufAct, -1, -1};
-        StepOp dn{kOpGemv, kEpiResidual, kXPlain, 0, H, e->I, (H + 1) / 2, w.down, nullptr, e->hidden, nullptr,
-                  nullptr, nullptr, kBufAct, kBufHidden, -1, -1};
+                   w.qkv, e->hidden, e->qkv, w.attn_norm, kc, vc};
+        StepOp att{kOpAttn, 0, 0, 0, 0, 0, 0, nullptr, nullptr, nullptr, nullptr, kc, vc};
+        StepOp o{kOpGemv, kEpiResidual, kXCombine, 0, H, e->h * e->d, (H + 1) / 2,
+                 w.o, e->attn, e->hidden, nullptr, nullptr, nullptr};
+        StepOp gu{kOpGemv, kEpiSwiglu, kXPlain, 2, e->I, H, e->I, w.gate_up, e->hidden, e->act, w.ffn_norm, nullptr, nullptr};
+        StepOp dn{kOpGemv, kEpiResidual, kXPlain, 0, H, e->I, (H + 1) / 2, w.down, e->act, e->hidden, nullptr, nullptr, nullptr};
         ops.push_back(qkv); ops.push_back(att); ops.push_back(o); ops.push_back(gu); ops.push_back(dn);
     }
     StepOp head{kOpGemv, kEpiPlain, c.num_layers == 0 ? kXEmbed : kXPlain, 1, e->V, H, (e->V + 1) / 2,
-                e->lm_head, nullptr, e->logits, e->final_norm, nullptr, nullptr, kBufHidden, kBufLogits, -1, -1};
-    StepOp fin{kOpFinal, 0, 0, 0, 0, 0, 0, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, kBufNone, kBufNone, -1, -1};
+                e->lm_head, e->hidden, e->logits, e->final_norm, nullptr, nullptr};
+    StepOp fin{kOpFinal, 0, 0, 0, 0, 0, 0, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     ops.push_back(head); ops.push_back(fin);
     StepParams p{};
     p.head_num = e->h; p.kv_head_num = e->hk; p.head_size = e->d; p.max_seq_len = c.max_seq_len;
     p.rotary_dim = c.rotary_dim; p.eps = c.rms_eps; p.rope_den = e->rope_den;
     p.step_dev = e->step_dev; p.ids_cur = e->ids_cur; p.ids_next = e->ids_next;
     p.embed = e->embed; p.vocab = e->V; p.hidden = H;
-    p.hidden_buf = e->hidden; p.qkv = e->qkv; p.logits = e->logits;
+    p.hidden_buf = e->hidden; p.qkv = e->qkv; p.attn = e->attn; p.logits = e->logits;
     const int k_max = std::max(std::max(H, e->I), e->h * e->d);
-    e->program = step_program_create(ops, p, e->batch, e->h, e->hk, e->d, k_max);
+    e->program = step_program_create(ops, p, e->batch, e->h, e->hk, e->d, k_max, e->attn_ws);
 }
 
 extern "C" const char* b200_engine_last_error(void) { return g_err.c_str(); }

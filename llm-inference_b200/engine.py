@@ -127,22 +127,15 @@ class Engine:
 
     # ---- control
     def step_trace(self):
-        """numpy uint64 [n_ops, 4]: %globaltimer stamps (op done, barrier passed, x staged) + ring stages landed at GEMV start,
-        of CTA 0 of the persistent kernel's last launch (B200_STEP_TRACE=1), or None. Also sets self.cta_trace
-        [n_ctas, n_ops + 1] (per-CTA op-done stamps, last column = SM id) and self.prefetch_stages."""
-        buf = np.zeros(1 << 18, np.uint64)
+        """numpy uint64 [n_ops, 4]: %globaltimer stamps (op done, barrier passed, x staged) + ring stages landed at GEMV start, or None"""
+        buf = np.zeros(4096, np.uint64)
         n = self.lib.b200_engine_step_trace(self.h, buf.ctypes.data_as(C.c_void_p), buf.size)
         if not n:
             return None
-        k = self.n_step_ops()
-        head = 4 * k + 1
-        self.prefetch_stages = int(buf[4 * k])
-        self.cta_trace = buf[head:n].reshape(-1, k + 1).copy() if n > head else None
+        k = n // 4
+        self.prefetch_stages = int(buf[4 * k]) if n > 4 * k else 0
         return np.concatenate([buf[:2 * k].reshape(k, 2), buf[2 * k:3 * k].reshape(k, 1),
                                buf[3 * k:4 * k].reshape(k, 1)], axis=1)
-
-    def n_step_ops(self):
-        return 5 * self.cfg.num_layers + 2
 
     def set_mode(self, fused=True, graph=True, persistent=False):
         """A fresh engine runs the persistent whole-step kernel where it applies (fp16, batch <= 4);

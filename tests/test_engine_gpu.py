@@ -13,6 +13,8 @@ from oracle import model as omodel
 pytestmark = pytest.mark.gpu
 
 SMALL = dict(num_layers=3, head_num=4, kv_head_num=2, head_size=128, inter_size=768, vocab_size=1000)
+# down_proj rows longer than one ring stage (K = 9216 -> chunks of 4096 + 4096 + 1024), h/hk = 1, odd vocab pairs
+WIDE = dict(num_layers=2, head_num=4, kv_head_num=4, head_size=128, inter_size=9216, vocab_size=2999)
 
 
 def download_weights(E, eng, n_layers):
@@ -156,12 +158,14 @@ def test_batched_decode_uses_tcgen05_linears(pkg, B, graph):
     eng.close()
 
 
-@pytest.mark.parametrize("B,ctx", [(1, 0), (1, 300), (3, 130), (4, 64), (2, 1000)])
-def test_persistent_step_kernel_vs_oracle_with_context(pkg, B, ctx):
+@pytest.mark.parametrize("cfg_name,B,ctx", [("small", 1, 0), ("small", 1, 300), ("small", 3, 130), ("small", 4, 64),
+                                            ("small", 2, 1000), ("wide", 1, 40), ("wide", 2, 200)])
+def test_persistent_step_kernel_vs_oracle_with_context(pkg, cfg_name, B, ctx):
     """The persistent whole-step kernel (ONE cooperative launch per token) teacher-forced against
     the CPU oracle from a pre-filled KV cache, so that several split-KV geometries (1..4+ splits,
     merged in the o_proj prologue), the device-side step and the grid barriers are exercised."""
     E = pkg.engine
+    SMALL = {"small": globals()["SMALL"], "wide": WIDE}[cfg_name]
     max_seq, steps = ctx + 16, 6
     eng = E.Engine(B, max_seq, dtype=pkg.F16, **SMALL)   # fresh engine: persistent path is the default
     eng.init_random(seed=33, std=0.05)

@@ -43,35 +43,3 @@ for k, (o, b, n, x, ld) in acc.items():
           f"{ld / n:4.1f})   barrier wait avg {b / n / 1e3:8.2f} us")
 print("L2 prefetch stages issued by CTA 0:", eng.prefetch_stages)
 print("first rows:", (t[:12] - start).tolist())
-ct = eng.cta_trace
-if ct is not None:
-    ct = ct.astype(np.int64)
-    smid = ct[:, -1]
-    done = ct[:, :-1]
-    print("per-op finish-time skew across CTAs (us): op kind, median (max - min), median (max - median)")
-    for k, kind in enumerate(names):
-        cols = [i for i in range(5 * 8, 160) if i % 5 == k]
-        rng = [(done[:, i].max() - done[:, i].min()) / 1e3 for i in cols]
-        top = [(done[:, i].max() - np.median(done[:, i])) / 1e3 for i in cols]
-        print(f"  {kind:8s} {np.median(rng):6.2f} {np.median(top):6.2f}")
-    # is lateness systematic per SM? average rank of each CTA's finish time over the gate_up ops
-    cols = [i for i in range(40, 160) if i % 5 == 3]
-    late = np.stack([done[:, i] - np.median(done[:, i]) for i in cols], 1) / 1e3   # [cta, op] us vs median
-    mean_late = late.mean(1)
-    order = np.argsort(mean_late)
-    print("gate_up: mean lateness vs median per CTA (us): min %.2f  p10 %.2f  median %.2f  p90 %.2f  max %.2f; per-CTA std over layers (median) %.2f"
-          % (mean_late.min(), np.percentile(mean_late, 10), np.median(mean_late), np.percentile(mean_late, 90),
-             mean_late.max(), np.median(late.std(1))))
-    print("latest 12 CTAs (cta, smid, mean lateness us):", [(int(c), int(smid[c]), round(float(mean_late[c]), 2)) for c in order[-12:]])
-    print("earliest 12 CTAs:", [(int(c), int(smid[c]), round(float(mean_late[c]), 2)) for c in order[:12]])
-if ct is not None:
-    for k, kind in enumerate(names):
-        cols = [i for i in range(40, 160) if i % 5 == k]
-        lt = np.stack([done[:, i] - np.median(done[:, i]) for i in cols], 1) / 1e3
-        ml = lt.mean(1)
-        od = np.argsort(ml)
-        print(f"{kind}: latest 8 CTAs (cta, smid, mean lateness us, std):",
-              [(int(c), int(smid[c]), round(float(ml[c]), 2), round(float(lt[c].std()), 2)) for c in od[-8:]],
-              " p50/p90/p99 of all (cta, op) lateness: %.2f %.2f %.2f" % tuple(np.percentile(lt, [50, 90, 99])))
-    by_sm = sorted((int(smid[c]), round(float(mean_late[c]), 2)) for c in range(len(smid)))
-    print("gate_up mean lateness by smid:", by_sm)

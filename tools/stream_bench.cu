@@ -70,7 +70,7 @@ __global__ void __launch_bounds__(256, 1) stream_kernel(const unsigned char* buf
         for (int s = 0; s < per_cta; ++s) {
             if (pass > 0) mbar_wait(&empty[slot], (pass - 1) & 1);
             const long long chunk = (first + s) % n_chunks;
-            if (lane == 0) mbar_expect_tx(&full[slot], kStage);
+            if (lane == 0) mbar_expect_tx(&full[slot], kLanes * kSeg);
             if (lane < kLanes) bulk_g2s(smem + (size_t)slot * kStage + lane * kSeg, buf + chunk * kStage + lane * kSeg, kSeg, &full[slot]);
             if (pf_ahead > 0 && s + pf_ahead < per_cta && lane < kLanes) {
                 const long long pc = (first + s + pf_ahead) % n_chunks;
@@ -181,7 +181,7 @@ int main(int argc, char** argv) {
             if (ms < best) best = ms;
         }
         cudaError_t err = cudaGetLastError();
-        const double bytes = (double)grid * per_cta * kStage;
+        const double bytes = (double)grid * per_cta * (ldg ? kStage : lanes * seg);
         printf("%s ws %5lld MB grid %3d stages %d copies %2d x %5d B pf %d consume %d : %7.3f ms %6.0f GB/s (%.1f GB/s per SM) %s\n",
                ldg ? "LDG" : "TMA", ws >> 20, grid, stages, lanes, seg, pf, consume, best, bytes / best / 1e6,
                bytes / best / 1e6 / grid, err ? cudaGetErrorString(err) : "");
@@ -192,6 +192,9 @@ int main(int argc, char** argv) {
         run(ws, 148, 7, 0, 1, 1, 28672, false);
         run(ws, 148, 7, 0, 1, 7, 4096, false);
         run(ws, 148, 7, 0, 1, 28, 1024, false);
+        run(ws, 148, 7, 0, 1, 2, 8192, false);
+        run(ws, 148, 7, 0, 0, 2, 8192, false);
+        run(ws, 148, 4, 0, 1, 2, 8192, false);
         for (int grid : {148, 74, 37}) run(ws, grid, 0, 0, 1, 0, 0, true);
     }
     {
