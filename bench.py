@@ -11,8 +11,10 @@ Workloads (BASELINE.json configs):
 `value`  : tokens/s with everything resident in HBM, CUDA events on the engine's stream, max over ranks.
 `e2e`    : same metric through the call a user of the reference makes per token
            (b200_engine_decode_step_host: H2D token ids from pinned memory, the step, D2H ids).
-`roofline`: the dominant kernel (weight-streaming GEMV; 98% of the step's bytes at cfg2) timed
-           alone, back to back, on the model's own weights; achieved = algorithmic bytes / time.
+`roofline`: the dominant kernel. cfg2: decode_step_kernel (the whole step is one launch of it):
+           algorithmic bytes of a step / its launch time (CUDA events over the timed region); the
+           stand-alone GEMV family (CUDA-graph timed) rides along as `roofline_gemv_family`.
+           cfg4: the split-KV decode attention, timed alone back to back on the model's own cache.
 `cpu_baseline`: the CPU oracle port (oracle/llama_cpu.c) on a bounded sample, host cores stated.
 --impl reference: the reference's own CPU test functions (oracle/_ref, tests/unittests/*.cu)
            composed into the decode step, on the host cores, same metric / config.
@@ -433,6 +435,26 @@ def main():
     tok_s = B_total * K / (ms_max * 1e-3)
     e2e_tok_s = B_total * K / (e2e_ms_max * 1e-3)
     step_bytes = eng.weight_bytes - 2 * 32000 * 4096 + 0 + B_local * 2 * 32 * 4096 * 2 * (ctx + W + K // 2)
+    roof_aux = None
+    if rank == 0 and eng.launches_per_step == 1:
+        # the whole step is ONE launch of decode_step_kernel: that kernel is the dominant (only) one, its
+        # launch duration is the step time measured above with CUDA events on the engine's stream, and its
+        # algorithmic bytes are the step's (all weights once + KV rows [0, step) once)
+        roof_aux = roof   # the stand-alone GEMV family stays in the line for comparison
+        per_launch_ms = ms / K
+        achieved = step_bytes / (per_launch_ms * 1e-3) / 1e9
+        traffic = None
+        try:   # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the committed ncu capture
+            traffic = float(json.load(open(os.path.join(ROOT, "profiles", "r01_decode_step_traffic.json")))["dram_bytes_per_launch"])
+        except Exception:
+            pass
+        roof = {"bound": "hbm", "kernel": "decode_step_kernel", "achieved": round(achieved, 1), "peak": peak,
+                "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": traffic,
+                "traffic_unit": "bytes/launch (ncu --set full, profiles/r01_decode_step_full.md)" if traffic else None,
+                "per_launch_us": round(per_launch_ms * 1e3, 1), "algorithmic_bytes_per_launch": int(step_bytes),
+                "peak_source": peak_src,
+                "note": "persistent whole-step kernel: one cooperative launch per token; per-launch time = the "
+                        "timed region's CUDA-event time / steps (rank 0)"}
     out = None
     if rank == 0:
         out = {"metric": "decode_tokens_per_s", "value": round(tok_s, 2), "unit": "tok/s", "n_gpus": world,
@@ -448,6 +470,8 @@ def main():
                "step_hbm": {"algorithmic_GB_per_step": round(step_bytes / 1e9, 3),
                             "achieved_GBps": round(step_bytes / (ms_max / K * 1e-3) / 1e9, 1)},
                "roofline": roof, "clocks": clk}
+        if roof_aux is not None:
+            out["roofline_gemv_family"] = roof_aux
         if not args.no_cpu_baseline:
             try:
                 out["cpu_baseline"] = cpu_baseline_port(wl)
