@@ -288,11 +288,7 @@ def main():
         torch.cuda.synchronize()
 
     # ---- shard the requests: independent sequences, no data-path collective
-    if wl["scaling"] == "weak":
-        B_local, B_total = wl["batch"], wl["batch"] * world
-    else:
-        assert wl["batch"] % world == 0
-        B_local, B_total = wl["batch"] // world, wl["batch"]
+    B_local, B_total = pkg.sharding.shard_requests(wl["batch"], world, rank, wl["scaling"])
     ctx, K, W = wl["context"], args.steps, args.warmup
     W = max(W, 3)
     max_seq = ctx + 2 * (W + K) + 8

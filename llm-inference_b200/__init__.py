@@ -14,5 +14,6 @@ from . import capi  # noqa: F401
 from .capi import lib, lib_path, F32, F16  # noqa: F401
 from . import ops  # noqa: F401
 from . import engine  # noqa: F401
+from . import sharding  # noqa: F401
 
-__all__ = ["capi", "ops", "engine", "lib", "lib_path", "F32", "F16"]
+__all__ = ["capi", "ops", "engine", "sharding", "lib", "lib_path", "F32", "F16"]

@@ -15,11 +15,15 @@ def rounder(kind):
 
 
 class OracleModel:
-    def __init__(self, weights, cfg, batch, max_seq_len, kind):
+    def __init__(self, weights, cfg, batch, max_seq_len, kind, allreduce=None):
         """weights: dict with 'layers' (list of dicts attn_norm,qkv,o,ffn_norm,gate_up,down),
-        'embed','final_norm','lm_head' — float32 arrays holding the (already rounded) values."""
+        'embed','final_norm','lm_head' — float32 arrays holding the (already rounded) values.
+        Tensor parallel: cfg holds this rank's head counts / FFN columns plus
+        'hidden_size' (the unsplit H), weights are this rank's shard, and `allreduce(a)` sums a
+        [n,H] partial result in place over the ranks after o_proj and after down_proj."""
         self.w, self.cfg, self.B, self.kind = weights, cfg, batch, kind
         self.rt = rounder(kind)
+        self.allreduce = allreduce
         L, hk, d = cfg["num_layers"], cfg["kv_head_num"], cfg["head_size"]
         self.k = np.zeros((L, batch, hk, max_seq_len, d), np.float32)
         self.v = np.zeros((L, batch, hk, max_seq_len, d), np.float32)
@@ -41,6 +45,9 @@ class OracleModel:
         dn = np.zeros((n, o.shape[1]), np.float32)
         cpu.linear(np.ascontiguousarray(act), w["down"], dn, True)
         dn = rt(dn)
+        if self.allreduce is not None:
+            self.allreduce(dn)
+            dn = rt(dn)
         cpu.add_residual(resid, dn)
         return rt(dn)
 
@@ -49,7 +56,7 @@ class OracleModel:
         appends k,v at row self.step and advances self.step"""
         c, rt, B = self.cfg, self.rt, self.B
         h, hk, d, I = c["head_num"], c["kv_head_num"], c["head_size"], c["inter_size"]
-        H = h * d
+        H, Hl = c.get("hidden_size", h * d), h * d   # Hl: this rank's attention columns
         eps, base, rot = c.get("rms_eps", 1e-5), c.get("rotary_base", 10000.0), c.get("rotary_dim", d)
         ref_step = self.step + 1
         x = np.ascontiguousarray(x, dtype=np.float32).copy()
@@ -62,12 +69,15 @@ class OracleModel:
             qkv = rt(qkv).reshape(B, h + 2 * hk, d)
             cpu.rope_decode(qkv, h, hk, ref_step, rot, base)
             qkv = rt(qkv)
-            att = np.zeros((B, H), np.float32)
+            att = np.zeros((B, Hl), np.float32)
             cpu.decode_attention(qkv, self.k[l], self.v[l], att, h, hk, ref_step, True)
             att = rt(att)
             o = np.zeros((B, H), np.float32)
             cpu.linear(att, w["o"], o, True)
             o = rt(o)
+            if self.allreduce is not None:
+                self.allreduce(o)
+                o = rt(o)
             cpu.fused_add_bias_residual_rmsnorm(resid, o, None, w["ffn_norm"], eps)
             resid, o = rt(resid), rt(o)
             x = self._ffn(w, o, resid, I)
@@ -132,7 +142,7 @@ class OracleModel:
 
     def decode_step(self, ids):
         c, rt, B = self.cfg, self.rt, self.B
-        H = c["head_num"] * c["head_size"]
+        H = c.get("hidden_size", c["head_num"] * c["head_size"])
         eps = c.get("rms_eps", 1e-5)
         x = np.zeros((B, H), np.float32)
         cpu.embedding(np.ascontiguousarray(ids, dtype=np.int32), self.w["embed"], x)

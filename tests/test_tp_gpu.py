@@ -1,0 +1,117 @@
+"""Tensor-parallel decode through the engine's allreduce hook (include/b200_engine.h:
+b200_engine_set_allreduce), two ranks, against the UNSHARDED CPU oracle.
+Each rank owns head_num/2 query heads, kv_head_num/2 kv heads and inter_size/2 FFN columns
+(sharding.tp_shard_layer); the hook sums the partial [B,H] after o_proj and after down_proj.
+With >= 2 GPUs the ranks sit on different devices and the sum is an NCCL allreduce enqueued on the
+engine's stream, captured in the step's CUDA graph; on a one-GPU box both ranks share cuda:0 and
+the sum is staged through host memory over gloo (graph capture off). fp32 rel <= 1e-5, fp16 <= 2e-2."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import ROOT, assert_close, load_package
+from oracle import model as omodel
+from test_sharding_gloo import make_weights
+
+pytestmark = pytest.mark.gpu
+CFG = dict(num_layers=2, head_num=8, kv_head_num=4, head_size=128, inter_size=1536, vocab_size=1031)
+B, MAX_SEQ, CTX, STEPS = 2, 48, 9, 4
+
+
+def free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, kind, fused, out_dir):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import torch.distributed as dist
+    pkg = load_package()
+    E, sh = pkg.engine, pkg.sharding
+    multi = torch.cuda.device_count() >= world
+    dev = rank if multi else 0
+    torch.cuda.set_device(dev)
+    backend = "nccl" if multi else "gloo"
+    kw = dict(device_id=torch.device("cuda", dev)) if multi else {}
+    dist.init_process_group(backend, init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world, **kw)
+    try:
+        full = make_weights(CFG, kind, 33)
+        eng = E.Engine(B, MAX_SEQ, dtype=pkg.F16 if kind == "fp16" else pkg.F32, tp_size=world, tp_rank=rank, **CFG)
+        for l, w in enumerate(full["layers"]):
+            s = sh.tp_shard_layer(w, CFG, world, rank)
+            for slot, key in ((E.W_ATTN_NORM, "attn_norm"), (E.W_QKV, "qkv"), (E.W_O, "o"),
+                              (E.W_FFN_NORM, "ffn_norm"), (E.W_GATE_UP, "gate_up"), (E.W_DOWN, "down")):
+                eng.set_weight(slot, l, s[key])
+        eng.set_weight(E.W_EMBED, 0, full["embed"])
+        eng.set_weight(E.W_FINAL_NORM, 0, full["final_norm"])
+        eng.set_weight(E.W_LM_HEAD, 0, full["lm_head"])
+        rng = np.random.default_rng(5)
+        rt = omodel.rounder(kind)
+        kfull = rt(rng.uniform(-1, 1, (CFG["num_layers"], B, CFG["kv_head_num"], MAX_SEQ, CFG["head_size"])))
+        vfull = rt(rng.uniform(-1, 1, kfull.shape))
+        hkl = CFG["kv_head_num"] // world
+        eng.fill_kv_random(CTX)      # step <- CTX; the rows are overwritten with this rank's shard below
+        kc, vc = eng.kv_caches()
+        kc.copy_(torch.from_numpy(kfull[:, :, rank * hkl:(rank + 1) * hkl]).to(kc.dtype))
+        vc.copy_(torch.from_numpy(vfull[:, :, rank * hkl:(rank + 1) * hkl]).to(vc.dtype))
+        torch.cuda.synchronize()
+        assert eng.step == CTX
+        eng.set_mode(fused=fused, graph=multi)
+        n_calls = [0]
+        inner = sh.make_allreduce()
+
+        def hook(ptr, count, dtype, stream):
+            n_calls[0] += 1
+            assert count == B * CFG["head_num"] * CFG["head_size"]
+            return inner(ptr, count, dtype, stream)
+
+        eng.set_allreduce(hook)
+        ids = np.array([7, 1000], np.int32)
+        logits, picked = [], []
+        for _ in range(STEPS):
+            ids = eng.decode_step_host(ids)
+            logits.append(eng.logits().float().cpu().numpy().copy())
+            picked.append(ids.copy())
+        if not multi:
+            assert n_calls[0] == STEPS * CFG["num_layers"] * 2, "two allreduces per layer per step"
+        kc, vc = eng.kv_caches()
+        np.savez(os.path.join(out_dir, f"rank{rank}.npz"), logits=np.stack(logits), ids=np.stack(picked),
+                 k=kc.float().cpu().numpy(), v=vc.float().cpu().numpy())
+        eng.close()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("fused", [True, False])
+@pytest.mark.parametrize("kind", ["fp32", "fp16"])
+def test_engine_tensor_parallel_two_ranks_vs_unsharded_oracle(tmp_path, kind, fused):
+    import torch.multiprocessing as mp
+    world = 2
+    mp.spawn(_worker, args=(world, free_port(), kind, fused, str(tmp_path)), nprocs=world, join=True)
+    full = make_weights(CFG, kind, 33)
+    om = omodel.OracleModel(full, CFG, B, MAX_SEQ, kind)
+    rng = np.random.default_rng(5)
+    rt = omodel.rounder(kind)
+    om.k[:] = rt(rng.uniform(-1, 1, om.k.shape))
+    om.v[:] = rt(rng.uniform(-1, 1, om.v.shape))
+    om.step = CTX
+    got = [np.load(os.path.join(tmp_path, f"rank{r}.npz")) for r in range(world)]
+    assert np.array_equal(got[0]["ids"], got[1]["ids"]), "ranks must pick the same tokens"
+    assert np.array_equal(got[0]["logits"], got[1]["logits"]), "ranks must hold identical logits"
+    ids = np.array([7, 1000], np.int32)
+    for s in range(STEPS):
+        want_logits, want_ids = om.decode_step(ids)
+        assert_close(got[0]["logits"][s], want_logits, kind, f"logits step {s}")
+        ids = got[0]["ids"][s]      # follow the engine's tokens so both sides see the same inputs
+        if kind == "fp32":
+            assert np.array_equal(ids, want_ids)
+    hkl = CFG["kv_head_num"] // world
+    for r in range(world):
+        assert_close(got[r]["k"], om.k[:, :, r * hkl:(r + 1) * hkl], kind, f"rank {r} K shard")
+        assert_close(got[r]["v"], om.v[:, :, r * hkl:(r + 1) * hkl], kind, f"rank {r} V shard")
