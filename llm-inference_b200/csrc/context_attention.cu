@@ -1,7 +1,444 @@
-// Prefill (context) attention without materialised scores; placeholder for now.
+// Prefill (context) attention on tcgen05 / TMEM without materialised scores, mask or repeated KV.
+//
+// Replaces the five-launch sequence of LLaMAContextAttentionLayer::forward
+// (src/layers/attention/context_attention.cpp:136-161): launchRepeatKVCache (repeat_kv.cu:76) ->
+// launchLinearStridedBatchGemm q*k^T (linear.cu:127) -> launchScaleMaskAndSoftmax
+// (attn_softmax_kernel.cu:337; scale, +(1-mask)*-10000, exp(x-max)/(sum+1e-6), :109-173) ->
+// launchLinearStridedBatchGemm p*v -> launchTransposeOutRemovePadding
+// (fused_transpose_and_remv_pad.cu:51). Semantics kept: query t of sequence b sits at absolute
+// position history_len[b] + t and sees cache rows [0, history_len[b] + t]; fp32 softmax with the
+// 1e-6 in the denominator; a masked key contributes exp(-10000 + ...) which is 0 in fp32, so masked
+// keys (and whole key tiles above the diagonal) are skipped instead of added; GQA reads kv head
+// head / (h / hk) directly (RepeatKV never materialised); the output is written token-major with the
+// padding removed.
+//
+// One CTA per (sequence, head, 128-query tile), 320 threads, heaviest (last) query tiles first:
+//   warp 0      TMA producer: Q tile once, then K_j / V_j tiles (128 keys x 128 dims, two 128B-swizzled
+//               [128 x 64] boxes each) into 2-stage rings;
+//   warp 1      MMA issuer: S_j = Q K_j^T (both K-major, 8 x UMMA K=16) into one of two TMEM score
+//               buffers; O_j = P_j V_j (A = P from smem, B = V as MN-major operand - V rows are keys,
+//               exactly what the PV contraction runs over) into one of two TMEM output buffers;
+//               S_{j+1} is issued before P_j V_j so the tensor pipe works under the softmax of tile j;
+//   warps 2-5   softmax: thread = query row; two passes over the TMEM row (max, then exp2 / sum),
+//               P_j written as fp16 into the swizzled K-major A-operand layout, alpha_j = exp(m_old - m_new)
+//               handed to the accumulate warps through smem;
+//   warps 6-9   accumulate: thread = query row, 128 fp32 outputs in registers,
+//               o = o * alpha_j + O_j (tcgen05.ld), final o / (l + 1e-6) -> fp16 -> out.
+// TMEM: 2 x 128 score columns + 2 x 128 output columns = 512. Shared memory: Q 32 KB + K 2 x 32 KB +
+// V 2 x 32 KB + P 2 x 32 KB + 3 KB of alpha / l / mbarriers = 226.7 KB (one CTA per SM).
+//
+// Roofline: tensor; 4 * d flops per (query, visible key) pair = 4 * B * h * d * S(S+1)/2 at history 0.
 #include "common.cuh"
-extern "C" int b200_context_attention(const void*, const void*, const void*, void*, const int*,
-                                      const int*, const int*, int, int, int, int, int, int, int,
-                                      int, void*) {
-    return B200_EUNSUPPORTED;
+#include "launch_count.h"
+#include "tc_common.cuh"
+
+namespace b200 {
+
+constexpr int kCtxThreads = 320;
+constexpr int kCtxTile = 128;                       // queries per CTA = keys per tile = head size
+constexpr uint32_t kBoxBytes = 128 * 64 * 2;        // one [128 rows x 64 fp16] swizzled box
+constexpr uint32_t kTileBytes = 2 * kBoxBytes;      // 128 x 128 fp16
+constexpr uint32_t kOffQ = 0;
+constexpr uint32_t kOffK = kOffQ + kTileBytes;      // [2]
+constexpr uint32_t kOffV = kOffK + 2 * kTileBytes;  // [2]
+constexpr uint32_t kOffP = kOffV + 2 * kTileBytes;  // [2]
+constexpr uint32_t kOffAlpha = kOffP + 2 * kTileBytes;          // float [4][128]
+constexpr uint32_t kOffL = kOffAlpha + 4 * 128 * 4;             // float [128]
+constexpr uint32_t kOffBar = kOffL + 128 * 4;                   // 20 mbarriers
+constexpr uint32_t kOffSlot = kOffBar + 20 * 8;
+constexpr uint32_t kCtxSmem = kOffSlot + 16;
+static_assert(kCtxSmem <= 232448, "context attention exceeds the 227 KB shared-memory limit");
+
+struct CtxParams {
+    __half* out;              // [token_num, head_num * 128]
+    const int* input_len;     // [batch]
+    const int* history_len;   // [batch]
+    int batch, seq_len, head_num, kv_head_num, max_seq_len, q_tiles;
+    float scale_log2;         // 1/sqrt(d) * log2(e)
+};
+
+// MN-major operand with the 128B swizzle (canonical layout ((8,n),(8,k)):((1,LBO),(8,SBO)) in 16-byte
+// units): rows of the smem tile are K indices (128 bytes = 64 MN elements each), 8 rows form a 1024-byte
+// swizzle atom; SBO = distance between 8-row groups along K, LBO = distance between 64-element
+// chunks along MN (checked on the B200: with the two swapped the P V product is wrong).
+__device__ __forceinline__ uint64_t make_mnmajor_sw128_desc(uint32_t smem_addr, uint32_t lbo_bytes,
+                                                            uint32_t sbo_bytes) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr & 0x3FFFFu) >> 4);
+    d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16;
+    d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+
+// mbarrier wait that traps after ~2 s instead of hanging the device if a pipeline invariant is broken
+__device__ __forceinline__ void ctx_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t done, spins = 0;
+    uint64_t t0 = 0;
+    for (;;) {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n"
+            : "=r"(done)
+            : "r"(smem_u32(bar)), "r"(parity)
+            : "memory");
+        if (done) return;
+        if ((++spins & 0xFFFu) == 0) {
+            uint64_t now;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > 2000000000ull) __trap();
+        }
+    }
+}
+
+__device__ __forceinline__ float ex2_approx(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ void fence_proxy_async_smem() {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ uint32_t pack_h2(float a, float b) {
+    const __half2 h = __floats2half2_rn(a, b);
+    return *reinterpret_cast<const uint32_t*>(&h);
+}
+
+__global__ void __launch_bounds__(kCtxThreads, 1)
+context_attn_tcgen05_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_k,
+                            const __grid_constant__ CUtensorMap map_v, const CtxParams p) {
+    extern __shared__ __align__(1024) unsigned char smem[];
+    pdl_wait();   // lengths, q and the caches come from the preceding kernels
+    // ---- which (query tile, sequence, head) ----
+    const int bh = p.batch * p.head_num;
+    const int qt = p.q_tiles - 1 - (int)(blockIdx.x / bh);
+    const int b = (int)(blockIdx.x % bh) / p.head_num, head = (int)(blockIdx.x % bh) % p.head_num;
+    const int in_len = p.input_len[b], hist = p.history_len[b];
+    const int q0 = qt * kCtxTile;
+    if (q0 >= in_len) return;   // the whole CTA leaves before touching barriers / TMEM
+    const int ctx_len = hist + in_len;
+    const int q_hi = min(q0 + kCtxTile, in_len);
+    const int kv_end = hist + q_hi;                     // keys [0, kv_end) are visible to this tile
+    const int n_kt = (kv_end + kCtxTile - 1) / kCtxTile;
+    const int kvh = head / (p.head_num / p.kv_head_num);
+
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kOffBar);
+    uint64_t* q_full = bars;
+    uint64_t* k_full = bars + 1;    // [2]
+    uint64_t* k_empty = bars + 3;   // [2]
+    uint64_t* v_full = bars + 5;    // [2]
+    uint64_t* v_empty = bars + 7;   // [2]
+    uint64_t* s_full = bars + 9;    // [2]
+    uint64_t* s_empty = bars + 11;  // [2]
+    uint64_t* p_full = bars + 13;   // [2]
+    uint64_t* o_full = bars + 15;   // [2]
+    uint64_t* o_empty = bars + 17;  // [2]
+    uint64_t* l_full = bars + 19;
+    float* alpha_s = reinterpret_cast<float*>(smem + kOffAlpha);
+    float* l_s = reinterpret_cast<float*>(smem + kOffL);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + kOffSlot);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        if (smem_u32(smem) & 1023u) __trap();   // swizzled tiles need a 1024-byte aligned base
+        mbar_init(q_full, 1);
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&k_full[s], 1);
+            mbar_init(&k_empty[s], 1);
+            mbar_init(&v_full[s], 1);
+            mbar_init(&v_empty[s], 1);
+            mbar_init(&s_full[s], 1);
+            mbar_init(&s_empty[s], 4);
+            mbar_init(&p_full[s], 4);
+            mbar_init(&o_full[s], 1);
+            mbar_init(&o_empty[s], 4);
+        }
+        mbar_init(l_full, 4);
+        mbar_fence_init();
+        tma_prefetch_desc(&map_q);
+        tma_prefetch_desc(&map_k);
+        tma_prefetch_desc(&map_v);
+    }
+    if (warp == 1) tmem_alloc(tmem_slot, 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    pdl_launch_dependents();
+
+    if (warp == 0) {
+        // ================= TMA producer =================
+        const int qrow = (b * p.head_num + head) * p.seq_len + q0;
+        const int krow = (b * p.kv_head_num + kvh) * p.max_seq_len;
+        if (lane == 0) {
+            mbar_expect_tx(q_full, kTileBytes);
+            tma_load_2d(smem + kOffQ, &map_q, 0, qrow, q_full);
+            tma_load_2d(smem + kOffQ + kBoxBytes, &map_q, 64, qrow, q_full);
+        }
+        for (int j = 0; j < n_kt; ++j) {
+            const int s = j & 1;
+            const uint32_t ph = (uint32_t)(j >> 1) & 1u;
+            ctx_wait(&k_empty[s], ph ^ 1u);
+            if (lane == 0) {
+                unsigned char* dst = smem + kOffK + (uint32_t)s * kTileBytes;
+                mbar_expect_tx(&k_full[s], kTileBytes);
+                tma_load_2d(dst, &map_k, 0, krow + j * kCtxTile, &k_full[s]);
+                tma_load_2d(dst + kBoxBytes, &map_k, 64, krow + j * kCtxTile, &k_full[s]);
+            }
+            ctx_wait(&v_empty[s], ph ^ 1u);
+            if (lane == 0) {
+                unsigned char* dst = smem + kOffV + (uint32_t)s * kTileBytes;
+                mbar_expect_tx(&v_full[s], kTileBytes);
+                tma_load_2d(dst, &map_v, 0, krow + j * kCtxTile, &v_full[s]);
+                tma_load_2d(dst + kBoxBytes, &map_v, 64, krow + j * kCtxTile, &v_full[s]);
+            }
+            __syncwarp();
+        }
+    } else if (warp == 1) {
+        // ================= MMA issuer =================
+        constexpr uint32_t idesc_s = make_idesc_f16(kCtxTile, kCtxTile);       // A, B K-major
+        constexpr uint32_t idesc_pv = idesc_s | (1u << 16);                    // B (= V) MN-major
+        const uint32_t q_addr = smem_u32(smem + kOffQ);
+        auto issue_s = [&](int j) {
+            const int s = j & 1;
+            const uint32_t ph = (uint32_t)(j >> 1) & 1u;
+            ctx_wait(&k_full[s], ph);
+            ctx_wait(&s_empty[s], ph ^ 1u);
+            tc_fence_after();
+            if (lane == 0) {
+                const uint32_t k_addr = smem_u32(smem + kOffK + (uint32_t)s * kTileBytes);
+#pragma unroll
+                for (int ks = 0; ks < kCtxTile / kUmmaK; ++ks) {
+                    const uint32_t off = (uint32_t)(ks >> 2) * kBoxBytes;
+                    umma_f16(tmem_base + (uint32_t)(s * kCtxTile),
+                             make_kmajor_sw128_desc(q_addr + off) + (uint64_t)(2 * (ks & 3)),
+                             make_kmajor_sw128_desc(k_addr + off) + (uint64_t)(2 * (ks & 3)), idesc_s, ks > 0 ? 1u : 0u);
+                }
+                umma_commit(&k_empty[s]);
+                umma_commit(&s_full[s]);
+            }
+            __syncwarp();
+        };
+        auto issue_pv = [&](int j) {
+            const int s = j & 1;
+            const uint32_t ph = (uint32_t)(j >> 1) & 1u;
+            ctx_wait(&v_full[s], ph);
+            ctx_wait(&p_full[s], ph);
+            ctx_wait(&o_empty[s], ph ^ 1u);
+            tc_fence_after();
+            if (lane == 0) {
+                const uint32_t p_addr = smem_u32(smem + kOffP + (uint32_t)s * kTileBytes);
+                const uint32_t v_addr = smem_u32(smem + kOffV + (uint32_t)s * kTileBytes);
+#pragma unroll
+                for (int ks = 0; ks < kCtxTile / kUmmaK; ++ks) {
+                    // 16 keys = two 8-row groups of 1024 bytes; the two 64-wide halves of d are 16 KB apart
+                    const uint64_t dv = make_mnmajor_sw128_desc(v_addr + (uint32_t)ks * 2048u, kBoxBytes, 1024u);
+                    umma_f16(tmem_base + (uint32_t)(256 + s * kCtxTile),
+                             make_kmajor_sw128_desc(p_addr + (uint32_t)(ks >> 2) * kBoxBytes) + (uint64_t)(2 * (ks & 3)), dv,
+                             idesc_pv, ks > 0 ? 1u : 0u);
+                }
+                umma_commit(&v_empty[s]);
+                umma_commit(&o_full[s]);
+            }
+            __syncwarp();
+        };
+        ctx_wait(q_full, 0);
+        issue_s(0);
+        for (int j = 0; j < n_kt; ++j) {
+            if (j + 1 < n_kt) issue_s(j + 1);
+            issue_pv(j);
+        }
+    } else if (warp < 6) {
+        // ================= softmax warps: thread = query row =================
+        const int quarter = warp & 3;
+        const int row = quarter * 32 + lane;
+        const int qpos = min(hist + q0 + row, ctx_len - 1);   // pad rows behave like the last real row
+        const float sl = p.scale_log2;
+        float m = -1e30f, l = 0.f;
+        for (int j = 0; j < n_kt; ++j) {
+            const int s = j & 1;
+            const uint32_t ph = (uint32_t)(j >> 1) & 1u;
+            const int kbase = j * kCtxTile;
+            const bool need_mask = kbase + kCtxTile - 1 > hist + q0;
+            ctx_wait(&s_full[s], ph);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(s * kCtxTile);
+            // pass 1: row maximum of the visible scores
+            float mx = m;
+#pragma unroll 1
+            for (int c = 0; c < 4; ++c) {
+                uint32_t v[32];
+                tmem_ld_32x32(taddr + (uint32_t)(c * 32), v);
+#pragma unroll
+                for (int e = 0; e < 32; ++e) {
+                    const float x = __uint_as_float(v[e]);
+                    const bool vis = !need_mask || (kbase + c * 32 + e <= qpos);
+                    mx = vis ? fmaxf(mx, x) : mx;
+                }
+            }
+            const float alpha = ex2_approx((m - mx) * sl);
+            m = mx;
+            const float msl = m * sl;
+            // P[s] was the A operand of P_{j-2} V_{j-2}: that MMA must have retired
+            if (j >= 2) ctx_wait(&o_full[s], ph ^ 1u);
+            // pass 2: p = exp2(x * sl - m * sl), row sum, fp16 P into the swizzled K-major layout
+            const uint32_t p_row = smem_u32(smem + kOffP + (uint32_t)s * kTileBytes) + (uint32_t)row * 128u;
+            float rs = 0.f;
+#pragma unroll 1
+            for (int c = 0; c < 4; ++c) {
+                uint32_t v[32];
+                tmem_ld_32x32(taddr + (uint32_t)(c * 32), v);
+                float pe[32];
+#pragma unroll
+                for (int e = 0; e < 32; ++e) {
+                    const bool vis = !need_mask || (kbase + c * 32 + e <= qpos);
+                    const float pv = ex2_approx(fmaf(__uint_as_float(v[e]), sl, -msl));
+                    pe[e] = vis ? pv : 0.f;
+                    rs += pe[e];
+                }
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int cc = c * 4 + q;   // 16-byte chunk (8 keys) of the 128-key row
+                    const uint32_t addr = p_row + (uint32_t)(cc >> 3) * kBoxBytes + (uint32_t)(((cc & 7) ^ (row & 7)) << 4);
+                    st_shared_v4(addr, pack_h2(pe[q * 8 + 0], pe[q * 8 + 1]), pack_h2(pe[q * 8 + 2], pe[q * 8 + 3]),
+                                 pack_h2(pe[q * 8 + 4], pe[q * 8 + 5]), pack_h2(pe[q * 8 + 6], pe[q * 8 + 7]));
+                }
+            }
+            l = l * alpha + rs;
+            alpha_s[(j & 3) * 128 + row] = alpha;
+            if (j == n_kt - 1) {
+                l_s[row] = l;
+                // cache rows at or beyond the context length are not ours: 0 * garbage must stay 0
+                const int valid = ctx_len - kbase;
+                if (valid < kCtxTile) {
+                    ctx_wait(&v_full[s], ph);
+                    if (row >= valid) {
+                        const uint32_t v_row = smem_u32(smem + kOffV + (uint32_t)s * kTileBytes) + (uint32_t)row * 128u;
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) {
+                            st_shared_v4(v_row + (uint32_t)(q << 4), 0u, 0u, 0u, 0u);
+                            st_shared_v4(v_row + kBoxBytes + (uint32_t)(q << 4), 0u, 0u, 0u, 0u);
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            fence_proxy_async_smem();   // P (and the zeroed V rows) become visible to the tensor core
+            __syncwarp();
+            if (lane == 0) {
+                mbar_arrive(&s_empty[s]);
+                mbar_arrive(&p_full[s]);
+                if (j == n_kt - 1) mbar_arrive(l_full);
+            }
+        }
+    } else {
+        // ================= accumulate warps: thread = query row, o[128] in registers =================
+        const int quarter = warp & 3;
+        const int row = quarter * 32 + lane;
+        float o[kCtxTile];
+#pragma unroll
+        for (int e = 0; e < kCtxTile; ++e) o[e] = 0.f;
+        for (int j = 0; j < n_kt; ++j) {
+            const int s = j & 1;
+            const uint32_t ph = (uint32_t)(j >> 1) & 1u;
+            ctx_wait(&o_full[s], ph);
+            tc_fence_after();
+            const float alpha = alpha_s[(j & 3) * 128 + row];   // written before p_full[s], which precedes P_j V_j
+            const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(256 + s * kCtxTile);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                uint32_t v[32];
+                tmem_ld_32x32(taddr + (uint32_t)(c * 32), v);
+#pragma unroll
+                for (int e = 0; e < 32; ++e) o[c * 32 + e] = fmaf(o[c * 32 + e], alpha, __uint_as_float(v[e]));
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&o_empty[s]);
+        }
+        ctx_wait(l_full, 0);
+        const int t = q0 + row;
+        if (t < in_len) {
+            int tok = t;
+            for (int i = 0; i < b; ++i) tok += p.input_len[i];
+            const float inv = 1.f / (l_s[row] + 1e-6f);
+            __half* dst = p.out + ((size_t)tok * p.head_num + head) * kCtxTile;
+#pragma unroll
+            for (int q = 0; q < 16; ++q) {
+                float f[8];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) f[e] = o[q * 8 + e] * inv;
+                st16(dst + q * 8, Unpack<__half>::put(f));
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_context_attention(const void* q, const void* k_cache_layer, const void* v_cache_layer,
+                                      void* out, const int* padding_offset, const int* input_len,
+                                      const int* history_len, int batch, int seq_len, int token_num,
+                                      int head_num, int kv_head_num, int head_size, int max_seq_len,
+                                      int dtype, void* stream) {
+    (void)padding_offset;   // the packed token index is the prefix sum of input_len (cal_paddingoffset.cu:51-72)
+    if (!q || !k_cache_layer || !v_cache_layer || !out || !input_len || !history_len) return B200_EINVAL;
+    if (batch < 1 || seq_len < 1 || token_num < 0 || head_num < 1 || kv_head_num < 1 || head_num % kv_head_num ||
+        max_seq_len < 1)
+        return B200_EINVAL;
+    // tensor-core tiles exist for fp16 with 128-wide heads; anything else takes the reference-order path
+    if (dtype != B200_F16 || head_size != kCtxTile) return B200_EUNSUPPORTED;
+    auto al = [](const void* x) { return (reinterpret_cast<uintptr_t>(x) & 15u) == 0; };
+    if (!al(q) || !al(k_cache_layer) || !al(v_cache_layer) || !al(out)) return B200_EUNSUPPORTED;
+    static int disabled = -1;
+    if (disabled < 0) {
+        const char* e = getenv("B200_NO_TCGEN05");
+        disabled = (e && e[0] == '1') ? 1 : 0;
+    }
+    if (disabled) return B200_EUNSUPPORTED;
+    const long long q_rows = (long long)batch * head_num * seq_len;
+    const long long kv_rows = (long long)batch * kv_head_num * max_seq_len;
+    if (q_rows + kCtxTile >= (1ll << 31) || kv_rows + kCtxTile >= (1ll << 31)) return B200_EUNSUPPORTED;
+    if (token_num == 0) return 0;
+    CUtensorMap mq, mk, mv;
+    if (!make_tma_map_2d(&mq, q, q_rows, kCtxTile, kCtxTile) || !make_tma_map_2d(&mk, k_cache_layer, kv_rows, kCtxTile, kCtxTile) ||
+        !make_tma_map_2d(&mv, v_cache_layer, kv_rows, kCtxTile, kCtxTile))
+        return B200_EUNSUPPORTED;
+    CtxParams p{};
+    p.out = reinterpret_cast<__half*>(out);
+    p.input_len = input_len;
+    p.history_len = history_len;
+    p.batch = batch; p.seq_len = seq_len; p.head_num = head_num; p.kv_head_num = kv_head_num;
+    p.max_seq_len = max_seq_len;
+    p.q_tiles = (seq_len + kCtxTile - 1) / kCtxTile;
+    p.scale_log2 = (1.0f / sqrtf((float)head_size)) * 1.4426950408889634f;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(context_attn_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)kCtxSmem);
+        if (e != cudaSuccess) return (int)e;
+        attr_set = true;
+    }
+    const long long grid = (long long)p.q_tiles * batch * head_num;
+    if (grid >= (1ll << 31)) return B200_EUNSUPPORTED;
+    cudaError_t e = launch_k(context_attn_tcgen05_kernel, dim3((unsigned)grid), dim3(kCtxThreads), (size_t)kCtxSmem,
+                             (cudaStream_t)stream, true, mq, mk, mv, p);
+    count_launch();
+    return (int)e;
 }

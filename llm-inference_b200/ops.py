@@ -255,3 +255,16 @@ def launchTopK(probs, topk_ids, topk_vals, k):
 def argmax(logits, out_ids):
     b, v = logits.shape
     _check(capi.lib().b200_argmax(_p(logits), _p(out_ids), b, v, _dt(logits), _stream()), "argmax")
+
+
+def context_attention(q, k_cache_layer, v_cache_layer, out, padding_offset, input_len, history_len):
+    """b200_context_attention: the tcgen05 flash kernel behind LLaMAContextAttentionLayer's fused path
+    (replaces context_attention.cpp:136-161). q [B, h, S, d]; cache layer slices [B, hk, max_seq, d];
+    out [num_tokens, h*d]; int32 device vectors as in the reference. Raises on unsupported shapes
+    (fp32 / head size != 128): the caller then runs the reference-order sequence on the GPU."""
+    b, h, s, d = q.shape
+    hk, max_seq = k_cache_layer.shape[1], k_cache_layer.shape[2]
+    _check(capi.lib().b200_context_attention(
+        _p(q), _p(k_cache_layer), _p(v_cache_layer), _p(out), _p(padding_offset), _p(input_len),
+        _p(history_len), b, s, out.shape[0], h, hk, d, max_seq, _dt(q), _stream()),
+        "b200_context_attention")
