@@ -1,13 +1,15 @@
 #!/usr/bin/env python
 """bench.py — LLaMA-2-7B fp16 decode tok/s on B200 (BASELINE.json metric), one JSON line.
 
-    python bench.py --gpus N --steps K --warmup W [--workload cfg2|cfg4] [--impl reference]
+    python bench.py --gpus N --steps K --warmup W [--workload cfg2|cfg3|cfg4] [--impl reference]
 
 A "step" is one decode step of the whole model for the whole batch (one new token per sequence).
 Workloads (BASELINE.json configs):
   cfg2 (default): LLaMA-2-7B fp16 random-init full model, batch 1 greedy decode at a 512-token
         context. N GPUs = N independent requests (weights replicated, no communication): weak.
   cfg4: batch 32 x KV length 4096, 32/N sequences per GPU (strong), no communication.
+  cfg3: prefill, batch 4 x 2048 prompt tokens per GPU (metric prefill_tokens_per_s; a step = one prompt
+        pass of the whole model: tcgen05 GEMMs + flash context attention; roofline = tensor).
 `value`  : tokens/s with everything resident in HBM, CUDA events on the engine's stream, max over ranks.
 `e2e`    : same metric through the call a user of the reference makes per token
            (b200_engine_decode_step_host: H2D token ids from pinned memory, the step, D2H ids).
@@ -39,7 +41,7 @@ def parse():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=128)
     ap.add_argument("--warmup", type=int, default=8)
-    ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg4"])
+    ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg3", "cfg4"])
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--context", type=int, default=None)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -47,6 +49,9 @@ def parse():
 
 
 def workload(args):
+    if args.workload == "cfg3":
+        return dict(name="LLaMA-2-7B fp16 prefill: context attention + tcgen05 GEMMs, batch 4 x seq 2048 (configs[2])",
+                    batch=4, context=args.context or 2048, scaling="weak")
     if args.workload == "cfg4":
         return dict(name="LLaMA-2-7B fp16 decode, batch 32 x KV 4096 (configs[3])", batch=32,
                     context=args.context or 4096, scaling="strong")
@@ -256,6 +261,234 @@ def reference_arm(args, wl):
 
 
 # --------------------------------------------------------------------------------------------
+# cfg3: prefill
+# --------------------------------------------------------------------------------------------
+def cpu_baseline_prefill(wl, n_tok=128):
+    """oracle port of the context decoder loop on a bounded sample: ONE 7B-shaped fp32 layer over one
+    sequence of n_tok prompt tokens (history 0), scaled to 32 layers"""
+    import numpy as np
+    from oracle import cpu, model as omodel
+    H, I = 4096, 11008
+    layer = dict(attn_norm=np.ones(H, np.float32), qkv=_cheap_random((3 * H, H), 0.02, 1), o=_cheap_random((H, H), 0.02, 2),
+                 ffn_norm=np.ones(H, np.float32), gate_up=_cheap_random((2 * I, H), 0.02, 3), down=_cheap_random((H, I), 0.02, 4))
+    om = omodel.OracleModel(dict(layers=[layer]), dict(L7B, num_layers=1), 1, n_tok + 1, "fp32")
+    x = _cheap_random((n_tok, H), 1.0, 5)
+    t0 = time.perf_counter()
+    om.prefill_layers(x, [n_tok], [0])
+    t = time.perf_counter() - t0
+    return {"value": round(n_tok / (32 * t), 3), "unit": "tok/s", "cores": cpu.num_threads(), "kind": "port",
+            "sample": f"1 of 32 LLaMA-2-7B fp32 layers of the context decoder over one {n_tok}-token prompt "
+                      f"({t:.2f} s measured), time scaled x32"}
+
+
+def reference_arm_prefill(args, wl):
+    """--impl reference --workload cfg3: the reference's CPUlinear (tests/unittests/test_linear.cu:13) on 1/FRAC of
+    one layer's linear columns over a 16-token prompt slice, sliced over all host cores; attention is 4% of
+    the flops at this shape and is left to the linear-time scaling (stated)."""
+    import numpy as np
+    cores = os.cpu_count() or 1
+    H, I = 4096, 11008
+    n_tok, FRAC = 16, 16
+    try:
+        ref, kind = RefCpu(), "reference"
+    except OSError:
+        ref, kind = None, "port"
+    from oracle import cpu
+    per = max(1, ((3 * H + H + 2 * I) // FRAC) // cores)
+    per2 = max(1, (H // FRAC) // cores)
+    x, xa = _cheap_random((n_tok, H), 1.0, 1), _cheap_random((n_tok, I), 1.0, 2)
+    w1 = [_cheap_random((H, per), 0.02, 10 + i) for i in range(cores)]
+    w2 = [_cheap_random((I, per2), 0.02, 30 + i) for i in range(cores)]
+    o1 = [np.zeros((n_tok, per), np.float32) for _ in range(cores)]
+    o2 = [np.zeros((n_tok, per2), np.float32) for _ in range(cores)]
+
+    def sample():
+        if ref:
+            for o in o1 + o2:
+                o[:] = 0
+            ref.linear_sliced(x, w1, o1)
+            ref.linear_sliced(xa, w2, o2)
+        else:
+            for ws, o in zip(w1, o1):
+                cpu.linear(x, ws, o, False)
+            for ws, o in zip(w2, o2):
+                cpu.linear(xa, ws, o, False)
+
+    for _ in range(max(1, min(args.warmup, 3))):
+        sample()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        sample()
+    t = (time.perf_counter() - t0) / args.steps
+    done = per * cores * H + per2 * cores * I                 # weight elements covered by one sample
+    t_layer = t * (3 * H * H + H * H + 2 * I * H + H * I) / done
+    value = n_tok / (32 * t_layer)
+    out = {"impl": "reference", "metric": "prefill_tokens_per_s", "value": round(value, 4), "unit": "tok/s",
+           "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(t * 1e3, 3),
+           "higher_is_better": True, "scaling": wl["scaling"], "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "config": {"workload": wl["name"], "batch": wl["batch"], "context": wl["context"]},
+           "cpu_baseline": {"value": round(value, 4), "unit": "tok/s", "cores": cores, "kind": kind,
+                            "sample": f"per step: 1/{FRAC} of one 7B layer's linear columns over {n_tok} prompt tokens "
+                                      f"through the reference's CPUlinear, {cores} threads; scaled to 32 layers "
+                                      f"(attention, 4% of the flops, not timed)"},
+           "e2e": {"value": round(value, 4), "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+           "gpu_launches": 0}
+    print(json.dumps(out))
+
+
+def bench_prefill(args, wl, rank, world, local_rank):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from __graft_entry__ import load_package
+    pkg = load_package()
+    E, capi, ops = pkg.engine, pkg.capi, pkg.ops
+    if not torch.cuda.is_available():
+        raise SystemExit("[b200][ERROR] bench.py needs a CUDA device: there is no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    B, S, K, W = wl["batch"], wl["context"], args.steps, max(args.warmup, 3)
+    eng = E.Engine(B, S + 8, dtype=capi.F16, **L7B)
+    eng.init_random(seed=1234 + rank, std=0.02)
+    stream = torch.cuda.ExternalStream(eng.stream)
+    ids = np.random.default_rng(7 + rank).integers(0, 32000, (B, S)).astype(np.int32)
+    for _ in range(W):
+        eng.reset()
+        eng.prefill(ids)
+    barrier()
+    clocks = Clocks(local_rank)
+    if rank == 0:
+        clocks.start()
+    capi.lib().b200_launch_count_reset()
+    # device-resident: the ids are re-sent (32 KB), nothing is read back; events on the engine's stream
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    for a, b in evs:
+        eng.reset()
+        with torch.cuda.stream(stream):
+            a.record()
+            eng.prefill(ids, sync=False)
+            b.record()
+    barrier()
+    launches = int(capi.lib().b200_launch_count())
+    ms = sum(a.elapsed_time(b) for a, b in evs)
+    clk = clocks.stop() if rank == 0 else None
+    # end to end: host ids in, first generated ids out on the host, every step
+    t0 = time.perf_counter()
+    for _ in range(K):
+        eng.reset()
+        eng.prefill(ids)
+    e2e_s = time.perf_counter() - t0
+    t = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max, e2e_ms_max = float(t[0]), float(t[1])
+    Nt, H, I = B * S, 4096, 11008
+    lin_flops = 2.0 * Nt * (3 * H * H + H * H + 2 * I * H + H * I) * 32
+    attn_flops = 4.0 * B * 32 * 128 * S * (S + 1) / 2 * 32
+    head_flops = 2.0 * B * 32000 * H
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops", 1400.0)))
+    peak_src = ("MEASURED_PEAKS.json bf16_tflops_sustained (cuBLAS bf16 back to back)" if peaks
+                else "fallback 1400 TFLOP/s")
+    roof = roof_attn = None
+    if rank == 0:
+        # the dominant kernel alone: the four tcgen05 GEMMs of every layer on the engine's weights
+        x_h = (torch.randn(Nt, H, device="cuda") * 0.1).half()
+        x_i = (torch.randn(Nt, I, device="cuda") * 0.1).half()
+        y_qkv = torch.empty(Nt, 3 * H, dtype=torch.float16, device="cuda")
+        y_h = torch.empty(Nt, H, dtype=torch.float16, device="cuda")
+        y_gu = torch.empty(Nt, 2 * I, dtype=torch.float16, device="cuda")
+
+        def gemm_pass():
+            for l in range(32):
+                ops.launchLinearGemm(x_h, eng.weight_view(E.W_QKV, l), y_qkv, trans_b=True)
+                ops.launchLinearGemm(x_h, eng.weight_view(E.W_O, l), y_h, trans_b=True)
+                ops.launchLinearGemm(x_h, eng.weight_view(E.W_GATE_UP, l), y_gu, trans_b=True)
+                ops.launchLinearGemm(x_i, eng.weight_view(E.W_DOWN, l), y_h, trans_b=True)
+
+        gemm_pass()
+        torch.cuda.synchronize()
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s0.record()
+        gemm_pass()
+        gemm_pass()
+        s1.record()
+        torch.cuda.synchronize()
+        g_ms = s0.elapsed_time(s1) / 2
+        ach = lin_flops / (g_ms * 1e-3) / 1e12
+        roof = {"bound": "tensor", "kernel": "gemm_tcgen05_kernel", "achieved": round(ach, 1), "peak": peak,
+                "unit": "TFLOP/s", "frac": round(ach / peak, 4), "traffic": None,
+                "per_launch_us": round(g_ms * 1e3 / 128, 1), "algorithmic_flops_per_launch": lin_flops / 128,
+                "peak_source": peak_src,
+                "note": f"128 GEMMs of one prompt pass (32 layers x qkv/o/gate_up/down, {Nt} tokens) back to back on "
+                        "the model's own weights; operands beyond L2 (12.9 GB of weights per pass)"}
+        # the flash context attention alone, 32 layers
+        q = (torch.rand(B, 32, S, 128, device="cuda") - 0.5).half()
+        kc, vc = eng.kv_caches()
+        out = torch.empty(Nt, H, dtype=torch.float16, device="cuda")
+        lens = torch.full((B,), S, dtype=torch.int32, device="cuda")
+        hist = torch.zeros(B, dtype=torch.int32, device="cuda")
+        pad = torch.zeros(Nt, dtype=torch.int32, device="cuda")
+
+        def attn_pass():
+            for l in range(32):
+                ops.context_attention(q, kc[l], vc[l], out, pad, lens, hist)
+
+        attn_pass()
+        torch.cuda.synchronize()
+        s0.record()
+        attn_pass()
+        attn_pass()
+        s1.record()
+        torch.cuda.synchronize()
+        a_ms = s0.elapsed_time(s1) / 2
+        ach = attn_flops / (a_ms * 1e-3) / 1e12
+        roof_attn = {"bound": "tensor", "kernel": "context_attn_tcgen05_kernel", "achieved": round(ach, 1), "peak": peak,
+                     "unit": "TFLOP/s", "frac": round(ach / peak, 4), "traffic": None,
+                     "per_launch_us": round(a_ms * 1e3 / 32, 1), "algorithmic_flops_per_launch": attn_flops / 32,
+                     "peak_source": peak_src, "note": "causal flops only (4*d per visible query-key pair)"}
+    if rank == 0:
+        tok_s = world * Nt * K / (ms_max * 1e-3)
+        flops = lin_flops + attn_flops + head_flops
+        out = {"metric": "prefill_tokens_per_s", "value": round(tok_s, 1), "unit": "tok/s", "n_gpus": world, "steps": K,
+               "warmup": W, "ms_per_step": round(ms_max / K, 3), "higher_is_better": True, "scaling": "weak",
+               "vs_baseline": None, "dtype": "f16", "data": "synthetic",
+               "config": {"workload": wl["name"], "batch_per_gpu": B, "seq_len": S, "tokens_per_step_per_gpu": Nt,
+                          "weights": "random-init N(0,0.02^2) fp16", "accumulate": "fp32",
+                          "l2": "inputs larger than L2 (12.9 GB of weights + 1.2 GB of activations per pass)",
+                          "parallelism": f"dp{world} (independent prompts, no collective)"},
+               "e2e": {"value": round(world * Nt * K / (e2e_ms_max * 1e-3), 1), "unit": "tok/s",
+                       "h2d_bytes_per_step": 4 * Nt + 12 * B, "d2h_bytes_per_step": 4 * B,
+                       "ms_per_step": round(e2e_ms_max / K, 3)},
+               "gpu_launches": launches, "launches_per_step": eng.prefill_launches,
+               "step_tensor": {"algorithmic_TFLOP_per_step": round(flops / 1e12, 2),
+                               "achieved_TFLOPs": round(flops / (ms_max / K * 1e-3) / 1e12, 1)},
+               "roofline": roof, "roofline_context_attention": roof_attn, "clocks": clk}
+        if not args.no_cpu_baseline:
+            try:
+                out["cpu_baseline"] = cpu_baseline_prefill(wl)
+            except Exception as ex:
+                out["cpu_baseline"] = {"value": None, "unit": "tok/s", "cores": os.cpu_count(), "kind": "port",
+                                       "sample": f"failed: {ex}"}
+        print(json.dumps(out))
+    eng.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+# --------------------------------------------------------------------------------------------
 # the B200 arm
 # --------------------------------------------------------------------------------------------
 def main():
@@ -267,8 +500,10 @@ def main():
 
     if args.impl == "reference":
         if rank == 0:
-            reference_arm(args, wl)
+            (reference_arm_prefill if args.workload == "cfg3" else reference_arm)(args, wl)
         return
+    if args.workload == "cfg3":
+        return bench_prefill(args, wl, rank, world, local_rank)
 
     import numpy as np
     import torch

@@ -111,6 +111,16 @@ int b200_engine_decode_step(b200_engine* e, const int* ids_in_dev);
  * host ids in (pinned or pageable), one decode step, host ids out; synchronises. */
 int b200_engine_decode_step_host(b200_engine* e, const int* ids_in_host, int* ids_out_host);
 
+/* The prompt pass (Llama<T>::firstTokenGen, llama.cpp:274-318): `len` tokens per sequence
+ * (ids_host int32 [batch, len], sequence-major), appended after the tokens already cached
+ * (history_length = current step, as in the reference's multi-round chat): embedding -> context
+ * decoder layers (tcgen05 GEMMs + flash context attention; K/V rows written to the cache) -> final
+ * norm + LM head on each sequence's last token -> top-1. On return step += len, the engine's current
+ * ids are the first generated tokens (decode_step(NULL) continues), and ids_out_host (may be NULL:
+ * then no host sync) receives them. */
+int b200_engine_prefill(b200_engine* e, const int* ids_host, int len, int* ids_out_host);
+int b200_engine_prefill_launches(const b200_engine* e);   /* kernel launches of the last prefill */
+
 /* device pointers into the engine (valid until destroy): logits [batch, vocab], ids [batch],
  * hidden [batch, H], caches; for parity tests and the bench. */
 void* b200_engine_logits(b200_engine* e);

@@ -64,6 +64,12 @@ struct b200_engine {
     void* lin_ws;          // split-K partials of the tcgen05 weight-streaming linears (batch > 8)
     size_t lin_ws_bytes;
     int* pinned_ids = nullptr;
+    // prefill scratch (grown on demand by b200_engine_prefill)
+    char* pf_arena = nullptr;
+    size_t pf_bytes = 0;
+    int* pf_pinned = nullptr;
+    size_t pf_pinned_ints = 0;
+    int prefill_launches = 0;
     // control
     cudaStream_t stream = nullptr;
     unsigned mode = B200_ENGINE_FUSED | B200_ENGINE_GRAPH | B200_ENGINE_PERSISTENT;
@@ -291,6 +297,8 @@ extern "C" void b200_engine_destroy(b200_engine* e) {
     b200::step_program_destroy(e->program);
     if (e->stream) cudaStreamDestroy(e->stream);
     if (e->pinned_ids) cudaFreeHost(e->pinned_ids);
+    if (e->pf_pinned) cudaFreeHost(e->pf_pinned);
+    cudaFree(e->pf_arena);
     cudaFree(e->arena);
     cudaFree(e->k_cache);
     cudaFree(e->v_cache);
@@ -595,3 +603,147 @@ extern "C" int b200_engine_decode_step_host(b200_engine* e, const int* ids_in_ho
     memcpy(ids_out_host, e->pinned_ids + e->batch, nb);
     return 0;
 }
+
+
+// ------------------------------------------------------------------------------------------
+// prefill: the prompt pass of Llama<T>::firstTokenGen (llama.cpp:274-318) =
+// launchInputEmbedding -> LlamaContextDecoder<T>::forward (context_decoder.cpp:48-140; per layer
+// RMSNorm -> qkv GEMM -> bias/RoPE/transpose -> ConcatKV -> attention -> o GEMM -> fused add+norm ->
+// gate_up GEMM -> SwiGLU -> down GEMM -> AddResidual) -> final RMSNorm -> LM head on the last token of
+// each sequence (llama.cpp:221-232) -> top-1. All sequences of the engine share one `step`
+// (llama.h keeps a single host `step` as well), so every sequence gets `len` prompt tokens, appended
+// after the `step` tokens already cached (history_length = step: the reference's multi-round chat).
+// The attention is b200_context_attention (tcgen05 flash kernel); for shapes it does not cover
+// (fp32, head size != 128) the reference-order GPU sequence runs instead.
+// ------------------------------------------------------------------------------------------
+namespace b200 {
+__global__ void set_ids_step_kernel(int* ids_cur, const int* ids_next, int* step, int batch, int ref_step) {
+    pdl_wait();
+    if (threadIdx.x < batch) ids_cur[threadIdx.x] = ids_next[threadIdx.x];
+    if (threadIdx.x == 0) *step = ref_step;
+}
+}  // namespace b200
+
+extern "C" int b200_engine_prefill(b200_engine* e, const int* ids_host, int len, int* ids_out_host) {
+    if (!e || !ids_host || len < 1) return fail("prefill: bad arguments");
+    const int dt = e->cfg.dtype, B = e->batch, H = e->H, hist = e->step;
+    if (hist + len > e->cfg.max_seq_len - 1) return fail("prefill: prompt does not fit the KV cache");
+    if ((long long)B * len >= (1ll << 24)) return fail("prefill: too many tokens");
+    const int Nt = B * len, ctx = hist + len;
+    const size_t es = e->esz;
+    cudaStream_t s = e->stream;
+    const uint64_t launches0 = b200_launch_count();
+    // ---- scratch layout
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off += align256(bytes); return o; };
+    const size_t o_x = take((size_t)Nt * H * es), o_res = take((size_t)Nt * H * es);
+    const size_t o_qkv = take((size_t)Nt * e->qkv_n * es);
+    const size_t o_q = take((size_t)Nt * e->h * e->d * es), o_k = take((size_t)Nt * e->hk * e->d * es),
+                 o_v = take((size_t)Nt * e->hk * e->d * es);
+    const size_t o_att = take((size_t)Nt * e->h * e->d * es);
+    const size_t o_gu = take((size_t)Nt * 2 * e->I * es), o_act = take((size_t)Nt * e->I * es);
+    const size_t o_ids = take((size_t)Nt * 4), o_pad = take((size_t)Nt * 4), o_cum = take((size_t)(B + 1) * 4),
+                 o_len = take((size_t)B * 4), o_hist = take((size_t)B * 4), o_ctx = take((size_t)B * 4);
+    size_t lin_ws = 0;
+    {
+        const int shapes[4][2] = {{e->qkv_n, H}, {H, e->h * e->d}, {2 * e->I, H}, {H, e->I}};
+        for (auto& sh : shapes) lin_ws = std::max(lin_ws, b200_linear_workspace_bytes(Nt, sh[0], sh[1], 1, dt));
+    }
+    const size_t o_lws = take(lin_ws + 256);
+    const bool flash = dt == B200_F16 && e->d == 128 && !(getenv("B200_NO_TCGEN05") && getenv("B200_NO_TCGEN05")[0] == '1');
+    size_t o_mask = 0, o_kr = 0, o_vr = 0, o_sc = 0, o_pv = 0;
+    if (!flash) {   // reference-order attention: dense mask, repeated KV, materialised scores
+        o_mask = take((size_t)B * len * ctx * es);
+        o_kr = take((size_t)B * e->h * ctx * e->d * es);
+        o_vr = take((size_t)B * e->h * ctx * e->d * es);
+        o_sc = take((size_t)B * e->h * len * ctx * es);
+        o_pv = take((size_t)Nt * e->h * e->d * es);
+    }
+    if (off > e->pf_bytes) {
+        CU(cudaStreamSynchronize(s));
+        cudaFree(e->pf_arena);
+        e->pf_arena = nullptr;
+        e->pf_bytes = 0;
+        CU(cudaMalloc(&e->pf_arena, off));
+        e->pf_bytes = off;
+    }
+    const size_t need_ints = (size_t)Nt + 3 * B;
+    if (need_ints > e->pf_pinned_ints) {
+        if (e->pf_pinned) cudaFreeHost(e->pf_pinned);
+        e->pf_pinned = nullptr;
+        e->pf_pinned_ints = 0;
+        CU(cudaMallocHost(&e->pf_pinned, need_ints * sizeof(int)));
+        e->pf_pinned_ints = need_ints;
+    }
+    char* a = e->pf_arena;
+    void *x = a + o_x, *res = a + o_res, *qkv = a + o_qkv, *q = a + o_q, *k = a + o_k, *v = a + o_v, *att = a + o_att,
+         *gu = a + o_gu, *act = a + o_act, *lws = a + o_lws;
+    int *ids = (int*)(a + o_ids), *pad = (int*)(a + o_pad), *cum = (int*)(a + o_cum), *lens = (int*)(a + o_len),
+        *hists = (int*)(a + o_hist), *ctxs = (int*)(a + o_ctx);
+    // ---- host -> device: token ids and the three length vectors (contiguous in the arena)
+    memcpy(e->pf_pinned, ids_host, (size_t)Nt * sizeof(int));
+    for (int b = 0; b < B; ++b) {
+        e->pf_pinned[Nt + b] = len;
+        e->pf_pinned[Nt + B + b] = hist;
+        e->pf_pinned[Nt + 2 * B + b] = ctx;
+    }
+    CU(cudaMemcpyAsync(ids, e->pf_pinned, (size_t)Nt * sizeof(int), cudaMemcpyHostToDevice, s));
+    CU(cudaMemcpyAsync(lens, e->pf_pinned + Nt, (size_t)B * sizeof(int), cudaMemcpyHostToDevice, s));
+    CU(cudaMemcpyAsync(hists, e->pf_pinned + Nt + B, (size_t)B * sizeof(int), cudaMemcpyHostToDevice, s));
+    CU(cudaMemcpyAsync(ctxs, e->pf_pinned + Nt + 2 * B, (size_t)B * sizeof(int), cudaMemcpyHostToDevice, s));
+    auto linear = [&](const void* in, const void* W, void* out, int N, int K) {
+        return b200_linear(in, W, nullptr, out, Nt, N, K, 1, dt, lws, lin_ws + 256, s);
+    };
+    const bool tp = e->cfg.tp_size > 1 && e->allreduce;
+    RC(b200_cal_padding_offset(pad, cum, lens, B, len, s));
+    if (!flash) RC(b200_build_causal_mask(a + o_mask, lens, ctxs, B, len, ctx, 1, dt, s));
+    RC(b200_embedding(ids, e->embed, x, Nt, H, e->V, dt, s));
+    for (int l = 0; l < e->cfg.num_layers; ++l) {
+        LayerW& w = e->layers[l];
+        const size_t layer_off = (size_t)l * e->layer_kv_elems;
+        RC(b200_rmsnorm(x, res, w.attn_norm, Nt, H, e->cfg.rms_eps, dt, s));
+        RC(linear(x, w.qkv, qkv, e->qkv_n, H));
+        RC(b200_qkv_bias_rope_transpose(q, k, v, qkv, nullptr, pad, hists, lens, B, len, Nt, e->h, e->hk, e->d,
+                                        e->cfg.rotary_dim, e->cfg.rotary_base, dt, s));
+        RC(b200_concat_kv_cache(k, v, e->k_cache, e->v_cache, layer_off, lens, hists, B, e->hk, len, e->cfg.max_seq_len,
+                                e->d, dt, s));
+        if (flash) {
+            RC(b200_context_attention(q, e->k_cache + layer_off * es, e->v_cache + layer_off * es, att, pad, lens, hists, B,
+                                      len, Nt, e->h, e->hk, e->d, e->cfg.max_seq_len, dt, s));
+        } else {
+            RC(b200_repeat_kv_cache(e->k_cache, e->v_cache, a + o_kr, a + o_vr, layer_off, ctxs, B, e->h, e->hk,
+                                    e->cfg.max_seq_len, ctx, e->d, dt, s));
+            RC(b200_batched_gemm(q, a + o_kr, a + o_sc, B * e->h, len, ctx, e->d, 1, dt, s));
+            RC(b200_scale_mask_softmax(a + o_sc, a + o_mask, a + o_sc, B, e->h, len, ctx, 1.0f / sqrtf((float)e->d), dt, s));
+            RC(b200_batched_gemm(a + o_sc, a + o_vr, a + o_pv, B * e->h, len, e->d, ctx, 0, dt, s));
+            RC(b200_transpose_remove_padding(a + o_pv, att, pad, Nt, B, len, e->h, e->d, dt, s));
+        }
+        RC(linear(att, w.o, x, H, e->h * e->d));
+        if (tp) RC(e->allreduce(x, (size_t)Nt * H, dt, s, e->allreduce_user));
+        RC(b200_fused_add_bias_residual_rmsnorm(res, x, nullptr, w.ffn_norm, Nt, H, e->cfg.rms_eps, dt, s));
+        RC(linear(x, w.gate_up, gu, 2 * e->I, H));
+        RC(b200_swiglu(gu, act, Nt, e->I, dt, s));
+        RC(linear(act, w.down, x, H, e->I));
+        if (tp) RC(e->allreduce(x, (size_t)Nt * H, dt, s, e->allreduce_user));
+        RC(b200_add_residual(res, x, Nt, H, dt, s));
+    }
+    // ---- last token of each sequence -> final norm -> LM head -> top-1 (llama.cpp:221-232, :305)
+    CU(cudaMemcpy2DAsync(e->hidden, (size_t)H * es, (const char*)x + (size_t)(len - 1) * H * es, (size_t)len * H * es,
+                         (size_t)H * es, (size_t)B, cudaMemcpyDeviceToDevice, s));
+    CU(cudaMemcpyAsync(e->partial, e->hidden, (size_t)B * H * es, cudaMemcpyDeviceToDevice, s));
+    RC(b200_rmsnorm(e->partial, nullptr, e->final_norm, B, H, e->cfg.rms_eps, dt, s));
+    RC(b200_linear(e->partial, e->lm_head, nullptr, e->logits, B, e->V, H, 1, dt, e->lin_ws, e->lin_ws_bytes, s));
+    RC(b200_argmax(e->logits, e->ids_next, B, e->V, dt, s));
+    CU(launch_k(set_ids_step_kernel, dim3(1), dim3(1024), 0, s, false, e->ids_cur, (const int*)e->ids_next, e->step_dev, B,
+                ctx + 1));
+    count_launch();
+    e->step = ctx;
+    e->prefill_launches = (int)(b200_launch_count() - launches0);
+    if (ids_out_host) {
+        CU(cudaMemcpyAsync(e->pinned_ids, e->ids_next, sizeof(int) * B, cudaMemcpyDeviceToHost, s));
+        CU(cudaStreamSynchronize(s));
+        memcpy(ids_out_host, e->pinned_ids, sizeof(int) * B);
+    }
+    return 0;
+}
+extern "C" int b200_engine_prefill_launches(const b200_engine* e) { return e ? e->prefill_launches : 0; }

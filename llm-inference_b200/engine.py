@@ -46,6 +46,8 @@ ENGINE_PROTOTYPES = {
     "b200_engine_v_cache": (_vp, [_vp]),
     "b200_engine_launches_per_step": (_i, [_vp]),
     "b200_engine_step_trace": (_i, [_vp, _vp, _i]),
+    "b200_engine_prefill": (_i, [_vp, _vp, _i, _vp]),
+    "b200_engine_prefill_launches": (_i, [_vp]),
     "b200_engine_weight_ptr": (_vp, [_vp, _i, _i]),
 }
 
@@ -187,6 +189,19 @@ class Engine:
             inp = ids_in.ctypes.data_as(C.c_void_p)
         self._ck(self.lib.b200_engine_decode_step_host(self.h, inp, out.ctypes.data_as(C.c_void_p)), "decode_step_host")
         return out
+
+    def prefill(self, ids, sync=True):
+        """numpy int32 [batch, len] prompt tokens -> numpy int32 [batch] first generated tokens
+        (b200_engine_prefill; sync=False skips the device->host read and returns None)"""
+        ids = np.ascontiguousarray(ids, dtype=np.int32).reshape(self.batch, -1)
+        out = np.empty(self.batch, np.int32) if sync else None
+        self._ck(self.lib.b200_engine_prefill(self.h, ids.ctypes.data_as(C.c_void_p), ids.shape[1],
+                                              out.ctypes.data_as(C.c_void_p) if sync else None), "prefill")
+        return out
+
+    @property
+    def prefill_launches(self):
+        return int(self.lib.b200_engine_prefill_launches(self.h))
 
     def _view(self, ptr, shape, torch_dtype):
         """zero-copy torch view of engine-owned device memory (tests / bench only)"""
