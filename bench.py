@@ -8,6 +8,9 @@ Workloads (BASELINE.json configs):
   cfg2 (default): LLaMA-2-7B fp16 random-init full model, batch 1 greedy decode at a 512-token
         context. N GPUs = N independent requests (weights replicated, no communication): weak.
   cfg4: batch 32 x KV length 4096, 32/N sequences per GPU (strong), no communication.
+  cfg5: LLaMA-2-70B-shaped GQA (64 q / 8 kv heads, 80 layers) fp16 decode, tensor parallel over the N GPUs
+        (strong scaling: heads / FFN columns split, allreduce after o_proj and down_proj only);
+        --comm p2p = the fused one-shot NVLink allreduce + residual kernel, --comm nccl = the NCCL baseline.
   cfg3: prefill, batch 4 x 2048 prompt tokens per GPU (metric prefill_tokens_per_s; a step = one prompt
         pass of the whole model: tcgen05 GEMMs + flash context attention; roofline = tensor).
 `value`  : tokens/s with everything resident in HBM, CUDA events on the engine's stream, max over ranks.
@@ -41,7 +44,10 @@ def parse():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=128)
     ap.add_argument("--warmup", type=int, default=8)
-    ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg3", "cfg4"])
+    ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg3", "cfg4", "cfg5"])
+    ap.add_argument("--comm", default="p2p", choices=["p2p", "nccl"],
+                    help="cfg5: fused one-shot NVLink allreduce (product) or ncclAllReduce + AddResidual (baseline)")
+    ap.add_argument("--batch", type=int, default=None)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--context", type=int, default=None)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -52,6 +58,9 @@ def workload(args):
     if args.workload == "cfg3":
         return dict(name="LLaMA-2-7B fp16 prefill: context attention + tcgen05 GEMMs, batch 4 x seq 2048 (configs[2])",
                     batch=4, context=args.context or 2048, scaling="weak")
+    if args.workload == "cfg5":
+        return dict(name="LLaMA-2-70B-shaped GQA (64 q / 8 kv heads) fp16 decode, tensor-parallel (configs[4])",
+                    batch=args.batch or 1, context=args.context or 512, scaling="strong")
     if args.workload == "cfg4":
         return dict(name="LLaMA-2-7B fp16 decode, batch 32 x KV 4096 (configs[3])", batch=32,
                     context=args.context or 4096, scaling="strong")
@@ -489,6 +498,115 @@ def bench_prefill(args, wl, rank, world, local_rank):
 
 
 # --------------------------------------------------------------------------------------------
+# cfg5: tensor-parallel decode of a 70B-shaped model
+# --------------------------------------------------------------------------------------------
+L70B = dict(num_layers=80, head_num=64, kv_head_num=8, head_size=128, inter_size=28672, vocab_size=32000)
+
+
+def bench_tp(args, wl, rank, world, local_rank):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from __graft_entry__ import load_package
+    pkg = load_package()
+    E, capi, sh = pkg.engine, pkg.capi, pkg.sharding
+    if not torch.cuda.is_available():
+        raise SystemExit("[b200][ERROR] bench.py needs a CUDA device: there is no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    B, ctx, K, W = wl["batch"], wl["context"], args.steps, max(args.warmup, 3)
+    cfg = dict(L70B)
+    if os.environ.get("B200_BENCH_LAYERS"):   # smoke runs on small boxes; the reported config is 80 layers
+        cfg["num_layers"] = int(os.environ["B200_BENCH_LAYERS"])
+    tp_size = world
+    if world == 1 and os.environ.get("B200_BENCH_TP_SIZE"):   # profiling aid: one rank's shard shapes on one GPU,
+        tp_size = int(os.environ["B200_BENCH_TP_SIZE"])        # partial sums simply not exchanged (ncu is 1-GPU only)
+    eng = E.Engine(B, ctx + 2 * (W + K) + 8, dtype=capi.F16, tp_size=tp_size, tp_rank=rank, **cfg)
+    eng.init_random(seed=1234 + rank, std=0.02)
+    eng.fill_kv_random(ctx, seed=7 + rank, amp=0.5)
+    eng.set_mode(fused=True, graph=True, persistent=False)
+    comm = None
+    if world > 1:
+        if args.comm == "p2p":
+            comm = sh.P2PComm(B * 8192 * 2)
+            eng.set_p2p(comm)
+        else:
+            eng.set_allreduce(sh.make_allreduce())
+    stream = torch.cuda.ExternalStream(eng.stream)
+    ids0 = np.full(B, 11, np.int32)   # every rank must feed the same tokens
+    eng.decode_step_host(ids0)
+    for _ in range(W - 1):
+        eng.decode_step()
+    barrier()
+    clocks = Clocks(local_rank)
+    if rank == 0:
+        clocks.start()
+    capi.lib().b200_launch_count_reset()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with torch.cuda.stream(stream):
+        ev0.record()
+        for _ in range(K):
+            eng.decode_step()
+        ev1.record()
+    barrier()
+    launches = int(capi.lib().b200_launch_count())
+    ms = ev0.elapsed_time(ev1)
+    clk = clocks.stop() if rank == 0 else None
+    ids = eng.decode_step_host(None)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(K):
+        ids = eng.decode_step_host(ids)
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    t = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max, e2e_ms_max = float(t[0]), float(t[1])
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        nl = cfg["num_layers"]
+        kv_bytes = B * nl * 2 * (8 // world if world <= 8 else 1) * 128 * 2 * (ctx + W + K // 2)
+        step_bytes = eng.weight_bytes - 32000 * 8192 * 2 + kv_bytes   # embedding table is a row gather
+        ach = step_bytes / (ms_max / K * 1e-3) / 1e9
+        out = {"metric": "decode_tokens_per_s", "value": round(B * K / (ms_max * 1e-3), 2), "unit": "tok/s",
+               "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": round(ms_max / K, 4), "higher_is_better": True,
+               "scaling": "strong", "vs_baseline": None, "dtype": "f16", "data": "synthetic",
+               "config": {"workload": wl["name"], "batch": B, "context": ctx, "layers": nl,
+                          "weights": f"random-init fp16, {eng.weight_bytes / 1e9:.1f} GB per GPU",
+                          "l2": "inputs larger than L2 (all weights streamed once per step)",
+                          "parallelism": f"tp{world}" + (f" ({'one-shot NVLink allreduce+residual kernel' if args.comm == 'p2p' else 'ncclAllReduce + AddResidual'}, 2 per layer)" if world > 1 else "")},
+               "e2e": {"value": round(B * K / (e2e_ms_max * 1e-3), 2), "unit": "tok/s", "h2d_bytes_per_step": 4 * B,
+                       "d2h_bytes_per_step": 4 * B, "ms_per_step": round(e2e_ms_max / K, 4)},
+               "gpu_launches": launches, "launches_per_step": eng.launches_per_step,
+               "roofline": {"bound": "hbm", "kernel": "gemv_stream_kernel (whole TP step per GPU)", "achieved": round(ach, 1),
+                            "peak": peak, "unit": "GB/s", "frac": round(ach / peak, 4), "traffic": None,
+                            "algorithmic_bytes_per_launch": int(step_bytes),
+                            "note": "per-GPU bytes of one step (this rank's weight shards + KV rows) / step time; "
+                                    "allreduce time is inside the step"},
+               "clocks": clk}
+        print(json.dumps(out))
+    eng.close()
+    if comm is not None:
+        comm.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+# --------------------------------------------------------------------------------------------
 # the B200 arm
 # --------------------------------------------------------------------------------------------
 def main():
@@ -504,6 +622,8 @@ def main():
         return
     if args.workload == "cfg3":
         return bench_prefill(args, wl, rank, world, local_rank)
+    if args.workload == "cfg5":
+        return bench_tp(args, wl, rank, world, local_rank)
 
     import numpy as np
     import torch

@@ -79,6 +79,22 @@ enum {
  * tensor-parallel group, enqueued on `stream`. NULL when tp_size == 1. */
 typedef int (*b200_allreduce_fn)(void* buf, size_t count, int dtype, void* stream, void* user);
 
+/* One-shot NVLink allreduce fused with the residual add (csrc/p2p_allreduce.cu): the product path of
+ * tensor-parallel decode; ncclAllReduce through the hook above is the baseline. One communicator per
+ * process (= per GPU): create -> exchange the 64-byte IPC handles of all ranks by any means (the
+ * Python plumbing uses torch.distributed.all_gather_object) -> connect. */
+typedef struct b200_p2p b200_p2p;
+size_t b200_p2p_handle_bytes(void);
+b200_p2p* b200_p2p_create(int world, int rank, size_t max_message_bytes);
+int b200_p2p_local_handle(b200_p2p* c, void* out_handle);
+int b200_p2p_connect(b200_p2p* c, const void* all_handles /* world x handle_bytes, rank-major */);
+/* hidden[count] += sum over ranks of partial[count] (same rounding points as allreduce + AddResidual) */
+int b200_p2p_allreduce_add(b200_p2p* c, const void* partial, void* hidden, size_t count, int dtype, void* stream);
+/* buf[count] <- sum over ranks of buf[count], in place (the batched / prefill paths) */
+int b200_p2p_allreduce(b200_p2p* c, void* buf, size_t count, int dtype, void* stream);
+size_t b200_p2p_max_message_bytes(const b200_p2p* c);
+void b200_p2p_destroy(b200_p2p* c);
+
 b200_engine* b200_engine_create(const b200_model_config* cfg, int batch);
 void b200_engine_destroy(b200_engine* e);
 const char* b200_engine_last_error(void);
@@ -88,6 +104,8 @@ size_t b200_engine_kv_bytes(const b200_engine* e);          /* K + V cache      
 size_t b200_engine_weight_elems(const b200_engine* e, int slot);
 int b200_engine_set_mode(b200_engine* e, unsigned flags);
 int b200_engine_set_allreduce(b200_engine* e, b200_allreduce_fn fn, void* user);
+/* use the fused one-shot NVLink allreduce + residual add instead of the hook (NULL = back to the hook) */
+int b200_engine_set_p2p(b200_engine* e, b200_p2p* comm);
 void* b200_engine_stream(b200_engine* e);
 
 /* weights: deterministic N(0, std^2) fill on the device (norm weights 1 + N(0,std^2)), or

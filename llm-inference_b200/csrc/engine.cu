@@ -75,6 +75,7 @@ struct b200_engine {
     unsigned mode = B200_ENGINE_FUSED | B200_ENGINE_GRAPH | B200_ENGINE_PERSISTENT;
     b200_allreduce_fn allreduce = nullptr;
     void* allreduce_user = nullptr;
+    b200_p2p* p2p = nullptr;   // fused one-shot NVLink allreduce + residual add (p2p_allreduce.cu)
     int step = 0;  // host mirror of *step_dev: tokens already in the cache
     std::map<int, cudaGraphExec_t> graphs;  // key: split-KV count
     b200::StepProgram* program = nullptr;   // persistent whole-step kernel (fp16, batch <= 4, tp 1)
@@ -347,6 +348,14 @@ extern "C" int b200_engine_set_allreduce(b200_engine* e, b200_allreduce_fn fn, v
     return B200_OK;
 }
 
+extern "C" int b200_engine_set_p2p(b200_engine* e, b200_p2p* comm) {
+    if (!e) return B200_EINVAL;
+    cudaStreamSynchronize(e->stream);
+    drop_graphs(e);
+    e->p2p = comm;
+    return B200_OK;
+}
+
 static int set_step(b200_engine* e, int n) {
     e->step = n;
     const int ref_step = n + 1;  // reference `step`: tokens in the cache including the new one
@@ -468,8 +477,21 @@ static int gemv(b200_engine* e, const void* x, const void* W, void* y, int N, in
 
 static int tp_allreduce_add(b200_engine* e) {
     // partial [B,H] -> sum over ranks -> hidden += partial
+    if (e->p2p) {
+        RC(b200_p2p_allreduce_add(e->p2p, e->partial, e->hidden, (size_t)e->batch * e->H, e->cfg.dtype, e->stream));
+        return 0;
+    }
     if (e->allreduce) RC(e->allreduce(e->partial, (size_t)e->batch * e->H, e->cfg.dtype, e->stream, e->allreduce_user));
     RC(b200_add_residual(e->partial, e->hidden, e->batch, e->H, e->cfg.dtype, e->stream));
+    return 0;
+}
+
+// in-place sum of buf over the tensor-parallel group: one-shot NVLink kernel when it fits, else the hook
+static int tp_sum(b200_engine* e, void* buf, size_t count) {
+    if (e->p2p && count * e->esz <= b200_p2p_max_message_bytes(e->p2p))
+        RC(b200_p2p_allreduce(e->p2p, buf, count, e->cfg.dtype, e->stream));
+    else if (e->allreduce)
+        RC(e->allreduce(buf, count, e->cfg.dtype, e->stream, e->allreduce_user));
     return 0;
 }
 
@@ -517,12 +539,12 @@ static int enqueue_step(b200_engine* e) {
             RC(b200_decode_attention_ex(e->qkv, kc, vc, e->attn, e->attn_ws, e->attn_ws_bytes, B, e->h, e->hk, e->d,
                                         e->cfg.max_seq_len, ref_step, e->step_dev, 1, dt, s));
             RC(linear(e->attn, w.o, e->hidden, H, e->h * e->d));
-            if (tp && e->allreduce) RC(e->allreduce(e->hidden, (size_t)B * H, dt, s, e->allreduce_user));
+            if (tp) RC(tp_sum(e, e->hidden, (size_t)B * H));
             RC(b200_fused_add_bias_residual_rmsnorm(e->residual, e->hidden, nullptr, w.ffn_norm, B, H, e->cfg.rms_eps, dt, s));
             RC(linear(e->hidden, w.gate_up, e->gate_up, 2 * e->I, H));
             RC(b200_swiglu(e->gate_up, e->act, B, e->I, dt, s));
             RC(linear(e->act, w.down, e->hidden, H, e->I));
-            if (tp && e->allreduce) RC(e->allreduce(e->hidden, (size_t)B * H, dt, s, e->allreduce_user));
+            if (tp) RC(tp_sum(e, e->hidden, (size_t)B * H));
             RC(b200_add_residual(e->residual, e->hidden, B, H, dt, s));
         }
     }
@@ -694,7 +716,7 @@ extern "C" int b200_engine_prefill(b200_engine* e, const int* ids_host, int len,
     auto linear = [&](const void* in, const void* W, void* out, int N, int K) {
         return b200_linear(in, W, nullptr, out, Nt, N, K, 1, dt, lws, lin_ws + 256, s);
     };
-    const bool tp = e->cfg.tp_size > 1 && e->allreduce;
+    const bool tp = e->cfg.tp_size > 1 && (e->allreduce || e->p2p);
     RC(b200_cal_padding_offset(pad, cum, lens, B, len, s));
     if (!flash) RC(b200_build_causal_mask(a + o_mask, lens, ctxs, B, len, ctx, 1, dt, s));
     RC(b200_embedding(ids, e->embed, x, Nt, H, e->V, dt, s));
@@ -719,12 +741,12 @@ extern "C" int b200_engine_prefill(b200_engine* e, const int* ids_host, int len,
             RC(b200_transpose_remove_padding(a + o_pv, att, pad, Nt, B, len, e->h, e->d, dt, s));
         }
         RC(linear(att, w.o, x, H, e->h * e->d));
-        if (tp) RC(e->allreduce(x, (size_t)Nt * H, dt, s, e->allreduce_user));
+        if (tp) RC(tp_sum(e, x, (size_t)Nt * H));
         RC(b200_fused_add_bias_residual_rmsnorm(res, x, nullptr, w.ffn_norm, Nt, H, e->cfg.rms_eps, dt, s));
         RC(linear(x, w.gate_up, gu, 2 * e->I, H));
         RC(b200_swiglu(gu, act, Nt, e->I, dt, s));
         RC(linear(act, w.down, x, H, e->I));
-        if (tp) RC(e->allreduce(x, (size_t)Nt * H, dt, s, e->allreduce_user));
+        if (tp) RC(tp_sum(e, x, (size_t)Nt * H));
         RC(b200_add_residual(res, x, Nt, H, dt, s));
     }
     // ---- last token of each sequence -> final norm -> LM head -> top-1 (llama.cpp:221-232, :305)

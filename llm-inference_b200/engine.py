@@ -47,6 +47,15 @@ ENGINE_PROTOTYPES = {
     "b200_engine_launches_per_step": (_i, [_vp]),
     "b200_engine_step_trace": (_i, [_vp, _vp, _i]),
     "b200_engine_prefill": (_i, [_vp, _vp, _i, _vp]),
+    "b200_engine_set_p2p": (_i, [_vp, _vp]),
+    "b200_p2p_handle_bytes": (C.c_size_t, []),
+    "b200_p2p_create": (_vp, [_i, _i, C.c_size_t]),
+    "b200_p2p_local_handle": (_i, [_vp, _vp]),
+    "b200_p2p_connect": (_i, [_vp, _vp]),
+    "b200_p2p_allreduce_add": (_i, [_vp, _vp, _vp, C.c_size_t, _i, _vp]),
+    "b200_p2p_allreduce": (_i, [_vp, _vp, C.c_size_t, _i, _vp]),
+    "b200_p2p_max_message_bytes": (C.c_size_t, [_vp]),
+    "b200_p2p_destroy": (None, [_vp]),
     "b200_engine_prefill_launches": (_i, [_vp]),
     "b200_engine_weight_ptr": (_vp, [_vp, _i, _i]),
 }
@@ -144,6 +153,11 @@ class Engine:
         an explicit set_mode() selects the multi-kernel paths unless persistent=True."""
         flags = (MODE_FUSED if fused else 0) | (MODE_GRAPH if graph else 0) | (MODE_PERSISTENT if persistent else 0)
         self._ck(self.lib.b200_engine_set_mode(self.h, flags), "set_mode")
+
+    def set_p2p(self, comm):
+        """comm: sharding.P2PComm (or None): the fused one-shot NVLink allreduce + residual add"""
+        self._p2p = comm
+        self._ck(self.lib.b200_engine_set_p2p(self.h, comm.handle if comm is not None else None), "set_p2p")
 
     def set_allreduce(self, pyfunc):
         """pyfunc(buf_ptr:int, count:int, dtype:int, stream_ptr:int) -> int"""

@@ -121,3 +121,57 @@ def make_allreduce(group=None):
         return 0
 
     return allreduce
+
+
+class P2PComm:
+    """One-shot NVLink allreduce communicator (include/b200_engine.h b200_p2p_*, csrc/p2p_allreduce.cu):
+    one per process / GPU. The 64-byte cudaIpc handles travel through torch.distributed
+    (all_gather_object); after that no library is involved in the collective — the kernel pushes
+    partials into the peers' mapped buffers over NVLink and sums locally."""
+
+    def __init__(self, max_message_bytes, group=None):
+        import ctypes as C
+        import torch.distributed as dist
+        from . import engine as E
+        self.lib = E._lib()
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.handle = self.lib.b200_p2p_create(self.world, self.rank, int(max_message_bytes))
+        if not self.handle:
+            raise RuntimeError("[b200][ERROR] b200_p2p_create failed")
+        n = int(self.lib.b200_p2p_handle_bytes())
+        mine = C.create_string_buffer(n)
+        rc = self.lib.b200_p2p_local_handle(self.handle, mine)
+        if rc != 0:
+            raise RuntimeError(f"[b200][ERROR] b200_p2p_local_handle: {rc}")
+        gathered = [None] * self.world
+        dist.all_gather_object(gathered, bytes(mine.raw), group=group)
+        rc = self.lib.b200_p2p_connect(self.handle, b"".join(gathered))
+        if rc != 0:
+            raise RuntimeError(f"[b200][ERROR] b200_p2p_connect: CUDA error {rc} (peer access over cudaIpc unavailable?)")
+        dist.barrier(group=group)
+
+    def allreduce_add(self, partial, hidden):
+        """hidden += sum over ranks of partial (torch CUDA tensors, same dtype/shape), on torch's current stream"""
+        import ctypes as C
+        import torch
+        from . import capi
+        dt = capi.F16 if partial.dtype == torch.float16 else capi.F32
+        rc = self.lib.b200_p2p_allreduce_add(self.handle, C.c_void_p(partial.data_ptr()), C.c_void_p(hidden.data_ptr()),
+                                             partial.numel(), dt, C.c_void_p(torch.cuda.current_stream().cuda_stream))
+        if rc != 0:
+            raise RuntimeError(f"[b200][ERROR] b200_p2p_allreduce_add: {rc}")
+
+    def allreduce(self, buf):
+        import ctypes as C
+        import torch
+        from . import capi
+        dt = capi.F16 if buf.dtype == torch.float16 else capi.F32
+        rc = self.lib.b200_p2p_allreduce(self.handle, C.c_void_p(buf.data_ptr()), buf.numel(), dt,
+                                         C.c_void_p(torch.cuda.current_stream().cuda_stream))
+        if rc != 0:
+            raise RuntimeError(f"[b200][ERROR] b200_p2p_allreduce: {rc}")
+
+    def close(self):
+        if self.handle:
+            self.lib.b200_p2p_destroy(self.handle)
+            self.handle = None

@@ -28,7 +28,7 @@ def free_port():
         return s.getsockname()[1]
 
 
-def _worker(rank, world, port, kind, fused, out_dir):
+def _worker(rank, world, port, kind, fused, out_dir, comm="hook"):
     sys.path.insert(0, ROOT)
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import torch.distributed as dist
@@ -71,29 +71,102 @@ def _worker(rank, world, port, kind, fused, out_dir):
             assert count == B * CFG["head_num"] * CFG["head_size"]
             return inner(ptr, count, dtype, stream)
 
-        eng.set_allreduce(hook)
+        p2p = None
+        if comm == "p2p":   # the fused one-shot NVLink allreduce + residual add (csrc/p2p_allreduce.cu)
+            p2p = sh.P2PComm(B * CFG["head_num"] * CFG["head_size"] * 4)
+            eng.set_p2p(p2p)
+        else:
+            eng.set_allreduce(hook)
         ids = np.array([7, 1000], np.int32)
         logits, picked = [], []
         for _ in range(STEPS):
             ids = eng.decode_step_host(ids)
             logits.append(eng.logits().float().cpu().numpy().copy())
             picked.append(ids.copy())
-        if not multi:
+        if not multi and comm == "hook":
             assert n_calls[0] == STEPS * CFG["num_layers"] * 2, "two allreduces per layer per step"
         kc, vc = eng.kv_caches()
         np.savez(os.path.join(out_dir, f"rank{rank}.npz"), logits=np.stack(logits), ids=np.stack(picked),
                  k=kc.float().cpu().numpy(), v=vc.float().cpu().numpy())
         eng.close()
+        if p2p is not None:
+            p2p.close()
     finally:
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("fused", [True, False])
-@pytest.mark.parametrize("kind", ["fp32", "fp16"])
-def test_engine_tensor_parallel_two_ranks_vs_unsharded_oracle(tmp_path, kind, fused):
+def _p2p_unit_worker(rank, world, port, out_dir):
+    """b200_p2p_allreduce_add / b200_p2p_allreduce against a torch sum of the same partials, many
+    back-to-back calls (buffer parity, epochs), eagerly and replayed from a CUDA graph"""
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import torch.distributed as dist
+    pkg = load_package()
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world,
+                            device_id=torch.device("cuda", rank))
+    try:
+        comm = pkg.sharding.P2PComm(32 * 8192 * 2)
+        ok = True
+        for dt, n in ((torch.float16, 8192), (torch.float16, 32 * 8192), (torch.float32, 4096), (torch.float16, 8)):
+            for it in range(6):
+                g = [torch.Generator(device="cuda").manual_seed(100 * it + r) for r in range(world)]
+                parts = [(torch.rand(n, device="cuda", generator=g[r]) - 0.5).to(dt) for r in range(world)]
+                hidden = torch.full((n,), 0.25, dtype=dt, device="cuda")
+                want = hidden.float()
+                acc = torch.zeros(n, dtype=torch.float32, device="cuda")
+                for r in range(world):
+                    acc += parts[r].float()
+                want_sum = acc.to(dt)
+                want = (want + want_sum.float()).to(dt)
+                comm.allreduce_add(parts[rank], hidden)
+                buf = parts[rank].clone()
+                comm.allreduce(buf)
+                torch.cuda.synchronize()
+                ok &= bool(torch.equal(hidden, want)) and bool(torch.equal(buf, want_sum))
+        # CUDA-graph replay: the call counters live on the device
+        n = 8192
+        part = torch.full((n,), float(rank + 1), dtype=torch.float16, device="cuda")
+        hidden = torch.zeros(n, dtype=torch.float16, device="cuda")
+        side = torch.cuda.Stream()
+        with torch.cuda.stream(side):
+            comm.allreduce_add(part, hidden)
+            torch.cuda.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph, stream=side):
+                comm.allreduce_add(part, hidden)
+                comm.allreduce_add(part, hidden)
+            for _ in range(5):
+                graph.replay()
+        torch.cuda.synchronize()
+        total = sum(range(1, world + 1))
+        ok &= bool(torch.all(hidden == 11 * total))
+        open(os.path.join(out_dir, f"p2p{rank}.txt"), "w").write("ok" if ok else "mismatch")
+        dist.barrier()
+        comm.close()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_p2p_oneshot_allreduce_two_gpus(tmp_path):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs with peer access (verified with gpurun --gpus 2, profiles/r01_tp2_*.json)")
     import torch.multiprocessing as mp
     world = 2
-    mp.spawn(_worker, args=(world, free_port(), kind, fused, str(tmp_path)), nprocs=world, join=True)
+    mp.spawn(_p2p_unit_worker, args=(world, free_port(), str(tmp_path)), nprocs=world, join=True)
+    for r in range(world):
+        assert open(os.path.join(tmp_path, f"p2p{r}.txt")).read() == "ok"
+
+
+@pytest.mark.parametrize("comm", ["hook", "p2p"])
+@pytest.mark.parametrize("fused", [True, False])
+@pytest.mark.parametrize("kind", ["fp32", "fp16"])
+def test_engine_tensor_parallel_two_ranks_vs_unsharded_oracle(tmp_path, kind, fused, comm):
+    import torch.multiprocessing as mp
+    world = 2
+    if comm == "p2p" and torch.cuda.device_count() < world:
+        pytest.skip("the one-shot NVLink allreduce needs one GPU per rank")
+    mp.spawn(_worker, args=(world, free_port(), kind, fused, str(tmp_path), comm), nprocs=world, join=True)
     full = make_weights(CFG, kind, 33)
     om = omodel.OracleModel(full, CFG, B, MAX_SEQ, kind)
     rng = np.random.default_rng(5)
