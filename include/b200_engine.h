@@ -90,6 +90,10 @@ int b200_p2p_local_handle(b200_p2p* c, void* out_handle);
 int b200_p2p_connect(b200_p2p* c, const void* all_handles /* world x handle_bytes, rank-major */);
 /* hidden[count] += sum over ranks of partial[count] (same rounding points as allreduce + AddResidual) */
 int b200_p2p_allreduce_add(b200_p2p* c, const void* partial, void* hidden, size_t count, int dtype, void* stream);
+/* fused form: b200_gemv_fused with args->p2p = comm (fp16, no epilogue mode, N % 4 == 0) pushes each
+ * finished row pair straight into the peers' receive buffers from the GEMV epilogue (y is not
+ * written); this call then waits for the lines of all ranks, sums and adds: hidden[count] += sum. */
+int b200_p2p_reduce_add(b200_p2p* c, void* hidden, size_t count, int dtype, void* stream);
 /* buf[count] <- sum over ranks of buf[count], in place (the batched / prefill paths) */
 int b200_p2p_allreduce(b200_p2p* c, void* buf, size_t count, int dtype, void* stream);
 size_t b200_p2p_max_message_bytes(const b200_p2p* c);

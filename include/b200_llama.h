@@ -170,6 +170,9 @@ typedef struct b200_gemv_args {
     const int* step_dev; /* optional DEVICE int overriding `step` (CUDA-graph replay) */
     const float* rope_den; /* optional DEVICE table [rotary_dim/2] of base^(2i/rotary_dim) from     */
                            /* b200_rope_table(); NULL = computed in the kernel                   */
+    void* p2p; /* optional b200_p2p* (b200_engine.h): tensor-parallel row-split linear, fp16, no epilogue */
+               /* mode: the partial outputs go straight to every rank's receive buffer over NVLink     */
+               /* (16-byte lines, payload + call tag) instead of y; b200_p2p_reduce_add() finishes     */
 } b200_gemv_args;
 int b200_gemv_fused(const b200_gemv_args* args, int dtype, void* stream);
 /* fills den[i] = base^(2i/rotary_dim), i < rotary_dim/2 (correctly rounded; see common.cuh) */

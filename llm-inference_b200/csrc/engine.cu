@@ -443,8 +443,9 @@ int attn_pick_splits_public(int batch, int kv_head_num, int step);  // decode_at
 }
 
 static int gemv(b200_engine* e, const void* x, const void* W, void* y, int N, int K, unsigned flags,
-                const void* gamma = nullptr, int layer = -1) {
+                const void* gamma = nullptr, int layer = -1, bool push_p2p = false) {
     b200_gemv_args a{};
+    if (push_p2p) a.p2p = e->p2p;
     a.x = x; a.W = W; a.y = y; a.gamma = gamma; a.eps = e->cfg.rms_eps;
     a.n_tokens = e->batch; a.N = N; a.K = K; a.flags = flags;
     if (flags & B200_GEMV_ROPE_KV) {
@@ -516,8 +517,12 @@ static int enqueue_step(b200_engine* e) {
             RC(gemv(e, e->hidden, w.qkv, e->qkv, e->qkv_n, H, B200_GEMV_NORM | B200_GEMV_ROPE_KV, w.attn_norm, l));
             RC(b200_decode_attention_ex(e->qkv, kc, vc, e->attn, e->attn_ws, e->attn_ws_bytes, B, e->h, e->hk,
                                         e->d, e->cfg.max_seq_len, ref_step, e->step_dev, 0, dt, s));
+            const bool fused_ar = tp && e->p2p && dt == B200_F16 && (H & 3) == 0 && B <= B200_GEMV_MAX_TOKENS;
             if (!tp) {
                 RC(gemv(e, e->attn, w.o, e->hidden, H, e->h * e->d, B200_GEMV_RESIDUAL));
+            } else if (fused_ar) {   // GEMV epilogue pushes its rows to the peers; the reduce kernel sums + adds
+                RC(gemv(e, e->attn, w.o, e->partial, H, e->h * e->d, 0, nullptr, -1, true));
+                RC(b200_p2p_reduce_add(e->p2p, e->hidden, (size_t)B * H, dt, s));
             } else {
                 RC(gemv(e, e->attn, w.o, e->partial, H, e->h * e->d, 0));
                 RC(tp_allreduce_add(e));
@@ -526,6 +531,9 @@ static int enqueue_step(b200_engine* e) {
                     B200_GEMV_NORM | B200_GEMV_NORM_GFIRST | B200_GEMV_SWIGLU, w.ffn_norm));
             if (!tp) {
                 RC(gemv(e, e->act, w.down, e->hidden, H, e->I, B200_GEMV_RESIDUAL));
+            } else if (fused_ar) {
+                RC(gemv(e, e->act, w.down, e->partial, H, e->I, 0, nullptr, -1, true));
+                RC(b200_p2p_reduce_add(e->p2p, e->hidden, (size_t)B * H, dt, s));
             } else {
                 RC(gemv(e, e->act, w.down, e->partial, H, e->I, 0));
                 RC(tp_allreduce_add(e));

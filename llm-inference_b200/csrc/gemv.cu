@@ -18,6 +18,7 @@
 //    x load waits for the predecessor.
 #include "common.cuh"
 #include "launch_count.h"
+#include "p2p_internal.h"
 
 namespace b200 {
 
@@ -50,6 +51,8 @@ struct GemvParams {
     float rotary_base;
     const int* step_dev;
     const float* rope_den;
+    P2PWire wire;   // world > 0 (plain mode, fp16): outputs are pushed to the peers instead of written to y
+    int token0;     // index of this launch's first token in the message (launches tiled over tokens)
 };
 
 // unit -> (row_a, row_b); row_b < 0 means "no second row"
@@ -147,6 +150,9 @@ __global__ void __launch_bounds__(kGemvThreads, 1) gemv_stream_kernel(const Gemv
     // ========================= consumers =========================
     // x (and the optional RMSNorm prologue) depend on the predecessor kernel.
     pdl_wait();
+    unsigned p2p_call = 0;   // number of the allreduce call these outputs belong to (p2p_allreduce.cu)
+    if (MODE == kModePlain && p.wire.world > 0)
+        p2p_call = *reinterpret_cast<volatile unsigned*>(p.wire.peer[p.wire.rank]) + 1u;
     {
         const int pk = p.K / E;  // packets per token
         const T* xg = reinterpret_cast<const T*>(p.x);
@@ -325,6 +331,22 @@ __global__ void __launch_bounds__(kGemvThreads, 1) gemv_stream_kernel(const Gemv
                             av += DT<T>::to_f(bias[ra]);
                             if (rb >= 0) bv += DT<T>::to_f(bias[rb]);
                         }
+                        if (MODE == kModePlain && sizeof(T) == 2 && p.wire.world > 0) {
+                            // tensor-parallel row-split linear: element pair (b, ra..ra+1) is half of a 16-byte
+                            // low-latency line {data, call, data, call} in slot `rank` of EVERY rank's receive
+                            // buffer (p2p_allreduce.cu); the 8-byte store is atomic, the tag makes it valid
+                            const unsigned call = p2p_call;
+                            const size_t e = (size_t)(b + p.token0) * p.N + ra;
+                            const size_t off = kP2PHeader + (size_t)(call & 1u) * p.wire.world * p.wire.slot_bytes +
+                                               (size_t)p.wire.rank * p.wire.slot_bytes + (e >> 2) * 16 + ((e >> 1) & 1) * 8;
+                            const __half2 hv = __floats2half2_rn(av, bv);
+                            const unsigned data = *reinterpret_cast<const unsigned*>(&hv);
+                            for (int r = 0; r < p.wire.world; ++r)
+                                asm volatile("st.volatile.global.v2.u32 [%0], {%1,%2};" ::"l"(p.wire.peer[r] + off), "r"(data),
+                                             "r"(call)
+                                             : "memory");
+                            continue;
+                        }
                         y[(size_t)b * p.N + ra] = DT<T>::from_f(av);
                         if (rb >= 0) y[(size_t)b * p.N + rb] = DT<T>::from_f(bv);
                     }
@@ -394,6 +416,7 @@ static int gemv_dispatch_nb(GemvParams p, int n_tokens, cudaStream_t s) {
             GemvParams q = p;
             q.x = (const char*)p.x + (size_t)t0 * p.K * esz;
             q.y = (char*)p.y + (size_t)t0 * y_stride * esz;
+            q.token0 = p.token0 + t0;
             if (MODE == kModeRopeKV) {
                 const size_t per_seq = (size_t)p.kv_head_num * p.max_seq_len * p.head_size * esz;
                 q.k_cache = (char*)p.k_cache + (size_t)t0 * per_seq;
@@ -436,6 +459,12 @@ static int gemv_fused_impl(const b200_gemv_args* a, cudaStream_t s) {
     p.head_num = a->head_num; p.kv_head_num = a->kv_head_num; p.head_size = a->head_size;
     p.max_seq_len = a->max_seq_len; p.step = a->step; p.rotary_dim = a->rotary_dim;
     p.rotary_base = a->rotary_base; p.step_dev = a->step_dev; p.rope_den = a->rope_den;
+    if (a->p2p) {
+        const b200_p2p* c = reinterpret_cast<const b200_p2p*>(a->p2p);
+        B200_RETURN_IF(epi != 0 || sizeof(T) != 2 || (a->N & 3) || a->bias, B200_EUNSUPPORTED);
+        B200_RETURN_IF((size_t)a->n_tokens * a->N * 4 > c->slot_bytes || (!c->connected && c->world > 1), B200_EINVAL);
+        p.wire = p2p_wire(c);
+    }
     if (epi == B200_GEMV_SWIGLU) {
         p.units = a->N;
         return gemv_dispatch_nb<T, kModeSwiglu>(p, a->n_tokens, s);

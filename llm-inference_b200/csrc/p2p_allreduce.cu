@@ -24,18 +24,10 @@
 #include "b200_engine.h"
 #include "common.cuh"
 #include "launch_count.h"
+#include "p2p_internal.h"
 
 namespace b200 {
-constexpr int kP2PThreads = 256;
-constexpr int kP2PMaxCtas = 64;
-constexpr int kP2PMaxWorld = 8;
-constexpr size_t kP2PHeader = 256;   // [0] call counter, [1] ticket
-
-struct P2PParams {
-    unsigned char* peer[kP2PMaxWorld];   // base of every rank's allocation as mapped in this process
-    int world, rank;
-    size_t slot_bytes;                   // capacity of one receive slot (lines)
-};
+using P2PParams = P2PWire;
 
 __device__ __forceinline__ void st16_volatile(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
     asm volatile("st.volatile.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
@@ -74,7 +66,8 @@ template <> struct Line<__half> {
 // ADD: hidden[i] <- round(hidden[i] + round(sum_r partial_r[i])): the two roundings of "allreduce, then
 // launchAddResidual" (oracle/model.py _ffn) are kept so TP results match the unsharded oracle.
 // !ADD: plain in-place allreduce, hidden (== partial) <- round(sum).
-template <typename T, bool ADD>
+// !PUSH: the lines of this call were already pushed by the producing GEMV's epilogue (gemv.cu, B200_GEMV_P2P).
+template <typename T, bool ADD, bool PUSH>
 __global__ void __launch_bounds__(kP2PThreads)
 p2p_allreduce_add_kernel(const P2PParams p, const T* partial, T* hidden, size_t lines) {
     const int me = p.rank;
@@ -85,7 +78,7 @@ p2p_allreduce_add_kernel(const P2PParams p, const T* partial, T* hidden, size_t 
     const size_t buf_off = kP2PHeader + (size_t)(call & 1u) * p.world * p.slot_bytes;
     const size_t tid = (size_t)blockIdx.x * kP2PThreads + threadIdx.x, nthr = (size_t)gridDim.x * kP2PThreads;
     // ---- push: line i of this rank's partial into slot `me` of every rank (its own included)
-    for (size_t i = tid; i < lines; i += nthr) {
+    for (size_t i = tid; PUSH && i < lines; i += nthr) {
         const uint2 v = ld8(reinterpret_cast<const unsigned char*>(partial) + i * 8);
 #pragma unroll 1
         for (int r = 0; r < p.world; ++r)
@@ -139,15 +132,6 @@ p2p_allreduce_add_kernel(const P2PParams p, const T* partial, T* hidden, size_t 
 }  // namespace b200
 
 using namespace b200;
-
-struct b200_p2p {
-    int world = 0, rank = 0;
-    size_t slot_bytes = 0, total = 0;
-    unsigned char* local = nullptr;
-    std::vector<unsigned char*> peers;   // mapped bases (peers[rank] == local)
-    std::vector<bool> opened;
-    bool connected = false;
-};
 
 extern "C" size_t b200_p2p_handle_bytes(void) { return sizeof(cudaIpcMemHandle_t); }
 
@@ -206,7 +190,8 @@ extern "C" void b200_p2p_destroy(b200_p2p* c) {
 }
 
 /* hidden[count] += sum over ranks of partial[count]; every rank must make the same sequence of calls */
-static int p2p_launch(b200_p2p* c, const void* partial, void* hidden, size_t count, int dtype, void* stream, bool add) {
+static int p2p_launch(b200_p2p* c, const void* partial, void* hidden, size_t count, int dtype, void* stream, bool add,
+                      bool push = true) {
     if (!c || !partial || !hidden) return B200_EINVAL;
     if (!c->connected && c->world > 1) return B200_EINVAL;
     const size_t es = dtype == B200_F16 ? 2 : 4;
@@ -218,20 +203,18 @@ static int p2p_launch(b200_p2p* c, const void* partial, void* hidden, size_t cou
     const size_t lines = bytes / 8;
     size_t ctas = (lines + kP2PThreads - 1) / kP2PThreads;
     if (ctas > (size_t)kP2PMaxCtas) ctas = kP2PMaxCtas;
-    P2PParams p{};
-    for (int r = 0; r < c->world; ++r) p.peer[r] = c->peers[r];
-    p.world = c->world;
-    p.rank = c->rank;
-    p.slot_bytes = c->slot_bytes;
+    const P2PParams p = p2p_wire(c);
     cudaError_t e;
     const dim3 g((unsigned)ctas), b(kP2PThreads);
     cudaStream_t s = (cudaStream_t)stream;
     if (dtype == B200_F16) {
-        if (add) e = launch_k(p2p_allreduce_add_kernel<__half, true>, g, b, 0, s, true, p, (const __half*)partial, (__half*)hidden, lines);
-        else e = launch_k(p2p_allreduce_add_kernel<__half, false>, g, b, 0, s, true, p, (const __half*)partial, (__half*)hidden, lines);
+        if (!push) e = launch_k(p2p_allreduce_add_kernel<__half, true, false>, g, b, 0, s, true, p, (const __half*)partial, (__half*)hidden, lines);
+        else if (add) e = launch_k(p2p_allreduce_add_kernel<__half, true, true>, g, b, 0, s, true, p, (const __half*)partial, (__half*)hidden, lines);
+        else e = launch_k(p2p_allreduce_add_kernel<__half, false, true>, g, b, 0, s, true, p, (const __half*)partial, (__half*)hidden, lines);
     } else {
-        if (add) e = launch_k(p2p_allreduce_add_kernel<float, true>, g, b, 0, s, true, p, (const float*)partial, (float*)hidden, lines);
-        else e = launch_k(p2p_allreduce_add_kernel<float, false>, g, b, 0, s, true, p, (const float*)partial, (float*)hidden, lines);
+        if (!push) return B200_EUNSUPPORTED;
+        if (add) e = launch_k(p2p_allreduce_add_kernel<float, true, true>, g, b, 0, s, true, p, (const float*)partial, (float*)hidden, lines);
+        else e = launch_k(p2p_allreduce_add_kernel<float, false, true>, g, b, 0, s, true, p, (const float*)partial, (float*)hidden, lines);
     }
     count_launch();
     return (int)e;
@@ -239,6 +222,11 @@ static int p2p_launch(b200_p2p* c, const void* partial, void* hidden, size_t cou
 extern "C" int b200_p2p_allreduce_add(b200_p2p* c, const void* partial, void* hidden, size_t count, int dtype,
                                       void* stream) {
     return p2p_launch(c, partial, hidden, count, dtype, stream, true);
+}
+/* second half of the fused GEMV + allreduce: the partials of this call were pushed by b200_gemv_fused with
+ * args->p2p set (fp16); hidden[count] += sum over ranks */
+extern "C" int b200_p2p_reduce_add(b200_p2p* c, void* hidden, size_t count, int dtype, void* stream) {
+    return p2p_launch(c, hidden, hidden, count, dtype, stream, true, false);
 }
 /* buf[count] <- sum over ranks of buf[count], in place */
 extern "C" int b200_p2p_allreduce(b200_p2p* c, void* buf, size_t count, int dtype, void* stream) {

@@ -54,6 +54,7 @@ ENGINE_PROTOTYPES = {
     "b200_p2p_connect": (_i, [_vp, _vp]),
     "b200_p2p_allreduce_add": (_i, [_vp, _vp, _vp, C.c_size_t, _i, _vp]),
     "b200_p2p_allreduce": (_i, [_vp, _vp, C.c_size_t, _i, _vp]),
+    "b200_p2p_reduce_add": (_i, [_vp, _vp, C.c_size_t, _i, _vp]),
     "b200_p2p_max_message_bytes": (C.c_size_t, [_vp]),
     "b200_p2p_destroy": (None, [_vp]),
     "b200_engine_prefill_launches": (_i, [_vp]),
