@@ -143,6 +143,20 @@ int b200_engine_decode_step_host(b200_engine* e, const int* ids_in_host, int* id
 int b200_engine_prefill(b200_engine* e, const int* ids_host, int len, int* ids_out_host);
 int b200_engine_prefill_launches(const b200_engine* e);   /* kernel launches of the last prefill */
 
+/* The generation loop of Llama<T>::Response (llama.cpp:363-448) without the tokenizer: prefill the
+ * prompt ([batch, prompt_len] host ids), then decode until every sequence has produced eos_id or
+ * max_new_tokens tokens are out. out_ids [batch, max_new_tokens] (host; padded with eos_id),
+ * n_generated [batch] (host, may be NULL). Returns the number of decode steps run, < 0 on error. */
+int b200_engine_generate(b200_engine* e, const int* prompt_ids_host, int prompt_len, int max_new_tokens,
+                         int eos_id, int* out_ids, int* n_generated);
+
+/* Load the reference's weight directory (LlamaWeight<T>::loadWeights llama_weights.cc:41-53,
+ * LlamaLayerWeight<T>::loadWeights layer_weights.cc:48-66): raw fp32 files model.norm.weight.bin,
+ * lm_head.weight.bin, model.embed_tokens.weight.bin, model.layers.<l>.{input_layernorm,
+ * post_attention_layernorm,self_attn.qkv,self_attn.o_proj,mlp.gate_up_proj,mlp.down_proj}.weight.bin,
+ * converted to the engine dtype; with tp_size > 1 each rank keeps its head / FFN-column shard. */
+int b200_engine_load_weights(b200_engine* e, const char* dir);
+
 /* device pointers into the engine (valid until destroy): logits [batch, vocab], ids [batch],
  * hidden [batch, H], caches; for parity tests and the bench. */
 void* b200_engine_logits(b200_engine* e);

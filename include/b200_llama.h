@@ -142,6 +142,13 @@ size_t b200_linear_workspace_bytes(int n_tokens, int N, int K, int trans_b, int 
 int b200_linear(const void* x, const void* W, const void* bias, void* y, int n_tokens, int N, int K,
                 int trans_b, int dtype, void* workspace, size_t workspace_bytes, void* stream);
 
+/* gate_up GEMM + SwiGLU in one launch (ffn.cpp:72-80): out[n_tokens, inter] = silu(x Wg^T) * (x Wu^T),
+ * W = [2*inter, K], gate rows first. tcgen05 GEMM with the activation as its epilogue (same fp16
+ * rounding points as b200_linear followed by b200_swiglu). B200_EUNSUPPORTED outside fp16 prefill
+ * shapes (n_tokens > 256, inter % 128 == 0): run b200_linear + b200_swiglu then. */
+int b200_linear_swiglu(const void* x, const void* W, void* out, int n_tokens, int inter, int K,
+                       int dtype, void* stream);
+
 /* Fused decode-time linears (engine path; the unfused reference sequence they replace is cited).
  * All take W [N, K] row-major, n_tokens <= B200_GEMV_MAX_TOKENS.
  *

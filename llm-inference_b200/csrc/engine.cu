@@ -6,6 +6,7 @@
 // CUDA-graph replay (one graph per split-KV geometry; `step` lives in device memory so the same
 // graph serves every position of its bucket).
 #include <algorithm>
+#include <cstdio>
 #include <map>
 #include <string>
 #include <vector>
@@ -751,8 +752,13 @@ extern "C" int b200_engine_prefill(b200_engine* e, const int* ids_host, int len,
         RC(linear(att, w.o, x, H, e->h * e->d));
         if (tp) RC(tp_sum(e, x, (size_t)Nt * H));
         RC(b200_fused_add_bias_residual_rmsnorm(res, x, nullptr, w.ffn_norm, Nt, H, e->cfg.rms_eps, dt, s));
-        RC(linear(x, w.gate_up, gu, 2 * e->I, H));
-        RC(b200_swiglu(gu, act, Nt, e->I, dt, s));
+        int rc_glu = b200_linear_swiglu(x, w.gate_up, act, Nt, e->I, H, dt, s);   // GEMM with SwiGLU epilogue
+        if (rc_glu == B200_EUNSUPPORTED) {
+            RC(linear(x, w.gate_up, gu, 2 * e->I, H));
+            RC(b200_swiglu(gu, act, Nt, e->I, dt, s));
+        } else if (rc_glu != 0) {
+            return fail("b200_linear_swiglu failed", rc_glu);
+        }
         RC(linear(act, w.down, x, H, e->I));
         if (tp) RC(tp_sum(e, x, (size_t)Nt * H));
         RC(b200_add_residual(res, x, Nt, H, dt, s));
@@ -777,3 +783,133 @@ extern "C" int b200_engine_prefill(b200_engine* e, const int* ids_host, int len,
     return 0;
 }
 extern "C" int b200_engine_prefill_launches(const b200_engine* e) { return e ? e->prefill_launches : 0; }
+
+
+// ------------------------------------------------------------------------------------------
+// weight files: the reference's on-disk format (LlamaWeight<T>::loadWeights, llama_weights.cc:41-53;
+// LlamaLayerWeight<T>::loadWeights, layer_weights.cc:48-66): one raw little-endian **fp32** file per
+// tensor (loadWeightFromBin<T, float>, weight_utils.cu:91-181 converts to T), names
+//   <dir>/model.norm.weight.bin  <dir>/lm_head.weight.bin  <dir>/model.embed_tokens.weight.bin
+//   <dir>/model.layers.<l>.{input_layernorm,post_attention_layernorm}.weight.bin
+//   <dir>/model.layers.<l>.self_attn.{qkv,o_proj}.weight.bin   <dir>/model.layers.<l>.mlp.{gate_up_proj,down_proj}.weight.bin
+// qkv rows are q heads, k heads, v heads; gate_up rows gate then up (act_kernel.cu:28-29). With
+// tp_size > 1 each rank keeps its head / FFN-column shard (Megatron split): rows of qkv and
+// gate_up, columns of o_proj and down_proj.
+// ------------------------------------------------------------------------------------------
+namespace b200 {
+static int read_f32(const std::string& path, std::vector<float>& buf, size_t elems) {
+    FILE* f = fopen(path.c_str(), "rb");
+    if (!f) return fail("load_weights: cannot open " + path);
+    buf.resize(elems);
+    const size_t got = fread(buf.data(), sizeof(float), elems, f);
+    int extra = fgetc(f);
+    fclose(f);
+    if (got != elems || extra != EOF) return fail("load_weights: " + path + " does not hold the expected number of fp32 values");
+    return 0;
+}
+// rows [r0, r0+nr) x cols [c0, c0+nc) of a row-major fp32 [rows, cols] matrix -> dst (engine dtype), appended at dst_row
+static void pack_block(const std::vector<float>& src, size_t cols, size_t r0, size_t nr, size_t c0, size_t nc, int dtype,
+                       std::vector<unsigned char>& dst, size_t dst_row) {
+    const size_t es = dtype == B200_F16 ? 2 : 4;
+    if (dst.size() < (dst_row + nr) * nc * es) dst.resize((dst_row + nr) * nc * es);
+    for (size_t r = 0; r < nr; ++r) {
+        const float* s = src.data() + (r0 + r) * cols + c0;
+        if (dtype == B200_F16) {
+            __half* d = reinterpret_cast<__half*>(dst.data()) + (dst_row + r) * nc;
+            for (size_t c = 0; c < nc; ++c) d[c] = __float2half_rn(s[c]);
+        } else {
+            memcpy(dst.data() + (dst_row + r) * nc * 4, s, nc * 4);
+        }
+    }
+}
+}  // namespace b200
+
+extern "C" int b200_engine_load_weights(b200_engine* e, const char* dir) {
+    if (!e || !dir) return B200_EINVAL;
+    const b200_model_config& c = e->cfg;
+    std::string base(dir);
+    if (!base.empty() && base.back() != '/') base += '/';
+    const int dt = c.dtype, tp = c.tp_size, rk = c.tp_rank;
+    const size_t H = e->H, d = e->d, I_all = c.inter_size, I = e->I, V = e->V;
+    const size_t h_all = c.head_num, hk_all = c.kv_head_num, h = e->h, hk = e->hk;
+    std::vector<float> buf;
+    std::vector<unsigned char> out;
+    auto upload = [&](int slot, int layer) {
+        const size_t bytes = slot_elems(e, slot) * e->esz;
+        if (out.size() < bytes) return fail("load_weights: internal size mismatch");
+        return b200_engine_set_weight(e, slot, layer, out.data(), bytes);
+    };
+    auto whole = [&](const std::string& name, size_t rows, size_t cols, int slot, int layer) {
+        RC(read_f32(base + name, buf, rows * cols));
+        out.clear();
+        pack_block(buf, cols, 0, rows, 0, cols, dt, out, 0);
+        return upload(slot, layer);
+    };
+    RC(whole("model.norm.weight.bin", 1, H, B200_W_FINAL_NORM, 0));
+    RC(whole("lm_head.weight.bin", V, H, B200_W_LM_HEAD, 0));
+    RC(whole("model.embed_tokens.weight.bin", V, H, B200_W_EMBED, 0));
+    for (int l = 0; l < c.num_layers; ++l) {
+        const std::string lp = "model.layers." + std::to_string(l);
+        RC(whole(lp + ".input_layernorm.weight.bin", 1, H, B200_W_ATTN_NORM, l));
+        RC(whole(lp + ".post_attention_layernorm.weight.bin", 1, H, B200_W_FFN_NORM, l));
+        // qkv [(h + 2 hk) d, H]: this rank's q heads, then its k heads, then its v heads
+        RC(read_f32(base + lp + ".self_attn.qkv.weight.bin", buf, (h_all + 2 * hk_all) * d * H));
+        out.clear();
+        pack_block(buf, H, (size_t)rk * h * d, h * d, 0, H, dt, out, 0);
+        pack_block(buf, H, (h_all + (size_t)rk * hk) * d, hk * d, 0, H, dt, out, h * d);
+        pack_block(buf, H, (h_all + hk_all + (size_t)rk * hk) * d, hk * d, 0, H, dt, out, (h + hk) * d);
+        RC(upload(B200_W_QKV, l));
+        // o_proj [H, h_all d]: this rank's input columns
+        RC(read_f32(base + lp + ".self_attn.o_proj.weight.bin", buf, H * h_all * d));
+        out.clear();
+        pack_block(buf, h_all * d, 0, H, (size_t)rk * h * d, h * d, dt, out, 0);
+        RC(upload(B200_W_O, l));
+        // gate_up [2 I_all, H]: gate rows of this rank, then its up rows
+        RC(read_f32(base + lp + ".mlp.gate_up_proj.weight.bin", buf, 2 * I_all * H));
+        out.clear();
+        pack_block(buf, H, (size_t)rk * I, I, 0, H, dt, out, 0);
+        pack_block(buf, H, I_all + (size_t)rk * I, I, 0, H, dt, out, I);
+        RC(upload(B200_W_GATE_UP, l));
+        // down [H, I_all]: this rank's input columns
+        RC(read_f32(base + lp + ".mlp.down_proj.weight.bin", buf, H * I_all));
+        out.clear();
+        pack_block(buf, I_all, 0, H, (size_t)rk * I, I, dt, out, 0);
+        RC(upload(B200_W_DOWN, l));
+    }
+    (void)tp;
+    return B200_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// generation loop of Llama<T>::Response (llama.cpp:363-448) without the tokenizer: prompt ids in,
+// firstTokenGen (prefill) once, continueTokenGen until every sequence has produced eos_id or
+// max_new_tokens are out. out_ids [batch, max_new_tokens] (sequence-major; positions after a
+// sequence's EOS are filled with eos_id), n_generated [batch] (may be NULL). As in the reference
+// the EOS token itself is not counted / emitted for a sequence (llama.cpp:415-419 breaks before
+// printing it). Returns the number of decode steps run (>= 0) or a negative / CUDA error code.
+// ------------------------------------------------------------------------------------------
+extern "C" int b200_engine_generate(b200_engine* e, const int* prompt_ids_host, int prompt_len, int max_new_tokens,
+                                    int eos_id, int* out_ids, int* n_generated) {
+    if (!e || !prompt_ids_host || !out_ids || max_new_tokens < 1) return B200_EINVAL;
+    const int B = e->batch;
+    std::vector<int> cur(B), done(B, 0), count(B, 0);
+    int rc = b200_engine_prefill(e, prompt_ids_host, prompt_len, cur.data());
+    if (rc != 0) return rc > 0 ? -1000 - rc : rc;
+    for (int i = 0; i < B * max_new_tokens; ++i) out_ids[i] = eos_id;
+    int steps = 0;
+    for (int t = 0; t < max_new_tokens; ++t) {
+        int alive = 0;
+        for (int b = 0; b < B; ++b) {
+            // the first token (from the prompt pass) is emitted unconditionally, as llama.cpp:410-413 does
+            if (!done[b] && t > 0 && cur[b] == eos_id) done[b] = 1;
+            if (!done[b]) { out_ids[(size_t)b * max_new_tokens + t] = cur[b]; count[b] = t + 1; ++alive; }
+        }
+        if (!alive || t == max_new_tokens - 1) break;
+        if (e->step + 1 >= e->cfg.max_seq_len) break;   // cache full
+        rc = b200_engine_decode_step_host(e, nullptr, cur.data());   // continues from the ids the engine holds
+        if (rc != 0) return rc > 0 ? -1000 - rc : rc;
+        ++steps;
+    }
+    if (n_generated) for (int b = 0; b < B; ++b) n_generated[b] = count[b];
+    return steps;
+}

@@ -53,7 +53,12 @@ struct GemmSmem {
     static constexpr int kTmemCols = (2 * BN < 32) ? 32 : 2 * BN;                // two accumulator stages
 };
 
-template <int BN, bool SWAP>
+// GLU (normal mode, BN = 256): W = [2*inter, K] with gate rows first (act_kernel.cu:28-29). The B tile of
+// feature tile nt is 128 gate rows (nt*128) followed by the matching 128 up rows (inter + nt*128), so the
+// accumulator holds gate in columns [0,128) and up in [128,256) of the same 128 features, and the epilogue
+// writes silu(gate)*up (launchAct, act_kernel.cu:57) straight to out [tokens, inter]: the [tokens, 2*inter]
+// intermediate of ffn.cpp:72-80 is never stored.
+template <int BN, bool SWAP, bool GLU = false>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                     const GemmParams p) {
@@ -108,7 +113,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
                     unsigned char* sa = tiles + (size_t)stage * S::kStageBytes;
                     mbar_expect_tx(&full_bar[stage], A_BYTES + B_BYTES);
                     tma_load_2d(sa, &map_a, kb * kBK, mt * kBM, &full_bar[stage]);
-                    tma_load_2d(sa + A_BYTES, &map_b, kb * kBK, nt * BN, &full_bar[stage]);
+                    if (GLU) {   // map_b boxes are 128 rows: gate rows, then the up rows of the same features
+                        tma_load_2d(sa + A_BYTES, &map_b, kb * kBK, nt * 128, &full_bar[stage]);
+                        tma_load_2d(sa + A_BYTES + B_BYTES / 2, &map_b, kb * kBK, p.rows_b + nt * 128, &full_bar[stage]);
+                    } else {
+                        tma_load_2d(sa + A_BYTES, &map_b, kb * kBK, nt * BN, &full_bar[stage]);
+                    }
                 }
                 __syncwarp();
                 if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -163,6 +173,32 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
             tc_fence_after();
             const int row = mt * kBM + quarter * 32 + lane;   // row of the A operand / of D
             const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN);
+            if (GLU) {
+                // rows_b = inter; gate in columns [0,128), up in [128,256); same rounding points as the unfused
+                // sequence: GEMM output rounded to fp16, silu(gate) rounded to fp16, product rounded to fp16
+#pragma unroll 1
+                for (int c0 = 0; c0 < 128; c0 += 32) {
+                    uint32_t g[32], u[32];
+                    tmem_ld_32x32(taddr + (uint32_t)c0, g);
+                    tmem_ld_32x32(taddr + (uint32_t)(128 + c0), u);
+                    const int col0 = nt * 128 + c0;
+                    if (row < p.tokens && col0 < p.rows_b) {
+                        __half* dst = C + (size_t)row * p.ldc + col0;
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            float f[8];
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) {
+                                const float gv = __half2float(__float2half_rn(__uint_as_float(g[q * 8 + e])));
+                                const float uv = __half2float(__float2half_rn(__uint_as_float(u[q * 8 + e])));
+                                const float sv = __half2float(__float2half_rn(gv / (1.f + expf(-gv))));
+                                f[e] = sv * uv;
+                            }
+                            if (col0 + q * 8 + 8 <= p.rows_b) st16(dst + q * 8, Unpack<__half>::put(f));
+                        }
+                    }
+                }
+            } else
 #pragma unroll 1
             for (int c0 = 0; c0 < BN; c0 += 32) {
                 uint32_t v[32];
@@ -304,9 +340,9 @@ bool make_tma_map_2d(CUtensorMap* out, const void* ptr, long long rows, int K, i
     return true;
 }
 
-template <int BN, bool SWAP>
+template <int BN, bool SWAP, bool GLU = false>
 static int gemm_launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, int grid, cudaStream_t s) {
-    auto kern = gemm_tcgen05_kernel<BN, SWAP>;
+    auto kern = gemm_tcgen05_kernel<BN, SWAP, GLU>;
     static bool attr_set = false;
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmSmem<BN>::kTotal);
@@ -391,6 +427,24 @@ int gemm_tcgen05_f16(const void* x, const void* W, const void* bias, void* y, in
         case 128: return gemm_launch<128, false>(ma, mb, p, grid, s);
         default: return gemm_launch<256, false>(ma, mb, p, grid, s);
     }
+}
+
+// out[M, inter] = silu(x W_gate^T) * (x W_up^T), W = [2*inter, K] (gate rows, then up rows): the gate_up GEMM of
+// ffn.cpp:72 with launchAct (ffn.cpp:80) as its epilogue. Prefill shapes only (M > 256, inter % 128 == 0).
+int gemm_tcgen05_f16_swiglu(const void* x, const void* W, void* out, int M, int inter, int K, cudaStream_t s) {
+    auto al = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15u) == 0; };
+    if (M <= 256 || inter < 128 || (inter & 127) || K < 8 || (K & 7) || !al(x) || !al(W) || !al(out)) return B200_EUNSUPPORTED;
+    const char* e = getenv("B200_NO_TCGEN05");
+    if (e && e[0] == '1') return B200_EUNSUPPORTED;
+    GemmParams p{};
+    p.C = out; p.bias = nullptr; p.K = K; p.ldc = inter; p.tokens = M;
+    p.k_blocks = (K + kBK - 1) / kBK;
+    p.rows_a = M; p.rows_b = inter;
+    p.m_tiles = (M + kBM - 1) / kBM; p.n_tiles = inter / 128; p.splits = 1;
+    CUtensorMap ma, mb;
+    if (!make_tma_map_2d(&ma, x, M, K, kBM) || !make_tma_map_2d(&mb, W, 2ll * inter, K, 128)) return B200_EUNSUPPORTED;
+    const int units = p.m_tiles * p.n_tiles, sms = sm_count();
+    return gemm_launch<256, false, true>(ma, mb, p, units < sms ? units : sms, s);
 }
 
 }  // namespace b200

@@ -17,6 +17,7 @@ int gemv_plain(const void* x, const void* W, const void* bias, void* y, int n_to
 int gemm_tcgen05_f16(const void* x, const void* W, const void* bias, void* y, int M, int N, int K,
                      void* workspace, size_t workspace_bytes, cudaStream_t s);
 size_t gemm_tcgen05_workspace_bytes(int M, int N, int K);
+int gemm_tcgen05_f16_swiglu(const void* x, const void* W, void* out, int M, int inter, int K, cudaStream_t s);
 
 constexpr int BM = 64, BN = 64, BK = 16;
 
@@ -150,4 +151,15 @@ extern "C" int b200_batched_gemm(const void* A, const void* B, void* C, int batc
     if (dtype == B200_F32)
         return gemm_simt<float>(A, B, nullptr, C, batch_count, m, n, k, trans_b != 0, s);
     return B200_EINVAL;
+}
+
+/* out[n_tokens, inter] = silu(x W_gate^T) * (x W_up^T) with W = [2*inter, K] (gate rows first): the gate_up
+ * launchLinearGemm (ffn.cpp:72) and launchAct (ffn.cpp:80, act_kernel.cu:57) as ONE tcgen05 GEMM whose epilogue
+ * applies SwiGLU; returns B200_EUNSUPPORTED outside fp16 prefill shapes (n_tokens > 256, inter % 128 == 0):
+ * the caller then runs b200_linear + b200_swiglu. */
+extern "C" int b200_linear_swiglu(const void* x, const void* W, void* out, int n_tokens, int inter, int K, int dtype,
+                                  void* stream) {
+    if (!x || !W || !out || n_tokens < 1 || inter < 1 || K < 1) return B200_EINVAL;
+    if (dtype != B200_F16) return B200_EUNSUPPORTED;
+    return b200::gemm_tcgen05_f16_swiglu(x, W, out, n_tokens, inter, K, (cudaStream_t)stream);
 }

@@ -48,6 +48,8 @@ ENGINE_PROTOTYPES = {
     "b200_engine_step_trace": (_i, [_vp, _vp, _i]),
     "b200_engine_prefill": (_i, [_vp, _vp, _i, _vp]),
     "b200_engine_set_p2p": (_i, [_vp, _vp]),
+    "b200_engine_generate": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp]),
+    "b200_engine_load_weights": (_i, [_vp, C.c_char_p]),
     "b200_p2p_handle_bytes": (C.c_size_t, []),
     "b200_p2p_create": (_vp, [_i, _i, C.c_size_t]),
     "b200_p2p_local_handle": (_i, [_vp, _vp]),
@@ -213,6 +215,21 @@ class Engine:
         self._ck(self.lib.b200_engine_prefill(self.h, ids.ctypes.data_as(C.c_void_p), ids.shape[1],
                                               out.ctypes.data_as(C.c_void_p) if sync else None), "prefill")
         return out
+
+    def generate(self, prompt_ids, max_new_tokens, eos_id=2):
+        """b200_engine_generate: prompt [batch, len] -> (ids [batch, max_new_tokens] padded with eos_id, counts [batch])"""
+        ids = np.ascontiguousarray(prompt_ids, dtype=np.int32).reshape(self.batch, -1)
+        out = np.empty((self.batch, max_new_tokens), np.int32)
+        cnt = np.empty(self.batch, np.int32)
+        rc = self.lib.b200_engine_generate(self.h, ids.ctypes.data_as(C.c_void_p), ids.shape[1], max_new_tokens, eos_id,
+                                           out.ctypes.data_as(C.c_void_p), cnt.ctypes.data_as(C.c_void_p))
+        if rc < 0:
+            raise RuntimeError(f"[b200][ERROR] generate: {rc} " + self.lib.b200_engine_last_error().decode())
+        return out, cnt
+
+    def load_weights(self, directory):
+        """the reference's weight directory (fp32 .bin files, llama_weights.cc:41-53 naming)"""
+        self._ck(self.lib.b200_engine_load_weights(self.h, str(directory).encode()), "load_weights")
 
     @property
     def prefill_launches(self):

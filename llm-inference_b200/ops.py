@@ -268,3 +268,14 @@ def context_attention(q, k_cache_layer, v_cache_layer, out, padding_offset, inpu
         _p(q), _p(k_cache_layer), _p(v_cache_layer), _p(out), _p(padding_offset), _p(input_len),
         _p(history_len), b, s, out.shape[0], h, hk, d, max_seq, _dt(q), _stream()),
         "b200_context_attention")
+
+
+def linear_swiglu(inp, weight, out):
+    """b200_linear_swiglu: out [Nt, I] = silu(inp Wg^T) * (inp Wu^T), weight [2I, K] gate rows first
+    (ffn.cpp:72-80 in one tcgen05 launch). Raises "unsupported shape" outside fp16 prefill shapes."""
+    nt, k = inp.shape
+    inter = out.shape[1]
+    if weight.shape[0] != 2 * inter or weight.shape[1] != k:
+        raise RuntimeError("[b200][ERROR] linear_swiglu: weight must be [2*inter, K] Assertion fail")
+    _check(capi.lib().b200_linear_swiglu(_p(inp), _p(weight), _p(out), nt, inter, k, _dt(inp), _stream()),
+           "b200_linear_swiglu")

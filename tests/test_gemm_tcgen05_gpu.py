@@ -76,3 +76,29 @@ def test_linearity_at_full_size(ops):
     ref = x1[rows].float() @ w.float().t()
     e2 = (y1[rows].float() - ref).abs().max().item() / ref.abs().max().item()
     assert e2 < 4e-3, e2
+
+
+@pytest.mark.parametrize("m,inter,k", [(257, 128, 64), (512, 1024, 512), (1000, 384, 264), (2048, 11008, 4096)])
+def test_gate_up_gemm_with_swiglu_epilogue(ops, m, inter, k):
+    """b200_linear_swiglu (ffn.cpp:72-80 in one launch) against the oracle's linear -> SwiGLU with the
+    reference's fp16 rounding points (GEMM output, silu(gate), product)."""
+    rng = np.random.default_rng(m + inter)
+    f16 = lambda a: a.astype(np.float16).astype(np.float32)
+    x = f16(rng.uniform(-1, 1, (m, k)))
+    w = f16(rng.standard_normal((2 * inter, k)) * 0.05)
+    gu = np.zeros((m, 2 * inter), np.float32)
+    cpu.linear(x, w, gu, True)
+    gu = f16(gu).reshape(m, 2, inter)
+    g = gu[:, 0]
+    want = f16(f16(g / (1.0 + np.exp(-g, dtype=np.float32))) * gu[:, 1])
+    out = torch.full((m, inter), float("nan"), dtype=torch.float16, device="cuda")
+    ops.linear_swiglu(torch.from_numpy(x).cuda().half(), torch.from_numpy(w).cuda().half(), out)
+    torch.cuda.synchronize()
+    assert_close(out.float().cpu().numpy(), want, "fp16", f"gate_up + SwiGLU {m}x{inter}x{k}")
+
+
+def test_gate_up_swiglu_rejects_decode_shapes(ops):
+    x = torch.zeros(8, 256, dtype=torch.float16, device="cuda")
+    w = torch.zeros(512, 256, dtype=torch.float16, device="cuda")
+    with pytest.raises(RuntimeError, match="unsupported"):
+        ops.linear_swiglu(x, w, torch.zeros(8, 256, dtype=torch.float16, device="cuda"))
