@@ -1,0 +1,260 @@
+// Two-CTA tcgen05 GEMM for the prefill linears (launchLinearGemm with many token rows, linear.cu:39-104):
+//   D[256, 256] (fp32, TMEM of two SMs) += A[256, 64] * B[256, 64]^T per K step, fp16 operands, K-major.
+// A cluster of two CTAs (one TPC) owns a 256 x 256 output tile: each CTA loads ITS 128 rows of A and ITS
+// 128 rows of B (half of the N extent) and keeps 128 rows x 256 columns of the accumulator in its own
+// TMEM; the leader CTA's single MMA thread issues tcgen05.mma.cta_group::2 (M = 256), which reads both
+// CTAs' shared memory. Against the one-CTA kernel (gemm_tcgen05.cu: 48 KB of operands per 512 tensor
+// clocks, 4 stages) a stage is 32 KB per SM for the same 512 clocks: the smem read rate per SM drops from
+// 96 to 64 B/clk and the ring holds 6 stages of look-ahead instead of 4.
+//   warp 0    TMA producer (both CTAs): its own A / B boxes, completion signalled on the LEADER's full barrier
+//   warp 1    TMEM allocation (both CTAs); MMA issue (leader only); tcgen05.commit multicast to both CTAs
+//   warps 2-5 epilogue (both CTAs): own 128 rows from own TMEM, then a remote arrive on the leader's
+//             accumulator-empty barrier
+// GLU: as in gemm_tcgen05.cu — the leader's B half is 128 gate rows, the peer's the matching 128 up rows.
+#include "common.cuh"
+#include "launch_count.h"
+#include "tc_common.cuh"
+
+namespace b200 {
+
+constexpr int k2Threads = 192;
+constexpr int k2BK = 64;
+constexpr int k2Stages = 6;
+constexpr uint32_t k2ABytes = 128 * k2BK * 2, k2BBytes = 128 * k2BK * 2, k2StageBytes = k2ABytes + k2BBytes;
+constexpr uint32_t k2OffBar = k2Stages * k2StageBytes;                  // full[6], empty[6], acc_full[2], acc_empty[2]
+constexpr uint32_t k2OffSlot = k2OffBar + (2 * k2Stages + 4) * 8;
+constexpr uint32_t k2Smem = k2OffSlot + 16;
+
+struct Gemm2Params {
+    __half* C;          // [tokens, ldc]
+    const __half* bias; // [N] or nullptr (not with GLU)
+    int tokens, n_out;  // valid rows of A; valid output features (GLU: inter)
+    int ldc, k_blocks;
+    int m_tiles, n_tiles;   // tiles of 256 rows x (256 features | GLU: 128 features)
+};
+
+template <bool GLU>
+__global__ void __launch_bounds__(k2Threads, 1)
+gemm2_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const Gemm2Params p) {
+    extern __shared__ __align__(1024) unsigned char smem[];
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + k2OffBar);
+    uint64_t* empty_bar = full_bar + k2Stages;
+    uint64_t* acc_full = empty_bar + k2Stages;   // [2]
+    uint64_t* acc_empty = acc_full + 2;          // [2], used in the leader only
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + k2OffSlot);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();     // 0 = leader
+    if (threadIdx.x == 0) {
+        if (smem_u32(smem) & 1023u) __trap();
+        for (int s = 0; s < k2Stages; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int a = 0; a < 2; ++a) {
+            mbar_init(&acc_full[a], 1);
+            mbar_init(&acc_empty[a], 8);   // 4 epilogue warps x 2 CTAs
+        }
+        mbar_fence_init();
+        tma_prefetch_desc(&map_a);
+        tma_prefetch_desc(&map_b);
+    }
+    if (warp == 1) tmem_alloc_pair(tmem_slot, 512);
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();   // the peer's barriers exist before anything is signalled on them
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    pdl_launch_dependents();
+    pdl_wait();
+
+    const int units = p.m_tiles * p.n_tiles;
+    const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
+
+    if (warp == 0) {
+        // ================= TMA producer (both CTAs) =================
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int u = cluster_id; u < units; u += n_clusters) {
+            const int mt = u % p.m_tiles, nt = u / p.m_tiles;
+            const int a_row = mt * 256 + (int)rank * 128;
+            const int b_row = GLU ? (rank == 0 ? nt * 128 : p.n_out + nt * 128) : nt * 256 + (int)rank * 128;
+            for (int kb = 0; kb < p.k_blocks; ++kb) {
+                mbar_wait_bounded(&empty_bar[stage], phase ^ 1);
+                if (lane == 0) {
+                    unsigned char* sa = smem + (size_t)stage * k2StageBytes;
+                    const uint32_t leader_full = mapa_shared(smem_u32(&full_bar[stage]), 0);
+                    if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * k2StageBytes);   // both CTAs' boxes
+                    tma_load_2d_pair(sa, &map_a, kb * k2BK, a_row, leader_full);
+                    tma_load_2d_pair(sa + k2ABytes, &map_b, kb * k2BK, b_row, leader_full);
+                }
+                __syncwarp();
+                if (++stage == k2Stages) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else if (warp == 1) {
+        // ================= MMA issuer (leader CTA only) =================
+        if (rank == 0) {
+            constexpr uint32_t idesc = make_idesc_f16(256, 256);
+            int stage = 0, acc = 0;
+            uint32_t phase = 0, acc_phase = 0;
+            for (int u = cluster_id; u < units; u += n_clusters) {
+                mbar_wait_bounded(&acc_empty[acc], acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + (uint32_t)(acc * 256);
+                for (int kb = 0; kb < p.k_blocks; ++kb) {
+                    mbar_wait_bounded(&full_bar[stage], phase);
+                    tc_fence_after();
+                    if (lane == 0) {
+                        const uint32_t sa = smem_u32(smem + (size_t)stage * k2StageBytes);
+                        const uint64_t da = make_kmajor_sw128_desc(sa);
+                        const uint64_t db = make_kmajor_sw128_desc(sa + k2ABytes);
+#pragma unroll
+                        for (int k = 0; k < k2BK / kUmmaK; ++k)
+                            umma_f16_pair(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb > 0 || k > 0) ? 1u : 0u);
+                        umma_commit_pair(&empty_bar[stage], 3);                      // both producers may refill
+                        if (kb == p.k_blocks - 1) umma_commit_pair(&acc_full[acc], 3);   // both epilogues may read
+                    }
+                    __syncwarp();
+                    if (++stage == k2Stages) { stage = 0; phase ^= 1; }
+                }
+                acc ^= 1;
+                if (acc == 0) acc_phase ^= 1;
+            }
+        }
+    } else {
+        // ================= epilogue warps (both CTAs) =================
+        const int quarter = warp & 3;
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        for (int u = cluster_id; u < units; u += n_clusters) {
+            const int mt = u % p.m_tiles, nt = u / p.m_tiles;
+            mbar_wait_bounded(&acc_full[acc], acc_phase);
+            tc_fence_after();
+            const int row = mt * 256 + (int)rank * 128 + quarter * 32 + lane;
+            const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * 256);
+            if (GLU) {
+#pragma unroll 1
+                for (int c0 = 0; c0 < 128; c0 += 32) {
+                    uint32_t g[32], uu[32];
+                    tmem_ld_32x32(taddr + (uint32_t)c0, g);
+                    tmem_ld_32x32(taddr + (uint32_t)(128 + c0), uu);
+                    const int col0 = nt * 128 + c0;
+                    if (row < p.tokens && col0 < p.n_out) {
+                        __half* dst = p.C + (size_t)row * p.ldc + col0;
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            float f[8];
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) {
+                                const float gv = __half2float(__float2half_rn(__uint_as_float(g[q * 8 + e])));
+                                const float uv = __half2float(__float2half_rn(__uint_as_float(uu[q * 8 + e])));
+                                const float sv = __half2float(__float2half_rn(gv / (1.f + expf(-gv))));
+                                f[e] = sv * uv;
+                            }
+                            if (col0 + q * 8 + 8 <= p.n_out) st16(dst + q * 8, Unpack<__half>::put(f));
+                        }
+                    }
+                }
+            } else {
+#pragma unroll 1
+                for (int c0 = 0; c0 < 256; c0 += 32) {
+                    uint32_t v[32];
+                    tmem_ld_32x32(taddr + (uint32_t)c0, v);
+                    const int col0 = nt * 256 + c0;
+                    if (row < p.tokens && col0 < p.n_out) {
+                        __half* dst = p.C + (size_t)row * p.ldc + col0;
+                        if (col0 + 32 <= p.n_out && (p.ldc & 7) == 0) {
+#pragma unroll
+                            for (int q = 0; q < 4; ++q) {
+                                float f[8];
+#pragma unroll
+                                for (int e = 0; e < 8; ++e) {
+                                    f[e] = __uint_as_float(v[q * 8 + e]);
+                                    if (p.bias) f[e] += __half2float(p.bias[col0 + q * 8 + e]);
+                                }
+                                st16(dst + q * 8, Unpack<__half>::put(f));
+                            }
+                        } else {
+                            for (int j = 0; j < 32 && col0 + j < p.n_out; ++j) {
+                                float f = __uint_as_float(v[j]);
+                                if (p.bias) f += __half2float(p.bias[col0 + j]);
+                                dst[j] = __float2half_rn(f);
+                            }
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(mapa_shared(smem_u32(&acc_empty[acc]), 0));
+            acc ^= 1;
+            if (acc == 0) acc_phase ^= 1;
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();   // neither CTA leaves while the other may still signal its barriers / read its smem
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc_pair(tmem_base, 512);
+    }
+}
+
+template <bool GLU>
+static int gemm2_launch(const CUtensorMap& ma, const CUtensorMap& mb, const Gemm2Params& p, int grid, cudaStream_t s) {
+    auto kern = gemm2_tcgen05_kernel<GLU>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k2Smem);
+        if (e != cudaSuccess) return (int)e;
+        attr_set = true;
+    }
+    prefer_max_smem_carveout(reinterpret_cast<const void*>(kern));
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(k2Threads);
+    cfg.dynamicSmemBytes = k2Smem;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[2];
+    int na = 0;
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = 2;
+    attr[na].val.clusterDim.y = 1;
+    attr[na].val.clusterDim.z = 1;
+    ++na;
+    if (pdl_enabled()) {
+        attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[na].val.programmaticStreamSerializationAllowed = 1;
+        ++na;
+    }
+    cfg.attrs = attr;
+    cfg.numAttrs = na;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ma, mb, p);
+    count_launch();
+    return (int)e;
+}
+
+// y[M, N] = x[M, K] W[N, K]^T (+ bias) or, with glu, out[M, N] = silu(x Wg^T) * (x Wu^T) with W = [2N, K].
+// Returns B200_EUNSUPPORTED for shapes the pair kernel does not cover (the one-CTA kernel takes them).
+int gemm2_tcgen05_f16(const void* x, const void* W, const void* bias, void* y, int M, int N, int K, bool glu, cudaStream_t s) {
+    static int mode = -1;   // B200_GEMM_PAIR=0 keeps the one-CTA kernel
+    if (mode < 0) { const char* e = getenv("B200_GEMM_PAIR"); mode = (e && e[0] == '0') ? 0 : 1; }
+    if (!mode) return B200_EUNSUPPORTED;
+    if (M < 512 || N < 256 || K < 64 || (K & 7)) return B200_EUNSUPPORTED;
+    if (glu && ((N & 127) || bias)) return B200_EUNSUPPORTED;
+    Gemm2Params p{};
+    p.C = reinterpret_cast<__half*>(y);
+    p.bias = reinterpret_cast<const __half*>(bias);
+    p.tokens = M; p.n_out = N; p.ldc = N;
+    p.k_blocks = (K + k2BK - 1) / k2BK;
+    p.m_tiles = (M + 255) / 256;
+    p.n_tiles = glu ? N / 128 : (N + 255) / 256;
+    CUtensorMap ma, mb;
+    if (!make_tma_map_2d(&ma, x, M, K, 128) || !make_tma_map_2d(&mb, W, glu ? 2ll * N : (long long)N, K, 128)) return B200_EUNSUPPORTED;
+    const int units = p.m_tiles * p.n_tiles;
+    int clusters = sm_count() / 2;
+    if (clusters > units) clusters = units;
+    return glu ? gemm2_launch<true>(ma, mb, p, 2 * clusters, s) : gemm2_launch<false>(ma, mb, p, 2 * clusters, s);
+}
+
+}  // namespace b200

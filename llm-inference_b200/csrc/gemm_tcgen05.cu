@@ -367,6 +367,8 @@ static int pick_splits(int m_tiles, int k_blocks, int sms) {
     return best;
 }
 
+int gemm2_tcgen05_f16(const void* x, const void* W, const void* bias, void* y, int M, int N, int K, bool glu, cudaStream_t s);
+
 size_t gemm_tcgen05_workspace_bytes(int M, int N, int K) {
     if (M <= B200_GEMV_MAX_TOKENS || M > 256) return 0;
     const int splits = pick_splits((N + kBM - 1) / kBM, (K + kBK - 1) / kBK, sm_count());
@@ -414,7 +416,11 @@ int gemm_tcgen05_f16(const void* x, const void* W, const void* bias, void* y, in
         count_launch();
         return (int)e;
     }
-    // normal: tokens on the M axis
+    // normal: tokens on the M axis; large shapes go to the two-CTA kernel (gemm2_tcgen05.cu)
+    {
+        const int rc2 = gemm2_tcgen05_f16(x, W, bias, y, M, N, K, false, s);
+        if (rc2 != B200_EUNSUPPORTED) return rc2;
+    }
     const int BN = N >= 256 ? 256 : N >= 128 ? 128 : N >= 64 ? 64 : 32;
     p.rows_a = M; p.rows_b = N;
     p.m_tiles = (M + kBM - 1) / kBM; p.n_tiles = (N + BN - 1) / BN; p.splits = 1;
@@ -436,6 +442,10 @@ int gemm_tcgen05_f16_swiglu(const void* x, const void* W, void* out, int M, int 
     if (M <= 256 || inter < 128 || (inter & 127) || K < 8 || (K & 7) || !al(x) || !al(W) || !al(out)) return B200_EUNSUPPORTED;
     const char* e = getenv("B200_NO_TCGEN05");
     if (e && e[0] == '1') return B200_EUNSUPPORTED;
+    {
+        const int rc2 = gemm2_tcgen05_f16(x, W, nullptr, out, M, inter, K, true, s);
+        if (rc2 != B200_EUNSUPPORTED) return rc2;
+    }
     GemmParams p{};
     p.C = out; p.bias = nullptr; p.K = K; p.ldc = inter; p.tokens = M;
     p.k_blocks = (K + kBK - 1) / kBK;
