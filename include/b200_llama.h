@@ -222,6 +222,10 @@ int b200_context_attention(const void* q, const void* k_cache_layer, const void*
                            int head_num, int kv_head_num, int head_size, int max_seq_len,
                            int dtype, void* stream);
 
+/* debug: %globaltimer stamps of CTA 0 of the following b200_context_attention launches (NULL = off);
+ * layout in csrc/context_attention.cu, reader tools/ctx_trace.py */
+void b200_context_attention_set_trace(void* dev_buf);
+
 /* ------------------------------------------------------------------------------------
  * next-tier ops bracketing a decode step
  * launchInputEmbedding   src/kernels/input_embedding.cu:30   out[t,:] = table[ids[t],:]

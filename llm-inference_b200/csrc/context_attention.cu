@@ -19,11 +19,13 @@
 //               buffers; O_j = P_j V_j (A = P from smem, B = V as MN-major operand - V rows are keys,
 //               exactly what the PV contraction runs over) into one of two TMEM output buffers;
 //               S_{j+1} is issued before P_j V_j so the tensor pipe works under the softmax of tile j;
-//   warps 2-5   softmax: thread = query row; two passes over the TMEM row (max, then exp2 / sum),
-//               P_j written as fp16 into the swizzled K-major A-operand layout, alpha_j = exp(m_old - m_new)
-//               handed to the accumulate warps through smem;
-//   warps 6-9   accumulate: thread = query row, 128 fp32 outputs in registers,
-//               o = o * alpha_j + O_j (tcgen05.ld), final o / (l + 1e-6) -> fp16 -> out.
+//   warps 2-9   compute: thread = (query row, 64-column half); warps w and w+4 share a TMEM lane quarter.
+//               The half row of scores is read from TMEM once into registers, the two halves exchange the
+//               row maximum through smem (one named barrier per tile), P_j written as fp16 into the
+//               swizzled K-major A-operand layout; then o = o * alpha_{j-1} + O_{j-1} for the thread's 64
+//               output columns (tcgen05.ld), so P_{j-1} V_{j-1} runs under the softmax of tile j;
+//               final o / (l0 + l1 + 1e-6) -> fp16 -> out. (First version: 4 softmax + 4 accumulate warps,
+//               one warp per scheduler on the critical exp2 chain: 5700 clocks per tile, tensor pipe 22 %.)
 // TMEM: 2 x 128 score columns + 2 x 128 output columns = 512. Shared memory: Q 32 KB + K 2 x 32 KB +
 // V 2 x 32 KB + P 2 x 32 KB + 3 KB of alpha / l / mbarriers = 226.7 KB (one CTA per SM).
 //
@@ -42,8 +44,8 @@ constexpr uint32_t kOffQ = 0;
 constexpr uint32_t kOffK = kOffQ + kTileBytes;      // [2]
 constexpr uint32_t kOffV = kOffK + 2 * kTileBytes;  // [2]
 constexpr uint32_t kOffP = kOffV + 2 * kTileBytes;  // [2]
-constexpr uint32_t kOffAlpha = kOffP + 2 * kTileBytes;          // float [4][128]
-constexpr uint32_t kOffL = kOffAlpha + 4 * 128 * 4;             // float [128]
+constexpr uint32_t kOffAlpha = kOffP + 2 * kTileBytes;          // float [2][128][2]: row-max / row-sum exchange between column halves
+constexpr uint32_t kOffL = kOffAlpha + 4 * 128 * 4;             // (spare)
 constexpr uint32_t kOffBar = kOffL + 128 * 4;                   // 20 mbarriers
 constexpr uint32_t kOffSlot = kOffBar + 20 * 8;
 constexpr uint32_t kCtxSmem = kOffSlot + 16;
@@ -55,6 +57,7 @@ struct CtxParams {
     const int* history_len;   // [batch]
     int batch, seq_len, head_num, kv_head_num, max_seq_len, q_tiles;
     float scale_log2;         // 1/sqrt(d) * log2(e)
+    unsigned long long* trace;   // debug (b200_context_attention_set_trace): %globaltimer stamps of CTA 0
 };
 
 // MN-major operand with the 128B swizzle (canonical layout ((8,n),(8,k)):((1,LBO),(8,SBO)) in 16-byte
@@ -96,10 +99,41 @@ __device__ __forceinline__ void ctx_wait(uint64_t* bar, uint32_t parity) {
     }
 }
 
+__device__ __forceinline__ void ctx_stamp(const CtxParams& p, int slot) {
+    if (p.trace && blockIdx.x == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        p.trace[slot] = t;
+    }
+}
+
 __device__ __forceinline__ float ex2_approx(float x) {
     float y;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
+}
+// packed fp32x2 arithmetic (sm_100: one FFMA2 / FADD2 issue slot for two lanes): the softmax is issue-bound
+__device__ __forceinline__ uint64_t pack2(uint32_t lo, uint32_t hi) {
+    uint64_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"(lo), "r"(hi));
+    return r;
+}
+__device__ __forceinline__ uint64_t pack2f(float lo, float hi) { return pack2(__float_as_uint(lo), __float_as_uint(hi)); }
+__device__ __forceinline__ void unpack2(uint64_t v, float& lo, float& hi) {
+    uint32_t a, b;
+    asm("mov.b64 {%0, %1}, %2;" : "=r"(a), "=r"(b) : "l"(v));
+    lo = __uint_as_float(a);
+    hi = __uint_as_float(b);
+}
+__device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
+    uint64_t d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ uint64_t add2(uint64_t a, uint64_t b) {
+    uint64_t d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
 }
 __device__ __forceinline__ void fence_proxy_async_smem() {
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -141,9 +175,7 @@ context_attn_tcgen05_kernel(const __grid_constant__ CUtensorMap map_q, const __g
     uint64_t* p_full = bars + 13;   // [2]
     uint64_t* o_full = bars + 15;   // [2]
     uint64_t* o_empty = bars + 17;  // [2]
-    uint64_t* l_full = bars + 19;
     float* alpha_s = reinterpret_cast<float*>(smem + kOffAlpha);
-    float* l_s = reinterpret_cast<float*>(smem + kOffL);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + kOffSlot);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -156,12 +188,11 @@ context_attn_tcgen05_kernel(const __grid_constant__ CUtensorMap map_q, const __g
             mbar_init(&v_full[s], 1);
             mbar_init(&v_empty[s], 1);
             mbar_init(&s_full[s], 1);
-            mbar_init(&s_empty[s], 4);
-            mbar_init(&p_full[s], 4);
+            mbar_init(&s_empty[s], 8);
+            mbar_init(&p_full[s], 8);
             mbar_init(&o_full[s], 1);
-            mbar_init(&o_empty[s], 4);
+            mbar_init(&o_empty[s], 8);
         }
-        mbar_init(l_full, 4);
         mbar_fence_init();
         tma_prefetch_desc(&map_q);
         tma_prefetch_desc(&map_k);
@@ -224,6 +255,7 @@ context_attn_tcgen05_kernel(const __grid_constant__ CUtensorMap map_q, const __g
                 }
                 umma_commit(&k_empty[s]);
                 umma_commit(&s_full[s]);
+                ctx_stamp(p, 8 * j + 0);   // S_j issued
             }
             __syncwarp();
         };
@@ -247,6 +279,7 @@ context_attn_tcgen05_kernel(const __grid_constant__ CUtensorMap map_q, const __g
                 }
                 umma_commit(&v_empty[s]);
                 umma_commit(&o_full[s]);
+                ctx_stamp(p, 8 * j + 1);   // P_j V_j issued
             }
             __syncwarp();
         };
@@ -256,126 +289,148 @@ context_attn_tcgen05_kernel(const __grid_constant__ CUtensorMap map_q, const __g
             if (j + 1 < n_kt) issue_s(j + 1);
             issue_pv(j);
         }
-    } else if (warp < 6) {
-        // ================= softmax warps: thread = query row =================
-        const int quarter = warp & 3;
+    } else {
+        // ================= compute warps 2..9: thread = (query row, column half) =================
+        // Warps w and w + 4 share TMEM lane quarter w & 3: the first takes score / output columns [0, 64),
+        // the second [64, 128). Two warps per scheduler hide each other's TMEM / MUFU latency; the row
+        // maximum is the only value the two halves exchange per tile (smem, one named barrier); the row
+        // sums stay per half and are added once at the end.
+        const int quarter = warp & 3, half = (warp - 2) >> 2;
         const int row = quarter * 32 + lane;
         const int qpos = min(hist + q0 + row, ctx_len - 1);   // pad rows behave like the last real row
         const float sl = p.scale_log2;
-        float m = -1e30f, l = 0.f;
-        for (int j = 0; j < n_kt; ++j) {
-            const int s = j & 1;
-            const uint32_t ph = (uint32_t)(j >> 1) & 1u;
-            const int kbase = j * kCtxTile;
-            const bool need_mask = kbase + kCtxTile - 1 > hist + q0;
-            ctx_wait(&s_full[s], ph);
+        const uint32_t lane_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(half * 64);
+        float m = -1e30f, l = 0.f, alpha_prev = 0.f;
+        uint64_t o2[32];   // this thread's 64 output columns as fp32 pairs
+#pragma unroll
+        for (int e = 0; e < 32; ++e) o2[e] = 0ull;
+        auto accumulate = [&](int jj, float alpha) {   // o = o * alpha + O_jj (this thread's 64 columns)
+            const int s = jj & 1;
+            ctx_wait(&o_full[s], (uint32_t)(jj >> 1) & 1u);
             tc_fence_after();
-            const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(s * kCtxTile);
-            // pass 1: row maximum of the visible scores
-            float mx = m;
-#pragma unroll 1
-            for (int c = 0; c < 4; ++c) {
+            const uint64_t a2 = pack2f(alpha, alpha);
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
                 uint32_t v[32];
-                tmem_ld_32x32(taddr + (uint32_t)(c * 32), v);
+                tmem_ld_32x32(lane_addr + (uint32_t)(256 + s * kCtxTile + c * 32), v);
 #pragma unroll
-                for (int e = 0; e < 32; ++e) {
-                    const float x = __uint_as_float(v[e]);
-                    const bool vis = !need_mask || (kbase + c * 32 + e <= qpos);
-                    mx = vis ? fmaxf(mx, x) : mx;
-                }
-            }
-            const float alpha = ex2_approx((m - mx) * sl);
-            m = mx;
-            const float msl = m * sl;
-            // P[s] was the A operand of P_{j-2} V_{j-2}: that MMA must have retired
-            if (j >= 2) ctx_wait(&o_full[s], ph ^ 1u);
-            // pass 2: p = exp2(x * sl - m * sl), row sum, fp16 P into the swizzled K-major layout
-            const uint32_t p_row = smem_u32(smem + kOffP + (uint32_t)s * kTileBytes) + (uint32_t)row * 128u;
-            float rs = 0.f;
-#pragma unroll 1
-            for (int c = 0; c < 4; ++c) {
-                uint32_t v[32];
-                tmem_ld_32x32(taddr + (uint32_t)(c * 32), v);
-                float pe[32];
-#pragma unroll
-                for (int e = 0; e < 32; ++e) {
-                    const bool vis = !need_mask || (kbase + c * 32 + e <= qpos);
-                    const float pv = ex2_approx(fmaf(__uint_as_float(v[e]), sl, -msl));
-                    pe[e] = vis ? pv : 0.f;
-                    rs += pe[e];
-                }
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const int cc = c * 4 + q;   // 16-byte chunk (8 keys) of the 128-key row
-                    const uint32_t addr = p_row + (uint32_t)(cc >> 3) * kBoxBytes + (uint32_t)(((cc & 7) ^ (row & 7)) << 4);
-                    st_shared_v4(addr, pack_h2(pe[q * 8 + 0], pe[q * 8 + 1]), pack_h2(pe[q * 8 + 2], pe[q * 8 + 3]),
-                                 pack_h2(pe[q * 8 + 4], pe[q * 8 + 5]), pack_h2(pe[q * 8 + 6], pe[q * 8 + 7]));
-                }
-            }
-            l = l * alpha + rs;
-            alpha_s[(j & 3) * 128 + row] = alpha;
-            if (j == n_kt - 1) {
-                l_s[row] = l;
-                // cache rows at or beyond the context length are not ours: 0 * garbage must stay 0
-                const int valid = ctx_len - kbase;
-                if (valid < kCtxTile) {
-                    ctx_wait(&v_full[s], ph);
-                    if (row >= valid) {
-                        const uint32_t v_row = smem_u32(smem + kOffV + (uint32_t)s * kTileBytes) + (uint32_t)row * 128u;
-#pragma unroll
-                        for (int q = 0; q < 8; ++q) {
-                            st_shared_v4(v_row + (uint32_t)(q << 4), 0u, 0u, 0u, 0u);
-                            st_shared_v4(v_row + kBoxBytes + (uint32_t)(q << 4), 0u, 0u, 0u, 0u);
-                        }
-                    }
-                }
-            }
-            tc_fence_before();
-            fence_proxy_async_smem();   // P (and the zeroed V rows) become visible to the tensor core
-            __syncwarp();
-            if (lane == 0) {
-                mbar_arrive(&s_empty[s]);
-                mbar_arrive(&p_full[s]);
-                if (j == n_kt - 1) mbar_arrive(l_full);
-            }
-        }
-    } else {
-        // ================= accumulate warps: thread = query row, o[128] in registers =================
-        const int quarter = warp & 3;
-        const int row = quarter * 32 + lane;
-        float o[kCtxTile];
-#pragma unroll
-        for (int e = 0; e < kCtxTile; ++e) o[e] = 0.f;
-        for (int j = 0; j < n_kt; ++j) {
-            const int s = j & 1;
-            const uint32_t ph = (uint32_t)(j >> 1) & 1u;
-            ctx_wait(&o_full[s], ph);
-            tc_fence_after();
-            const float alpha = alpha_s[(j & 3) * 128 + row];   // written before p_full[s], which precedes P_j V_j
-            const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(256 + s * kCtxTile);
-#pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                uint32_t v[32];
-                tmem_ld_32x32(taddr + (uint32_t)(c * 32), v);
-#pragma unroll
-                for (int e = 0; e < 32; ++e) o[c * 32 + e] = fmaf(o[c * 32 + e], alpha, __uint_as_float(v[e]));
+                for (int e = 0; e < 16; ++e) o2[c * 16 + e] = fma2(o2[c * 16 + e], a2, pack2(v[2 * e], v[2 * e + 1]));
             }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&o_empty[s]);
+        };
+        for (int j = 0; j < n_kt; ++j) {
+            const int s = j & 1;
+            const uint32_t ph = (uint32_t)(j >> 1) & 1u;
+            const int kbase = j * kCtxTile + half * 64;       // first key of this thread's columns
+            const bool need_mask = j * kCtxTile + kCtxTile - 1 > hist + q0;
+            ctx_wait(&s_full[s], ph);
+            tc_fence_after();
+            if (threadIdx.x == 64) ctx_stamp(p, 8 * j + 2);   // S_j visible to the softmax
+            const uint32_t taddr = lane_addr + (uint32_t)(s * kCtxTile);
+            // this thread's 64 scores, read from TMEM ONCE (TMEM reads run at 64 B/clk per SM: the two-pass
+            // version read 192 KB per tile = 3072 clocks against 1024 clocks of MMA work)
+            uint32_t sv[64];
+            tmem_ld_32x32(taddr, *reinterpret_cast<uint32_t(*)[32]>(&sv[0]));
+            tmem_ld_32x32(taddr + 32u, *reinterpret_cast<uint32_t(*)[32]>(&sv[32]));
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&s_empty[s]);   // the score buffer is free for S_{j+2}
+            float mx = -1e30f;
+            if (need_mask) {
+#pragma unroll
+                for (int e = 0; e < 64; ++e) mx = (kbase + e <= qpos) ? fmaxf(mx, __uint_as_float(sv[e])) : mx;
+            } else {
+#pragma unroll
+                for (int e = 0; e < 64; ++e) mx = fmaxf(mx, __uint_as_float(sv[e]));
+            }
+            float* xch = alpha_s + (j & 1) * 256;             // [128 rows][2 halves], double buffered per tile
+            xch[row * 2 + half] = mx;
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            mx = fmaxf(fmaxf(mx, xch[row * 2 + (half ^ 1)]), m);
+            if (threadIdx.x == 64) ctx_stamp(p, 8 * j + 3);   // row maxima exchanged
+            const float alpha = ex2_approx((m - mx) * sl);
+            m = mx;
+            const float msl = m * sl;
+            // p = exp2(x * sl - m * sl), row sum, fp16 P into the swizzled K-major A-operand layout.
+            // P[s] was the A operand of P_{j-2} V_{j-2}; this thread has already consumed O_{j-2} (below).
+            const uint32_t p_row = smem_u32(smem + kOffP + (uint32_t)s * kTileBytes) + (uint32_t)half * kBoxBytes + (uint32_t)row * 128u;
+            float rs = 0.f;
+            if (need_mask) {   // diagonal tiles: per-element visibility
+#pragma unroll
+                for (int c8 = 0; c8 < 8; ++c8) {   // 16-byte chunk (8 keys) inside this half's 64-key box
+                    float pe[8];
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) {
+                        const float pv = ex2_approx(fmaf(__uint_as_float(sv[c8 * 8 + e]), sl, -msl));
+                        pe[e] = (kbase + c8 * 8 + e <= qpos) ? pv : 0.f;
+                        rs += pe[e];
+                    }
+                    st_shared_v4(p_row + (uint32_t)((c8 ^ (row & 7)) << 4), pack_h2(pe[0], pe[1]), pack_h2(pe[2], pe[3]),
+                                 pack_h2(pe[4], pe[5]), pack_h2(pe[6], pe[7]));
+                }
+            } else {           // every key of the tile is visible: packed fp32x2 arithmetic, no selects
+                const uint64_t sl2 = pack2f(sl, sl), nm2 = pack2f(-msl, -msl);
+                uint64_t rs2 = 0ull;
+#pragma unroll
+                for (int c8 = 0; c8 < 8; ++c8) {
+                    uint32_t h[4];
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        float a0, a1;
+                        unpack2(fma2(pack2(sv[c8 * 8 + 2 * e], sv[c8 * 8 + 2 * e + 1]), sl2, nm2), a0, a1);
+                        const float p0 = ex2_approx(a0), p1 = ex2_approx(a1);
+                        rs2 = add2(rs2, pack2f(p0, p1));
+                        h[e] = pack_h2(p0, p1);
+                    }
+                    st_shared_v4(p_row + (uint32_t)((c8 ^ (row & 7)) << 4), h[0], h[1], h[2], h[3]);
+                }
+                float r0, r1;
+                unpack2(rs2, r0, r1);
+                rs = r0 + r1;
+            }
+            l = l * alpha + rs;
+            if (j == n_kt - 1) {
+                // cache rows at or beyond the context length are not ours: 0 * garbage must stay 0
+                const int valid = ctx_len - j * kCtxTile;
+                if (valid < kCtxTile) {
+                    ctx_wait(&v_full[s], ph);
+                    if (row >= valid) {
+                        const uint32_t v_row = smem_u32(smem + kOffV + (uint32_t)s * kTileBytes) + (uint32_t)half * kBoxBytes + (uint32_t)row * 128u;
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) st_shared_v4(v_row + (uint32_t)(q << 4), 0u, 0u, 0u, 0u);
+                    }
+                }
+            }
+            fence_proxy_async_smem();   // P (and the zeroed V rows) become visible to the tensor core
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&p_full[s]);
+            if (threadIdx.x == 64) ctx_stamp(p, 8 * j + 4);   // P_j published
+            if (j > 0) accumulate(j - 1, alpha_prev);   // P_{j-1} V_{j-1} ran under this tile's softmax
+            if (threadIdx.x == 64) ctx_stamp(p, 8 * j + 5);   // O_{j-1} folded in
+            alpha_prev = alpha;
         }
-        ctx_wait(l_full, 0);
+        accumulate(n_kt - 1, alpha_prev);
+        // ---- row sum over both halves, normalise, packed token-major store
+        float* xch = alpha_s + (n_kt & 1) * 256;   // the buffer tile n_kt would use: its last readers passed a barrier since
+        xch[row * 2 + half] = l;
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        const float inv = 1.f / (l + xch[row * 2 + (half ^ 1)] + 1e-6f);
         const int t = q0 + row;
         if (t < in_len) {
             int tok = t;
             for (int i = 0; i < b; ++i) tok += p.input_len[i];
-            const float inv = 1.f / (l_s[row] + 1e-6f);
-            __half* dst = p.out + ((size_t)tok * p.head_num + head) * kCtxTile;
+            __half* dst = p.out + ((size_t)tok * p.head_num + head) * kCtxTile + half * 64;
 #pragma unroll
-            for (int q = 0; q < 16; ++q) {
+            for (int q = 0; q < 8; ++q) {
                 float f[8];
 #pragma unroll
-                for (int e = 0; e < 8; ++e) f[e] = o[q * 8 + e] * inv;
+                for (int e = 0; e < 4; ++e) {
+                    unpack2(o2[q * 4 + e], f[2 * e], f[2 * e + 1]);
+                    f[2 * e] *= inv;
+                    f[2 * e + 1] *= inv;
+                }
                 st16(dst + q * 8, Unpack<__half>::put(f));
             }
         }
@@ -391,6 +446,11 @@ context_attn_tcgen05_kernel(const __grid_constant__ CUtensorMap map_q, const __g
 }  // namespace b200
 
 using namespace b200;
+
+static unsigned long long* g_ctx_trace = nullptr;
+/* debug: device buffer of >= 8 * tiles u64; CTA 0 (the last query tile of sequence 0, head 0) stamps %globaltimer per
+ * key tile j at [8j + 0..5] = S_j issued, P_j V_j issued, S_j visible, maxima exchanged, P_j published, O_{j-1} folded */
+extern "C" void b200_context_attention_set_trace(void* dev_buf) { g_ctx_trace = (unsigned long long*)dev_buf; }
 
 extern "C" int b200_context_attention(const void* q, const void* k_cache_layer, const void* v_cache_layer,
                                       void* out, const int* padding_offset, const int* input_len,
@@ -428,6 +488,7 @@ extern "C" int b200_context_attention(const void* q, const void* k_cache_layer, 
     p.max_seq_len = max_seq_len;
     p.q_tiles = (seq_len + kCtxTile - 1) / kCtxTile;
     p.scale_log2 = (1.0f / sqrtf((float)head_size)) * 1.4426950408889634f;
+    p.trace = g_ctx_trace;
     static bool attr_set = false;
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(context_attn_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,

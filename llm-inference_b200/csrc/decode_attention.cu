@@ -286,19 +286,23 @@ decode_attn_generic_kernel(const AttnParams p, float* __restrict__ scores) {
 // ------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------
-static int attn_pick_splits(int batch, int kv_head_num, int step) {
+static int attn_pick_splits(int batch, int kv_head_num, int step, int group) {
     const int ctas = batch * kv_head_num;
     const int target = 2 * sm_count();
     int splits = (target + ctas - 1) / ctas;
-    const int max_by_len = (step + 63) / 64;  // keep >= 64 keys per split
+    // keep >= 64 (key, query head) pairs per split, at least 16 keys: with GQA every key row serves `group`
+    // query heads, and tensor-parallel shards leave few kv heads per rank (70B tp8: ONE) to spread over the SMs
+    int min_keys = 64 / (group < 1 ? 1 : group);
+    if (min_keys < 16) min_keys = 16;
+    const int max_by_len = (step + min_keys - 1) / min_keys;
     if (splits > max_by_len) splits = max_by_len;
     if (splits < 1) splits = 1;
     if (splits > 64) splits = 64;
     return splits;
 }
 
-int attn_pick_splits_public(int batch, int kv_head_num, int step) {
-    return attn_pick_splits(batch, kv_head_num, step);
+int attn_pick_splits_public(int batch, int kv_head_num, int step, int group) {
+    return attn_pick_splits(batch, kv_head_num, step, group);
 }
 
 static bool attn_fast_shape(int head_num, int kv_head_num, int head_size, int esz) {
@@ -374,7 +378,7 @@ extern "C" int b200_decode_attention_ex(const void* qkv, void* k_cache_layer, vo
     const bool fast = attn_fast_shape(head_num, kv_head_num, head_size, esz) && al(qkv) &&
                       al(k_cache_layer) && al(v_cache_layer);
     if (fast) {
-        const int splits = attn_pick_splits(batch, kv_head_num, step);
+        const int splits = attn_pick_splits(batch, kv_head_num, step, head_num / kv_head_num);
         if (splits > 1) {
             const size_t ml = (size_t)batch * head_num * splits * 2 * sizeof(float);
             const size_t need = ((ml + 255) & ~(size_t)255) +

@@ -440,7 +440,7 @@ extern "C" int b200_engine_fill_kv_random(b200_engine* e, int len, uint64_t seed
 // one decode step
 // ------------------------------------------------------------------------------------------
 namespace b200 {
-int attn_pick_splits_public(int batch, int kv_head_num, int step);  // decode_attention.cu
+int attn_pick_splits_public(int batch, int kv_head_num, int step, int group);  // decode_attention.cu
 }
 
 static int gemv(b200_engine* e, const void* x, const void* W, void* y, int N, int K, unsigned flags,
@@ -588,7 +588,7 @@ static int run_step(b200_engine* e) {
         e->step += 1;
         return 0;
     }
-    const int key = attn_pick_splits_public(e->batch, e->hk, e->step + 1);
+    const int key = attn_pick_splits_public(e->batch, e->hk, e->step + 1, e->h / e->hk);
     auto it = e->graphs.find(key);
     if (it == e->graphs.end()) {
         const uint64_t before = b200_launch_count();
