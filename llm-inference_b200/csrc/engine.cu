@@ -494,6 +494,8 @@ static int tp_sum(b200_engine* e, void* buf, size_t count) {
         RC(b200_p2p_allreduce(e->p2p, buf, count, e->cfg.dtype, e->stream));
     else if (e->allreduce)
         RC(e->allreduce(buf, count, e->cfg.dtype, e->stream, e->allreduce_user));
+    else if (e->p2p)   // never skip the exchange silently: partial sums would pass for results
+        return fail("tensor-parallel sum: message larger than the b200_p2p communicator and no allreduce hook installed");
     return 0;
 }
 
