@@ -24,8 +24,14 @@
 //               row maximum through smem (one named barrier per tile), P_j written as fp16 into the
 //               swizzled K-major A-operand layout; then o = o * alpha_{j-1} + O_{j-1} for the thread's 64
 //               output columns (tcgen05.ld), so P_{j-1} V_{j-1} runs under the softmax of tile j;
-//               final o / (l0 + l1 + 1e-6) -> fp16 -> out. (First version: 4 softmax + 4 accumulate warps,
-//               one warp per scheduler on the critical exp2 chain: 5700 clocks per tile, tensor pipe 22 %.)
+//               final o / (l0 + l1 + 1e-6) -> fp16 -> out.
+//               Measured history (ncu at cfg3, tools/ctx_trace.py): v1 = 4 softmax + 4 accumulate warps with two
+//               TMEM passes, 324 us per layer; this version 261 us, a key tile = 2850 clocks of the compute warps
+//               (425 score read + max exchange, 1580 exp2 - the 128x128 ex2 alone are 1024 clocks of the 16/clk
+//               MUFU pipe -, 670 fold) against 1024 tensor clocks. Tried and dropped: two warp groups on
+//               alternating key tiles with private (m, l, O) streams merged at the end (so that one group's MUFU
+//               phase would run under the other's TMEM phases): 128 fp32 outputs per thread cap the kernel at
+//               168 registers for 320 threads (register allocation in 4-warp units) -> spills, 317 us.
 // TMEM: 2 x 128 score columns + 2 x 128 output columns = 512. Shared memory: Q 32 KB + K 2 x 32 KB +
 // V 2 x 32 KB + P 2 x 32 KB + 3 KB of alpha / l / mbarriers = 226.7 KB (one CTA per SM).
 //
