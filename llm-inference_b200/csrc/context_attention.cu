@@ -31,7 +31,9 @@
 //               MUFU pipe -, 670 fold) against 1024 tensor clocks. Tried and dropped: two warp groups on
 //               alternating key tiles with private (m, l, O) streams merged at the end (so that one group's MUFU
 //               phase would run under the other's TMEM phases): 128 fp32 outputs per thread cap the kernel at
-//               168 registers for 320 threads (register allocation in 4-warp units) -> spills, 317 us.
+//               168 registers for 320 threads (register allocation in 4-warp units) -> spills, 317 us;
+//               ex2.approx.f16x2 (one MUFU op per pair, MUFU.EX2.F16 in SASS) off the diagonal: 271 us, no gain
+//               (the extra cvt / unpack instructions cost what the MUFU pipe saves).
 // TMEM: 2 x 128 score columns + 2 x 128 output columns = 512. Shared memory: Q 32 KB + K 2 x 32 KB +
 // V 2 x 32 KB + P 2 x 32 KB + 3 KB of alpha / l / mbarriers = 226.7 KB (one CTA per SM).
 //
