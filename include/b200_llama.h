@@ -86,6 +86,14 @@ int b200_qkv_bias_rope_transpose(void* q, void* k, void* v, const void* qkv, con
                                  int head_num, int kv_head_num, int head_size, int rotary_dim,
                                  float rotary_base, int dtype, void* stream);
 
+/* a8 + a9 in one pass (engine prefill): q as above; rotated k and v go straight to rows
+ * history_len[b] + t of the cache layer slice [batch, kv_head_num, max_seq_len, head_size]. */
+int b200_qkv_bias_rope_to_cache(void* q, void* k_cache_layer, void* v_cache_layer, const void* qkv,
+                                const void* bias, const int* padding_offset, const int* history_len,
+                                int batch, int seq_len, int token_num, int head_num, int kv_head_num,
+                                int head_size, int max_seq_len, int rotary_dim, float rotary_base,
+                                int dtype, void* stream);
+
 /* a9  launchConcatKVCache      src/kernels/concat_past_kv.cu:103
  * k_src,v_src [batch, kv_head_num, max_q_len, head_size] -> cache layer slice
  * [batch, kv_head_num, max_seq_len, head_size] at row history_len[b]+t for t < cur_len[b].

@@ -736,10 +736,10 @@ extern "C" int b200_engine_prefill(b200_engine* e, const int* ids_host, int len,
         const size_t layer_off = (size_t)l * e->layer_kv_elems;
         RC(b200_rmsnorm(x, res, w.attn_norm, Nt, H, e->cfg.rms_eps, dt, s));
         RC(linear(x, w.qkv, qkv, e->qkv_n, H));
-        RC(b200_qkv_bias_rope_transpose(q, k, v, qkv, nullptr, pad, hists, lens, B, len, Nt, e->h, e->hk, e->d,
-                                        e->cfg.rotary_dim, e->cfg.rotary_base, dt, s));
-        RC(b200_concat_kv_cache(k, v, e->k_cache, e->v_cache, layer_off, lens, hists, B, e->hk, len, e->cfg.max_seq_len,
-                                e->d, dt, s));
+        // bias/RoPE/transpose with ConcatKV folded in: k, v land in the cache rows directly
+        RC(b200_qkv_bias_rope_to_cache(q, e->k_cache + layer_off * es, e->v_cache + layer_off * es, qkv, nullptr, pad, hists,
+                                       B, len, Nt, e->h, e->hk, e->d, e->cfg.max_seq_len, e->cfg.rotary_dim,
+                                       e->cfg.rotary_base, dt, s));
         if (flash) {
             RC(b200_context_attention(q, e->k_cache + layer_off * es, e->v_cache + layer_off * es, att, pad, lens, hists, B,
                                       len, Nt, e->h, e->hk, e->d, e->cfg.max_seq_len, dt, s));

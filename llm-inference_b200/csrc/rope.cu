@@ -54,7 +54,7 @@ qkv_rope_transpose_kernel(T* __restrict__ q, T* __restrict__ k, T* __restrict__ 
                           const T* __restrict__ qkv, const T* __restrict__ bias,
                           const int* __restrict__ padding_offset,
                           const int* __restrict__ history_len, int seq_len, int head_num,
-                          int kv_head_num, int head_size, int rot_dim, float base) {
+                          int kv_head_num, int head_size, int rot_dim, float base, int kv_rows, int to_cache) {
     constexpr int E = DT<T>::kPer16B;
     extern __shared__ float2 cs[];  // [head_size/2]; identity beyond rot_dim/2
     pdl_wait();
@@ -63,6 +63,10 @@ qkv_rope_transpose_kernel(T* __restrict__ q, T* __restrict__ k, T* __restrict__ 
     const int b = dst_token / seq_len;
     const int local = dst_token - b * seq_len;
     const int pos = history_len[b] + local;
+    // k / v destination rows: the padded [B, hk, seq_len, d] buffers of the reference, or (to_cache) straight
+    // the KV-cache layer slice [B, hk, kv_rows = max_seq, d] at row history + local, which is where
+    // launchConcatKVCache (concat_past_kv.cu:17-56) would copy them next
+    const int kv_local = to_cache ? pos : local;
     const int half_d = head_size >> 1, half_rot = rot_dim >> 1;
     for (int i = threadIdx.x; i < half_d; i += blockDim.x)
         cs[i] = (i < half_rot) ? rope_cos_sin(i, rot_dim, base, (float)pos) : make_float2(1.f, 0.f);
@@ -99,7 +103,7 @@ qkv_rope_transpose_kernel(T* __restrict__ q, T* __restrict__ k, T* __restrict__ 
             if (head < head_num)
                 d = q + (((size_t)b * head_num + head) * seq_len + local) * head_size + p * E;
             else
-                d = k + (((size_t)b * kv_head_num + (head - head_num)) * seq_len + local) * head_size + p * E;
+                d = k + (((size_t)b * kv_head_num + (head - head_num)) * kv_rows + kv_local) * head_size + p * E;
             st16(d, Unpack<T>::put(lo));
             st16(d + half_d, Unpack<T>::put(hi));
         } else {
@@ -116,7 +120,7 @@ qkv_rope_transpose_kernel(T* __restrict__ q, T* __restrict__ k, T* __restrict__ 
                 for (int i = 0; i < E; ++i) f[i] += bf[i];
                 val = Unpack<T>::put(f);
             }
-            st16(v + (((size_t)b * kv_head_num + head) * seq_len + local) * head_size + p * E, val);
+            st16(v + (((size_t)b * kv_head_num + head) * kv_rows + kv_local) * head_size + p * E, val);
         }
     }
     pdl_launch_dependents();
@@ -136,19 +140,20 @@ template <typename T>
 static int qkv_rope_impl(void* q, void* k, void* v, const void* qkv, const void* bias,
                          const int* padding_offset, const int* history_len, int seq_len,
                          int token_num, int head_num, int kv_head_num, int head_size, int rot_dim,
-                         float base, cudaStream_t s) {
+                         float base, cudaStream_t s, int kv_rows = 0, int to_cache = 0) {
     constexpr int E = DT<T>::kPer16B;
+    if (!to_cache) kv_rows = seq_len;
     B200_RETURN_IF((head_size / 2) % E != 0, B200_EUNSUPPORTED);
     const size_t smem = (size_t)(head_size / 2) * sizeof(float2);
     cudaError_t e;
     if (bias)
         e = launch_k(qkv_rope_transpose_kernel<T, true>, dim3(token_num), dim3(256), smem, s, true,
                      (T*)q, (T*)k, (T*)v, (const T*)qkv, (const T*)bias, padding_offset,
-                     history_len, seq_len, head_num, kv_head_num, head_size, rot_dim, base);
+                     history_len, seq_len, head_num, kv_head_num, head_size, rot_dim, base, kv_rows, to_cache);
     else
         e = launch_k(qkv_rope_transpose_kernel<T, false>, dim3(token_num), dim3(256), smem, s,
                      true, (T*)q, (T*)k, (T*)v, (const T*)qkv, (const T*)nullptr, padding_offset,
-                     history_len, seq_len, head_num, kv_head_num, head_size, rot_dim, base);
+                     history_len, seq_len, head_num, kv_head_num, head_size, rot_dim, base, kv_rows, to_cache);
     count_launch();
     return (int)e;
 }
@@ -203,5 +208,32 @@ extern "C" int b200_qkv_bias_rope_transpose(void* q, void* k, void* v, const voi
         return b200::qkv_rope_impl<__half>(q, k, v, qkv, bias, padding_offset, history_len,
                                            seq_len, token_num, head_num, kv_head_num, head_size,
                                            rotary_dim, rotary_base, s);
+    return B200_EINVAL;
+}
+
+/* launchAddFusedQKVBiasTransposeAndRoPE (qkv_bias_and_RoPE.cu:248) and launchConcatKVCache
+ * (concat_past_kv.cu:103) in one pass: q goes to [batch, head_num, seq_len, head_size] as before, the rotated
+ * keys and the values go straight to rows history_len[b] + t of the KV-cache layer slice
+ * [batch, kv_head_num, max_seq_len, head_size] (the padded k / v buffers are never written). */
+extern "C" int b200_qkv_bias_rope_to_cache(void* q, void* k_cache_layer, void* v_cache_layer, const void* qkv,
+                                           const void* bias, const int* padding_offset, const int* history_len,
+                                           int batch, int seq_len, int token_num, int head_num, int kv_head_num,
+                                           int head_size, int max_seq_len, int rotary_dim, float rotary_base,
+                                           int dtype, void* stream) {
+    B200_RETURN_IF(!q || !k_cache_layer || !v_cache_layer || !qkv || !padding_offset || !history_len, B200_EINVAL);
+    B200_RETURN_IF(batch <= 0 || seq_len <= 0 || token_num < 0 || head_num <= 0 || kv_head_num <= 0 ||
+                       head_size <= 0 || max_seq_len <= 0,
+                   B200_EINVAL);
+    B200_RETURN_IF(rotary_dim <= 0 || rotary_dim > head_size || (rotary_dim & 1), B200_EINVAL);
+    if (token_num == 0) return B200_OK;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (dtype == B200_F32)
+        return b200::qkv_rope_impl<float>(q, k_cache_layer, v_cache_layer, qkv, bias, padding_offset, history_len,
+                                          seq_len, token_num, head_num, kv_head_num, head_size, rotary_dim,
+                                          rotary_base, s, max_seq_len, 1);
+    if (dtype == B200_F16)
+        return b200::qkv_rope_impl<__half>(q, k_cache_layer, v_cache_layer, qkv, bias, padding_offset, history_len,
+                                           seq_len, token_num, head_num, kv_head_num, head_size, rotary_dim,
+                                           rotary_base, s, max_seq_len, 1);
     return B200_EINVAL;
 }
