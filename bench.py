@@ -62,7 +62,7 @@ def workload(args):
         return dict(name="LLaMA-2-70B-shaped GQA (64 q / 8 kv heads) fp16 decode, tensor-parallel (configs[4])",
                     batch=args.batch or 1, context=args.context or 512, scaling="strong")
     if args.workload == "cfg4":
-        return dict(name="LLaMA-2-7B fp16 decode, batch 32 x KV 4096 (configs[3])", batch=32,
+        return dict(name="LLaMA-2-7B fp16 decode, batch 32 x KV 4096 (configs[3])", batch=args.batch or 32,
                     context=args.context or 4096, scaling="strong")
     return dict(name="LLaMA-2-7B fp16 random-init full model, batch 1 greedy decode, 512-token context (configs[1])",
                 batch=1, context=args.context or 512, scaling="weak")

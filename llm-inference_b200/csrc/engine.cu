@@ -507,7 +507,9 @@ static int enqueue_step(b200_engine* e) {
     // fused GEMV path: batches that fit the GEMV tile. Larger batches run the reference's launch
     // sequence with the linears on the tcgen05 weight-streaming GEMM (weights are read once per
     // step instead of once per 8-token tile).
-    const bool fused = (e->mode & B200_ENGINE_FUSED) && B <= B200_GEMV_MAX_TOKENS;
+    // fp16 batches of 5..8 also take the tensor-core path: eight x-rows of K = 11008 crowd the GEMV's weight ring out
+    // of shared memory (measured at batch 8 x KV 4096: 12.0 ms per step fused vs the figure in DESIGN §4c)
+    const bool fused = (e->mode & B200_ENGINE_FUSED) && B <= (dt == B200_F16 && !tp ? 4 : B200_GEMV_MAX_TOKENS);
     auto linear = [&](const void* x, const void* W, void* y, int N, int K) {
         return b200_linear(x, W, nullptr, y, B, N, K, 1, dt, e->lin_ws, e->lin_ws_bytes, s);
     };

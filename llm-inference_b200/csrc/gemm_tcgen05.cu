@@ -370,7 +370,7 @@ static int pick_splits(int m_tiles, int k_blocks, int sms) {
 int gemm2_tcgen05_f16(const void* x, const void* W, const void* bias, void* y, int M, int N, int K, bool glu, cudaStream_t s);
 
 size_t gemm_tcgen05_workspace_bytes(int M, int N, int K) {
-    if (M <= B200_GEMV_MAX_TOKENS || M > 256) return 0;
+    if (M <= 4 || M > 256) return 0;
     const int splits = pick_splits((N + kBM - 1) / kBM, (K + kBK - 1) / kBK, sm_count());
     return splits > 1 ? (size_t)splits * M * N * sizeof(float) : 0;
 }

@@ -129,6 +129,13 @@ extern "C" int b200_linear(const void* x, const void* W, const void* bias, void*
     cudaStream_t s = (cudaStream_t)stream;
     const int E = dtype == B200_F16 ? 8 : 4;
     auto al = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; };
+    // fp16 with 5..8 token rows: the GEMV keeps all 8 x-rows in shared memory, which at K = 11008 leaves no room for
+    // its weight ring (it then walks the tokens in two halves and streams the weights twice); the tcgen05
+    // weight-streaming GEMM reads every weight byte once, so it takes these shapes when it can
+    if (trans_b && dtype == B200_F16 && n_tokens > 4 && n_tokens <= B200_GEMV_MAX_TOKENS) {
+        int rc = gemm_tcgen05_f16(x, W, bias, y, n_tokens, N, K, workspace, workspace_bytes, s);
+        if (rc != B200_EUNSUPPORTED) return rc;
+    }
     if (trans_b && n_tokens <= B200_GEMV_MAX_TOKENS && K % E == 0 && al(x) && al(W)) {
         int rc = gemv_plain(x, W, bias, y, n_tokens, N, K, dtype, s);
         if (rc != B200_EUNSUPPORTED) return rc;

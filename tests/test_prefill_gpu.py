@@ -92,3 +92,40 @@ def test_prefill_matches_token_by_token_decode(pkg):
     assert_close(va.float().cpu().numpy(), vb.float().cpu().numpy(), "fp16", "v cache")
     a.close()
     b.close()
+
+
+@pytest.mark.parametrize("kind", ["fp16", "fp32"])
+def test_rope_to_cache_equals_transpose_then_concat(pkg, kind):
+    """b200_qkv_bias_rope_to_cache = launchAddFusedQKVBiasTransposeAndRoPE + launchConcatKVCache in one pass:
+    bit-exact against the two-kernel sequence (both ours; each is pinned by the oracle in test_parity_gpu)."""
+    import ctypes as C
+    import torch
+    ops, capi = pkg.ops, pkg.capi
+    dt = torch.float16 if kind == "fp16" else torch.float32
+    B, h, hk, d, S, max_seq = 3, 4, 2, 128, 9, 40
+    lens = np.array([5, 9, 2], np.int32)
+    hist = np.array([7, 0, 30], np.int32)
+    nt = int(lens.sum())
+    g = torch.Generator(device="cuda").manual_seed(3)
+    qkv = (torch.rand(nt, h + 2 * hk, d, device="cuda", generator=g) - 0.5).to(dt)
+    bias = (torch.rand((h + 2 * hk) * d, device="cuda", generator=g) - 0.5).to(dt)
+    dev = lambda a: torch.from_numpy(a).cuda()
+    pad = torch.zeros(B * S, dtype=torch.int32, device="cuda")
+    cum = torch.zeros(B + 1, dtype=torch.int32, device="cuda")
+    ops.launchCalPaddingoffset(pad.view(B, S), cum, dev(lens))
+    q1 = torch.zeros(B, h, S, d, dtype=dt, device="cuda")
+    k1 = torch.zeros(B, hk, S, d, dtype=dt, device="cuda")
+    v1 = torch.zeros(B, hk, S, d, dtype=dt, device="cuda")
+    ops.launchAddFusedQKVBiasTransposeAndRoPE(q1, k1, v1, qkv, bias, pad, dev(hist), dev(lens), 128, 10000.0)
+    kc1 = torch.full((1, B, hk, max_seq, d), 3.0, dtype=dt, device="cuda")
+    vc1 = torch.full((1, B, hk, max_seq, d), 3.0, dtype=dt, device="cuda")
+    ops.launchConcatKVCache(k1, v1, 0, dev(lens), dev(hist), kc1, vc1)
+    q2 = torch.zeros_like(q1)
+    kc2, vc2 = torch.full_like(kc1, 3.0), torch.full_like(vc1, 3.0)
+    p = lambda t: C.c_void_p(t.data_ptr())
+    hd = dev(hist)
+    rc = capi.lib().b200_qkv_bias_rope_to_cache(p(q2), p(kc2), p(vc2), p(qkv), p(bias), p(pad), p(hd), B, S, nt, h, hk, d,
+                                                max_seq, 128, 10000.0, capi.F16 if kind == "fp16" else capi.F32, None)
+    torch.cuda.synchronize()
+    assert rc == 0
+    assert torch.equal(q1, q2) and torch.equal(kc1, kc2) and torch.equal(vc1, vc2)
