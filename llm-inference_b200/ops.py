@@ -218,8 +218,9 @@ def launchDecoderMaskedMHA(qkv_buf, layer_id, k_cache, v_cache, step, mha_output
 
 def gemv_fused(x, W, y, flags=0, bias=None, gamma=None, eps=0.0, N=None, k_cache_layer=None,
                v_cache_layer=None, head_num=0, kv_head_num=0, head_size=0, step=0, rotary_dim=0,
-               rotary_base=10000.0, step_dev=None, rope_den=None):
-    """b200_gemv_fused: decode-time linear with fused prologue / epilogue (engine path)."""
+               rotary_base=10000.0, step_dev=None, rope_den=None, p2p=None):
+    """b200_gemv_fused: decode-time linear with fused prologue / epilogue (engine path).
+    p2p: a b200_p2p* handle (int / c_void_p): the outputs are pushed to the ranks' receive buffers instead of y."""
     a = capi.GemvArgs()
     a.x, a.W, a.y = x.data_ptr(), W.data_ptr(), y.data_ptr()
     a.bias = bias.data_ptr() if bias is not None else None
@@ -236,6 +237,7 @@ def gemv_fused(x, W, y, flags=0, bias=None, gamma=None, eps=0.0, N=None, k_cache
     a.step, a.rotary_dim, a.rotary_base = int(step), rotary_dim, rotary_base
     a.step_dev = step_dev.data_ptr() if step_dev is not None else None
     a.rope_den = rope_den.data_ptr() if rope_den is not None else None
+    a.p2p = p2p
     _check(capi.lib().b200_gemv_fused(C.byref(a), _dt(x), _stream()), "b200_gemv_fused")
 
 

@@ -188,3 +188,42 @@ def test_engine_tensor_parallel_two_ranks_vs_unsharded_oracle(tmp_path, kind, fu
     for r in range(world):
         assert_close(got[r]["k"], om.k[:, :, r * hkl:(r + 1) * hkl], kind, f"rank {r} K shard")
         assert_close(got[r]["v"], om.v[:, :, r * hkl:(r + 1) * hkl], kind, f"rank {r} V shard")
+
+
+def test_p2p_single_rank_gemv_push_and_reduce(pkg):
+    """One-GPU coverage of the fused GEMV-push + reduce path (world = 1: the only slot is this rank's own, the
+    wire format, tags, buffer parity and call counter are exercised exactly as with peers): b200_gemv_fused with
+    args.p2p followed by b200_p2p_reduce_add must equal the GEMV with the residual epilogue, bit for bit, over
+    several calls; b200_p2p_allreduce_add / b200_p2p_allreduce with one rank are the identity sum."""
+    import ctypes as C
+    E, ops, capi = pkg.engine, pkg.ops, pkg.capi
+    lib = E._lib()
+    B, N, K = 2, 4096, 1024
+    comm = lib.b200_p2p_create(1, 0, B * N * 2)
+    assert comm
+    h = C.create_string_buffer(int(lib.b200_p2p_handle_bytes()))
+    assert lib.b200_p2p_local_handle(comm, h) == 0
+    assert lib.b200_p2p_connect(comm, h.raw) == 0
+    g = torch.Generator(device="cuda").manual_seed(1)
+    W = ((torch.rand(N, K, device="cuda", generator=g) - 0.5) * 0.1).half()
+    for it in range(5):
+        x = (torch.rand(B, K, device="cuda", generator=g) - 0.5).half()
+        hidden = (torch.rand(B, N, device="cuda", generator=g) - 0.5).half()
+        want = hidden.clone()
+        ops.gemv_fused(x, W, want, capi.GEMV_RESIDUAL)
+        got = hidden.clone()
+        scratch = torch.zeros(B, N, dtype=torch.float16, device="cuda")
+        ops.gemv_fused(x, W, scratch, 0, p2p=comm)
+        st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        assert lib.b200_p2p_reduce_add(comm, C.c_void_p(got.data_ptr()), B * N, capi.F16, st) == 0
+        torch.cuda.synchronize()
+        assert torch.equal(got, want), f"call {it}"
+        assert float(scratch.abs().max()) == 0.0, "with p2p the GEMV must not write y"
+        part = (torch.rand(B, N, device="cuda", generator=g) - 0.5).half()
+        acc = hidden.clone()
+        assert lib.b200_p2p_allreduce_add(comm, C.c_void_p(part.data_ptr()), C.c_void_p(acc.data_ptr()), B * N, capi.F16, st) == 0
+        buf = part.clone()
+        assert lib.b200_p2p_allreduce(comm, C.c_void_p(buf.data_ptr()), B * N, capi.F16, st) == 0
+        torch.cuda.synchronize()
+        assert torch.equal(acc, (hidden.float() + part.float()).half()) and torch.equal(buf, part)
+    lib.b200_p2p_destroy(comm)
