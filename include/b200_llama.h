@@ -75,6 +75,11 @@ int b200_rope_decode_ex(void* qkv, int batch, int head_num, int kv_head_num, int
                         const int* step_dev, int rotary_dim, float rotary_base, int dtype,
                         void* stream);
 
+/* same with the DEVICE table of b200_rope_table() (rope_den may be NULL) */
+int b200_rope_decode_tab(void* qkv, int batch, int head_num, int kv_head_num, int head_size, int step,
+                         const int* step_dev, int rotary_dim, float rotary_base, const float* rope_den,
+                         int dtype, void* stream);
+
 /* a8  launchAddFusedQKVBiasTransposeAndRoPE   src/kernels/qkv_bias_and_RoPE.cu:248
  * QKV [token_num, head_num+2*kv_head_num, head_size] (no padding) ->
  * q [batch, head_num, seq_len, head_size], k,v [batch, kv_head_num, seq_len, head_size];

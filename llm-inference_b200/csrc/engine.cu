@@ -547,8 +547,8 @@ static int enqueue_step(b200_engine* e) {
             // the reference's launch sequence, one kernel per launch* (self_decoder.cpp:53-85)
             RC(b200_rmsnorm(e->hidden, e->residual, w.attn_norm, B, H, e->cfg.rms_eps, dt, s));
             RC(linear(e->hidden, w.qkv, e->qkv, e->qkv_n, H));
-            RC(b200_rope_decode_ex(e->qkv, B, e->h, e->hk, e->d, ref_step, e->step_dev, e->cfg.rotary_dim,
-                                   e->cfg.rotary_base, dt, s));
+            RC(b200_rope_decode_tab(e->qkv, B, e->h, e->hk, e->d, ref_step, e->step_dev, e->cfg.rotary_dim,
+                                    e->cfg.rotary_base, e->rope_den, dt, s));
             RC(b200_decode_attention_ex(e->qkv, kc, vc, e->attn, e->attn_ws, e->attn_ws_bytes, B, e->h, e->hk, e->d,
                                         e->cfg.max_seq_len, ref_step, e->step_dev, 1, dt, s));
             RC(linear(e->attn, w.o, e->hidden, H, e->h * e->d));

@@ -20,27 +20,53 @@ __device__ __forceinline__ float2 rope_cos_sin(int pair, int rot_dim, float base
 template <typename T>
 __global__ void __launch_bounds__(256)
 rope_decode_kernel(T* __restrict__ qkv, int head_num, int kv_head_num, int head_size, int pos,
-                   const int* __restrict__ step_dev, int rot_dim, float base) {
-    extern __shared__ float2 cs[];  // [rot_dim/2]
-    const int half_rot = rot_dim >> 1;
+                   const int* __restrict__ step_dev, int rot_dim, float base, const float* __restrict__ den) {
+    constexpr int E = DT<T>::kPer16B;
+    extern __shared__ float2 cs[];  // [head_size/2]; identity beyond rot_dim/2
+    const int half_rot = rot_dim >> 1, half_d = head_size >> 1;
     // step_dev (CUDA-graph replay) is only ever written by the LAST kernel of the previous step,
     // which has fully completed before any kernel of this step starts, so it may be read early
     if (step_dev) pos = *step_dev - 1;
-    for (int i = threadIdx.x; i < half_rot; i += blockDim.x)
-        cs[i] = rope_cos_sin(i, rot_dim, base, (float)pos);
+    for (int i = threadIdx.x; i < half_d; i += blockDim.x) {
+        if (i >= half_rot) { cs[i] = make_float2(1.f, 0.f); continue; }
+        // den[i] = base^(2i/rot_dim) from b200_rope_table(): the same correctly rounded float rope_angle() forms
+        const float ang = den ? (float)pos / den[i] : rope_angle(i, rot_dim, base, (float)pos);
+        cs[i] = make_float2(cosf(ang), sinf(ang));
+    }
     pdl_wait();
     __syncthreads();
     const int qkv_heads = head_num + 2 * kv_head_num;
     T* tok = qkv + (size_t)blockIdx.x * qkv_heads * head_size;
-    const int half_d = head_size >> 1;
-    const int items = (head_num + kv_head_num) * half_rot;  // q heads then k heads are contiguous
-    for (int it = threadIdx.x; it < items; it += blockDim.x) {
-        const int head = it / half_rot, i = it - head * half_rot;
-        T* p = tok + (size_t)head * head_size + i;
-        const float a = DT<T>::to_f(p[0]), b = DT<T>::to_f(p[half_d]);
-        const float2 c = cs[i];
-        p[0] = DT<T>::from_f(c.x * a - c.y * b);
-        p[half_d] = DT<T>::from_f(c.x * b + c.y * a);
+    if ((half_d % E) == 0 && (reinterpret_cast<uintptr_t>(qkv) & 15u) == 0) {
+        // 16-byte packets: item = packet p of the low half + packet p of the high half of one q / k head
+        const int pk_half = half_d / E;
+        const int items = (head_num + kv_head_num) * pk_half;
+        for (int it = threadIdx.x; it < items; it += blockDim.x) {
+            const int head = it / pk_half, pkt = it - head * pk_half;
+            T* p = tok + (size_t)head * head_size + pkt * E;
+            float lo[E], hi[E];
+            Unpack<T>::get(ld16(p), lo);
+            Unpack<T>::get(ld16(p + half_d), hi);
+#pragma unroll
+            for (int i = 0; i < E; ++i) {
+                const float2 c = cs[pkt * E + i];
+                const float a = lo[i], b = hi[i];
+                lo[i] = c.x * a - c.y * b;
+                hi[i] = c.x * b + c.y * a;
+            }
+            st16(p, Unpack<T>::put(lo));
+            st16(p + half_d, Unpack<T>::put(hi));
+        }
+    } else {
+        const int items = (head_num + kv_head_num) * half_rot;  // q heads then k heads are contiguous
+        for (int it = threadIdx.x; it < items; it += blockDim.x) {
+            const int head = it / half_rot, i = it - head * half_rot;
+            T* p = tok + (size_t)head * head_size + i;
+            const float a = DT<T>::to_f(p[0]), b = DT<T>::to_f(p[half_d]);
+            const float2 c = cs[i];
+            p[0] = DT<T>::from_f(c.x * a - c.y * b);
+            p[half_d] = DT<T>::from_f(c.x * b + c.y * a);
+        }
     }
     pdl_launch_dependents();
 }
@@ -128,10 +154,11 @@ qkv_rope_transpose_kernel(T* __restrict__ q, T* __restrict__ k, T* __restrict__ 
 
 template <typename T>
 static int rope_decode_impl(void* qkv, int batch, int head_num, int kv_head_num, int head_size,
-                            int step, const int* step_dev, int rot_dim, float base, cudaStream_t s) {
+                            int step, const int* step_dev, int rot_dim, float base, cudaStream_t s,
+                            const float* den = nullptr) {
     cudaError_t e = launch_k(rope_decode_kernel<T>, dim3(batch), dim3(256),
-                             (size_t)(rot_dim / 2) * sizeof(float2), s, true, (T*)qkv, head_num,
-                             kv_head_num, head_size, step - 1, step_dev, rot_dim, base);
+                             (size_t)(head_size / 2) * sizeof(float2), s, true, (T*)qkv, head_num,
+                             kv_head_num, head_size, step - 1, step_dev, rot_dim, base, den);
     count_launch();
     return (int)e;
 }
@@ -160,9 +187,19 @@ static int qkv_rope_impl(void* q, void* k, void* v, const void* qkv, const void*
 
 }  // namespace b200
 
+extern "C" int b200_rope_decode_tab(void* qkv, int batch, int head_num, int kv_head_num, int head_size, int step,
+                                    const int* step_dev, int rotary_dim, float rotary_base, const float* rope_den,
+                                    int dtype, void* stream);
 extern "C" int b200_rope_decode_ex(void* qkv, int batch, int head_num, int kv_head_num,
                                    int head_size, int step, const int* step_dev, int rotary_dim,
                                    float rotary_base, int dtype, void* stream) {
+    return b200_rope_decode_tab(qkv, batch, head_num, kv_head_num, head_size, step, step_dev, rotary_dim, rotary_base,
+                                nullptr, dtype, stream);
+}
+/* rope_den: optional DEVICE table from b200_rope_table() (saves the double-precision pow per launch) */
+extern "C" int b200_rope_decode_tab(void* qkv, int batch, int head_num, int kv_head_num, int head_size, int step,
+                                    const int* step_dev, int rotary_dim, float rotary_base, const float* rope_den,
+                                    int dtype, void* stream) {
     B200_RETURN_IF(!qkv || batch < 0 || head_num <= 0 || kv_head_num <= 0 || head_size <= 0,
                    B200_EINVAL);
     B200_RETURN_IF(step < 1 || rotary_dim <= 0 || rotary_dim > head_size || (rotary_dim & 1) ||
@@ -172,10 +209,10 @@ extern "C" int b200_rope_decode_ex(void* qkv, int batch, int head_num, int kv_he
     cudaStream_t s = (cudaStream_t)stream;
     if (dtype == B200_F32)
         return b200::rope_decode_impl<float>(qkv, batch, head_num, kv_head_num, head_size, step,
-                                             step_dev, rotary_dim, rotary_base, s);
+                                             step_dev, rotary_dim, rotary_base, s, rope_den);
     if (dtype == B200_F16)
         return b200::rope_decode_impl<__half>(qkv, batch, head_num, kv_head_num, head_size, step,
-                                              step_dev, rotary_dim, rotary_base, s);
+                                              step_dev, rotary_dim, rotary_base, s, rope_den);
     return B200_EINVAL;
 }
 
