@@ -162,6 +162,12 @@ int b200_linear(const void* x, const void* W, const void* bias, void* y, int n_t
 int b200_linear_swiglu(const void* x, const void* W, void* out, int n_tokens, int inter, int K,
                        int dtype, void* stream);
 
+/* linear + launchAddResidual (add_residual.cu:58) in one launch: y = residual + x W^T, linear output
+ * rounded to fp16 before the sum as in the unfused pair. fp16 prefill shapes only, else
+ * B200_EUNSUPPORTED (run b200_linear + b200_add_residual). */
+int b200_linear_residual(const void* x, const void* W, const void* residual, void* y, int n_tokens,
+                         int N, int K, int dtype, void* stream);
+
 /* Fused decode-time linears (engine path; the unfused reference sequence they replace is cited).
  * All take W [N, K] row-major, n_tokens <= B200_GEMV_MAX_TOKENS.
  *

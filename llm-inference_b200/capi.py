@@ -61,6 +61,7 @@ PROTOTYPES = {
     "b200_context_attention_set_trace": (None, [_vp]),
     "b200_rope_decode_tab": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _i, C.c_float, _vp, _i, _vp]),
     "b200_qkv_bias_rope_to_cache": (_i, [_vp] * 7 + [_i] * 8 + [C.c_float, _i, _vp]),
+    "b200_linear_residual": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     "b200_linear_swiglu": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     "b200_topk": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp]),
 }

@@ -763,9 +763,14 @@ extern "C" int b200_engine_prefill(b200_engine* e, const int* ids_host, int len,
         } else if (rc_glu != 0) {
             return fail("b200_linear_swiglu failed", rc_glu);
         }
-        RC(linear(act, w.down, x, H, e->I));
-        if (tp) RC(tp_sum(e, x, (size_t)Nt * H));
-        RC(b200_add_residual(res, x, Nt, H, dt, s));
+        int rc_res = tp ? B200_EUNSUPPORTED : b200_linear_residual(act, w.down, res, x, Nt, H, e->I, dt, s);   // down + AddResidual
+        if (rc_res == B200_EUNSUPPORTED) {
+            RC(linear(act, w.down, x, H, e->I));
+            if (tp) RC(tp_sum(e, x, (size_t)Nt * H));
+            RC(b200_add_residual(res, x, Nt, H, dt, s));
+        } else if (rc_res != 0) {
+            return fail("b200_linear_residual failed", rc_res);
+        }
     }
     // ---- last token of each sequence -> final norm -> LM head -> top-1 (llama.cpp:221-232, :305)
     CU(cudaMemcpy2DAsync(e->hidden, (size_t)H * es, (const char*)x + (size_t)(len - 1) * H * es, (size_t)len * H * es,

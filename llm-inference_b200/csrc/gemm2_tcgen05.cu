@@ -28,6 +28,7 @@ constexpr uint32_t k2Smem = k2OffSlot + 16;
 struct Gemm2Params {
     __half* C;          // [tokens, ldc]
     const __half* bias; // [N] or nullptr (not with GLU)
+    const __half* residual;   // [tokens, ldc] or nullptr: C = half(half(acc + bias) + residual), launchAddResidual folded in
     int tokens, n_out;  // valid rows of A; valid output features (GLU: inter)
     int ldc, k_blocks;
     int m_tiles, n_tiles;   // tiles of 256 rows x (256 features | GLU: 128 features)
@@ -172,12 +173,19 @@ gemm2_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
                                     f[e] = __uint_as_float(v[q * 8 + e]);
                                     if (p.bias) f[e] += __half2float(p.bias[col0 + q * 8 + e]);
                                 }
+                                if (p.residual) {   // the linear's output is rounded to fp16 first, as the unfused pair does
+                                    float r[8];
+                                    Unpack<__half>::get(ld16(p.residual + (size_t)row * p.ldc + col0 + q * 8), r);
+#pragma unroll
+                                    for (int e = 0; e < 8; ++e) f[e] = __half2float(__float2half_rn(f[e])) + r[e];
+                                }
                                 st16(dst + q * 8, Unpack<__half>::put(f));
                             }
                         } else {
                             for (int j = 0; j < 32 && col0 + j < p.n_out; ++j) {
                                 float f = __uint_as_float(v[j]);
                                 if (p.bias) f += __half2float(p.bias[col0 + j]);
+                                if (p.residual) f = __half2float(__float2half_rn(f)) + __half2float(p.residual[(size_t)row * p.ldc + col0 + j]);
                                 dst[j] = __float2half_rn(f);
                             }
                         }
@@ -236,15 +244,17 @@ static int gemm2_launch(const CUtensorMap& ma, const CUtensorMap& mb, const Gemm
 
 // y[M, N] = x[M, K] W[N, K]^T (+ bias) or, with glu, out[M, N] = silu(x Wg^T) * (x Wu^T) with W = [2N, K].
 // Returns B200_EUNSUPPORTED for shapes the pair kernel does not cover (the one-CTA kernel takes them).
-int gemm2_tcgen05_f16(const void* x, const void* W, const void* bias, void* y, int M, int N, int K, bool glu, cudaStream_t s) {
+int gemm2_tcgen05_f16(const void* x, const void* W, const void* bias, void* y, int M, int N, int K, bool glu, cudaStream_t s,
+                      const void* residual) {
     static int mode = -1;   // B200_GEMM_PAIR=0 keeps the one-CTA kernel
     if (mode < 0) { const char* e = getenv("B200_GEMM_PAIR"); mode = (e && e[0] == '0') ? 0 : 1; }
     if (!mode) return B200_EUNSUPPORTED;
     if (M < 512 || N < 256 || K < 64 || (K & 7)) return B200_EUNSUPPORTED;
-    if (glu && ((N & 127) || bias)) return B200_EUNSUPPORTED;
+    if (glu && ((N & 127) || bias || residual)) return B200_EUNSUPPORTED;
     Gemm2Params p{};
     p.C = reinterpret_cast<__half*>(y);
     p.bias = reinterpret_cast<const __half*>(bias);
+    p.residual = reinterpret_cast<const __half*>(residual);
     p.tokens = M; p.n_out = N; p.ldc = N;
     p.k_blocks = (K + k2BK - 1) / k2BK;
     p.m_tiles = (M + 255) / 256;

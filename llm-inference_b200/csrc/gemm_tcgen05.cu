@@ -367,7 +367,8 @@ static int pick_splits(int m_tiles, int k_blocks, int sms) {
     return best;
 }
 
-int gemm2_tcgen05_f16(const void* x, const void* W, const void* bias, void* y, int M, int N, int K, bool glu, cudaStream_t s);
+int gemm2_tcgen05_f16(const void* x, const void* W, const void* bias, void* y, int M, int N, int K, bool glu, cudaStream_t s,
+                      const void* residual = nullptr);
 
 size_t gemm_tcgen05_workspace_bytes(int M, int N, int K) {
     if (M <= 4 || M > 256) return 0;
@@ -455,6 +456,16 @@ int gemm_tcgen05_f16_swiglu(const void* x, const void* W, void* out, int M, int 
     if (!make_tma_map_2d(&ma, x, M, K, kBM) || !make_tma_map_2d(&mb, W, 2ll * inter, K, 128)) return B200_EUNSUPPORTED;
     const int units = p.m_tiles * p.n_tiles, sms = sm_count();
     return gemm_launch<256, false, true>(ma, mb, p, units < sms ? units : sms, s);
+}
+
+// y[M, N] = residual[M, N] + half(x W^T): launchLinearGemm followed by launchAddResidual (ffn.cpp:88 +
+// context_decoder.cpp:134) in the epilogue of the two-CTA GEMM; B200_EUNSUPPORTED outside its shapes
+int gemm_tcgen05_f16_residual(const void* x, const void* W, const void* residual, void* y, int M, int N, int K, cudaStream_t s) {
+    auto al = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15u) == 0; };
+    if (!al(x) || !al(W) || !al(y) || !al(residual) || (N & 7)) return B200_EUNSUPPORTED;
+    const char* e = getenv("B200_NO_TCGEN05");
+    if (e && e[0] == '1') return B200_EUNSUPPORTED;
+    return gemm2_tcgen05_f16(x, W, nullptr, y, M, N, K, false, s, residual);
 }
 
 }  // namespace b200

@@ -18,6 +18,7 @@ int gemm_tcgen05_f16(const void* x, const void* W, const void* bias, void* y, in
                      void* workspace, size_t workspace_bytes, cudaStream_t s);
 size_t gemm_tcgen05_workspace_bytes(int M, int N, int K);
 int gemm_tcgen05_f16_swiglu(const void* x, const void* W, void* out, int M, int inter, int K, cudaStream_t s);
+int gemm_tcgen05_f16_residual(const void* x, const void* W, const void* residual, void* y, int M, int N, int K, cudaStream_t s);
 
 constexpr int BM = 64, BN = 64, BK = 16;
 
@@ -169,4 +170,14 @@ extern "C" int b200_linear_swiglu(const void* x, const void* W, void* out, int n
     if (!x || !W || !out || n_tokens < 1 || inter < 1 || K < 1) return B200_EINVAL;
     if (dtype != B200_F16) return B200_EUNSUPPORTED;
     return b200::gemm_tcgen05_f16_swiglu(x, W, out, n_tokens, inter, K, (cudaStream_t)stream);
+}
+
+/* y[n_tokens, N] = residual + x W^T (W [N, K]): launchLinearGemm + launchAddResidual (add_residual.cu:58) in one
+ * tcgen05 launch, same rounding points (linear output rounded to fp16, then the sum). y may not alias x;
+ * B200_EUNSUPPORTED outside fp16 prefill shapes (n_tokens >= 512): run b200_linear + b200_add_residual then. */
+extern "C" int b200_linear_residual(const void* x, const void* W, const void* residual, void* y, int n_tokens, int N,
+                                    int K, int dtype, void* stream) {
+    if (!x || !W || !residual || !y || n_tokens < 1 || N < 1 || K < 1) return B200_EINVAL;
+    if (dtype != B200_F16) return B200_EUNSUPPORTED;
+    return b200::gemm_tcgen05_f16_residual(x, W, residual, y, n_tokens, N, K, (cudaStream_t)stream);
 }

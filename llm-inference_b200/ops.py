@@ -281,3 +281,11 @@ def linear_swiglu(inp, weight, out):
         raise RuntimeError("[b200][ERROR] linear_swiglu: weight must be [2*inter, K] Assertion fail")
     _check(capi.lib().b200_linear_swiglu(_p(inp), _p(weight), _p(out), nt, inter, k, _dt(inp), _stream()),
            "b200_linear_swiglu")
+
+
+def linear_residual(inp, weight, residual, out):
+    """b200_linear_residual: out = residual + inp W^T (launchLinearGemm + launchAddResidual in one tcgen05 launch)"""
+    nt, k = inp.shape
+    n = out.shape[1]
+    _check(capi.lib().b200_linear_residual(_p(inp), _p(weight), _p(residual), _p(out), nt, n, k, _dt(inp), _stream()),
+           "b200_linear_residual")

@@ -102,3 +102,21 @@ def test_gate_up_swiglu_rejects_decode_shapes(ops):
     w = torch.zeros(512, 256, dtype=torch.float16, device="cuda")
     with pytest.raises(RuntimeError, match="unsupported"):
         ops.linear_swiglu(x, w, torch.zeros(8, 256, dtype=torch.float16, device="cuda"))
+
+
+@pytest.mark.parametrize("m,n,k", [(512, 256, 64), (1000, 520, 264), (2048, 4096, 11008)])
+def test_linear_with_residual_epilogue(ops, m, n, k):
+    """b200_linear_residual against the oracle's linear (rounded to fp16) followed by add_residual"""
+    rng = np.random.default_rng(m + n)
+    f16 = lambda a: a.astype(np.float16).astype(np.float32)
+    x = f16(rng.uniform(-1, 1, (m, k)))
+    w = f16(rng.standard_normal((n, k)) * 0.05)
+    res = f16(rng.uniform(-2, 2, (m, n)))
+    y = np.zeros((m, n), np.float32)
+    cpu.linear(x, w, y, True)
+    want = f16(f16(y) + res)
+    out = torch.full((m, n), float("nan"), dtype=torch.float16, device="cuda")
+    ops.linear_residual(torch.from_numpy(x).cuda().half(), torch.from_numpy(w).cuda().half(),
+                        torch.from_numpy(res).cuda().half(), out)
+    torch.cuda.synchronize()
+    assert_close(out.float().cpu().numpy(), want, "fp16", f"linear + residual {m}x{n}x{k}")
