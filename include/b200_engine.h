@@ -141,6 +141,19 @@ int b200_engine_decode_step_host(b200_engine* e, const int* ids_in_host, int* id
  * ids are the first generated tokens (decode_step(NULL) continues), and ids_out_host (may be NULL:
  * then no host sync) receives them. */
 int b200_engine_prefill(b200_engine* e, const int* ids_host, int len, int* ids_out_host);
+
+/* Ragged batch (per-sequence lengths: the `step` per request SURVEY 8f-2 asks for instead of the
+ * reference's single host scalar, llama.h): sequence b gets lens_host[b] >= 1 prompt tokens,
+ * ids_host holds them packed back to back (sum(lens) ids, the padding-free layout the context
+ * decoder works on, llama.cpp:158-185), each appended after what THAT sequence has cached. When
+ * the lengths end up different, the decode steps that follow run with per-sequence positions and
+ * key counts (b200_rope_decode_ragged / b200_decode_attention_ragged; the unfused launch order,
+ * CUDA-graphed) and every sequence advances by one token per step; b200_engine_get_step() then
+ * reports the longest sequence, b200_engine_get_seq_steps() all of them (tokens cached, host int
+ * [batch]). b200_engine_reset / fill_kv_random return the engine to one shared step. */
+int b200_engine_prefill_ragged(b200_engine* e, const int* ids_host, const int* lens_host,
+                               int* ids_out_host);
+int b200_engine_get_seq_steps(const b200_engine* e, int* steps_out_host);
 int b200_engine_prefill_launches(const b200_engine* e);   /* kernel launches of the last prefill */
 
 /* The generation loop of Llama<T>::Response (llama.cpp:363-448) without the tokenizer: prefill the

@@ -79,6 +79,10 @@ int b200_rope_decode_ex(void* qkv, int batch, int head_num, int kv_head_num, int
 int b200_rope_decode_tab(void* qkv, int batch, int head_num, int kv_head_num, int head_size, int step,
                          const int* step_dev, int rotary_dim, float rotary_base, const float* rope_den,
                          int dtype, void* stream);
+/* ragged batch: token b sits at position seq_steps_dev[b] - 1 (DEVICE int [batch]) */
+int b200_rope_decode_ragged(void* qkv, int batch, int head_num, int kv_head_num, int head_size,
+                            const int* seq_steps_dev, int rotary_dim, float rotary_base,
+                            const float* rope_den, int dtype, void* stream);
 
 /* a8  launchAddFusedQKVBiasTransposeAndRoPE   src/kernels/qkv_bias_and_RoPE.cu:248
  * QKV [token_num, head_num+2*kv_head_num, head_size] (no padding) ->
@@ -230,6 +234,13 @@ int b200_decode_attention_ex(const void* qkv, void* k_cache_layer, void* v_cache
                              void* workspace, size_t workspace_bytes, int batch, int head_num,
                              int kv_head_num, int head_size, int max_seq_len, int step,
                              const int* step_dev, int append_kv, int dtype, void* stream);
+/* ragged batch: sequence b attends over seq_steps_dev[b] keys (DEVICE int [batch]; its new token
+ * is row seq_steps_dev[b]-1); max_step >= every entry sizes the split count and the workspace. */
+int b200_decode_attention_ragged(const void* qkv, void* k_cache_layer, void* v_cache_layer,
+                                 void* out, void* workspace, size_t workspace_bytes, int batch,
+                                 int head_num, int kv_head_num, int head_size, int max_seq_len,
+                                 int max_step, const int* seq_steps_dev, int append_kv, int dtype,
+                                 void* stream);
 
 /* Prefill attention without materialising scores / mask / repeated KV (replaces
  * context_attention.cpp:136-161: RepeatKV + QK^T + ScaleMaskSoftmax + PV + transpose):

@@ -30,6 +30,7 @@ struct AttnParams {
     float* part_o;    // [B, h, splits, d]
     int batch, head_num, kv_head_num, head_size, max_seq_len, step;
     const int* step_dev;
+    int step_stride;  // 0: *step_dev is the one step all sequences share; 1: step_dev[b] (ragged batch)
     int append_kv;
 };
 
@@ -50,9 +51,9 @@ decode_attn_split_kernel(const AttnParams p) {
     extern __shared__ float sm[];  // [kAttnWarps][G][2 + D]
 
     pdl_wait();
-    const int step = p.step_dev ? *p.step_dev : p.step;
     const int bh = blockIdx.x;
     const int b = bh / p.kv_head_num, kvh = bh - b * p.kv_head_num;
+    const int step = p.step_dev ? p.step_dev[b * p.step_stride] : p.step;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int pi = lane % PR, ks = lane / PR;
     const int qkv_heads = p.head_num + 2 * p.kv_head_num;
@@ -232,9 +233,9 @@ __global__ void __launch_bounds__(128)
 decode_attn_generic_kernel(const AttnParams p, float* __restrict__ scores) {
     __shared__ float scratch[33];
     pdl_wait();
-    const int step = p.step_dev ? *p.step_dev : p.step;
     const int d = p.head_size;
     const int b = blockIdx.x / p.head_num, head = blockIdx.x - b * p.head_num;
+    const int step = p.step_dev ? p.step_dev[b * p.step_stride] : p.step;
     const int kvh = head / (p.head_num / p.kv_head_num);
     const int qkv_heads = p.head_num + 2 * p.kv_head_num;
     const T* tok = reinterpret_cast<const T*>(p.qkv) + (size_t)b * qkv_heads * d;
@@ -357,11 +358,11 @@ extern "C" size_t b200_decode_attention_workspace_bytes(int batch, int head_num,
     return (part > generic ? part : generic) + 256;
 }
 
-extern "C" int b200_decode_attention_ex(const void* qkv, void* k_cache_layer, void* v_cache_layer,
-                                        void* out, void* workspace, size_t workspace_bytes,
-                                        int batch, int head_num, int kv_head_num, int head_size,
-                                        int max_seq_len, int step, const int* step_dev,
-                                        int append_kv, int dtype, void* stream) {
+static int decode_attention_impl(const void* qkv, void* k_cache_layer, void* v_cache_layer,
+                                 void* out, void* workspace, size_t workspace_bytes,
+                                 int batch, int head_num, int kv_head_num, int head_size,
+                                 int max_seq_len, int step, const int* step_dev, int step_stride,
+                                 int append_kv, int dtype, void* stream) {
     B200_RETURN_IF(!qkv || !k_cache_layer || !v_cache_layer || !out, B200_EINVAL);
     B200_RETURN_IF(batch <= 0 || head_num <= 0 || kv_head_num <= 0 || head_size <= 0 ||
                        max_seq_len <= 0 || head_num % kv_head_num != 0,
@@ -373,7 +374,7 @@ extern "C" int b200_decode_attention_ex(const void* qkv, void* k_cache_layer, vo
     AttnParams p{};
     p.qkv = qkv; p.k_cache = k_cache_layer; p.v_cache = v_cache_layer; p.out = out;
     p.batch = batch; p.head_num = head_num; p.kv_head_num = kv_head_num; p.head_size = head_size;
-    p.max_seq_len = max_seq_len; p.step = step; p.step_dev = step_dev; p.append_kv = append_kv;
+    p.max_seq_len = max_seq_len; p.step = step; p.step_dev = step_dev; p.step_stride = step_stride; p.append_kv = append_kv;
     auto al = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15u) == 0; };
     const bool fast = attn_fast_shape(head_num, kv_head_num, head_size, esz) && al(qkv) &&
                       al(k_cache_layer) && al(v_cache_layer);
@@ -401,6 +402,29 @@ extern "C" int b200_decode_attention_ex(const void* qkv, void* k_cache_layer, vo
                      true, p, (float*)workspace);
     count_launch();
     return (int)e;
+}
+
+extern "C" int b200_decode_attention_ex(const void* qkv, void* k_cache_layer, void* v_cache_layer,
+                                        void* out, void* workspace, size_t workspace_bytes,
+                                        int batch, int head_num, int kv_head_num, int head_size,
+                                        int max_seq_len, int step, const int* step_dev,
+                                        int append_kv, int dtype, void* stream) {
+    return decode_attention_impl(qkv, k_cache_layer, v_cache_layer, out, workspace, workspace_bytes, batch,
+                                 head_num, kv_head_num, head_size, max_seq_len, step, step_dev, 0, append_kv,
+                                 dtype, stream);
+}
+
+/* ragged batch: sequence b attends over seq_steps_dev[b] keys (its new token at row seq_steps_dev[b]-1);
+ * max_step >= every entry sizes the split count and the workspace, nothing else */
+extern "C" int b200_decode_attention_ragged(const void* qkv, void* k_cache_layer, void* v_cache_layer,
+                                            void* out, void* workspace, size_t workspace_bytes,
+                                            int batch, int head_num, int kv_head_num, int head_size,
+                                            int max_seq_len, int max_step, const int* seq_steps_dev,
+                                            int append_kv, int dtype, void* stream) {
+    B200_RETURN_IF(!seq_steps_dev, B200_EINVAL);
+    return decode_attention_impl(qkv, k_cache_layer, v_cache_layer, out, workspace, workspace_bytes, batch,
+                                 head_num, kv_head_num, head_size, max_seq_len, max_step, seq_steps_dev, 1,
+                                 append_kv, dtype, stream);
 }
 
 extern "C" int b200_decode_attention(const void* qkv, void* k_cache_layer, void* v_cache_layer,

@@ -77,7 +77,12 @@ struct b200_engine {
     b200_allreduce_fn allreduce = nullptr;
     void* allreduce_user = nullptr;
     b200_p2p* p2p = nullptr;   // fused one-shot NVLink allreduce + residual add (p2p_allreduce.cu)
-    int step = 0;  // host mirror of *step_dev: tokens already in the cache
+    int step = 0;  // host mirror of *step_dev: tokens already in the cache (ragged batch: of the longest sequence)
+    // ragged batch (per-sequence lengths): seq_steps[b] = reference `step` of sequence b (device), seq_cached its host
+    // mirror minus one. Uniform batches keep every entry equal to `step` and never read the device array.
+    int* seq_steps = nullptr;
+    std::vector<int> seq_cached;
+    bool ragged = false;
     std::map<int, cudaGraphExec_t> graphs;  // key: split-KV count
     b200::StepProgram* program = nullptr;   // persistent whole-step kernel (fp16, batch <= 4, tp 1)
     int launches_per_step = 0;
@@ -154,6 +159,16 @@ __global__ void fill_uniform_rows_kernel(T* cache, size_t rows_total, int max_se
 __global__ void advance_kernel(int* ids_cur, const int* ids_next, int* step, int batch) {
     pdl_wait();
     if (threadIdx.x < batch) ids_cur[threadIdx.x] = ids_next[threadIdx.x];
+    if (threadIdx.x == 0) *step += 1;
+}
+
+// ragged batch: every sequence moves on by one token from its own length
+__global__ void advance_ragged_kernel(int* ids_cur, const int* ids_next, int* step, int* seq_steps, int batch) {
+    pdl_wait();
+    for (int b = threadIdx.x; b < batch; b += blockDim.x) {
+        ids_cur[b] = ids_next[b];
+        seq_steps[b] += 1;
+    }
     if (threadIdx.x == 0) *step += 1;
 }
 
@@ -262,7 +277,7 @@ extern "C" b200_engine* b200_engine_create(const b200_model_config* c, int batch
     const size_t o_hidden = take(B * e->H), o_resid = take(B * e->H), o_qkv = take(B * e->qkv_n),
                  o_attn = take(B * e->h * e->d), o_act = take(B * e->I),
                  o_gu = take(B * 2 * e->I), o_logits = take(B * e->V), o_part = take(B * e->H);
-    const size_t o_ids = off; off += align256(2 * B * sizeof(int) + sizeof(int) + 64);
+    const size_t o_ids = off; off += align256(3 * B * sizeof(int) + sizeof(int) + 64);
     const size_t o_den = off; off += align256((size_t)c->rotary_dim / 2 * sizeof(float) + 64);
     const size_t o_ws = off; off += align256(e->attn_ws_bytes);
     e->lin_ws_bytes = 0;
@@ -280,6 +295,8 @@ extern "C" b200_engine* b200_engine_create(const b200_model_config* c, int batch
     e->hidden = a + o_hidden; e->residual = a + o_resid; e->qkv = a + o_qkv; e->attn = a + o_attn;
     e->act = a + o_act; e->gate_up = a + o_gu; e->logits = a + o_logits; e->partial = a + o_part;
     e->ids_cur = (int*)(a + o_ids); e->ids_next = e->ids_cur + B; e->step_dev = e->ids_next + B;
+    e->seq_steps = e->step_dev + 1;
+    e->seq_cached.assign(B, 0);
     e->attn_ws = a + o_ws;
     e->lin_ws = a + o_lws;
     e->rope_den = (float*)(a + o_den);
@@ -359,6 +376,8 @@ extern "C" int b200_engine_set_p2p(b200_engine* e, b200_p2p* comm) {
 
 static int set_step(b200_engine* e, int n) {
     e->step = n;
+    e->seq_cached.assign(e->batch, n);
+    e->ragged = false;
     const int ref_step = n + 1;  // reference `step`: tokens in the cache including the new one
     CU(cudaMemcpyAsync(e->step_dev, &ref_step, sizeof(int), cudaMemcpyHostToDevice, e->stream));
     CU(cudaStreamSynchronize(e->stream));
@@ -509,7 +528,7 @@ static int enqueue_step(b200_engine* e) {
     // step instead of once per 8-token tile).
     // fp16 batches of 5..8 also take the tensor-core path: eight x-rows of K = 11008 crowd the GEMV's weight ring out
     // of shared memory (measured at batch 8 x KV 4096: 12.0 ms per step fused vs the figure in DESIGN §4c)
-    const bool fused = (e->mode & B200_ENGINE_FUSED) && B <= (dt == B200_F16 && !tp ? 4 : B200_GEMV_MAX_TOKENS);
+    const bool fused = !e->ragged && (e->mode & B200_ENGINE_FUSED) && B <= (dt == B200_F16 && !tp ? 4 : B200_GEMV_MAX_TOKENS);
     auto linear = [&](const void* x, const void* W, void* y, int N, int K) {
         return b200_linear(x, W, nullptr, y, B, N, K, 1, dt, e->lin_ws, e->lin_ws_bytes, s);
     };
@@ -547,10 +566,17 @@ static int enqueue_step(b200_engine* e) {
             // the reference's launch sequence, one kernel per launch* (self_decoder.cpp:53-85)
             RC(b200_rmsnorm(e->hidden, e->residual, w.attn_norm, B, H, e->cfg.rms_eps, dt, s));
             RC(linear(e->hidden, w.qkv, e->qkv, e->qkv_n, H));
-            RC(b200_rope_decode_tab(e->qkv, B, e->h, e->hk, e->d, ref_step, e->step_dev, e->cfg.rotary_dim,
-                                    e->cfg.rotary_base, e->rope_den, dt, s));
-            RC(b200_decode_attention_ex(e->qkv, kc, vc, e->attn, e->attn_ws, e->attn_ws_bytes, B, e->h, e->hk, e->d,
-                                        e->cfg.max_seq_len, ref_step, e->step_dev, 1, dt, s));
+            if (e->ragged) {   // per-sequence positions and key counts; ref_step (the longest) only sizes the launch
+                RC(b200_rope_decode_ragged(e->qkv, B, e->h, e->hk, e->d, e->seq_steps, e->cfg.rotary_dim,
+                                           e->cfg.rotary_base, e->rope_den, dt, s));
+                RC(b200_decode_attention_ragged(e->qkv, kc, vc, e->attn, e->attn_ws, e->attn_ws_bytes, B, e->h, e->hk,
+                                                e->d, e->cfg.max_seq_len, ref_step, e->seq_steps, 1, dt, s));
+            } else {
+                RC(b200_rope_decode_tab(e->qkv, B, e->h, e->hk, e->d, ref_step, e->step_dev, e->cfg.rotary_dim,
+                                        e->cfg.rotary_base, e->rope_den, dt, s));
+                RC(b200_decode_attention_ex(e->qkv, kc, vc, e->attn, e->attn_ws, e->attn_ws_bytes, B, e->h, e->hk, e->d,
+                                            e->cfg.max_seq_len, ref_step, e->step_dev, 1, dt, s));
+            }
             RC(linear(e->attn, w.o, e->hidden, H, e->h * e->d));
             if (tp) RC(tp_sum(e, e->hidden, (size_t)B * H));
             RC(b200_fused_add_bias_residual_rmsnorm(e->residual, e->hidden, nullptr, w.ffn_norm, B, H, e->cfg.rms_eps, dt, s));
@@ -571,17 +597,26 @@ static int enqueue_step(b200_engine* e) {
         RC(linear(e->partial, e->lm_head, e->logits, e->V, H));
     }
     RC(b200_argmax(e->logits, e->ids_next, B, e->V, dt, s));
-    CU(launch_k(advance_kernel, dim3(1), dim3(1024), 0, s, true, e->ids_cur, (const int*)e->ids_next, e->step_dev, B));
+    if (e->ragged)
+        CU(launch_k(advance_ragged_kernel, dim3(1), dim3(1024), 0, s, true, e->ids_cur, (const int*)e->ids_next,
+                    e->step_dev, e->seq_steps, B));
+    else
+        CU(launch_k(advance_kernel, dim3(1), dim3(1024), 0, s, true, e->ids_cur, (const int*)e->ids_next, e->step_dev, B));
     count_launch();
     return 0;
 }
 
+static void stepped(b200_engine* e) {
+    e->step += 1;
+    for (int& c : e->seq_cached) c += 1;
+}
+
 static int run_step(b200_engine* e) {
     if (e->step + 1 > e->cfg.max_seq_len) return fail("KV cache full (step == max_seq_len)");
-    if (e->program && (e->mode & B200_ENGINE_FUSED) && (e->mode & B200_ENGINE_PERSISTENT)) {
+    if (e->program && !e->ragged && (e->mode & B200_ENGINE_FUSED) && (e->mode & B200_ENGINE_PERSISTENT)) {
         RC(step_program_launch(e->program, e->step + 1, e->stream));
         e->launches_per_step = 1;
-        e->step += 1;
+        stepped(e);
         return 0;
     }
     const bool use_graph = (e->mode & B200_ENGINE_GRAPH) != 0;
@@ -589,10 +624,11 @@ static int run_step(b200_engine* e) {
         const uint64_t before = b200_launch_count();
         RC(enqueue_step(e));
         e->launches_per_step = (int)(b200_launch_count() - before);
-        e->step += 1;
+        stepped(e);
         return 0;
     }
-    const int key = attn_pick_splits_public(e->batch, e->hk, e->step + 1, e->h / e->hk);
+    // one graph per split count of the decode attention; ragged batches record different kernels
+    const int key = attn_pick_splits_public(e->batch, e->hk, e->step + 1, e->h / e->hk) | (e->ragged ? 1 << 20 : 0);
     auto it = e->graphs.find(key);
     if (it == e->graphs.end()) {
         const uint64_t before = b200_launch_count();
@@ -613,7 +649,7 @@ static int run_step(b200_engine* e) {
         count_launch((uint64_t)e->launches_per_step);
     }
     CU(cudaGraphLaunch(it->second, e->stream));
-    e->step += 1;
+    stepped(e);
     return 0;
 }
 
@@ -659,12 +695,29 @@ __global__ void set_ids_step_kernel(int* ids_cur, const int* ids_next, int* step
 }
 }  // namespace b200
 
-extern "C" int b200_engine_prefill(b200_engine* e, const int* ids_host, int len, int* ids_out_host) {
-    if (!e || !ids_host || len < 1) return fail("prefill: bad arguments");
-    const int dt = e->cfg.dtype, B = e->batch, H = e->H, hist = e->step;
-    if (hist + len > e->cfg.max_seq_len - 1) return fail("prefill: prompt does not fit the KV cache");
+// lens_host == nullptr: every sequence gets `uniform_len` tokens. Otherwise sequence b gets lens_host[b] tokens and
+// ids_host holds them packed back to back (the reference's padding-free [num_tokens] layout, llama.cpp:158-185);
+// each sequence's history is what IT has cached so far.
+static int prefill_impl(b200_engine* e, const int* ids_host, const int* lens_host, int uniform_len, int* ids_out_host) {
+    const int dt = e->cfg.dtype, B = e->batch, H = e->H;
+    long long total = 0;
+    int len = 0, ctx = 0;   // longest prompt / longest context of this call: the padded extents
+    std::vector<int> len_b(B), hist_b(B), cum_b(B + 1, 0);
+    for (int b = 0; b < B; ++b) {
+        len_b[b] = lens_host ? lens_host[b] : uniform_len;
+        hist_b[b] = e->seq_cached[b];
+        if (len_b[b] < 1) return fail("prefill: every sequence needs at least one prompt token");
+        if (hist_b[b] + len_b[b] > e->cfg.max_seq_len - 1) return fail("prefill: prompt does not fit the KV cache");
+        total += len_b[b];
+        cum_b[b + 1] = (int)total;
+        len = std::max(len, len_b[b]);
+        ctx = std::max(ctx, hist_b[b] + len_b[b]);
+    }
     if ((long long)B * len >= (1ll << 24)) return fail("prefill: too many tokens");
-    const int Nt = B * len, ctx = hist + len;
+    const int Nt = (int)total;
+    const size_t Np = (size_t)B * len;   // rows of the re-padded [B, h, len, d] buffers
+    bool ragged = false;
+    for (int b = 1; b < B; ++b) ragged |= hist_b[b] + len_b[b] != hist_b[0] + len_b[0];
     const size_t es = e->esz;
     cudaStream_t s = e->stream;
     const uint64_t launches0 = b200_launch_count();
@@ -673,8 +726,8 @@ extern "C" int b200_engine_prefill(b200_engine* e, const int* ids_host, int len,
     auto take = [&](size_t bytes) { size_t o = off; off += align256(bytes); return o; };
     const size_t o_x = take((size_t)Nt * H * es), o_res = take((size_t)Nt * H * es);
     const size_t o_qkv = take((size_t)Nt * e->qkv_n * es);
-    const size_t o_q = take((size_t)Nt * e->h * e->d * es), o_k = take((size_t)Nt * e->hk * e->d * es),
-                 o_v = take((size_t)Nt * e->hk * e->d * es);
+    const size_t o_q = take(Np * e->h * e->d * es), o_k = take(Np * e->hk * e->d * es),
+                 o_v = take(Np * e->hk * e->d * es);
     const size_t o_att = take((size_t)Nt * e->h * e->d * es);
     const size_t o_gu = take((size_t)Nt * 2 * e->I * es), o_act = take((size_t)Nt * e->I * es);
     const size_t o_ids = take((size_t)Nt * 4), o_pad = take((size_t)Nt * 4), o_cum = take((size_t)(B + 1) * 4),
@@ -692,7 +745,7 @@ extern "C" int b200_engine_prefill(b200_engine* e, const int* ids_host, int len,
         o_kr = take((size_t)B * e->h * ctx * e->d * es);
         o_vr = take((size_t)B * e->h * ctx * e->d * es);
         o_sc = take((size_t)B * e->h * len * ctx * es);
-        o_pv = take((size_t)Nt * e->h * e->d * es);
+        o_pv = take(Np * e->h * e->d * es);
     }
     if (off > e->pf_bytes) {
         CU(cudaStreamSynchronize(s));
@@ -702,7 +755,7 @@ extern "C" int b200_engine_prefill(b200_engine* e, const int* ids_host, int len,
         CU(cudaMalloc(&e->pf_arena, off));
         e->pf_bytes = off;
     }
-    const size_t need_ints = (size_t)Nt + 3 * B;
+    const size_t need_ints = (size_t)Nt + 4 * B;
     if (need_ints > e->pf_pinned_ints) {
         if (e->pf_pinned) cudaFreeHost(e->pf_pinned);
         e->pf_pinned = nullptr;
@@ -718,19 +771,26 @@ extern "C" int b200_engine_prefill(b200_engine* e, const int* ids_host, int len,
     // ---- host -> device: token ids and the three length vectors (contiguous in the arena)
     memcpy(e->pf_pinned, ids_host, (size_t)Nt * sizeof(int));
     for (int b = 0; b < B; ++b) {
-        e->pf_pinned[Nt + b] = len;
-        e->pf_pinned[Nt + B + b] = hist;
-        e->pf_pinned[Nt + 2 * B + b] = ctx;
+        e->pf_pinned[Nt + b] = len_b[b];
+        e->pf_pinned[Nt + B + b] = hist_b[b];
+        e->pf_pinned[Nt + 2 * B + b] = hist_b[b] + len_b[b];
+        e->pf_pinned[Nt + 3 * B + b] = hist_b[b] + len_b[b] + 1;   // the reference `step` of its first decode
     }
     CU(cudaMemcpyAsync(ids, e->pf_pinned, (size_t)Nt * sizeof(int), cudaMemcpyHostToDevice, s));
     CU(cudaMemcpyAsync(lens, e->pf_pinned + Nt, (size_t)B * sizeof(int), cudaMemcpyHostToDevice, s));
     CU(cudaMemcpyAsync(hists, e->pf_pinned + Nt + B, (size_t)B * sizeof(int), cudaMemcpyHostToDevice, s));
     CU(cudaMemcpyAsync(ctxs, e->pf_pinned + Nt + 2 * B, (size_t)B * sizeof(int), cudaMemcpyHostToDevice, s));
+    CU(cudaMemcpyAsync(e->seq_steps, e->pf_pinned + Nt + 3 * B, (size_t)B * sizeof(int), cudaMemcpyHostToDevice, s));
     auto linear = [&](const void* in, const void* W, void* out, int N, int K) {
         return b200_linear(in, W, nullptr, out, Nt, N, K, 1, dt, lws, lin_ws + 256, s);
     };
     const bool tp = e->cfg.tp_size > 1 && (e->allreduce || e->p2p);
     RC(b200_cal_padding_offset(pad, cum, lens, B, len, s));
+    if (!flash && ragged) {   // shorter sequences leave rows of the repeated K/V unwritten: 0 * stale NaN must not reach PV
+        CU(cudaMemsetAsync(a + o_kr, 0, (size_t)B * e->h * ctx * e->d * es, s));
+        CU(cudaMemsetAsync(a + o_vr, 0, (size_t)B * e->h * ctx * e->d * es, s));
+        CU(cudaMemsetAsync(q, 0, Np * e->h * e->d * es, s));
+    }
     if (!flash) RC(b200_build_causal_mask(a + o_mask, lens, ctxs, B, len, ctx, 1, dt, s));
     RC(b200_embedding(ids, e->embed, x, Nt, H, e->V, dt, s));
     for (int l = 0; l < e->cfg.num_layers; ++l) {
@@ -773,8 +833,14 @@ extern "C" int b200_engine_prefill(b200_engine* e, const int* ids_host, int len,
         }
     }
     // ---- last token of each sequence -> final norm -> LM head -> top-1 (llama.cpp:221-232, :305)
-    CU(cudaMemcpy2DAsync(e->hidden, (size_t)H * es, (const char*)x + (size_t)(len - 1) * H * es, (size_t)len * H * es,
-                         (size_t)H * es, (size_t)B, cudaMemcpyDeviceToDevice, s));
+    if (!lens_host) {
+        CU(cudaMemcpy2DAsync(e->hidden, (size_t)H * es, (const char*)x + (size_t)(len - 1) * H * es, (size_t)len * H * es,
+                             (size_t)H * es, (size_t)B, cudaMemcpyDeviceToDevice, s));
+    } else {
+        for (int b = 0; b < B; ++b)
+            CU(cudaMemcpyAsync((char*)e->hidden + (size_t)b * H * es, (const char*)x + (size_t)(cum_b[b + 1] - 1) * H * es,
+                               (size_t)H * es, cudaMemcpyDeviceToDevice, s));
+    }
     CU(cudaMemcpyAsync(e->partial, e->hidden, (size_t)B * H * es, cudaMemcpyDeviceToDevice, s));
     RC(b200_rmsnorm(e->partial, nullptr, e->final_norm, B, H, e->cfg.rms_eps, dt, s));
     RC(b200_linear(e->partial, e->lm_head, nullptr, e->logits, B, e->V, H, 1, dt, e->lin_ws, e->lin_ws_bytes, s));
@@ -783,6 +849,8 @@ extern "C" int b200_engine_prefill(b200_engine* e, const int* ids_host, int len,
                 ctx + 1));
     count_launch();
     e->step = ctx;
+    for (int b = 0; b < B; ++b) e->seq_cached[b] = hist_b[b] + len_b[b];
+    e->ragged = ragged;
     e->prefill_launches = (int)(b200_launch_count() - launches0);
     if (ids_out_host) {
         CU(cudaMemcpyAsync(e->pinned_ids, e->ids_next, sizeof(int) * B, cudaMemcpyDeviceToHost, s));
@@ -792,6 +860,22 @@ extern "C" int b200_engine_prefill(b200_engine* e, const int* ids_host, int len,
     return 0;
 }
 extern "C" int b200_engine_prefill_launches(const b200_engine* e) { return e ? e->prefill_launches : 0; }
+
+extern "C" int b200_engine_prefill(b200_engine* e, const int* ids_host, int len, int* ids_out_host) {
+    if (!e || !ids_host || len < 1) return fail("prefill: bad arguments");
+    return prefill_impl(e, ids_host, nullptr, len, ids_out_host);
+}
+
+extern "C" int b200_engine_prefill_ragged(b200_engine* e, const int* ids_host, const int* lens_host, int* ids_out_host) {
+    if (!e || !ids_host || !lens_host) return fail("prefill_ragged: bad arguments");
+    return prefill_impl(e, ids_host, lens_host, 0, ids_out_host);
+}
+
+extern "C" int b200_engine_get_seq_steps(const b200_engine* e, int* steps_out_host) {
+    if (!e || !steps_out_host) return B200_EINVAL;
+    for (int b = 0; b < e->batch; ++b) steps_out_host[b] = e->seq_cached[b];
+    return B200_OK;
+}
 
 
 // ------------------------------------------------------------------------------------------

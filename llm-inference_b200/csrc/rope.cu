@@ -20,13 +20,15 @@ __device__ __forceinline__ float2 rope_cos_sin(int pair, int rot_dim, float base
 template <typename T>
 __global__ void __launch_bounds__(256)
 rope_decode_kernel(T* __restrict__ qkv, int head_num, int kv_head_num, int head_size, int pos,
-                   const int* __restrict__ step_dev, int rot_dim, float base, const float* __restrict__ den) {
+                   const int* __restrict__ step_dev, int rot_dim, float base, const float* __restrict__ den,
+                   int step_stride) {
     constexpr int E = DT<T>::kPer16B;
     extern __shared__ float2 cs[];  // [head_size/2]; identity beyond rot_dim/2
     const int half_rot = rot_dim >> 1, half_d = head_size >> 1;
     // step_dev (CUDA-graph replay) is only ever written by the LAST kernel of the previous step,
     // which has fully completed before any kernel of this step starts, so it may be read early
-    if (step_dev) pos = *step_dev - 1;
+    // step_stride 1: step_dev[b] is sequence b's own step (ragged batch)
+    if (step_dev) pos = step_dev[blockIdx.x * step_stride] - 1;
     for (int i = threadIdx.x; i < half_d; i += blockDim.x) {
         if (i >= half_rot) { cs[i] = make_float2(1.f, 0.f); continue; }
         // den[i] = base^(2i/rot_dim) from b200_rope_table(): the same correctly rounded float rope_angle() forms
@@ -155,10 +157,10 @@ qkv_rope_transpose_kernel(T* __restrict__ q, T* __restrict__ k, T* __restrict__ 
 template <typename T>
 static int rope_decode_impl(void* qkv, int batch, int head_num, int kv_head_num, int head_size,
                             int step, const int* step_dev, int rot_dim, float base, cudaStream_t s,
-                            const float* den = nullptr) {
+                            const float* den = nullptr, int step_stride = 0) {
     cudaError_t e = launch_k(rope_decode_kernel<T>, dim3(batch), dim3(256),
                              (size_t)(head_size / 2) * sizeof(float2), s, true, (T*)qkv, head_num,
-                             kv_head_num, head_size, step - 1, step_dev, rot_dim, base, den);
+                             kv_head_num, head_size, step - 1, step_dev, rot_dim, base, den, step_stride);
     count_launch();
     return (int)e;
 }
@@ -213,6 +215,24 @@ extern "C" int b200_rope_decode_tab(void* qkv, int batch, int head_num, int kv_h
     if (dtype == B200_F16)
         return b200::rope_decode_impl<__half>(qkv, batch, head_num, kv_head_num, head_size, step,
                                               step_dev, rotary_dim, rotary_base, s, rope_den);
+    return B200_EINVAL;
+}
+
+/* ragged batch: token b sits at position seq_steps_dev[b] - 1 */
+extern "C" int b200_rope_decode_ragged(void* qkv, int batch, int head_num, int kv_head_num, int head_size,
+                                       const int* seq_steps_dev, int rotary_dim, float rotary_base,
+                                       const float* rope_den, int dtype, void* stream) {
+    B200_RETURN_IF(!qkv || !seq_steps_dev || batch < 0 || head_num <= 0 || kv_head_num <= 0 || head_size <= 0,
+                   B200_EINVAL);
+    B200_RETURN_IF(rotary_dim <= 0 || rotary_dim > head_size || (rotary_dim & 1) || (head_size & 1), B200_EINVAL);
+    if (batch == 0) return B200_OK;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (dtype == B200_F32)
+        return b200::rope_decode_impl<float>(qkv, batch, head_num, kv_head_num, head_size, 1, seq_steps_dev,
+                                             rotary_dim, rotary_base, s, rope_den, 1);
+    if (dtype == B200_F16)
+        return b200::rope_decode_impl<__half>(qkv, batch, head_num, kv_head_num, head_size, 1, seq_steps_dev,
+                                              rotary_dim, rotary_base, s, rope_den, 1);
     return B200_EINVAL;
 }
 

@@ -47,6 +47,8 @@ ENGINE_PROTOTYPES = {
     "b200_engine_launches_per_step": (_i, [_vp]),
     "b200_engine_step_trace": (_i, [_vp, _vp, _i]),
     "b200_engine_prefill": (_i, [_vp, _vp, _i, _vp]),
+    "b200_engine_prefill_ragged": (_i, [_vp, _vp, _vp, _vp]),
+    "b200_engine_get_seq_steps": (_i, [_vp, _vp]),
     "b200_engine_set_p2p": (_i, [_vp, _vp]),
     "b200_engine_generate": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp]),
     "b200_engine_load_weights": (_i, [_vp, C.c_char_p]),
@@ -214,6 +216,24 @@ class Engine:
         out = np.empty(self.batch, np.int32) if sync else None
         self._ck(self.lib.b200_engine_prefill(self.h, ids.ctypes.data_as(C.c_void_p), ids.shape[1],
                                               out.ctypes.data_as(C.c_void_p) if sync else None), "prefill")
+        return out
+
+    def prefill_ragged(self, prompts, sync=True):
+        """list of `batch` int sequences of different lengths -> numpy int32 [batch] first generated tokens
+        (b200_engine_prefill_ragged: ids packed back to back, per-sequence steps from here on)"""
+        assert len(prompts) == self.batch
+        lens = np.array([len(p) for p in prompts], np.int32)
+        ids = np.ascontiguousarray(np.concatenate([np.asarray(p, np.int32).reshape(-1) for p in prompts]))
+        out = np.empty(self.batch, np.int32) if sync else None
+        self._ck(self.lib.b200_engine_prefill_ragged(self.h, ids.ctypes.data_as(C.c_void_p), lens.ctypes.data_as(C.c_void_p),
+                                                     out.ctypes.data_as(C.c_void_p) if sync else None), "prefill_ragged")
+        return out
+
+    @property
+    def seq_steps(self):
+        """tokens cached per sequence (numpy int32 [batch])"""
+        out = np.empty(self.batch, np.int32)
+        self._ck(self.lib.b200_engine_get_seq_steps(self.h, out.ctypes.data_as(C.c_void_p)), "get_seq_steps")
         return out
 
     def generate(self, prompt_ids, max_new_tokens, eos_id=2):

@@ -289,3 +289,24 @@ def linear_residual(inp, weight, residual, out):
     n = out.shape[1]
     _check(capi.lib().b200_linear_residual(_p(inp), _p(weight), _p(residual), _p(out), nt, n, k, _dt(inp), _stream()),
            "b200_linear_residual")
+
+
+def rope_decode_ragged(qkv_buf, seq_steps, rotary_embedding_dim, rotary_embedding_base, kv_head_num):
+    """launchRoPE with one `step` per sequence (b200_rope_decode_ragged): seq_steps int32 DEVICE [B]"""
+    b, qh, d = qkv_buf.shape
+    _check(capi.lib().b200_rope_decode_ragged(_p(qkv_buf), b, qh - 2 * kv_head_num, kv_head_num, d, _p(seq_steps),
+                                              rotary_embedding_dim, rotary_embedding_base, None, _dt(qkv_buf),
+                                              _stream()), "rope_decode_ragged")
+
+
+def decode_attention_ragged(qkv_buf, layer_id, k_cache, v_cache, seq_steps, max_step, mha_output, append_kv=True):
+    """launchDecoderMaskedMHA with one `step` per sequence (b200_decode_attention_ragged)"""
+    b, qh, d = qkv_buf.shape
+    hk, max_seq = k_cache.shape[2], k_cache.shape[3]
+    h = qh - 2 * hk
+    lib = capi.lib()
+    ws = _attn_workspace(qkv_buf.device, lib.b200_decode_attention_workspace_bytes(b, h, d, max_seq))
+    kl, vl = k_cache[int(layer_id)], v_cache[int(layer_id)]
+    _check(lib.b200_decode_attention_ragged(
+        _p(qkv_buf), _p(kl), _p(vl), _p(mha_output), _p(ws), ws.numel(), b, h, hk, d, max_seq, int(max_step),
+        _p(seq_steps), 1 if append_kv else 0, _dt(qkv_buf), _stream()), "decode_attention_ragged")
