@@ -147,8 +147,8 @@ int b200_engine_prefill(b200_engine* e, const int* ids_host, int len, int* ids_o
  * ids_host holds them packed back to back (sum(lens) ids, the padding-free layout the context
  * decoder works on, llama.cpp:158-185), each appended after what THAT sequence has cached. When
  * the lengths end up different, the decode steps that follow run with per-sequence positions and
- * key counts (b200_rope_decode_ragged / b200_decode_attention_ragged; the unfused launch order,
- * CUDA-graphed) and every sequence advances by one token per step; b200_engine_get_step() then
+ * key counts (b200_rope_decode_ragged / b200_decode_attention_ragged, or the GEMV epilogue with
+ * b200_gemv_args.step_stride = 1 in the fused order; CUDA-graphed, not the persistent kernel) and every sequence advances by one token per step; b200_engine_get_step() then
  * reports the longest sequence, b200_engine_get_seq_steps() all of them (tokens cached, host int
  * [batch]). b200_engine_reset / fill_kv_random return the engine to one shared step. */
 int b200_engine_prefill_ragged(b200_engine* e, const int* ids_host, const int* lens_host,

@@ -202,6 +202,7 @@ typedef struct b200_gemv_args {
                            /* b200_rope_table(); NULL = computed in the kernel                   */
     void* p2p; /* optional b200_p2p* (b200_engine.h): tensor-parallel row-split linear, fp16, no epilogue */
                /* mode: the partial outputs go straight to every rank's receive buffer over NVLink     */
+    int step_stride; /* 0: *step_dev is the step all tokens share; 1: step_dev[token] (ragged batch)          */
                /* (16-byte lines, payload + call tag) instead of y; b200_p2p_reduce_add() finishes     */
 } b200_gemv_args;
 int b200_gemv_fused(const b200_gemv_args* args, int dtype, void* stream);

@@ -20,6 +20,7 @@ class GemvArgs(C.Structure):
         ("head_num", C.c_int), ("kv_head_num", C.c_int), ("head_size", C.c_int),
         ("max_seq_len", C.c_int), ("step", C.c_int), ("rotary_dim", C.c_int),
         ("rotary_base", C.c_float), ("step_dev", C.c_void_p), ("rope_den", C.c_void_p), ("p2p", C.c_void_p),
+        ("step_stride", C.c_int),
     ]
 
 

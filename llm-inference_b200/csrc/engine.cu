@@ -474,7 +474,8 @@ static int gemv(b200_engine* e, const void* x, const void* W, void* y, int N, in
         a.head_num = e->h; a.kv_head_num = e->hk; a.head_size = e->d;
         a.max_seq_len = e->cfg.max_seq_len; a.step = e->step + 1;
         a.rotary_dim = e->cfg.rotary_dim; a.rotary_base = e->cfg.rotary_base;
-        a.step_dev = e->step_dev;
+        a.step_dev = e->ragged ? e->seq_steps : e->step_dev;
+        a.step_stride = e->ragged ? 1 : 0;
         a.rope_den = e->rope_den;
     }
     // batches above the GEMV tile are walked in tiles of B200_GEMV_MAX_TOKENS
@@ -489,6 +490,7 @@ static int gemv(b200_engine* e, const void* x, const void* W, void* y, int N, in
             const size_t per_seq = (size_t)e->hk * e->cfg.max_seq_len * e->d * e->esz;
             t.k_cache_layer = (char*)a.k_cache_layer + (size_t)t0 * per_seq;
             t.v_cache_layer = (char*)a.v_cache_layer + (size_t)t0 * per_seq;
+            if (a.step_stride) t.step_dev = a.step_dev + t0;
         }
         int rc = b200_gemv_fused(&t, e->cfg.dtype, e->stream);
         if (rc != 0) return rc;
@@ -528,7 +530,7 @@ static int enqueue_step(b200_engine* e) {
     // step instead of once per 8-token tile).
     // fp16 batches of 5..8 also take the tensor-core path: eight x-rows of K = 11008 crowd the GEMV's weight ring out
     // of shared memory (measured at batch 8 x KV 4096: 12.0 ms per step fused vs the figure in DESIGN §4c)
-    const bool fused = !e->ragged && (e->mode & B200_ENGINE_FUSED) && B <= (dt == B200_F16 && !tp ? 4 : B200_GEMV_MAX_TOKENS);
+    const bool fused = (e->mode & B200_ENGINE_FUSED) && B <= (dt == B200_F16 && !tp ? 4 : B200_GEMV_MAX_TOKENS);
     auto linear = [&](const void* x, const void* W, void* y, int N, int K) {
         return b200_linear(x, W, nullptr, y, B, N, K, 1, dt, e->lin_ws, e->lin_ws_bytes, s);
     };
@@ -539,8 +541,12 @@ static int enqueue_step(b200_engine* e) {
         void* vc = e->v_cache + (size_t)l * e->layer_kv_elems * e->esz;
         if (fused) {
             RC(gemv(e, e->hidden, w.qkv, e->qkv, e->qkv_n, H, B200_GEMV_NORM | B200_GEMV_ROPE_KV, w.attn_norm, l));
-            RC(b200_decode_attention_ex(e->qkv, kc, vc, e->attn, e->attn_ws, e->attn_ws_bytes, B, e->h, e->hk,
-                                        e->d, e->cfg.max_seq_len, ref_step, e->step_dev, 0, dt, s));
+            if (e->ragged)
+                RC(b200_decode_attention_ragged(e->qkv, kc, vc, e->attn, e->attn_ws, e->attn_ws_bytes, B, e->h, e->hk,
+                                                e->d, e->cfg.max_seq_len, ref_step, e->seq_steps, 0, dt, s));
+            else
+                RC(b200_decode_attention_ex(e->qkv, kc, vc, e->attn, e->attn_ws, e->attn_ws_bytes, B, e->h, e->hk,
+                                            e->d, e->cfg.max_seq_len, ref_step, e->step_dev, 0, dt, s));
             const bool fused_ar = tp && e->p2p && dt == B200_F16 && (H & 3) == 0 && B <= B200_GEMV_MAX_TOKENS;
             if (!tp) {
                 RC(gemv(e, e->attn, w.o, e->hidden, H, e->h * e->d, B200_GEMV_RESIDUAL));

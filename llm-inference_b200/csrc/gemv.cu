@@ -50,6 +50,7 @@ struct GemvParams {
     int head_num, kv_head_num, head_size, max_seq_len, step, rotary_dim;
     float rotary_base;
     const int* step_dev;
+    int step_stride;   // 1: step_dev[token] is each sequence's own step (ragged batch); 0: one shared *step_dev
     const float* rope_den;
     P2PWire wire;   // world > 0 (plain mode, fp16): outputs are pushed to the peers instead of written to y
     int token0;     // index of this launch's first token in the message (launches tiled over tokens)
@@ -286,8 +287,9 @@ __global__ void __launch_bounds__(kGemvThreads, 1) gemv_stream_kernel(const Gemv
                     const int d = p.head_size, hd = d >> 1;
                     const int head = ra / d, i = ra - head * d;
                     const int qkv_heads = p.head_num + 2 * p.kv_head_num;
+                    const bool rotated = head < p.head_num + p.kv_head_num && i < (p.rotary_dim >> 1);
                     float c = 1.f, s = 0.f;
-                    if (head < p.head_num + p.kv_head_num && i < (p.rotary_dim >> 1)) {
+                    if (rotated) {
                         const float ang = p.rope_den ? (float)(step - 1) / p.rope_den[i]
                                                      : rope_angle(i, p.rotary_dim, p.rotary_base, (float)(step - 1));
                         c = cosf(ang);
@@ -296,6 +298,15 @@ __global__ void __launch_bounds__(kGemvThreads, 1) gemv_stream_kernel(const Gemv
 #pragma unroll
                     for (int b = 0; b < NB; ++b) {
                         if (b >= p.nb) break;
+                        if (p.step_stride) {   // ragged batch: token b sits at its own position
+                            step = p.step_dev[b * p.step_stride];
+                            if (rotated) {
+                                const float ang = p.rope_den ? (float)(step - 1) / p.rope_den[i]
+                                                             : rope_angle(i, p.rotary_dim, p.rotary_base, (float)(step - 1));
+                                c = cosf(ang);
+                                s = sinf(ang);
+                            }
+                        }
                         float av = acc_a[b], bv = acc_b[b];
                         if (bias) { av += DT<T>::to_f(bias[ra]); bv += DT<T>::to_f(bias[rb]); }
                         av = DT<T>::to_f(DT<T>::from_f(av));  // qkv_buf is stored in T before RoPE
@@ -417,6 +428,7 @@ static int gemv_dispatch_nb(GemvParams p, int n_tokens, cudaStream_t s) {
             q.x = (const char*)p.x + (size_t)t0 * p.K * esz;
             q.y = (char*)p.y + (size_t)t0 * y_stride * esz;
             q.token0 = p.token0 + t0;
+            if (p.step_dev) q.step_dev = p.step_dev + (size_t)t0 * p.step_stride;
             if (MODE == kModeRopeKV) {
                 const size_t per_seq = (size_t)p.kv_head_num * p.max_seq_len * p.head_size * esz;
                 q.k_cache = (char*)p.k_cache + (size_t)t0 * per_seq;
@@ -459,6 +471,7 @@ static int gemv_fused_impl(const b200_gemv_args* a, cudaStream_t s) {
     p.head_num = a->head_num; p.kv_head_num = a->kv_head_num; p.head_size = a->head_size;
     p.max_seq_len = a->max_seq_len; p.step = a->step; p.rotary_dim = a->rotary_dim;
     p.rotary_base = a->rotary_base; p.step_dev = a->step_dev; p.rope_den = a->rope_den;
+    p.step_stride = (a->step_dev && a->step_stride) ? 1 : 0;
     if (a->p2p) {
         const b200_p2p* c = reinterpret_cast<const b200_p2p*>(a->p2p);
         B200_RETURN_IF(epi != 0 || sizeof(T) != 2 || (a->N & 3) || a->bias, B200_EUNSUPPORTED);

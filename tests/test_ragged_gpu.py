@@ -60,12 +60,13 @@ def test_rope_and_decode_attention_per_sequence_steps(ops, kind, h, hk, d, steps
     assert np.array_equal(g_k.float().cpu().numpy(), wk) and np.array_equal(g_v.float().cpu().numpy(), wv)
 
 
-def _check_against_single_sequence_oracles(pkg, kind, rounds, n_decode):
+def _check_against_single_sequence_oracles(pkg, kind, rounds, n_decode, fused=True):
     E = pkg.engine
     B = len(rounds[0])
     max_seq = max(sum(r[b] for r in rounds) for b in range(B)) + n_decode + 4
     eng = E.Engine(B, max_seq, dtype=pkg.F16 if kind == "fp16" else pkg.F32, **SMALL)
     eng.init_random(seed=11, std=0.05)
+    eng.set_mode(fused=fused, graph=True, persistent=fused)   # a ragged batch never takes the persistent kernel
     w = download_weights(E, eng, SMALL["num_layers"])
     oras = [omodel.OracleModel(w, SMALL, 1, max_seq, kind) for _ in range(B)]
     rng = np.random.default_rng(B * 1000 + rounds[0][0])
@@ -107,10 +108,14 @@ def _check_against_single_sequence_oracles(pkg, kind, rounds, n_decode):
     eng.close()
 
 
+@pytest.mark.parametrize("fused", [True, False], ids=["fused_gemv", "unfused"])
 @pytest.mark.parametrize("kind,rounds", [("fp16", [[37, 5, 140]]), ("fp16", [[130, 1], [4, 150]]),
+                                         ("fp16", [[3, 40, 7, 1, 22, 9]]),   # > 4 sequences: tcgen05 linears in both modes
                                          ("fp32", [[9, 3, 14]]), ("fp32", [[6, 2], [1, 11]])])
-def test_ragged_prefill_then_decode_vs_single_sequence_oracles(pkg, kind, rounds):
-    _check_against_single_sequence_oracles(pkg, kind, rounds, n_decode=3)
+def test_ragged_prefill_then_decode_vs_single_sequence_oracles(pkg, kind, rounds, fused):
+    """fused: the GEMV epilogue rotates and appends each token at its own position (b200_gemv_args.step_stride);
+    unfused: b200_rope_decode_ragged + b200_decode_attention_ragged in the reference's launch order"""
+    _check_against_single_sequence_oracles(pkg, kind, rounds, n_decode=3, fused=fused)
 
 
 def test_equal_lengths_stay_on_the_shared_step_path(pkg):
