@@ -162,6 +162,10 @@ int b200_engine_prefill_launches(const b200_engine* e);   /* kernel launches of 
  * n_generated [batch] (host, may be NULL). Returns the number of decode steps run, < 0 on error. */
 int b200_engine_generate(b200_engine* e, const int* prompt_ids_host, int prompt_len, int max_new_tokens,
                          int eos_id, int* out_ids, int* n_generated);
+/* the same for prompts of different lengths: ids packed back to back + lens_host[batch]
+ * (b200_engine_prefill_ragged), every sequence decoding from its own length */
+int b200_engine_generate_ragged(b200_engine* e, const int* prompt_ids_host, const int* lens_host,
+                                int max_new_tokens, int eos_id, int* out_ids, int* n_generated);
 
 /* Load the reference's weight directory (LlamaWeight<T>::loadWeights llama_weights.cc:41-53,
  * LlamaLayerWeight<T>::loadWeights layer_weights.cc:48-66): raw fp32 files model.norm.weight.bin,

@@ -987,12 +987,13 @@ extern "C" int b200_engine_load_weights(b200_engine* e, const char* dir) {
 // the EOS token itself is not counted / emitted for a sequence (llama.cpp:415-419 breaks before
 // printing it). Returns the number of decode steps run (>= 0) or a negative / CUDA error code.
 // ------------------------------------------------------------------------------------------
-extern "C" int b200_engine_generate(b200_engine* e, const int* prompt_ids_host, int prompt_len, int max_new_tokens,
-                                    int eos_id, int* out_ids, int* n_generated) {
+static int generate_impl(b200_engine* e, const int* prompt_ids_host, const int* lens_host, int prompt_len,
+                         int max_new_tokens, int eos_id, int* out_ids, int* n_generated) {
     if (!e || !prompt_ids_host || !out_ids || max_new_tokens < 1) return B200_EINVAL;
     const int B = e->batch;
     std::vector<int> cur(B), done(B, 0), count(B, 0);
-    int rc = b200_engine_prefill(e, prompt_ids_host, prompt_len, cur.data());
+    int rc = lens_host ? b200_engine_prefill_ragged(e, prompt_ids_host, lens_host, cur.data())
+                       : b200_engine_prefill(e, prompt_ids_host, prompt_len, cur.data());
     if (rc != 0) return rc > 0 ? -1000 - rc : rc;
     for (int i = 0; i < B * max_new_tokens; ++i) out_ids[i] = eos_id;
     int steps = 0;
@@ -1011,4 +1012,17 @@ extern "C" int b200_engine_generate(b200_engine* e, const int* prompt_ids_host, 
     }
     if (n_generated) for (int b = 0; b < B; ++b) n_generated[b] = count[b];
     return steps;
+}
+
+extern "C" int b200_engine_generate(b200_engine* e, const int* prompt_ids_host, int prompt_len, int max_new_tokens,
+                                    int eos_id, int* out_ids, int* n_generated) {
+    if (prompt_len < 1) return B200_EINVAL;
+    return generate_impl(e, prompt_ids_host, nullptr, prompt_len, max_new_tokens, eos_id, out_ids, n_generated);
+}
+
+// prompts of different lengths: ids packed back to back, lens_host[batch] (b200_engine_prefill_ragged)
+extern "C" int b200_engine_generate_ragged(b200_engine* e, const int* prompt_ids_host, const int* lens_host,
+                                           int max_new_tokens, int eos_id, int* out_ids, int* n_generated) {
+    if (!lens_host) return B200_EINVAL;
+    return generate_impl(e, prompt_ids_host, lens_host, 0, max_new_tokens, eos_id, out_ids, n_generated);
 }

@@ -51,6 +51,7 @@ ENGINE_PROTOTYPES = {
     "b200_engine_get_seq_steps": (_i, [_vp, _vp]),
     "b200_engine_set_p2p": (_i, [_vp, _vp]),
     "b200_engine_generate": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp]),
+    "b200_engine_generate_ragged": (_i, [_vp, _vp, _vp, _i, _i, _vp, _vp]),
     "b200_engine_load_weights": (_i, [_vp, C.c_char_p]),
     "b200_p2p_handle_bytes": (C.c_size_t, []),
     "b200_p2p_create": (_vp, [_i, _i, C.c_size_t]),
@@ -245,6 +246,20 @@ class Engine:
                                            out.ctypes.data_as(C.c_void_p), cnt.ctypes.data_as(C.c_void_p))
         if rc < 0:
             raise RuntimeError(f"[b200][ERROR] generate: {rc} " + self.lib.b200_engine_last_error().decode())
+        return out, cnt
+
+    def generate_ragged(self, prompts, max_new_tokens, eos_id=2):
+        """b200_engine_generate_ragged: `batch` prompts of different lengths -> (ids [batch, max_new_tokens], counts)"""
+        assert len(prompts) == self.batch
+        lens = np.array([len(p) for p in prompts], np.int32)
+        ids = np.ascontiguousarray(np.concatenate([np.asarray(p, np.int32).reshape(-1) for p in prompts]))
+        out = np.empty((self.batch, max_new_tokens), np.int32)
+        cnt = np.empty(self.batch, np.int32)
+        rc = self.lib.b200_engine_generate_ragged(self.h, ids.ctypes.data_as(C.c_void_p), lens.ctypes.data_as(C.c_void_p),
+                                                  max_new_tokens, eos_id, out.ctypes.data_as(C.c_void_p),
+                                                  cnt.ctypes.data_as(C.c_void_p))
+        if rc < 0:
+            raise RuntimeError(f"[b200][ERROR] generate_ragged: {rc} " + self.lib.b200_engine_last_error().decode())
         return out, cnt
 
     def load_weights(self, directory):

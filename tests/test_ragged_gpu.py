@@ -151,3 +151,31 @@ def test_reset_returns_to_one_step(pkg):
     with pytest.raises(RuntimeError):
         eng.prefill_ragged([np.arange(5, dtype=np.int32), np.arange(64, dtype=np.int32)])
     eng.close()
+
+
+def test_generate_ragged_equals_each_prompt_generated_alone(pkg):
+    """b200_engine_generate_ragged on three prompts of different lengths == b200_engine_generate on each prompt
+    alone (batch 1): sequences share nothing but the weights. Token ids are compared where the single-sequence
+    run's top-1 margin is clear of the fp16 band; a sequence is followed only up to its first ambiguous token."""
+    E = pkg.engine
+    rng = np.random.default_rng(21)
+    prompts = [rng.integers(3, SMALL["vocab_size"], n).astype(np.int32) for n in (12, 45, 3)]
+    n_new, max_seq = 12, 80
+    eng = E.Engine(3, max_seq, dtype=pkg.F16, **SMALL)
+    eng.init_random(seed=17, std=0.05)
+    got, cnt = eng.generate_ragged(prompts, n_new, eos_id=-1)
+    assert list(cnt) == [n_new] * 3 and list(eng.seq_steps) == [len(p) + n_new - 1 for p in prompts]
+    eng.close()
+    for b, p in enumerate(prompts):
+        one = E.Engine(1, max_seq, dtype=pkg.F16, **SMALL)
+        one.init_random(seed=17, std=0.05)
+        first = one.prefill(p[None, :])
+        toks = [int(first[0])]
+        for t in range(n_new):
+            lg = np.sort(one.logits().float().cpu().numpy()[0])
+            if toks[-1] != got[b, t] :
+                assert lg[-1] - lg[-2] <= 8e-2 * np.max(np.abs(lg)), f"sequence {b} token {t}: {toks[-1]} vs {got[b, t]}"
+                break
+            if t + 1 < n_new:
+                toks.append(int(one.decode_step_host(None)[0]))
+        one.close()
