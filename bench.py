@@ -127,45 +127,52 @@ def _cheap_random(shape, scale, seed):
     return np.resize(blk, n).reshape(shape)
 
 
-def cpu_baseline_port(wl, budget_layers=2):
-    """oracle port (plain C, pthreads over all host cores): one decode step of `budget_layers`
-    LLaMA-2-7B-shaped layers + final norm + LM head at the workload's batch/context, scaled to 32."""
+def cpu_baseline_port(wl, budget_s=10.0):
+    """oracle port (plain C, pthreads over all host cores): whole decode steps of a LLaMA-2-7B-shaped fp32 model
+    (32 layers that share ONE 0.8 GB set of layer weights - far larger than the host caches, so every layer still
+    streams its weights from DRAM - + final norm + LM head) at the workload's batch/context, repeated for about
+    `budget_s` seconds after one untimed step. Long-context batches keep 4 sequences and 4 layers (the fp32 KV cache
+    of 32 layers x 4 x 4096 keys would be 17 GB of host memory) and scale, saying so."""
     import numpy as np
     from oracle import cpu, model as omodel
     B, ctx = wl["batch"], wl["context"]
-    if B > 4:
-        B_s = 4      # bounded sample: 4 of the sequences, tokens/s scales with batch on the CPU too
-    else:
-        B_s = B
+    B_s = min(B, 4)   # bounded sample: tokens/s scales with batch on the CPU too
+    n_layers = 32 if B_s * ctx <= 4096 else 4
     H, I, V = 4096, 11008, 32000
     layers = [dict(attn_norm=np.ones(H, np.float32), qkv=_cheap_random((3 * H, H), 0.02, 1),
                    o=_cheap_random((H, H), 0.02, 2), ffn_norm=np.ones(H, np.float32),
-                   gate_up=_cheap_random((2 * I, H), 0.02, 3), down=_cheap_random((H, I), 0.02, 4))
-              for _ in range(1)] * budget_layers
+                   gate_up=_cheap_random((2 * I, H), 0.02, 3), down=_cheap_random((H, I), 0.02, 4))] * n_layers
     w = dict(layers=layers, embed=_cheap_random((V, H), 0.02, 5), final_norm=np.ones(H, np.float32),
              lm_head=_cheap_random((V, H), 0.02, 6))
-    cfg = dict(L7B, num_layers=budget_layers)
-    om = omodel.OracleModel(w, cfg, B_s, ctx + 4, "fp32")
+    cfg = dict(L7B, num_layers=n_layers)
+    max_steps = 64
+    om = omodel.OracleModel(w, cfg, B_s, ctx + max_steps + 4, "fp32")
     om.k[:] = 0.1
     om.v[:] = 0.1
     om.step = ctx
     ids = np.zeros(B_s, np.int32)
-    t0 = time.perf_counter()
-    om.decode_step(ids)
-    t_all = time.perf_counter() - t0
-    # split the LM-head part out so only the layer part is scaled by 32/budget_layers
+    om.decode_step(ids)   # untimed: first touch of every buffer
     x = np.zeros((B_s, H), np.float32)
     lg = np.zeros((B_s, V), np.float32)
     t0 = time.perf_counter()
     cpu.linear(x, w["lm_head"], lg, True)
     t_head = time.perf_counter() - t0
-    t_step = (t_all - t_head) * (32 / budget_layers) + t_head
-    return {"value": round(B_s / t_step * (wl["batch"] / B_s), 4), "unit": "tok/s", "cores": cpu.num_threads(),
+    steps, t0 = 0, time.perf_counter()
+    while steps < max_steps - 2:
+        om.decode_step(ids)
+        steps += 1
+        t_all = time.perf_counter() - t0
+        if t_all >= budget_s:
+            break
+    t_step = t_all / steps
+    if n_layers != 32:   # only the layer part scales
+        t_step = (t_step - t_head) * (32 / n_layers) + t_head
+    return {"value": round(B_s / t_step * (B / B_s), 4), "unit": "tok/s", "cores": cpu.num_threads(),
             "kind": "port",
-            "sample": f"1 decode step, {budget_layers} of 32 LLaMA-2-7B fp32 layers + LM head, batch {B_s}, "
-                      f"context {ctx}, layer time scaled x{32 // budget_layers}"
-                      + (f", tokens/s scaled x{wl['batch'] // B_s} to batch {wl['batch']}" if B_s != wl["batch"] else "")
-                      + f" ({t_all:.2f} s measured)"}
+            "sample": f"{steps} decode steps of {n_layers} LLaMA-2-7B fp32 layers + LM head, batch {B_s}, context {ctx}+"
+                      + (f", layer time scaled x{32 // n_layers}" if n_layers != 32 else "")
+                      + (f", tokens/s scaled x{B // B_s} to batch {B}" if B_s != B else "")
+                      + f" ({t_all:.1f} s measured after one untimed step)"}
 
 
 class RefCpu:
