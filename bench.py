@@ -50,6 +50,8 @@ def parse():
     ap.add_argument("--batch", type=int, default=None)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--context", type=int, default=None)
+    ap.add_argument("--mode", default=None, choices=["persistent", "fused_graph", "unfused_graph"],
+                    help="cfg2 / cfg4: force a decode launch order (default: the engine's own choice)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
 
@@ -657,6 +659,8 @@ def main():
     eng = E.Engine(B_local, max_seq, dtype=capi.F16, **L7B)
     eng.init_random(seed=1234 + rank, std=0.02)
     eng.fill_kv_random(ctx, seed=7 + rank, amp=0.5)   # context already in the cache (prefill is not the metric)
+    if args.mode:
+        eng.set_mode(fused=args.mode != "unfused_graph", graph=True, persistent=args.mode == "persistent")
     stream = torch.cuda.ExternalStream(eng.stream)
     ids0 = np.random.default_rng(7 + rank).integers(0, 32000, B_local).astype(np.int32)
 

@@ -307,6 +307,13 @@ extern "C" b200_engine* b200_engine_create(const b200_model_config* c, int batch
     cudaMemcpy(e->step_dev, &ref_step0, sizeof(int), cudaMemcpyHostToDevice);
     cudaDeviceSynchronize();
     build_program(e);
+    // default launch order by batch (measured, tools/route_sweep.sh, 7B fp16, ms per step at context 512 / 4096):
+    //   batch 2: persistent 3.52 / 4.71, graph + GEMV 3.53 / 4.46, graph + tcgen05 GEMM 3.79 / 4.73
+    //   batch 3: persistent 4.58 / 6.87, graph + GEMV 4.30 / 5.51, graph + tcgen05 GEMM 3.84 / 5.06
+    //   batch 4: persistent 4.82 / 7.14, graph + GEMV 4.41 / 6.01, graph + tcgen05 GEMM 3.95 / 5.52
+    // the GEMV's inner loop is issue-bound from 3 token rows on (2.8 TB/s at 4 rows), the weight-streaming GEMM is not.
+    // b200_engine_set_mode() still selects the fused / persistent kernels explicitly for any batch <= 4.
+    if (c->dtype == B200_F16 && c->tp_size == 1 && batch >= 3) e->mode = B200_ENGINE_GRAPH;
     return e;
 }
 

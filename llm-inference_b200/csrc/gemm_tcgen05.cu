@@ -370,8 +370,16 @@ static int pick_splits(int m_tiles, int k_blocks, int sms) {
 int gemm2_tcgen05_f16(const void* x, const void* W, const void* bias, void* y, int M, int N, int K, bool glu, cudaStream_t s,
                       const void* residual = nullptr);
 
+// fewest token rows b200_linear sends to the tcgen05 weight-streaming GEMM instead of the GEMV (B200_GEMM_MIN_TOKENS
+// overrides, for sweeps)
+int gemm_min_tokens() {
+    static int v = -1;
+    if (v < 0) { const char* e = getenv("B200_GEMM_MIN_TOKENS"); v = e ? atoi(e) : 3; if (v < 1) v = 1; }
+    return v;
+}
+
 size_t gemm_tcgen05_workspace_bytes(int M, int N, int K) {
-    if (M <= 4 || M > 256) return 0;
+    if (M < gemm_min_tokens() || M > 256) return 0;
     const int splits = pick_splits((N + kBM - 1) / kBM, (K + kBK - 1) / kBK, sm_count());
     return splits > 1 ? (size_t)splits * M * N * sizeof(float) : 0;
 }

@@ -17,6 +17,7 @@ int gemv_plain(const void* x, const void* W, const void* bias, void* y, int n_to
 int gemm_tcgen05_f16(const void* x, const void* W, const void* bias, void* y, int M, int N, int K,
                      void* workspace, size_t workspace_bytes, cudaStream_t s);
 size_t gemm_tcgen05_workspace_bytes(int M, int N, int K);
+int gemm_min_tokens();
 int gemm_tcgen05_f16_swiglu(const void* x, const void* W, void* out, int M, int inter, int K, cudaStream_t s);
 int gemm_tcgen05_f16_residual(const void* x, const void* W, const void* residual, void* y, int M, int N, int K, cudaStream_t s);
 
@@ -130,10 +131,10 @@ extern "C" int b200_linear(const void* x, const void* W, const void* bias, void*
     cudaStream_t s = (cudaStream_t)stream;
     const int E = dtype == B200_F16 ? 8 : 4;
     auto al = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; };
-    // fp16 with 5..8 token rows: the GEMV keeps all 8 x-rows in shared memory, which at K = 11008 leaves no room for
-    // its weight ring (it then walks the tokens in two halves and streams the weights twice); the tcgen05
-    // weight-streaming GEMM reads every weight byte once, so it takes these shapes when it can
-    if (trans_b && dtype == B200_F16 && n_tokens > 4 && n_tokens <= B200_GEMV_MAX_TOKENS) {
+    // fp16 with 3..8 token rows: the GEMV's inner loop is issue-bound from 3 rows on (2.8 TB/s at 4 rows), and at 5..8
+    // rows x K = 11008 its x-rows leave no room for the weight ring (tokens walked in two halves = weights streamed
+    // twice); the tcgen05 weight-streaming GEMM reads every weight byte once at 4.0-4.6 TB/s, so it takes these shapes
+    if (trans_b && dtype == B200_F16 && n_tokens >= b200::gemm_min_tokens() && n_tokens <= B200_GEMV_MAX_TOKENS) {
         int rc = gemm_tcgen05_f16(x, W, bias, y, n_tokens, N, K, workspace, workspace_bytes, s);
         if (rc != B200_EUNSUPPORTED) return rc;
     }

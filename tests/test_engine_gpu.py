@@ -167,8 +167,9 @@ def test_persistent_step_kernel_vs_oracle_with_context(pkg, cfg_name, B, ctx):
     E = pkg.engine
     SMALL = {"small": globals()["SMALL"], "wide": WIDE}[cfg_name]
     max_seq, steps = ctx + 16, 6
-    eng = E.Engine(B, max_seq, dtype=pkg.F16, **SMALL)   # fresh engine: persistent path is the default
+    eng = E.Engine(B, max_seq, dtype=pkg.F16, **SMALL)
     eng.init_random(seed=33, std=0.05)
+    eng.set_mode(fused=True, graph=True, persistent=True)   # the default for batch <= 2; batches 3-4 on request
     if ctx:
         eng.fill_kv_random(ctx, seed=5, amp=0.5)
     ora = omodel.OracleModel(download_weights(E, eng, SMALL["num_layers"]), SMALL, B, max_seq, "fp16")

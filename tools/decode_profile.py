@@ -16,6 +16,7 @@ ap.add_argument("--layers", type=int, default=2)
 ap.add_argument("--batch", type=int, default=32)
 ap.add_argument("--context", type=int, default=4096)
 ap.add_argument("--steps", type=int, default=2)
+ap.add_argument("--unfused", action="store_true", help="the reference's launch order instead of the fused GEMV order")
 a = ap.parse_args()
 pkg = load_package()
 E = pkg.engine
@@ -23,7 +24,7 @@ cfg = dict(num_layers=a.layers, head_num=32, kv_head_num=32, head_size=128, inte
 eng = E.Engine(a.batch, a.context + 16, dtype=pkg.F16, **cfg)
 eng.init_random(seed=1, std=0.02)
 eng.fill_kv_random(a.context)
-eng.set_mode(fused=True, graph=False)
+eng.set_mode(fused=not a.unfused, graph=False)
 ids = np.zeros(a.batch, np.int32)
 eng.decode_step_host(ids)
 torch.cuda.synchronize()
