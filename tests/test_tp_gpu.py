@@ -227,3 +227,84 @@ def test_p2p_single_rank_gemv_push_and_reduce(pkg):
         torch.cuda.synchronize()
         assert torch.equal(acc, (hidden.float() + part.float()).half()) and torch.equal(buf, part)
     lib.b200_p2p_destroy(comm)
+
+
+RAGGED_LENS, RAGGED_STEPS = [11, 4], 3
+
+
+def _ragged_worker(rank, world, port, kind, out_dir, comm):
+    """tensor-parallel engine, prompts of different lengths: b200_engine_prefill_ragged (row-split o / down summed
+    over the ranks for sum(lens) tokens), then free-running decode steps with per-sequence positions"""
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import torch.distributed as dist
+    pkg = load_package()
+    E, sh = pkg.engine, pkg.sharding
+    multi = torch.cuda.device_count() >= world
+    dev = rank if multi else 0
+    torch.cuda.set_device(dev)
+    kw = dict(device_id=torch.device("cuda", dev)) if multi else {}
+    dist.init_process_group("nccl" if multi else "gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank,
+                            world_size=world, **kw)
+    try:
+        full = make_weights(CFG, kind, 33)
+        eng = E.Engine(B, MAX_SEQ, dtype=pkg.F16 if kind == "fp16" else pkg.F32, tp_size=world, tp_rank=rank, **CFG)
+        for l, w in enumerate(full["layers"]):
+            s = sh.tp_shard_layer(w, CFG, world, rank)
+            for slot, key in ((E.W_ATTN_NORM, "attn_norm"), (E.W_QKV, "qkv"), (E.W_O, "o"),
+                              (E.W_FFN_NORM, "ffn_norm"), (E.W_GATE_UP, "gate_up"), (E.W_DOWN, "down")):
+                eng.set_weight(slot, l, s[key])
+        eng.set_weight(E.W_EMBED, 0, full["embed"])
+        eng.set_weight(E.W_FINAL_NORM, 0, full["final_norm"])
+        eng.set_weight(E.W_LM_HEAD, 0, full["lm_head"])
+        eng.set_mode(fused=True, graph=multi)
+        p2p = None
+        if comm == "p2p":
+            p2p = sh.P2PComm(64 * CFG["head_num"] * CFG["head_size"] * 4)   # the prompt pass sums sum(lens) rows at once
+            eng.set_p2p(p2p)
+        else:
+            eng.set_allreduce(sh.make_allreduce())
+        rng = np.random.default_rng(77)
+        prompts = [rng.integers(0, CFG["vocab_size"], n).astype(np.int32) for n in RAGGED_LENS]
+        ids = eng.prefill_ragged(prompts)
+        logits, picked = [eng.logits().float().cpu().numpy().copy()], [ids.copy()]
+        for _ in range(RAGGED_STEPS):
+            ids = eng.decode_step_host(None)
+            logits.append(eng.logits().float().cpu().numpy().copy())
+            picked.append(ids.copy())
+        assert list(eng.seq_steps) == [n + RAGGED_STEPS for n in RAGGED_LENS]
+        kc, _ = eng.kv_caches()
+        np.savez(os.path.join(out_dir, f"ragged{rank}.npz"), logits=np.stack(logits), ids=np.stack(picked),
+                 k=kc.float().cpu().numpy(), prompts=np.concatenate(prompts))
+        eng.close()
+        if p2p is not None:
+            p2p.close()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("kind,comm", [("fp16", "p2p"), ("fp16", "hook"), ("fp32", "hook")])
+def test_engine_tensor_parallel_ragged_batch(tmp_path, kind, comm):
+    """each sequence of a ragged tensor-parallel batch against the UNSHARDED oracle run on that sequence alone"""
+    import torch.multiprocessing as mp
+    from test_prefill_gpu import oracle_prefill
+    world = 2
+    if comm == "p2p" and torch.cuda.device_count() < world:
+        pytest.skip("the one-shot NVLink allreduce needs one GPU per rank")
+    mp.spawn(_ragged_worker, args=(world, free_port(), kind, str(tmp_path), comm), nprocs=world, join=True)
+    got = [np.load(os.path.join(tmp_path, f"ragged{r}.npz")) for r in range(world)]
+    assert np.array_equal(got[0]["ids"], got[1]["ids"]) and np.array_equal(got[0]["logits"], got[1]["logits"])
+    full = make_weights(CFG, kind, 33)
+    hkl = CFG["kv_head_num"] // world
+    off = 0
+    for b, n in enumerate(RAGGED_LENS):
+        om = omodel.OracleModel(full, CFG, 1, MAX_SEQ, kind)
+        prompt = got[0]["prompts"][off:off + n]
+        off += n
+        want, _ = oracle_prefill(om, full, CFG, prompt[None, :], 0)
+        assert_close(got[0]["logits"][0][b], want[0], kind, f"prefill logits of sequence {b}")
+        for s in range(RAGGED_STEPS):
+            want, _ = om.decode_step(got[0]["ids"][s][b:b + 1])   # follow the engine's tokens
+            assert_close(got[0]["logits"][s + 1][b], want[0], kind, f"sequence {b} decode step {s}")
+        for r in range(world):
+            assert_close(got[r]["k"][:, b], om.k[:, 0, r * hkl:(r + 1) * hkl], kind, f"rank {r} K shard of sequence {b}")
