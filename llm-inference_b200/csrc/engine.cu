@@ -307,13 +307,16 @@ extern "C" b200_engine* b200_engine_create(const b200_model_config* c, int batch
     cudaMemcpy(e->step_dev, &ref_step0, sizeof(int), cudaMemcpyHostToDevice);
     cudaDeviceSynchronize();
     build_program(e);
-    // default launch order by batch (measured, tools/route_sweep.sh, 7B fp16, ms per step at context 512 / 4096):
-    //   batch 2: persistent 3.52 / 4.71, graph + GEMV 3.53 / 4.46, graph + tcgen05 GEMM 3.79 / 4.73
-    //   batch 3: persistent 4.58 / 6.87, graph + GEMV 4.30 / 5.51, graph + tcgen05 GEMM 3.84 / 5.06
-    //   batch 4: persistent 4.82 / 7.14, graph + GEMV 4.41 / 6.01, graph + tcgen05 GEMM 3.95 / 5.52
-    // the GEMV's inner loop is issue-bound from 3 token rows on (2.8 TB/s at 4 rows), the weight-streaming GEMM is not.
-    // b200_engine_set_mode() still selects the fused / persistent kernels explicitly for any batch <= 4.
-    if (c->dtype == B200_F16 && c->tp_size == 1 && batch >= 3) e->mode = B200_ENGINE_GRAPH;
+    // default launch order by batch (measured, tools/route_sweep.sh, 7B fp16, ms per step at context 512 / 4096; the
+    // GEMV below is the tensor-core consumer, gemv.cu):
+    //   batch 2: persistent 3.53 / 4.72, fused GEMV graph 3.39 / 5.06, launch sequence graph 3.48 / 4.42
+    //   batch 3: persistent 4.58 / 6.91, fused GEMV graph 3.82 / 5.96, launch sequence graph 3.82 / 5.03
+    //   batch 4: persistent 4.83 / 7.16, fused GEMV graph 4.07 / 6.91, launch sequence graph 3.92 / 5.52
+    // (the persistent kernel still runs the scalar FHFMA loop, issue-bound from 2 token rows on). So batch 1 keeps the
+    // persistent kernel and fp16 batches >= 2 default to the graphed launch sequence, whose linears are the tensor-core
+    // GEMV up to 4 token rows and the tcgen05 weight-streaming GEMM above. b200_engine_set_mode() still selects the
+    // fused / persistent kernels explicitly for any batch <= 4.
+    if (c->dtype == B200_F16 && c->tp_size == 1 && batch >= 2) e->mode = B200_ENGINE_GRAPH;
     return e;
 }
 

@@ -374,7 +374,7 @@ int gemm2_tcgen05_f16(const void* x, const void* W, const void* bias, void* y, i
 // overrides, for sweeps)
 int gemm_min_tokens() {
     static int v = -1;
-    if (v < 0) { const char* e = getenv("B200_GEMM_MIN_TOKENS"); v = e ? atoi(e) : 3; if (v < 1) v = 1; }
+    if (v < 0) { const char* e = getenv("B200_GEMM_MIN_TOKENS"); v = e ? atoi(e) : 5; if (v < 1) v = 1; }
     return v;
 }
 

@@ -13,6 +13,8 @@
 //  * 8 consumer warps: warp w owns unit w of the stage, dots both rows against x held in
 //    shared memory (one x packet read serves two weight packets), fp32 accumulation
 //    (fma.rn.f32.f16 -> FHFMA for half), warp-shuffle reduce at the end of the row;
+//    from 2 fp16 token rows on the consumers switch to mma.sync (kSegPitchMma below): measured at batch 2 / 3 / 4,
+//    7B shapes, fused order, context 512: 3.50 / 4.45 / 4.71 -> 3.39 / 3.82 / 4.07 ms per step;
 //  * under programmatic dependent launch the producer starts streaming WEIGHTS before
 //    griddepcontrol.wait, so the HBM pipe stays busy across kernel boundaries; only the
 //    x load waits for the predecessor.
@@ -28,6 +30,15 @@ constexpr int kSegBytes = 2048;                     // K-segment per row per sta
 constexpr int kStageBytes = kGemvWarps * 2 * kSegBytes;  // 32 KB
 constexpr int kMaxStages = 4;
 constexpr int kJ = kSegBytes / 16 / 32;  // 16B packets per lane per row-segment (=4)
+// Tensor-core consumer (fp16, 2..8 token rows): one FHFMA per weight element PER TOKEN makes the scalar loop
+// issue-bound from 2 rows on (2.8 TB/s at 4 rows). The MMA consumer keeps the same 2 KB contiguous row stream but
+// reads the stage as a [16 rows x 1024 k] fp16 matrix: warp w takes k in [128 w, 128 w + 128) of ALL 16 rows with
+// eight mma.sync.m16n8k16 (A = weights, B = the <= 8 token rows of x, fp32 accumulate), and the eight warps' partial
+// [16 x 8] sums meet in shared memory once per row group. Row pitch 2 KB + 16 B and x pitch K + 8 elements keep every
+// fragment load (one 32-bit word per lane) conflict-free.
+constexpr int kSegPitchMma = kSegBytes + 16;
+constexpr int kStageBytesMma = kGemvWarps * 2 * kSegPitchMma;
+constexpr int kXPadMma = 8;   // elements
 
 enum { kModePlain = 0, kModeResidual = 1, kModeSwiglu = 2, kModeRopeKV = 3 };
 
@@ -77,17 +88,28 @@ __device__ __forceinline__ void consumer_bar() {
     asm volatile("bar.sync 1, %0;" ::"n"(kGemvWarps * 32) : "memory");
 }
 
-template <typename T, int NB, int MODE>
+__device__ __forceinline__ void mma_f16_16816(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
+                                              uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+template <typename T, int NB, int MODE, bool MMA = false>
 __global__ void __launch_bounds__(kGemvThreads, 1) gemv_stream_kernel(const GemvParams p) {
     constexpr int E = DT<T>::kPer16B;
     constexpr int KSEG = kSegBytes / (int)sizeof(T);  // elements per segment
+    constexpr int PITCH = MMA ? kSegPitchMma : kSegBytes;        // bytes between the rows of a stage
+    constexpr int STAGE = MMA ? kStageBytesMma : kStageBytes;
     extern __shared__ __align__(128) unsigned char smem[];
     unsigned char* ring = smem;
-    T* xs = reinterpret_cast<T*>(smem + (size_t)p.stages * kStageBytes);
+    const int xp = MMA ? p.K + kXPadMma : p.K;                   // elements between the token rows of x
+    T* xs = reinterpret_cast<T*>(smem + (size_t)p.stages * STAGE);
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(
-        smem + (size_t)p.stages * kStageBytes + (((size_t)NB * p.K * sizeof(T) + 15) & ~(size_t)15));
+        smem + (size_t)p.stages * STAGE + (((size_t)NB * xp * sizeof(T) + 15) & ~(size_t)15));
     uint64_t* empty_bar = full_bar + kMaxStages;
     float* red = reinterpret_cast<float*>(empty_bar + kMaxStages);  // [NB][kGemvWarps] + [NB]
+    float* red_mma = red + NB * kGemvWarps + NB;                    // MMA: [kGemvWarps][16][8]
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int nseg = (p.K + KSEG - 1) / KSEG;
@@ -130,13 +152,13 @@ __global__ void __launch_bounds__(kGemvThreads, 1) gemv_stream_kernel(const Gemv
                 if (r >= 0) src = Wb + (size_t)r * row_bytes;
             }
             const uint32_t rows_here = __popc(__ballot_sync(0xffffffffu, src != nullptr));
-            unsigned char* dst_lane = ring + (size_t)lane * kSegBytes;
+            unsigned char* dst_lane = ring + (size_t)lane * PITCH;
             for (int seg = 0; seg < nseg; ++seg) {
                 if (wrapped) mbar_wait(&empty_bar[slot], phase);
                 const uint32_t seg_bytes = (seg == nseg - 1) ? (uint32_t)last_seg_bytes : (uint32_t)kSegBytes;
                 if (lane == 0) mbar_expect_tx(&full_bar[slot], seg_bytes * rows_here);
                 if (src)
-                    bulk_g2s(dst_lane + (size_t)slot * kStageBytes, src + (size_t)seg * kSegBytes, seg_bytes,
+                    bulk_g2s(dst_lane + (size_t)slot * STAGE, src + (size_t)seg * kSegBytes, seg_bytes,
                              &full_bar[slot]);
                 if (++slot == nstages) {
                     slot = 0;
@@ -165,7 +187,7 @@ __global__ void __launch_bounds__(kGemvThreads, 1) gemv_stream_kernel(const Gemv
             for (int b = 0; b < NB; ++b) {
                 if (b >= p.nb) break;
                 Pack16 v = ld16(xg + (size_t)b * p.K + (size_t)i * E);
-                st16(xs + (size_t)b * p.K + (size_t)i * E, v);
+                st16(xs + (size_t)b * xp + (size_t)i * E, v);
                 if (p.flags & B200_GEMV_NORM) {
                     float f[E];
                     Unpack<T>::get(v, f);
@@ -197,12 +219,12 @@ __global__ void __launch_bounds__(kGemvThreads, 1) gemv_stream_kernel(const Gemv
                     if (b >= p.nb) break;
                     const float inv = red[NB * kGemvWarps + b];
                     float f[E];
-                    Unpack<T>::get(ld16(xs + (size_t)b * p.K + (size_t)i * E), f);
+                    Unpack<T>::get(ld16(xs + (size_t)b * xp + (size_t)i * E), f);
 #pragma unroll
                     for (int e = 0; e < E; ++e)
                         f[e] = gfirst ? (g[e] * f[e]) * inv
                                                                : (f[e] * inv) * g[e];
-                    st16(xs + (size_t)b * p.K + (size_t)i * E, Unpack<T>::put(f));  // rounds to T
+                    st16(xs + (size_t)b * xp + (size_t)i * E, Unpack<T>::put(f));  // rounds to T
                 }
             }
         }
@@ -226,9 +248,35 @@ __global__ void __launch_bounds__(kGemvThreads, 1) gemv_stream_kernel(const Gemv
       const bool active = unit < u1;
       int ra = 0, rb = -1;
       if (active) unit_rows<MODE>(p, unit, ra, rb);
+      float cm[4] = {0.f, 0.f, 0.f, 0.f};   // MMA: this warp's k-slice of rows (lane/4, lane/4 + 8) x tokens (2(lane%4), +1)
       for (int seg = 0; seg < nseg; ++seg) {
         mbar_wait(&full_bar[slot], full_phase);
-        if (active) {
+        if constexpr (MMA) {
+            const int gq = lane >> 2, tq = lane & 3;
+            const int seg_len = (seg == nseg - 1) ? last_seg_pk * E : KSEG;   // elements; a multiple of 16 (host check)
+            const unsigned char* st = ring + (size_t)slot * STAGE;
+            const unsigned char* ar0 = st + (size_t)gq * PITCH;
+            const unsigned char* ar1 = st + (size_t)(gq + 8) * PITCH;
+            const T* xr = xs + (size_t)gq * xp + (size_t)seg * KSEG;   // token gq (zero fragment when gq >= nb)
+            const bool tok = gq < p.nb;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int kk = warp * 128 + i * 16;
+                if (kk < seg_len) {
+                    const int o = (kk + 2 * tq) * 2;
+                    const uint32_t a0 = *reinterpret_cast<const uint32_t*>(ar0 + o);
+                    const uint32_t a1 = *reinterpret_cast<const uint32_t*>(ar1 + o);
+                    const uint32_t a2 = *reinterpret_cast<const uint32_t*>(ar0 + o + 16);
+                    const uint32_t a3 = *reinterpret_cast<const uint32_t*>(ar1 + o + 16);
+                    uint32_t b0 = 0u, b1 = 0u;
+                    if (tok) {
+                        b0 = *reinterpret_cast<const uint32_t*>(xr + kk + 2 * tq);
+                        b1 = *reinterpret_cast<const uint32_t*>(xr + kk + 2 * tq + 8);
+                    }
+                    mma_f16_16816(cm, a0, a1, a2, a3, b0, b1);
+                }
+            }
+        } else if (active) {
             const int seg_pk = (seg == nseg - 1) ? last_seg_pk : KSEG / E;
             const unsigned char* sa = ring + (size_t)slot * kStageBytes + (2 * warp) * kSegBytes;
             const unsigned char* sb = sa + kSegBytes;
@@ -248,7 +296,7 @@ __global__ void __launch_bounds__(kGemvThreads, 1) gemv_stream_kernel(const Gemv
                 if (pkt < seg_pk) {
 #pragma unroll
                     for (int b = 0; b < NB; ++b) {
-                        const Pack16 xv = ld16(xseg + (size_t)b * p.K + (size_t)pkt * E);
+                        const Pack16 xv = ld16(xseg + (size_t)b * xp + (size_t)pkt * E);
                         acc_a[b] = dot16<T>(wa[j], xv, acc_a[b]);
                         if (rb >= 0) acc_b[b] = dot16<T>(wb[j], xv, acc_b[b]);
                     }
@@ -262,12 +310,37 @@ __global__ void __launch_bounds__(kGemvThreads, 1) gemv_stream_kernel(const Gemv
             full_phase ^= 1;
         }
 
+        if constexpr (MMA) {
+            if (seg == nseg - 1) {
+                // ---- end of the row group: the eight warps' k-slices meet; warp w then owns rows 2w, 2w+1 as before
+                const int gq = lane >> 2, tq = lane & 3;
+                float* part = red_mma + warp * 128;
+                part[gq * 8 + 2 * tq] = cm[0];
+                part[gq * 8 + 2 * tq + 1] = cm[1];
+                part[(gq + 8) * 8 + 2 * tq] = cm[2];
+                part[(gq + 8) * 8 + 2 * tq + 1] = cm[3];
+                consumer_bar();
+                float sum = 0.f;
+                if (lane < 16) {
+#pragma unroll
+                    for (int w = 0; w < kGemvWarps; ++w) sum += red_mma[w * 128 + (2 * warp + (lane >> 3)) * 8 + (lane & 7)];
+                }
+                consumer_bar();   // red_mma is free for the next group
+#pragma unroll
+                for (int b = 0; b < NB; ++b) {
+                    acc_a[b] = __shfl_sync(0xffffffffu, sum, b);
+                    acc_b[b] = __shfl_sync(0xffffffffu, sum, 8 + b);
+                }
+            }
+        }
         if (seg == nseg - 1 && active) {
             // ---- end of the row pair: reduce + epilogue (lane 0 writes) ----
+            if constexpr (!MMA) {
 #pragma unroll
-            for (int b = 0; b < NB; ++b) {
-                acc_a[b] = warp_sum(acc_a[b]);
-                acc_b[b] = warp_sum(acc_b[b]);
+                for (int b = 0; b < NB; ++b) {
+                    acc_a[b] = warp_sum(acc_a[b]);
+                    acc_b[b] = warp_sum(acc_b[b]);
+                }
             }
             if (lane == 0) {
                 const T* bias = reinterpret_cast<const T*>(p.bias);
@@ -374,10 +447,17 @@ __global__ void __launch_bounds__(kGemvThreads, 1) gemv_stream_kernel(const Gemv
 // ------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------
-static size_t gemv_smem_bytes(int stages, int NB, int K, int esz) {
-    size_t x = (((size_t)NB * K * esz) + 15) & ~(size_t)15;
-    return (size_t)stages * kStageBytes + x + 2 * kMaxStages * sizeof(uint64_t) +
-           (size_t)(NB * kGemvWarps + NB) * sizeof(float) + 16;
+static size_t gemv_smem_bytes(int stages, int NB, int K, int esz, bool mma = false) {
+    size_t x = (((size_t)NB * (K + (mma ? kXPadMma : 0)) * esz) + 15) & ~(size_t)15;
+    return (size_t)stages * (mma ? kStageBytesMma : kStageBytes) + x + 2 * kMaxStages * sizeof(uint64_t) +
+           (size_t)(NB * kGemvWarps + NB) * sizeof(float) + (mma ? (size_t)kGemvWarps * 128 * sizeof(float) : 0) + 16;
+}
+
+// tensor-core consumer: fp16, 2..8 token rows, K a multiple of 16 (B200_GEMV_MMA=0 keeps the scalar loop, for A/B runs)
+static bool gemv_use_mma(int NB, int K, int esz) {
+    static int on = -1;
+    if (on < 0) { const char* e = getenv("B200_GEMV_MMA"); on = (e && e[0] == '0') ? 0 : 1; }
+    return on && esz == 2 && NB >= 2 && (K & 15) == 0;
 }
 
 static int gemv_max_stages() {
@@ -392,14 +472,15 @@ static int gemv_max_stages() {
 }
 
 static int gemv_pick_stages(int NB, int K, int esz) {
+    const bool mma = gemv_use_mma(NB, K, esz);
     for (int st = gemv_max_stages(); st >= 2; --st)
-        if (gemv_smem_bytes(st, NB, K, esz) <= 227 * 1024) return st;
+        if (gemv_smem_bytes(st, NB, K, esz, mma) <= 227 * 1024) return st;
     return 0;
 }
 
-template <typename T, int NB, int MODE>
+template <typename T, int NB, int MODE, bool MMA = false>
 static int gemv_launch_one(const GemvParams& p, size_t smem, int grid, cudaStream_t s) {
-    auto kern = gemv_stream_kernel<T, NB, MODE>;
+    auto kern = gemv_stream_kernel<T, NB, MODE, MMA>;
     static bool attr_set = false;  // per instantiation
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -442,11 +523,21 @@ static int gemv_dispatch_nb(GemvParams p, int n_tokens, cudaStream_t s) {
     }
     p.stages = stages;
     p.nb = n_tokens;
-    const size_t smem = gemv_smem_bytes(stages, NB, p.K, esz);
+    const bool mma = gemv_use_mma(NB, p.K, esz);
+    const size_t smem = gemv_smem_bytes(stages, NB, p.K, esz, mma);
     int grid = sm_count();
     const int groups = (p.units + kGemvWarps - 1) / kGemvWarps;
     if (grid > groups) grid = groups;
     if (grid < 1) grid = 1;
+    if constexpr (sizeof(T) == 2) {
+        if (mma) {
+            switch (NB) {
+                case 2: return gemv_launch_one<T, 2, MODE, true>(p, smem, grid, s);
+                case 4: return gemv_launch_one<T, 4, MODE, true>(p, smem, grid, s);
+                default: return gemv_launch_one<T, 8, MODE, true>(p, smem, grid, s);
+            }
+        }
+    }
     switch (NB) {
         case 1: return gemv_launch_one<T, 1, MODE>(p, smem, grid, s);
         case 2: return gemv_launch_one<T, 2, MODE>(p, smem, grid, s);

@@ -131,9 +131,9 @@ extern "C" int b200_linear(const void* x, const void* W, const void* bias, void*
     cudaStream_t s = (cudaStream_t)stream;
     const int E = dtype == B200_F16 ? 8 : 4;
     auto al = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; };
-    // fp16 with 3..8 token rows: the GEMV's inner loop is issue-bound from 3 rows on (2.8 TB/s at 4 rows), and at 5..8
-    // rows x K = 11008 its x-rows leave no room for the weight ring (tokens walked in two halves = weights streamed
-    // twice); the tcgen05 weight-streaming GEMM reads every weight byte once at 4.0-4.6 TB/s, so it takes these shapes
+    // fp16 with 5..8 token rows: at K = 11008 the GEMV's x-rows leave no room for its weight ring (tokens walked in two
+    // halves = weights streamed twice); the tcgen05 weight-streaming GEMM reads every weight byte once, so it takes
+    // these shapes. Up to 4 rows the GEMV (tensor-core consumer from 2 rows on) is as fast or faster (route_sweep.sh).
     if (trans_b && dtype == B200_F16 && n_tokens >= b200::gemm_min_tokens() && n_tokens <= B200_GEMV_MAX_TOKENS) {
         int rc = gemm_tcgen05_f16(x, W, bias, y, n_tokens, N, K, workspace, workspace_bytes, s);
         if (rc != B200_EUNSUPPORTED) return rc;

@@ -169,7 +169,7 @@ def test_persistent_step_kernel_vs_oracle_with_context(pkg, cfg_name, B, ctx):
     max_seq, steps = ctx + 16, 6
     eng = E.Engine(B, max_seq, dtype=pkg.F16, **SMALL)
     eng.init_random(seed=33, std=0.05)
-    eng.set_mode(fused=True, graph=True, persistent=True)   # the default for batch <= 2; batches 3-4 on request
+    eng.set_mode(fused=True, graph=True, persistent=True)   # the default for batch 1; batches 2-4 on request
     if ctx:
         eng.fill_kv_random(ctx, seed=5, amp=0.5)
     ora = omodel.OracleModel(download_weights(E, eng, SMALL["num_layers"]), SMALL, B, max_seq, "fp16")
