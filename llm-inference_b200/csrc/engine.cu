@@ -307,16 +307,15 @@ extern "C" b200_engine* b200_engine_create(const b200_model_config* c, int batch
     cudaMemcpy(e->step_dev, &ref_step0, sizeof(int), cudaMemcpyHostToDevice);
     cudaDeviceSynchronize();
     build_program(e);
-    // default launch order by batch (measured, tools/route_sweep.sh, 7B fp16, ms per step at context 512 / 4096; the
-    // GEMV below is the tensor-core consumer, gemv.cu):
-    //   batch 2: persistent 3.53 / 4.72, fused GEMV graph 3.39 / 5.06, launch sequence graph 3.48 / 4.42
-    //   batch 3: persistent 4.58 / 6.91, fused GEMV graph 3.82 / 5.96, launch sequence graph 3.82 / 5.03
-    //   batch 4: persistent 4.83 / 7.16, fused GEMV graph 4.07 / 6.91, launch sequence graph 3.92 / 5.52
+    // default launch order by batch (measured, tools/order_sweep.sh + route_sweep.sh, 7B fp16, ms per step at
+    // context 512 / 4096; GEMV = the tensor-core consumer, gemv.cu):
+    //   batch 2: persistent 3.53 / 4.72, fused GEMV graph 3.30 / 4.24, reference launch order graph 3.49 / 4.42
+    //   batch 3: persistent 4.58 / 6.91, fused GEMV graph 3.69 / 4.91, reference launch order graph 3.82 / 5.03
+    //   batch 4: persistent 4.83 / 7.16, fused GEMV graph 3.90 / 5.53, reference launch order graph 3.93 / 5.53
     // (the persistent kernel still runs the scalar FHFMA loop, issue-bound from 2 token rows on). So batch 1 keeps the
-    // persistent kernel and fp16 batches >= 2 default to the graphed launch sequence, whose linears are the tensor-core
-    // GEMV up to 4 token rows and the tcgen05 weight-streaming GEMM above. b200_engine_set_mode() still selects the
-    // fused / persistent kernels explicitly for any batch <= 4.
-    if (c->dtype == B200_F16 && c->tp_size == 1 && batch >= 2) e->mode = B200_ENGINE_GRAPH;
+    // persistent kernel, fp16 batches 2-4 default to the graphed fused-GEMV order; batches >= 5 run the reference
+    // launch order on the tcgen05 weight-streaming GEMM whatever the FUSED flag says (enqueue_step).
+    if (c->dtype == B200_F16 && c->tp_size == 1 && batch >= 2) e->mode = B200_ENGINE_FUSED | B200_ENGINE_GRAPH;
     return e;
 }
 
