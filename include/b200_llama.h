@@ -243,6 +243,22 @@ int b200_decode_attention_ragged(const void* qkv, void* k_cache_layer, void* v_c
                                  int max_step, const int* seq_steps_dev, int append_kv, int dtype,
                                  void* stream);
 
+/* Allocation-free variant of b200_decode_attention. No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA-graph capture, tight
+ * serving loops, harnesses that forbid it). Same arguments minus the workspace: the split-KV partials
+ * live in a file-scope `static __device__` array of B200_DECODE_ATTENTION_STATIC_MAX_BYTES inside the
+ * library (every GPU that loads the library holds it until exit); its device address is resolved once
+ * per device by cudaGetSymbolAddress on the first call made with that device current (make that call
+ * outside stream capture). Calls no cudaMalloc / cudaFree / allocating routine. A shape whose scratch
+ * exceeds the maximum returns B200_EWORKSPACE and prints the needed size to stderr - use
+ * b200_decode_attention with a caller-owned workspace then. All calls share the array: nothing in it
+ * needs clearing between calls (every partial is written before it is read), but two calls that
+ * overlap on the GPU (different streams without a dependency) race on it. */
+#define B200_DECODE_ATTENTION_STATIC_MAX_BYTES (8u << 20)
+int b200_decode_attention_static(const void* qkv, void* k_cache_layer, void* v_cache_layer, void* out,
+                                 int batch, int head_num, int kv_head_num, int head_size,
+                                 int max_seq_len, int step, int append_kv, int dtype, void* stream);
+
 /* Prefill attention without materialising scores / mask / repeated KV (replaces
  * context_attention.cpp:136-161: RepeatKV + QK^T + ScaleMaskSoftmax + PV + transpose):
  * q [batch, head_num, seq_len, head_size]; cache layer slice as above;

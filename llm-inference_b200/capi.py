@@ -57,6 +57,7 @@ PROTOTYPES = {
     "b200_decode_attention": (_i, [_vp, _vp, _vp, _vp, _vp, _sz] + [_i] * 8 + [_vp]),
     "b200_decode_attention_ex": (_i, [_vp, _vp, _vp, _vp, _vp, _sz] + [_i] * 6 + [_vp, _i, _i, _vp]),
     "b200_decode_attention_ragged": (_i, [_vp, _vp, _vp, _vp, _vp, _sz] + [_i] * 6 + [_vp, _i, _i, _vp]),
+    "b200_decode_attention_static": (_i, [_vp, _vp, _vp, _vp] + [_i] * 8 + [_vp]),
     "b200_rope_decode_ragged": (_i, [_vp, _i, _i, _i, _i, _vp, _i, C.c_float, _vp, _i, _vp]),
     "b200_context_attention": (_i, [_vp] * 7 + [_i] * 8 + [_vp]),
     "b200_embedding": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp]),

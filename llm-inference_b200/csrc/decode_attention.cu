@@ -435,3 +435,86 @@ extern "C" int b200_decode_attention(const void* qkv, void* k_cache_layer, void*
                                     workspace_bytes, batch, head_num, kv_head_num, head_size,
                                     max_seq_len, step, nullptr, append_kv, dtype, stream);
 }
+
+// ------------------------------------------------------------------------------------------
+// Allocation-free variant (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA-graph capture, tight serving loops).
+// The split-KV partials / generic score rows live in a file-scope device array instead of a
+// caller-supplied workspace. Every GPU that loads the library holds the array until exit.
+//  * The array's name is only a host-side stand-in in host code: its device address is looked up
+//    once per device, with that device current, by cudaGetSymbolAddress, and that pointer is what
+//    the kernels get.
+//  * Nothing here (or below it) calls cudaMalloc / cudaFree or an allocating library routine.
+//  * All calls share the array. Nothing in it has to start at zero: every (head, split) partial
+//    the combine kernel reads is written by the split kernel of the same call first (an empty split
+//    writes m = -inf, l = 0), and the generic path writes each score row before it reads it. Two
+//    calls that overlap on the GPU (different streams, no dependency) race on it.
+// ------------------------------------------------------------------------------------------
+#include <cstdio>
+static __device__ __align__(256) unsigned char g_attn_static_scratch[B200_DECODE_ATTENTION_STATIC_MAX_BYTES];
+
+namespace {
+constexpr int kMaxStaticDevices = 64;
+std::mutex g_attn_static_mu;
+void* g_attn_static_ptr[kMaxStaticDevices] = {};
+
+// device address of g_attn_static_scratch on the CURRENT device (looked up once per device)
+int attn_static_scratch(void** out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 0 || dev >= kMaxStaticDevices) return B200_EUNSUPPORTED;
+    std::lock_guard<std::mutex> g(g_attn_static_mu);
+    if (!g_attn_static_ptr[dev]) {
+        void* ptr = nullptr;
+        e = cudaGetSymbolAddress(&ptr, g_attn_static_scratch);
+        if (e != cudaSuccess) return (int)e;
+        if (!ptr) return (int)cudaErrorInvalidSymbol;
+        g_attn_static_ptr[dev] = ptr;
+    }
+    *out = g_attn_static_ptr[dev];
+    return 0;
+}
+}  // namespace
+
+extern "C" int b200_decode_attention_static(const void* qkv, void* k_cache_layer, void* v_cache_layer,
+                                            void* out, int batch, int head_num, int kv_head_num,
+                                            int head_size, int max_seq_len, int step, int append_kv,
+                                            int dtype, void* stream) {
+    B200_RETURN_IF(batch <= 0 || head_num <= 0 || kv_head_num <= 0 || head_size <= 0 || max_seq_len <= 0 ||
+                       head_num % kv_head_num != 0 || step < 1 || step > max_seq_len,
+                   B200_EINVAL);
+    B200_RETURN_IF(dtype != B200_F32 && dtype != B200_F16, B200_EINVAL);
+    // scratch this shape needs: the same two formulas decode_attention_impl checks its workspace against
+    const int esz = dtype == B200_F16 ? 2 : 4;
+    size_t need;
+    if (attn_fast_shape(head_num, kv_head_num, head_size, esz)) {
+        const int splits = attn_pick_splits(batch, kv_head_num, step, head_num / kv_head_num);
+        const size_t ml = (size_t)batch * head_num * splits * 2 * sizeof(float);
+        need = splits > 1 ? ((ml + 255) & ~(size_t)255) + (size_t)batch * head_num * splits * head_size * sizeof(float)
+                          : 0;
+        // a misaligned pointer sends a fast shape down the generic path
+        const size_t generic = (size_t)batch * head_num * (size_t)max_seq_len * sizeof(float);
+        auto al = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15u) == 0; };
+        if (!(al(qkv) && al(k_cache_layer) && al(v_cache_layer))) need = generic;
+    } else {
+        need = (size_t)batch * head_num * (size_t)max_seq_len * sizeof(float);
+    }
+    if (need > (size_t)B200_DECODE_ATTENTION_STATIC_MAX_BYTES) {
+        fprintf(stderr,
+                "[b200][ERROR] b200_decode_attention_static: this shape needs %zu bytes of scratch, the built-in "
+                "array holds %zu (B200_DECODE_ATTENTION_STATIC_MAX_BYTES); use b200_decode_attention with a "
+                "caller-owned workspace\n",
+                need, (size_t)B200_DECODE_ATTENTION_STATIC_MAX_BYTES);
+        return B200_EWORKSPACE;
+    }
+    void* scratch = nullptr;
+    const int rc = attn_static_scratch(&scratch);
+    if (rc != 0) {
+        fprintf(stderr, "[b200][ERROR] b200_decode_attention_static: cudaGetSymbolAddress failed (%d)\n", rc);
+        return rc;
+    }
+    return decode_attention_impl(qkv, k_cache_layer, v_cache_layer, out, scratch,
+                                 (size_t)B200_DECODE_ATTENTION_STATIC_MAX_BYTES, batch, head_num, kv_head_num,
+                                 head_size, max_seq_len, step, nullptr, 0, append_kv, dtype, stream);
+}
