@@ -100,6 +100,10 @@ int b200_p2p_reduce_add(b200_p2p* c, void* hidden, size_t count, int dtype, void
 /* buf[count] <- sum over ranks of buf[count], in place (the batched / prefill paths) */
 int b200_p2p_allreduce(b200_p2p* c, void* buf, size_t count, int dtype, void* stream);
 size_t b200_p2p_max_message_bytes(const b200_p2p* c);
+/* Frees this rank's receive buffer and unmaps the peers'. ALL ranks must have finished (stream-synchronised) their
+ * last call on the communicator and then passed a barrier of the caller's (e.g. torch.distributed.barrier) before any
+ * rank destroys it: a lagging peer would otherwise still push into, or read from, freed memory. The library only
+ * synchronises the local device. */
 void b200_p2p_destroy(b200_p2p* c);
 
 b200_engine* b200_engine_create(const b200_model_config* cfg, int batch);

@@ -40,7 +40,8 @@ __device__ __forceinline__ Pack16 ld16(const void* p) {
 __device__ __forceinline__ void st16(void* p, const Pack16& v) {
     *reinterpret_cast<Pack16*>(p) = v;
 }
-// streaming (read-once) global load that does not allocate in L1
+// streaming (read-once) global load that does not allocate in L1. Read-only (.nc) path: only for
+// data that no thread of the running kernel writes.
 __device__ __forceinline__ Pack16 ld16_stream(const void* p) {
     Pack16 r;
     asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
@@ -217,15 +218,32 @@ __device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, uint3
 // ---------------------------------------------------------------------------
 // host-side helpers
 // ---------------------------------------------------------------------------
+// Per-DEVICE caches: function attributes and the SM count belong to the device that is current at
+// the call, not to the process (a process may drive engines on several GPUs).
+constexpr int kMaxDevices = 64;
+inline int current_device() {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    return (dev < 0 || dev >= kMaxDevices) ? 0 : dev;
+}
 inline int sm_count() {
-    static int n = 0;
-    if (n == 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-        if (n <= 0) n = 148;
+    static int n[kMaxDevices] = {};
+    const int dev = current_device();
+    if (n[dev] == 0) {
+        int v = 0;
+        cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
+        n[dev] = v > 0 ? v : 148;
     }
-    return n;
+    return n[dev];
+}
+// cudaFuncAttributeMaxDynamicSharedMemorySize once per (kernel instantiation, device). `done` is the
+// caller's function-local `static unsigned long long` bit mask (one per instantiation).
+inline cudaError_t ensure_max_dynamic_smem(const void* func, int bytes, unsigned long long& done) {
+    const int dev = current_device();
+    if (done & (1ull << dev)) return cudaSuccess;
+    const cudaError_t e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e == cudaSuccess) done |= 1ull << dev;
+    return e;
 }
 
 inline bool pdl_enabled() {
@@ -242,9 +260,10 @@ inline bool pdl_enabled() {
 // and a PDL-launched successor would have to wait for the SM to drain.
 inline void prefer_max_smem_carveout(const void* func) {
     static std::mutex mu;
-    static std::unordered_set<const void*> done;
+    static std::unordered_set<const void*> done[kMaxDevices];
+    const int dev = current_device();
     std::lock_guard<std::mutex> g(mu);
-    if (done.insert(func).second)
+    if (done[dev].insert(func).second)
         cudaFuncSetAttribute(func, cudaFuncAttributePreferredSharedMemoryCarveout,
                              cudaSharedmemCarveoutMaxShared);
 }

@@ -497,12 +497,10 @@ extern "C" int b200_context_attention(const void* q, const void* k_cache_layer, 
     p.q_tiles = (seq_len + kCtxTile - 1) / kCtxTile;
     p.scale_log2 = (1.0f / sqrtf((float)head_size)) * 1.4426950408889634f;
     p.trace = g_ctx_trace;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(context_attn_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)kCtxSmem);
+    static unsigned long long attr_done = 0;   // one bit per device
+    {
+        cudaError_t e = ensure_max_dynamic_smem(reinterpret_cast<const void*>(context_attn_tcgen05_kernel), (int)kCtxSmem, attr_done);
         if (e != cudaSuccess) return (int)e;
-        attr_set = true;
     }
     const long long grid = (long long)p.q_tiles * batch * head_num;
     if (grid >= (1ll << 31)) return B200_EUNSUPPORTED;

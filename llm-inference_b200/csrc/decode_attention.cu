@@ -77,8 +77,11 @@ decode_attn_split_kernel(const AttnParams p) {
             st16(vc + (size_t)(step - 1) * D + t * E,
                  ld16(tok + (size_t)(p.head_num + p.kv_head_num + kvh) * D + t * E));
         }
-        __syncthreads();
     }
+
+    const T* knew = tok + (size_t)(p.head_num + kvh) * D;
+    const T* vnew = tok + (size_t)(p.head_num + p.kv_head_num + kvh) * D;
+    const int new_row = p.append_kv ? step - 1 : -1;
 
     // q packets for the G heads of this kv group stay packed in T
     Pack16 q[G];
@@ -103,12 +106,14 @@ decode_attn_split_kernel(const AttnParams p) {
         for (int u = 0; u < kUnroll; ++u) {
             const int key = base + u * KPI + ks;
             ok[u] = key < k1;
-            if (ok[u]) kp[u] = ld16_stream(kc + (size_t)key * D + pi * E);
+            // the row this kernel appended is taken from qkv, never re-read from the cache through the
+            // read-only (.nc) path: .nc is only defined for data no thread of the kernel writes
+            if (ok[u]) kp[u] = ld16_stream((key == new_row ? knew : kc + (size_t)key * D) + pi * E);
         }
 #pragma unroll
         for (int u = 0; u < kUnroll; ++u) {
             const int key = base + u * KPI + ks;
-            if (ok[u]) vp[u] = ld16_stream(vc + (size_t)key * D + pi * E);
+            if (ok[u]) vp[u] = ld16_stream((key == new_row ? vnew : vc + (size_t)key * D) + pi * E);
         }
         float s[G][kUnroll];
 #pragma unroll

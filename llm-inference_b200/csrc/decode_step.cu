@@ -485,7 +485,7 @@ __device__ __forceinline__ uint32_t gemv_consume(const StepOp& op, const StepPar
 
         for (int seg = 0; seg < nseg; ++seg) {
             mbar_wait(&r_full[slot], phase);
-            if (active && !(p.debug_flags & 1)) {
+            if (active) {
                 const int seg_pk = (seg == nseg - 1) ? last_seg_pk : KSEG / 8;
                 const unsigned char* sa = r_base + (size_t)slot * kStageB + (2 * warp) * kSegB;
                 const unsigned char* sb = sa + kSegB;   // row b's slot (stale data when rb < 0: result unused)
@@ -899,11 +899,10 @@ static size_t step_smem(int stages, size_t xs_bytes, int nb_t) {
 template <int NB, int G>
 static cudaError_t step_launch_t(const StepProgram& sp, cudaStream_t s) {
     auto kern = decode_step_kernel<NB, G>;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024);   // static smem holds params + op
+    static unsigned long long attr_done = 0;   // per instantiation, one bit per device
+    {
+        cudaError_t e = ensure_max_dynamic_smem(reinterpret_cast<const void*>(kern), 227 * 1024 - 1024, attr_done);   // static smem holds params + op
         if (e != cudaSuccess) return e;
-        attr_set = true;
     }
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(sp.grid);
@@ -1002,10 +1001,6 @@ StepProgram* step_program_create(const std::vector<StepOp>& ops, StepParams para
     {
         const char* a = getenv("B200_STEP_L2_AHEAD_KB");
         sp->params.l2_ahead_bytes = (long long)(a ? atoi(a) : 0) * 1024;
-    }
-    {
-        const char* d = getenv("B200_STEP_DEBUG");
-        sp->params.debug_flags = d ? atoi(d) : 0;
     }
     {
         const char* t = getenv("B200_STEP_TRACE");

@@ -47,7 +47,6 @@ struct StepParams {
     int stages;
     size_t xs_bytes;
     long long l2_ahead_bytes;    // per-CTA distance of the L2 prefetch cursor in front of the smem ring (0 = off)
-    int debug_flags;             // experiments only (B200_STEP_DEBUG): 1 = consumers skip the dot products
     unsigned long long* trace;   // optional [2*n_ops] %globaltimer stamps of CTA 0 (op done, barrier passed)
 };
 

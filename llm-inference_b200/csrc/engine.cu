@@ -70,6 +70,7 @@ struct b200_engine {
     size_t pf_bytes = 0;
     int* pf_pinned = nullptr;
     size_t pf_pinned_ints = 0;
+    cudaEvent_t pf_copied = nullptr;   // recorded after the H2D copies out of pf_pinned
     int prefill_launches = 0;
     // control
     cudaStream_t stream = nullptr;
@@ -326,6 +327,7 @@ extern "C" void b200_engine_destroy(b200_engine* e) {
     if (e->stream) cudaStreamDestroy(e->stream);
     if (e->pinned_ids) cudaFreeHost(e->pinned_ids);
     if (e->pf_pinned) cudaFreeHost(e->pf_pinned);
+    if (e->pf_copied) cudaEventDestroy(e->pf_copied);
     cudaFree(e->pf_arena);
     cudaFree(e->arena);
     cudaFree(e->k_cache);
@@ -771,6 +773,10 @@ static int prefill_impl(b200_engine* e, const int* ids_host, const int* lens_hos
         e->pf_bytes = off;
     }
     const size_t need_ints = (size_t)Nt + 4 * B;
+    // the staging buffer is reused by every prompt pass: the copies a previous (unsynchronised) pass queued
+    // from it must have run before it is overwritten or freed
+    if (e->pf_copied) CU(cudaEventSynchronize(e->pf_copied));
+    else CU(cudaEventCreateWithFlags(&e->pf_copied, cudaEventDisableTiming));
     if (need_ints > e->pf_pinned_ints) {
         if (e->pf_pinned) cudaFreeHost(e->pf_pinned);
         e->pf_pinned = nullptr;
@@ -796,6 +802,7 @@ static int prefill_impl(b200_engine* e, const int* ids_host, const int* lens_hos
     CU(cudaMemcpyAsync(hists, e->pf_pinned + Nt + B, (size_t)B * sizeof(int), cudaMemcpyHostToDevice, s));
     CU(cudaMemcpyAsync(ctxs, e->pf_pinned + Nt + 2 * B, (size_t)B * sizeof(int), cudaMemcpyHostToDevice, s));
     CU(cudaMemcpyAsync(e->seq_steps, e->pf_pinned + Nt + 3 * B, (size_t)B * sizeof(int), cudaMemcpyHostToDevice, s));
+    CU(cudaEventRecord(e->pf_copied, s));
     auto linear = [&](const void* in, const void* W, void* out, int N, int K) {
         return b200_linear(in, W, nullptr, out, Nt, N, K, 1, dt, lws, lin_ws + 256, s);
     };

@@ -211,11 +211,10 @@ gemm2_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
 template <bool GLU>
 static int gemm2_launch(const CUtensorMap& ma, const CUtensorMap& mb, const Gemm2Params& p, int grid, cudaStream_t s) {
     auto kern = gemm2_tcgen05_kernel<GLU>;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k2Smem);
+    static unsigned long long attr_done = 0;   // per instantiation, one bit per device
+    {
+        cudaError_t e = ensure_max_dynamic_smem(reinterpret_cast<const void*>(kern), (int)k2Smem, attr_done);
         if (e != cudaSuccess) return (int)e;
-        attr_set = true;
     }
     prefer_max_smem_carveout(reinterpret_cast<const void*>(kern));
     cudaLaunchConfig_t cfg{};

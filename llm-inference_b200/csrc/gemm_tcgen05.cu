@@ -343,11 +343,10 @@ bool make_tma_map_2d(CUtensorMap* out, const void* ptr, long long rows, int K, i
 template <int BN, bool SWAP, bool GLU = false>
 static int gemm_launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, int grid, cudaStream_t s) {
     auto kern = gemm_tcgen05_kernel<BN, SWAP, GLU>;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmSmem<BN>::kTotal);
+    static unsigned long long attr_done = 0;   // per instantiation, one bit per device
+    {
+        cudaError_t e = ensure_max_dynamic_smem(reinterpret_cast<const void*>(kern), GemmSmem<BN>::kTotal, attr_done);
         if (e != cudaSuccess) return (int)e;
-        attr_set = true;
     }
     cudaError_t e = launch_k(kern, dim3(grid), dim3(kGemmThreads), (size_t)GemmSmem<BN>::kTotal, s, true, ma, mb, p);
     count_launch();

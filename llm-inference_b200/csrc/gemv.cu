@@ -487,12 +487,10 @@ static int gemv_pick_stages(int NB, int K, int esz) {
 template <typename T, int NB, int MODE, bool MMA = false>
 static int gemv_launch_one(const GemvParams& p, size_t smem, int grid, cudaStream_t s) {
     auto kern = gemv_stream_kernel<T, NB, MODE, MMA>;
-    static bool attr_set = false;  // per instantiation
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             227 * 1024);
+    static unsigned long long attr_done = 0;  // per instantiation, one bit per device
+    {
+        cudaError_t e = ensure_max_dynamic_smem(reinterpret_cast<const void*>(kern), 227 * 1024, attr_done);
         if (e != cudaSuccess) return (int)e;
-        attr_set = true;
     }
     cudaError_t e = launch_k(kern, dim3(grid), dim3(kGemvThreads), smem, s, true, p);
     count_launch();

@@ -26,7 +26,9 @@ concat_kv_kernel(const char* __restrict__ k_src, const char* __restrict__ v_src,
         r /= max_q_len;
         const int head = (int)(r % kv_heads);
         const int b = (int)(r / kv_heads);
-        if (t < cur_len[b]) {
+        // rows that would land beyond the cache slice (history + length > max_seq_len: a caller error the launcher
+        // cannot see, the lengths live on the device) are dropped, never written outside the slice
+        if (t < cur_len[b] && history_len[b] + t < max_seq_len && history_len[b] >= 0) {
             const size_t drow = ((size_t)b * kv_heads + head) * max_seq_len + history_len[b] + t;
             const char* s = src + it * PB;
             char* d = dst + (drow * row_packets + p) * PB;

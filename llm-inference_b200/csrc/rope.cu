@@ -95,6 +95,9 @@ qkv_rope_transpose_kernel(T* __restrict__ q, T* __restrict__ k, T* __restrict__ 
     // the KV-cache layer slice [B, hk, kv_rows = max_seq, d] at row history + local, which is where
     // launchConcatKVCache (concat_past_kv.cu:17-56) would copy them next
     const int kv_local = to_cache ? pos : local;
+    // to_cache: a row beyond the cache slice (history + length > max_seq_len, a caller error the launcher cannot see:
+    // the lengths live on the device) is dropped, never written outside the slice
+    const bool kv_ok = kv_local >= 0 && kv_local < kv_rows;
     const int half_d = head_size >> 1, half_rot = rot_dim >> 1;
     for (int i = threadIdx.x; i < half_d; i += blockDim.x)
         cs[i] = (i < half_rot) ? rope_cos_sin(i, rot_dim, base, (float)pos) : make_float2(1.f, 0.f);
@@ -130,8 +133,10 @@ qkv_rope_transpose_kernel(T* __restrict__ q, T* __restrict__ k, T* __restrict__ 
             T* d;
             if (head < head_num)
                 d = q + (((size_t)b * head_num + head) * seq_len + local) * head_size + p * E;
-            else
+            else if (kv_ok)
                 d = k + (((size_t)b * kv_head_num + (head - head_num)) * kv_rows + kv_local) * head_size + p * E;
+            else
+                continue;
             st16(d, Unpack<T>::put(lo));
             st16(d + half_d, Unpack<T>::put(hi));
         } else {
@@ -148,7 +153,7 @@ qkv_rope_transpose_kernel(T* __restrict__ q, T* __restrict__ k, T* __restrict__ 
                 for (int i = 0; i < E; ++i) f[i] += bf[i];
                 val = Unpack<T>::put(f);
             }
-            st16(v + (((size_t)b * kv_head_num + head) * kv_rows + kv_local) * head_size + p * E, val);
+            if (kv_ok) st16(v + (((size_t)b * kv_head_num + head) * kv_rows + kv_local) * head_size + p * E, val);
         }
     }
     pdl_launch_dependents();

@@ -22,6 +22,7 @@ class CudaAllocator : public BaseAllocator {
         std::multimap<size_t, void*> free_blocks;      // capacity -> block
         std::unordered_map<void*, size_t> live;        // block -> capacity
         size_t reserved = 0;
+        size_t cached = 0;                             // bytes sitting in free_blocks
     };
     std::map<int, DevicePool> pools_;
     std::recursive_mutex mu_;
@@ -59,6 +60,7 @@ public:
         if (it != pool.free_blocks.end() && it->first <= 2 * cap) {
             void* p = it->second;
             pool.live[p] = it->first;
+            pool.cached -= it->first;
             pool.free_blocks.erase(it);
             return p;
         }
@@ -82,10 +84,9 @@ public:
             auto it = kv.second.live.find(ptr);
             if (it == kv.second.live.end()) continue;
             kv.second.free_blocks.emplace(it->second, ptr);
+            kv.second.cached += it->second;   // running total: no walk over the free list per call
             kv.second.live.erase(it);
-            size_t cached = 0;
-            for (auto& fb : kv.second.free_blocks) cached += fb.first;
-            if (cached > trim_threshold_) trim(kv.first);
+            if (kv.second.cached > trim_threshold_) trim(kv.first);
             return;
         }
         CHECK(cudaFree(ptr));  // not ours: behave like the reference's fallback (cuda_allocator.h:300-305)
@@ -99,6 +100,7 @@ public:
         cudaSetDevice(dev);
         for (auto& fb : pit->second.free_blocks) { cudaFree(fb.second); pit->second.reserved -= fb.first; }
         pit->second.free_blocks.clear();
+        pit->second.cached = 0;
         cudaSetDevice(cur);
     }
     void releaseAll() {

@@ -134,7 +134,7 @@ class P2PComm:
         import torch.distributed as dist
         from . import engine as E
         self.lib = E._lib()
-        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.world, self.rank, self.group = dist.get_world_size(group), dist.get_rank(group), group
         self.handle = self.lib.b200_p2p_create(self.world, self.rank, int(max_message_bytes))
         if not self.handle:
             raise RuntimeError("[b200][ERROR] b200_p2p_create failed")
@@ -172,6 +172,13 @@ class P2PComm:
             raise RuntimeError(f"[b200][ERROR] b200_p2p_allreduce: {rc}")
 
     def close(self):
+        """quiesce, then free: every rank synchronises its device and meets the others at a barrier before any of them
+        unmaps / frees the receive buffers (b200_p2p_destroy's contract: a lagging peer must not push into freed memory)"""
         if self.handle:
+            import torch
+            import torch.distributed as dist
+            torch.cuda.synchronize()
+            if dist.is_available() and dist.is_initialized() and self.world > 1:
+                dist.barrier(group=self.group)
             self.lib.b200_p2p_destroy(self.handle)
             self.handle = None

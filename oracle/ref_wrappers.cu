@@ -18,6 +18,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string>
+#include <thread>
 #include <vector>
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
@@ -90,6 +91,26 @@ API void ref_cpu_masked_attn(float* q, float* k, float* v, float* k_cache, float
 }
 API void ref_cpu_linear(float* in, float* w, float* out, int m, int k, int n) {
     t_linear::CPUlinear(in, w, out, m, k, n);
+}
+// The same CPUlinear over W stored as n/block consecutive column blocks [k, block] (its inner loop walks W
+// with a stride of n floats: narrow blocks keep that stride inside a few cache lines), the blocks dealt
+// round-robin to `threads` host threads. out [m, n] is overwritten. Used by bench.py --impl reference.
+API void ref_cpu_linear_blocked(float* in, float* w_blocks, float* out, int m, int k, int n, int block, int threads) {
+    const int nblk = n / block;
+    if (threads < 1) threads = 1;
+    auto work = [&](int t) {
+        std::vector<float> tmp((size_t)m * block);
+        for (int b = t; b < nblk; b += threads) {
+            std::fill(tmp.begin(), tmp.end(), 0.f);   // CPUlinear accumulates into its output
+            t_linear::CPUlinear(in, w_blocks + (size_t)b * k * block, tmp.data(), m, k, block);
+            for (int i = 0; i < m; ++i)
+                for (int j = 0; j < block; ++j) out[(size_t)i * n + (size_t)b * block + j] = tmp[(size_t)i * block + j];
+        }
+    };
+    std::vector<std::thread> th;
+    for (int t = 1; t < threads; ++t) th.emplace_back(work, t);
+    work(0);
+    for (auto& x : th) x.join();
 }
 API void ref_cpu_causal_mask(float* mask, const int* q_lens, const int* k_lens, int max_q, int max_k,
                          int batch) {
@@ -205,5 +226,15 @@ API int ref_gpu_rope_decode_f32(float* qkv, int b, int qkv_heads, int d, int ste
 API int ref_gpu_softmax_f32(float* qk, float* mask, float* score, int b, int h, int q, int k, float scale) {
     TensorWrapper<float> a(Device::GPU, FP32, {b, h, q, k}, qk), m(Device::GPU, FP32, {b, q, k}, mask), o(Device::GPU, FP32, {b, h, q, k}, score);
     launchScaleMaskAndSoftmax(&a, &m, &o, scale);
+    return done();
+}
+// launchTopKforBeamSearch (src/kernels/topK.cu:147): K = 5, 8 blocks per row, probs [rows, vocab].
+// Its heap starts at val = 1e-20 / id = -1, so it is only meaningful on positive data.
+API int ref_gpu_topk_f32(float* probs, int* tmp_ids, float* tmp_vals, int* final_ids, float* final_vals,
+                         int rows, int vocab) {
+    TensorWrapper<float> p(Device::GPU, FP32, {rows, vocab}, probs);
+    TensorWrapper<int> ti(Device::GPU, INT32, {rows, 1, 8, 5}, tmp_ids), fi(Device::GPU, INT32, {rows, 1, 5}, final_ids);
+    TensorWrapper<float> tv(Device::GPU, FP32, {rows, 1, 8, 5}, tmp_vals), fv(Device::GPU, FP32, {rows, 1, 5}, final_vals);
+    launchTopKforBeamSearch(&p, &ti, &tv, &fi, &fv);
     return done();
 }

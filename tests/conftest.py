@@ -27,6 +27,7 @@ def load_package():
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+    config.addinivalue_line("markers", "slow: full-size case (tens of seconds); still part of the gpu suite")
 
 
 @pytest.fixture(scope="session")

@@ -163,3 +163,29 @@ def test_softmax_f32_vs_reference_kernel_small_rows(ref, ops):
     assert ref.ref_gpu_softmax_f32(P(qk), P(mask), P(want), b, h, q, k, C.c_float(0.125)) == 0
     ops.launchScaleMaskAndSoftmax(qk, mask, got, 0.125)
     assert_close(got.cpu().numpy(), want.cpu().numpy(), "fp32", "scale-mask-softmax")
+
+
+@pytest.mark.parametrize("rows,vocab", [(1, 32000), (3, 32000), (2, 1031)])
+def test_topk_indices_vs_reference_kernel(ref, ops, rows, vocab):
+    """launchTopKforBeamSearch (topK.cu:147, K = 5, cub BlockReduce) on tie-free POSITIVE data (its
+    heap starts at 1e-20 / id -1, topK.h:13-18): our b200_topk must return the same indices, in the
+    same (descending) order, and the same values; our top-1 pick = its first index."""
+    rng = np.random.default_rng(17 + rows)
+    probs = np.stack([rng.permutation(vocab).astype(np.float32) + 1.0 for _ in range(rows)]) / vocab   # all distinct
+    p = torch.from_numpy(probs).cuda()
+    tmp_i = torch.zeros(rows * 8 * 5, dtype=torch.int32, device="cuda")
+    tmp_v = torch.zeros(rows * 8 * 5, device="cuda")
+    fin_i = torch.zeros(rows, 5, dtype=torch.int32, device="cuda")
+    fin_v = torch.zeros(rows, 5, device="cuda")
+    assert ref.ref_gpu_topk_f32(P(p), P(tmp_i), P(tmp_v), P(fin_i), P(fin_v), rows, vocab) == 0
+    ids = torch.zeros(rows, 5, dtype=torch.int32, device="cuda")
+    vals = torch.zeros(rows, 5, device="cuda")
+    ops.launchTopK(p, ids, vals, 5)
+    top1 = torch.zeros(rows, dtype=torch.int32, device="cuda")
+    ops.argmax(p, top1)
+    torch.cuda.synchronize()
+    want = np.argsort(-probs, axis=1)[:, :5]
+    assert np.array_equal(fin_i.cpu().numpy(), want), "the reference kernel itself disagrees with a sort"
+    assert np.array_equal(ids.cpu().numpy(), fin_i.cpu().numpy()), "top-K indices differ from the reference kernel"
+    assert np.array_equal(vals.cpu().numpy(), fin_v.cpu().numpy())
+    assert np.array_equal(top1.cpu().numpy(), fin_i.cpu().numpy()[:, 0])
