@@ -83,7 +83,7 @@ class Clocks:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=lambda: [self.lines.append(l) for l in self.proc.stdout], daemon=True)
             self.t.start()
@@ -93,6 +93,9 @@ class Clocks:
     def stop(self):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        t_end = time.time() + 3.0
+        while len(self.lines) < 2 and time.time() < t_end:   # nvidia-smi needs ~0.2 s before its first line
+            time.sleep(0.05)
         self.proc.terminate()
         try:
             self.proc.wait(timeout=2)
@@ -911,14 +914,14 @@ def main():
     stream = torch.cuda.ExternalStream(eng.stream)
     ids0 = np.random.default_rng(7 + rank).integers(0, 32000, B_local).astype(np.int32)
 
-    # ---- device-resident timed region
+    # ---- device-resident timed region (clocks sampled from the warm-up on, through the end-to-end loop)
+    clocks = Clocks(local_rank)
+    if rank == 0:
+        clocks.start()
     eng.decode_step_host(ids0)
     for _ in range(W - 1):
         eng.decode_step()
     barrier()
-    clocks = Clocks(local_rank)
-    if rank == 0:
-        clocks.start()
     capi.lib().b200_launch_count_reset()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with torch.cuda.stream(stream):
@@ -929,7 +932,6 @@ def main():
     barrier()
     launches = int(capi.lib().b200_launch_count())
     ms = ev0.elapsed_time(ev1)
-    clk = clocks.stop() if rank == 0 else None
 
     # ---- end to end: host ids in, host ids out, every step
     ids = eng.decode_step_host(None)
@@ -939,6 +941,7 @@ def main():
         ids = eng.decode_step_host(ids)
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
+    clk = clocks.stop() if rank == 0 else None
 
     t = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
     if world > 1:

@@ -96,6 +96,30 @@ __device__ __forceinline__ void grid_barrier_wait(unsigned* sync, unsigned targe
     consumers_sync();
 }
 
+// Dynamic shared memory of the step kernel: [ring: stages x kStageB][xs: x rows / attention merge][full / empty mbarriers]
+// [red: NB*8 + NB + 32 floats][scratch: kStepScratchBytes]. The noinline consumers recompute these few pointers from the
+// parameters (which live in shared memory) instead of receiving them as arguments: arguments beyond the register
+// window travel through local memory, and local memory is an L2 round trip in this kernel.
+template <int NB>
+struct StepSmem {
+    unsigned char* ring;
+    __half* xs;
+    uint64_t* full;
+    uint64_t* empty;
+    float* red;
+    float* scratch;
+    long long* starved;   // trace mode: cycles warp 0 waited for weights in the current op
+    __device__ __forceinline__ StepSmem(unsigned char* smem, int stages, size_t xs_bytes) {
+        ring = smem;
+        xs = reinterpret_cast<__half*>(smem + (size_t)stages * kStageB);
+        full = reinterpret_cast<uint64_t*>(smem + (size_t)stages * kStageB + xs_bytes);
+        empty = full + kStepMaxStages;
+        red = reinterpret_cast<float*>(empty + kStepMaxStages);
+        scratch = red + (NB * kStepWarps + NB + 32);
+        starved = reinterpret_cast<long long*>((reinterpret_cast<uintptr_t>(scratch) + kStepScratchBytes - 16) & ~(uintptr_t)7);
+    }
+};
+
 struct Ring {
     unsigned char* base;
     uint64_t* full;
@@ -107,7 +131,7 @@ struct Ring {
 
 template <int EPI>
 __device__ __forceinline__ void op_unit_rows(const StepOp& op, int head_size, int u, int& ra, int& rb) {
-    if (EPI == kEpiSwiglu) {
+    if (EPI == kEpiSwiglu || EPI == kEpiSwigluDown) {
         ra = u;
         rb = op.N + u;
     } else if (EPI == kEpiRopeKV) {
@@ -125,25 +149,22 @@ __device__ __forceinline__ void op_unit_rows(const StepOp& op, int head_size, in
 // producer warp: streams the weights of every GEMV op of the step, in program order
 // ------------------------------------------------------------------------------------------
 __device__ __forceinline__ void op_rows_rt(const StepOp& op, int head_size, int u, int& ra, int& rb) {
-    if (op.epi == kEpiSwiglu) op_unit_rows<kEpiSwiglu>(op, head_size, u, ra, rb);
+    if (op.epi == kEpiSwiglu || op.epi == kEpiSwigluDown) op_unit_rows<kEpiSwiglu>(op, head_size, u, ra, rb);
     else if (op.epi == kEpiRopeKV) op_unit_rows<kEpiRopeKV>(op, head_size, u, ra, rb);
     else op_unit_rows<kEpiPlain>(op, head_size, u, ra, rb);
 }
 
-// bulk L2 prefetch (no smem destination, no completion tracking): size % 16 == 0
-__device__ __forceinline__ void bulk_prefetch_l2(const void* gsrc, uint32_t bytes) {
-    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gsrc), "r"(bytes) : "memory");
-}
-
-// this CTA's slice of one GEMV op, as the producer / prefetcher see it
+// this CTA's slice of one GEMV op, as the producer sees it
 struct OpSlice {
     const unsigned char* W;
+    const unsigned char* W2;   // kEpiSwigluDown: transposed down weights (rows [u0, u1) are this CTA's), else nullptr
     int epi, N, K, u0, u1, ngroups;
 };
 __device__ __forceinline__ bool load_slice(const StepOp* ops, int oi, OpSlice& sl) {
     if (ops[oi].type != kOpGemv) return false;
     sl.W = reinterpret_cast<const unsigned char*>(ops[oi].W);
     sl.epi = ops[oi].epi; sl.N = ops[oi].N; sl.K = ops[oi].K;
+    sl.W2 = sl.epi == kEpiSwigluDown ? reinterpret_cast<const unsigned char*>(ops[oi].W2) : nullptr;
     const int units = ops[oi].units;
     sl.u0 = (int)(((long long)units * blockIdx.x) / gridDim.x);
     sl.u1 = (int)(((long long)units * (blockIdx.x + 1)) / gridDim.x);
@@ -157,7 +178,7 @@ __device__ __forceinline__ const unsigned char* slice_lane_row(const OpSlice& sl
     if (lane >= 2 * nu) return nullptr;
     const int u = ubase + (lane >> 1);
     int ra, rb;
-    if (sl.epi == kEpiSwiglu) { ra = u; rb = sl.N + u; }
+    if (sl.epi == kEpiSwiglu || sl.epi == kEpiSwigluDown) { ra = u; rb = sl.N + u; }
     else if (sl.epi == kEpiRopeKV) {
         const int hd = head_size >> 1;
         const int head = u / hd, i = u - head * hd;
@@ -168,17 +189,22 @@ __device__ __forceinline__ const unsigned char* slice_lane_row(const OpSlice& sl
     return r >= 0 ? sl.W + (size_t)r * ((size_t)sl.K * 2) : nullptr;
 }
 
-// position of a producer cursor in the step's sequence of ring stages: (op, row group, K segment)
+// position of the producer in the step's sequence of ring stages. Phase 1 of an op: (row group, K segment), one
+// 2 KB row segment per lane. Phase 2 (kEpiSwigluDown only): the CTA's rows [u0, u1) of W2 are ONE contiguous byte
+// range, streamed as stages of kStageB bytes in 2 KB pieces (lane l = piece l).
 struct Cursor {
     OpSlice sl;
-    const unsigned char* src;   // this lane's source row in the current group (nullptr: lane idle)
+    const unsigned char* src;   // phase 1: this lane's source row in the current group (nullptr: lane idle)
     int oi, g, seg, nseg;
     uint32_t rows_here, last_seg_bytes;
-    bool valid;
+    int s2, n2;                 // phase 2: stage index / number of stages (0: the op has no second phase)
+    long long bytes2;           // phase 2: bytes of the CTA's W2 slice
+    bool valid, phase2;
 };
 __device__ __forceinline__ void cursor_seek(Cursor& c, const StepOp* ops, int n_ops, int lane, int head_size) {
     // first GEMV op at or after c.oi that has rows for this CTA
     c.valid = false;
+    c.phase2 = false;
     while (c.oi < n_ops) {
         if (load_slice(ops, c.oi, c.sl) && c.sl.ngroups > 0) {
             constexpr int KSEG = kSegB / 2;
@@ -188,6 +214,9 @@ __device__ __forceinline__ void cursor_seek(Cursor& c, const StepOp* ops, int n_
             c.seg = 0;
             c.src = slice_lane_row(c.sl, 0, lane, head_size);
             c.rows_here = __popc(__ballot_sync(0xffffffffu, c.src != nullptr));
+            c.s2 = 0;
+            c.bytes2 = c.sl.W2 ? (long long)(c.sl.u1 - c.sl.u0) * c.sl.K * 2 : 0;
+            c.n2 = (int)((c.bytes2 + kStageB - 1) / kStageB);
             c.valid = true;
             return;
         }
@@ -195,12 +224,21 @@ __device__ __forceinline__ void cursor_seek(Cursor& c, const StepOp* ops, int n_
     }
 }
 __device__ __forceinline__ void cursor_next(Cursor& c, const StepOp* ops, int n_ops, int lane, int head_size) {
-    if (++c.seg < c.nseg) return;
-    c.seg = 0;
-    if (++c.g < c.sl.ngroups) {
-        c.src = slice_lane_row(c.sl, c.g, lane, head_size);
-        c.rows_here = __popc(__ballot_sync(0xffffffffu, c.src != nullptr));
-        return;
+    if (c.phase2) {
+        if (++c.s2 < c.n2) return;
+    } else {
+        if (++c.seg < c.nseg) return;
+        c.seg = 0;
+        if (++c.g < c.sl.ngroups) {
+            c.src = slice_lane_row(c.sl, c.g, lane, head_size);
+            c.rows_here = __popc(__ballot_sync(0xffffffffu, c.src != nullptr));
+            return;
+        }
+        if (c.n2 > 0) {
+            c.phase2 = true;
+            c.s2 = 0;
+            return;
+        }
     }
     ++c.oi;
     cursor_seek(c, ops, n_ops, lane, head_size);
@@ -219,13 +257,10 @@ __device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
     return done != 0;
 }
 
-// Producer warp. The ring cursor issues bulk copies global -> smem stage as the consumers free
-// slots. While the consumers sit at a grid barrier / in a prologue the ring fills up and HBM
-// would go idle (the ring covers ~4 us of stall chip-wide); the producer notices this state -
-// it cannot get an empty slot AND the stage it issued last has already landed - and only then
-// runs a second cursor ahead of the ring with cp.async.bulk.prefetch.L2 (UBLKPF), up to
-// `pf_max` stages, so HBM keeps streaming into L2 and the ring catches up from L2 afterwards.
-// (Prefetching ahead unconditionally was measured slower: 2.88 -> 3.3 ms per step.)
+// Producer warp: issues bulk copies global -> ring stage as the consumers free slots, in program order and
+// without ever stopping at an op boundary. (An L2-prefetch cursor running ahead of the ring while the consumers
+// sit at a barrier was measured not to help - 2.88 -> 3.3 ms always on, no gain when stalled only: an SM ingests
+// 2 KB bulk copies at 47.8 GB/s from L2 exactly as from HBM, DESIGN section 4 - and is gone from the code.)
 __device__ __noinline__ void step_producer(const StepParams& p, Ring rg, int lane) {
     unsigned char* const r_base = rg.base;
     uint64_t* const r_full = rg.full;
@@ -233,51 +268,34 @@ __device__ __noinline__ void step_producer(const StepParams& p, Ring rg, int lan
     const int r_stages = rg.stages;
     const int n_ops = p.n_ops, head_size = p.head_size;
     const StepOp* ops = p.ops;
-    const int pf_max = (int)(p.l2_ahead_bytes / kStageB);
 
     int slot = 0, pass = 0;   // pass = number of times the ring has wrapped
-    unsigned long long pf_issued = 0;
-    Cursor rc{}, pc{};
-    int lead = 0;             // stages the prefetch cursor is ahead of the ring cursor
+    Cursor rc{};
     rc.oi = 0;
     cursor_seek(rc, ops, n_ops, lane, head_size);
     while (rc.valid) {
-        if (pass > 0) {
-            const uint32_t eparity = (uint32_t)(pass - 1) & 1u;
-            if (pf_max > 0) {
-                // stage issued last: slot-1 of this pass, or the last slot of the previous pass
-                const int lslot = slot ? slot - 1 : r_stages - 1;
-                const uint32_t lparity = (uint32_t)(slot ? pass : pass - 1) & 1u;
-                while (!mbar_test(&r_empty[slot], eparity)) {
-                    if (lead < pf_max && mbar_test(&r_full[lslot], lparity)) {
-                        if (lead == 0) pc = rc;
-                        if (!pc.valid) { lead = pf_max; continue; }
-                        const uint32_t bytes = (pc.seg == pc.nseg - 1) ? pc.last_seg_bytes : (uint32_t)kSegB;
-                        if (pc.src) bulk_prefetch_l2(pc.src + (size_t)pc.seg * kSegB, bytes);
-                        cursor_next(pc, ops, n_ops, lane, head_size);
-                        ++lead;
-                        ++pf_issued;
-                    } else {
-                        __nanosleep(64);   // leave the issue slots to the consumer warps
-                    }
-                }
-            } else {
-                mbar_wait(&r_empty[slot], eparity);
-            }
+        if (pass > 0) mbar_wait(&r_empty[slot], (uint32_t)(pass - 1) & 1u);
+        unsigned char* const dst = r_base + (size_t)slot * kStageB;
+        if (!rc.phase2) {
+            const uint32_t seg_bytes = (rc.seg == rc.nseg - 1) ? rc.last_seg_bytes : (uint32_t)kSegB;
+            if (lane == 0) mbar_expect_tx(&r_full[slot], seg_bytes * rc.rows_here);
+            if (rc.src) bulk_g2s(dst + (size_t)lane * kSegB, rc.src + (size_t)rc.seg * kSegB, seg_bytes, &r_full[slot]);
+        } else {
+            const long long off = (long long)rc.s2 * kStageB;
+            const long long left = rc.bytes2 - off;
+            const uint32_t stage_bytes = left < (long long)kStageB ? (uint32_t)left : (uint32_t)kStageB;
+            if (lane == 0) mbar_expect_tx(&r_full[slot], stage_bytes);
+            const uint32_t lo = (uint32_t)lane * kSegB;
+            if (lo < stage_bytes)
+                bulk_g2s(dst + lo, rc.sl.W2 + (size_t)rc.sl.u0 * rc.sl.K * 2 + off + lo,
+                         stage_bytes - lo < (uint32_t)kSegB ? stage_bytes - lo : (uint32_t)kSegB, &r_full[slot]);
         }
-        const uint32_t seg_bytes = (rc.seg == rc.nseg - 1) ? rc.last_seg_bytes : (uint32_t)kSegB;
-        if (lane == 0) mbar_expect_tx(&r_full[slot], seg_bytes * rc.rows_here);
-        if (rc.src)
-            bulk_g2s(r_base + (size_t)slot * kStageB + (size_t)lane * kSegB, rc.src + (size_t)rc.seg * kSegB,
-                     seg_bytes, &r_full[slot]);
         cursor_next(rc, ops, n_ops, lane, head_size);
-        if (lead > 0) --lead;
         if (++slot == r_stages) {
             slot = 0;
             ++pass;
         }
     }
-    if (p.trace && blockIdx.x == 0 && lane == 0) p.trace[4 * n_ops] = pf_issued;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -377,6 +395,44 @@ __device__ __noinline__ void stage_x(const StepOp& op, const StepParams& p, __ha
             // with a single split the attention op has already written the merged fp16 output
             xg = reinterpret_cast<const __half*>(op.xsrc == kXCombine ? p.attn : op.x) + (size_t)b * K;
         }
+        if (op.xsrc == kXResidAcc) {
+            // the residual add of the K-split projection: T(x + T(sum)), the rounding points of "linear output stored
+            // in T, then launchAddResidual" (add_residual.cu:58); CTA 0 publishes the new residual stream to xout
+            const float4* ag = reinterpret_cast<const float4*>(op.acc_in) + (size_t)b * (K / 4);
+            for (int i0 = tid; i0 < pk; i0 += 2 * kStepConsumers) {
+                const int i1 = i0 + kStepConsumers;
+                const Pack16 va = ld16_cg_nv(xg + (size_t)i0 * 8);
+                const float4 a0 = __ldcg(ag + 2 * i0), a1 = __ldcg(ag + 2 * i0 + 1);
+                Pack16 vb = va;
+                float4 b0 = a0, b1 = a1;
+                if (i1 < pk) {
+                    vb = ld16_cg_nv(xg + (size_t)i1 * 8);
+                    b0 = __ldcg(ag + 2 * i1);
+                    b1 = __ldcg(ag + 2 * i1 + 1);
+                }
+#pragma unroll
+                for (int u = 0; u < 2; ++u) {
+                    const int i = u ? i1 : i0;
+                    if (i >= pk) break;
+                    float f[8];
+                    Unpack<__half>::get(u ? vb : va, f);
+                    const float4 s0 = u ? b0 : a0, s1 = u ? b1 : a1;
+                    f[0] += __half2float(__float2half_rn(s0.x)); f[1] += __half2float(__float2half_rn(s0.y));
+                    f[2] += __half2float(__float2half_rn(s0.z)); f[3] += __half2float(__float2half_rn(s0.w));
+                    f[4] += __half2float(__float2half_rn(s1.x)); f[5] += __half2float(__float2half_rn(s1.y));
+                    f[6] += __half2float(__float2half_rn(s1.z)); f[7] += __half2float(__float2half_rn(s1.w));
+                    const Pack16 v = Unpack<__half>::put(f);
+                    st16(xs + (size_t)b * K + (size_t)i * 8, v);
+                    if (blockIdx.x == 0) st16(reinterpret_cast<__half*>(op.xout) + (size_t)b * K + (size_t)i * 8, v);
+                    if (op.norm) {
+                        Unpack<__half>::get(v, f);   // the norm sees the rounded sum
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) ss[b] = fmaf(f[e], f[e], ss[b]);
+                    }
+                }
+            }
+            continue;
+        }
         for (int i0 = tid; i0 < pk; i0 += 4 * kStepConsumers) {
             Pack16 v4[4];
 #pragma unroll
@@ -391,7 +447,7 @@ __device__ __noinline__ void stage_x(const StepOp& op, const StepParams& p, __ha
                 const Pack16 v = v4[u];
                 st16(xs + (size_t)b * K + (size_t)i * 8, v);
                 if (op.xsrc == kXEmbed && blockIdx.x == 0)   // the residual stream starts as the embedding
-                    st16(reinterpret_cast<__half*>(p.hidden_buf) + (size_t)b * K + (size_t)i * 8, v);
+                    st16(reinterpret_cast<__half*>(op.xout) + (size_t)b * K + (size_t)i * 8, v);
                 if (op.norm) {
                     float f[8];
                     Unpack<__half>::get(v, f);
@@ -434,14 +490,123 @@ __device__ __noinline__ void stage_x(const StepOp& op, const StepParams& p, __ha
 }
 
 // ------------------------------------------------------------------------------------------
+// consumers: second phase of kEpiSwigluDown. The CTA holds act[u0, u1) (the SwiGLU outputs it has just computed) in
+// shared memory and streams rows [u0, u1) of W2 = down^T [I, H]: y[0, H) += act[j] * W2[j][0, H) - the down projection
+// (ffn.cpp:88) split along K over the CTAs. A ring stage is kStageB / (2K) whole rows; thread t owns 16-byte packets
+// t, t + 256, .. of every row (rows narrower than 256 packets: several row groups in parallel), so there is no
+// cross-lane reduction at all; the CTA's partial [H] goes to the fp32 accumulator with red.global.add.v4.f32 and
+// the consumer of the sum (next op's x staging) rounds it to T before the residual add.
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void red_add_v4(float* gptr, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(gptr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+template <int NB, int PPT>
+__device__ __forceinline__ uint32_t down_consume(const StepOp& op, const StepParams& p, uint32_t state, const int n_rows) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    const StepSmem<NB> sm(smem, p.stages, p.xs_bytes);
+    unsigned char* const r_base = sm.ring;
+    uint64_t* const r_full = sm.full;
+    uint64_t* const r_empty = sm.empty;
+    const int r_stages = p.stages;
+    const __half* const act_s = reinterpret_cast<const __half*>(sm.scratch);
+    const int act_stride = op.act_stride;
+#ifdef B200_STEP_STARVE_TRACE
+    long long* const starved = sm.starved;
+    const bool traced = p.trace != nullptr && threadIdx.x < 32 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1);
+#endif
+    int slot = (int)(state & 0xffu);
+    uint32_t phase = state >> 8;
+    const int K = op.K, nb = p.nb;
+    const int PR = K / 8;                                              // packets per row
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int PRc = PR < kStepConsumers ? PR : kStepConsumers;
+    const int rg = tid / PRc, nrg = kStepConsumers / PRc;              // row groups working in parallel on a stage
+    const int p0 = tid - rg * PRc;
+    const int rows_per_stage = kStageB / (K * 2);
+    const int n2 = (n_rows + rows_per_stage - 1) / rows_per_stage;
+    float acc[NB][PPT][8];
+#pragma unroll
+    for (int b = 0; b < NB; ++b)
+#pragma unroll
+        for (int i = 0; i < PPT; ++i)
+#pragma unroll
+            for (int e = 0; e < 8; ++e) acc[b][i][e] = 0.f;
+
+    for (int s2 = 0; s2 < n2; ++s2) {
+#ifdef B200_STEP_STARVE_TRACE
+        if (traced) {
+            const long long c0 = clock64();
+            mbar_wait(&r_full[slot], phase);
+            if (lane == 0) *starved += clock64() - c0;
+        } else
+#endif
+            mbar_wait(&r_full[slot], phase);
+        const int r0 = s2 * rows_per_stage;
+        const int r1 = min(n_rows, r0 + rows_per_stage);
+        const unsigned char* st = r_base + (size_t)slot * kStageB;
+        for (int r = r0 + rg; r < r1; r += nrg) {
+            uint16_t a[NB];
+#pragma unroll
+            for (int b = 0; b < NB; ++b) a[b] = (b < nb) ? __half_as_ushort(act_s[b * act_stride + r]) : (uint16_t)0;
+            const unsigned char* row = st + (size_t)(r - r0) * K * 2;
+#pragma unroll
+            for (int i = 0; i < PPT; ++i) {
+                const int pk = p0 + i * kStepConsumers;
+                if (pk < PR) {
+                    const Pack16 w = ld16(row + (size_t)pk * 16);
+#pragma unroll
+                    for (int b = 0; b < NB; ++b) {
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            acc[b][i][2 * e] = fma_h((uint16_t)(w.w[e] & 0xffffu), a[b], acc[b][i][2 * e]);
+                            acc[b][i][2 * e + 1] = fma_h((uint16_t)(w.w[e] >> 16), a[b], acc[b][i][2 * e + 1]);
+                        }
+                    }
+                }
+            }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&r_empty[slot]);
+        if (++slot == r_stages) {
+            slot = 0;
+            phase ^= 1;
+        }
+    }
+    // the CTA's partial sums -> the fp32 accumulator (L2 adds; order over the CTAs is not fixed)
+    if (rg < n_rows) {
+#pragma unroll
+        for (int b = 0; b < NB; ++b) {
+            if (b < nb) {
+#pragma unroll
+                for (int i = 0; i < PPT; ++i) {
+                    const int pk = p0 + i * kStepConsumers;
+                    if (pk < PR) {
+                        float* dst = op.acc_out + (size_t)b * K + (size_t)pk * 8;
+                        red_add_v4(dst, acc[b][i][0], acc[b][i][1], acc[b][i][2], acc[b][i][3]);
+                        red_add_v4(dst + 4, acc[b][i][4], acc[b][i][5], acc[b][i][6], acc[b][i][7]);
+                    }
+                }
+            }
+        }
+    }
+    return (uint32_t)slot | (phase << 8);
+}
+
+// ------------------------------------------------------------------------------------------
 // consumers: one GEMV op. Warp w owns row pair w of every ring stage; two rows share each x packet.
 // Epilogues are those of gemv.cu (same rounding points as the unfused launch sequence).
 // ------------------------------------------------------------------------------------------
 template <int NB>
 __device__ __forceinline__ uint32_t gemv_consume(const StepOp& op, const StepParams& p, unsigned char* const r_base,
                                                  uint64_t* const r_full, uint64_t* const r_empty, const int r_stages,
-                                                 uint32_t state, const __half* xs, const int step) {
+                                                 uint32_t state, const __half* xs, const int step, const int op_index,
+                                                 float* scratch) {
     constexpr int KSEG = kSegB / 2;
+#ifdef B200_STEP_STARVE_TRACE   // build with -DB200_STEP_STARVE_TRACE: cycles warp 0 waited for weights, per op, into the trace
+    long long* const starved = reinterpret_cast<long long*>(
+        (reinterpret_cast<uintptr_t>(scratch) + kStepScratchBytes - 16) & ~(uintptr_t)7);
+#endif
     // everything the loops need sits in registers: with ~220 KB of shared memory in use there is
     // no L1 left, so any local-memory access (spill, indexed array) would be an L2 round trip
     int slot = (int)(state & 0xffu);
@@ -455,13 +620,17 @@ __device__ __forceinline__ uint32_t gemv_consume(const StepOp& op, const StepPar
     const int u1 = (int)(((long long)units * (blockIdx.x + 1)) / gridDim.x);
     const int ngroups = (u1 - u0 + kStepWarps - 1) / kStepWarps;
     __half* const y = reinterpret_cast<__half*>(op.y);
+#ifdef B200_STEP_STARVE_TRACE
+    const bool traced = p.trace != nullptr && warp == 0 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1);
+    if (traced && lane == 0) *starved = 0;
+#endif
 
     for (int g = 0; g < ngroups; ++g) {
         const int unit = u0 + g * kStepWarps + warp;
         const bool active = unit < u1;
         int ra = 0, rb = -1;
         if (active) {
-            if (epi == kEpiSwiglu) { ra = unit; rb = N + unit; }
+            if (epi == kEpiSwiglu || epi == kEpiSwigluDown) { ra = unit; rb = N + unit; }
             else if (epi == kEpiRopeKV) {
                 const int hd = head_size >> 1;
                 const int head = unit / hd, i = unit - head * hd;
@@ -484,7 +653,14 @@ __device__ __forceinline__ uint32_t gemv_consume(const StepOp& op, const StepPar
         for (int b = 0; b < NB; ++b) acc_a[b] = acc_b[b] = 0.f;
 
         for (int seg = 0; seg < nseg; ++seg) {
-            mbar_wait(&r_full[slot], phase);
+#ifdef B200_STEP_STARVE_TRACE
+            if (traced) {   // cycles this warp spends starved for weights
+                const long long c0 = clock64();
+                mbar_wait(&r_full[slot], phase);
+                if (lane == 0) *starved += clock64() - c0;
+            } else
+#endif
+                mbar_wait(&r_full[slot], phase);
             if (active) {
                 const int seg_pk = (seg == nseg - 1) ? last_seg_pk : KSEG / 8;
                 const unsigned char* sa = r_base + (size_t)slot * kStageB + (2 * warp) * kSegB;
@@ -520,13 +696,16 @@ __device__ __forceinline__ uint32_t gemv_consume(const StepOp& op, const StepPar
             }
             if (lane == 0) {
                 auto rnd = [](float v) { return __half2float(__float2half_rn(v)); };
-                if (epi == kEpiSwiglu) {
+                if (epi == kEpiSwiglu || epi == kEpiSwigluDown) {
 #pragma unroll
                     for (int b = 0; b < NB; ++b) {
                         if (b < nb) {
                             const float gv = rnd(acc_a[b]), uv = rnd(acc_b[b]);   // gate/up are stored in T unfused
                             const float sg = rnd(gv / (1.f + expf(-gv)));
-                            y[(size_t)b * N + ra] = __float2half_rn(sg * uv);
+                            const __half av = __float2half_rn(sg * uv);
+                            if (epi == kEpiSwiglu) y[(size_t)b * N + ra] = av;
+                            else   // stays in this CTA ([nb][act_stride] in `scratch`): it multiplies its own W2 rows
+                                reinterpret_cast<__half*>(scratch)[b * op.act_stride + (unit - u0)] = av;
                         }
                     }
                 } else if (epi == kEpiRopeKV) {
@@ -576,7 +755,32 @@ __device__ __forceinline__ uint32_t gemv_consume(const StepOp& op, const StepPar
             }
         }
     }
+#ifdef B200_STEP_STARVE_TRACE
+    if (traced && lane == 0) p.trace[4 * p.n_ops + 1 + (blockIdx.x == 0 ? 0 : p.n_ops) + op_index] = (unsigned long long)*starved;
+#endif
     return (uint32_t)slot | (phase << 8);
+}
+
+// second phase of a kEpiSwigluDown op: ONE out-of-line entry (own register allocation; called from the kernel loop
+// where little is live), the packets-per-thread variants are chosen inside
+template <int NB>
+__device__ __noinline__ uint32_t down_phase(const StepOp& op, const StepParams& p, uint32_t state, const int op_index) {
+    consumers_sync();   // the whole act slice is in shared memory
+    const int units = op.units;
+    const int u0 = (int)(((long long)units * blockIdx.x) / gridDim.x);
+    const int u1 = (int)(((long long)units * (blockIdx.x + 1)) / gridDim.x);
+    const int ppt = (op.K / 8 + kStepConsumers - 1) / kStepConsumers;   // 16-byte packets of a W2 row per thread
+    if (ppt <= 1) state = down_consume<NB, 1>(op, p, state, u1 - u0);
+    else if (ppt == 2) state = down_consume<NB, 2>(op, p, state, u1 - u0);
+    else state = down_consume<NB, (NB <= 2 ? 4 : 2)>(op, p, state, u1 - u0);
+#ifdef B200_STEP_STARVE_TRACE
+    if (p.trace != nullptr && threadIdx.x == 0 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) {
+        extern __shared__ __align__(128) unsigned char smem[];
+        const StepSmem<NB> sm(smem, p.stages, p.xs_bytes);
+        p.trace[4 * p.n_ops + 1 + (blockIdx.x == 0 ? 0 : p.n_ops) + op_index] = (unsigned long long)*sm.starved;
+    }
+#endif
+    return state;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -790,6 +994,20 @@ __device__ __noinline__ void final_consume(const StepParams& p, float* sv, int* 
     }
 }
 
+// trace mode: x staged stamp + ring stages already landed when the GEMV of op `oi` starts (CTA 0, thread 0)
+__device__ __noinline__ void trace_gemv_start(const StepParams& p, uint32_t ring_state, int oi) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + (size_t)p.stages * kStageB + p.xs_bytes);
+    p.trace[2 * p.n_ops + oi] = global_timer_ns();
+    int sl = (int)(ring_state & 0xffu), landed = 0;
+    uint32_t ph = ring_state >> 8;
+    for (int i = 0; i < p.stages; ++i) {
+        landed += mbar_test(&full_bar[sl], ph) ? 1 : 0;
+        if (++sl == p.stages) { sl = 0; ph ^= 1; }
+    }
+    p.trace[3 * p.n_ops + oi] = (unsigned long long)landed;
+}
+
 // ------------------------------------------------------------------------------------------
 // the kernel
 // ------------------------------------------------------------------------------------------
@@ -806,7 +1024,7 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const __gr
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + (size_t)gp.stages * kStageB + gp.xs_bytes);
     uint64_t* empty_bar = full_bar + kStepMaxStages;
     float* red = reinterpret_cast<float*>(empty_bar + kStepMaxStages);   // [NB*8 + NB + 32] floats, also argmax scratch
-    float* scratch = red + (NB * kStepWarps + NB + 32);                  // split-KV merge weights
+    float* scratch = red + (NB * kStepWarps + NB + 32);                  // split-KV merge weights / act slice
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x == 0) {
@@ -844,25 +1062,24 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const __gr
                          : "memory");
         asm volatile("cp.async.commit_group;" ::: "memory");
         const int type = op.type;
+        if (op.zero) {   // an accumulator consumed one op earlier is cleared for its next use (ops in between: >= 2 barriers)
+            const int per = (((op.n_zero + (int)gridDim.x - 1) / (int)gridDim.x) + 3) & ~3;
+            const int z0 = per * blockIdx.x, z1 = min(op.n_zero, z0 + per);
+            for (int i = z0 + 4 * (int)threadIdx.x; i < z1; i += 4 * kStepConsumers)
+                *reinterpret_cast<float4*>(op.zero + i) = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
         if (type == kOpGemv) {
             stage_x<NB>(op, p, xs, red, scratch);
-            if (gp.trace && blockIdx.x == 0 && threadIdx.x == 0) {
-                gp.trace[2 * n_ops + oi] = global_timer_ns();
-                int sl = (int)(ring_state & 0xffu), landed = 0;   // ring stages already landed when the GEMV starts
-                uint32_t ph = ring_state >> 8;
-                for (int i = 0; i < gp.stages; ++i) {
-                    landed += mbar_test(&full_bar[sl], ph) ? 1 : 0;
-                    if (++sl == gp.stages) { sl = 0; ph ^= 1; }
-                }
-                gp.trace[3 * n_ops + oi] = (unsigned long long)landed;
-            }
-            ring_state = gemv_consume<NB>(op, p, ring, full_bar, empty_bar, gp.stages, ring_state, xs, step);
+            if (gp.trace && blockIdx.x == 0 && threadIdx.x == 0) trace_gemv_start(p, ring_state, oi);
+            ring_state = gemv_consume<NB>(op, p, ring, full_bar, empty_bar, gp.stages, ring_state, xs, step, oi, scratch);
+            if (op.epi == kEpiSwigluDown) ring_state = down_phase<NB>(op, p, ring_state, oi);
         } else if (type == kOpAttn) {
             attn_consume<G>(op, p, reinterpret_cast<float*>(xs), step);
         } else {
             final_consume(p, red, reinterpret_cast<int*>(red + 16));
         }
         if (gp.trace && blockIdx.x == 0 && threadIdx.x == 0) gp.trace[2 * oi] = global_timer_ns();
+        if (gp.trace && threadIdx.x == 0) gp.trace[6 * n_ops + 1 + (size_t)oi * gridDim.x + blockIdx.x] = global_timer_ns();
         if (oi + 1 < n_ops) {
             ++epoch;
             asm volatile("cp.async.wait_group 0;" ::: "memory");   // the next op's descriptor has landed
@@ -945,7 +1162,7 @@ int step_program_launch(const StepProgram* sp, int step, cudaStream_t s) {
 
 int step_program_trace(const StepProgram* sp, unsigned long long* host_dst, int max_entries) {
     if (!sp || !sp->params.trace) return 0;
-    int n = 4 * sp->params.n_ops + 1;
+    int n = 6 * sp->params.n_ops + 1 + sp->params.n_ops * sp->grid;
     if (n > max_entries) n = max_entries;
     cudaMemcpy(host_dst, sp->params.trace, (size_t)n * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
     return n;
@@ -999,12 +1216,11 @@ StepProgram* step_program_create(const std::vector<StepOp>& ops, StepParams para
     sp->params.stages = stages;
     sp->params.xs_bytes = xs_bytes;
     {
-        const char* a = getenv("B200_STEP_L2_AHEAD_KB");
-        sp->params.l2_ahead_bytes = (long long)(a ? atoi(a) : 0) * 1024;
-    }
-    {
         const char* t = getenv("B200_STEP_TRACE");
-        if (t && t[0] == '1') cudaMalloc(&sp->params.trace, (4 * ops.size() + 1) * sizeof(unsigned long long));
+        if (t && t[0] == '1') {
+            const size_t n = (6 * ops.size() + 1 + ops.size() * (size_t)sp->grid) * sizeof(unsigned long long);
+            if (cudaMalloc(&sp->params.trace, n) == cudaSuccess) cudaMemset(sp->params.trace, 0, n);
+        }
     }
     return sp;
 }

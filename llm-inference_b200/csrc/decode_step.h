@@ -7,8 +7,12 @@
 namespace b200 {
 
 enum { kOpGemv = 0, kOpAttn = 1, kOpFinal = 2 };
-enum { kEpiPlain = 0, kEpiResidual = 1, kEpiSwiglu = 2, kEpiRopeKV = 3 };
-enum { kXPlain = 0, kXEmbed = 1, kXCombine = 2 };
+// kEpiSwigluDown: gate_up GEMV + SwiGLU, then - without a grid barrier - the CTA multiplies the slice of `act` it has
+// just produced by ITS rows of the transposed down weights W2 [I, H] and adds the partial [H] into acc_out with
+// red.global.add.v4.f32 (the down projection split along K over the CTAs; L2 does the cross-CTA sum)
+enum { kEpiPlain = 0, kEpiResidual = 1, kEpiSwiglu = 2, kEpiRopeKV = 3, kEpiSwigluDown = 4 };
+// kXResidAcc: x = T(x + T(acc_in)) - the residual add of a K-split projection, done where its result is first needed
+enum { kXPlain = 0, kXEmbed = 1, kXCombine = 2, kXResidAcc = 3 };
 
 struct StepOp {
     int type;        // kOp*
@@ -16,13 +20,22 @@ struct StepOp {
     int xsrc;        // kX*   (gemv)
     int norm;        // 0 none, 1 (x*inv)*gamma, 2 (gamma*x)*inv   (gemv prologue)
     int N, K, units;
+    int n_zero;      // floats of `zero` cleared (split over the CTAs) when this op starts
+    int act_stride;  // kEpiSwigluDown: halves between the batch rows of the CTA's act slice in shared memory
+    int pad1;
     const void* W;
     const void* x;
     void* y;
     const void* gamma;
     void* k_cache;   // layer slice [B, hk, max_seq, d] (RoPE/KV epilogue, attention)
     void* v_cache;
+    const void* W2;        // kEpiSwigluDown: down weights transposed, [N = I rows, K = H]
+    const float* acc_in;   // kXResidAcc: fp32 sums [nb, K] of the preceding K-split projection
+    float* acc_out;        // kEpiSwigluDown: fp32 accumulator [nb, K]
+    void* xout;            // kXEmbed / kXResidAcc: CTA 0 stores the new residual stream [nb, K] here
+    float* zero;           // accumulator to clear for its next use (consumed one op earlier), or nullptr
 };
+static_assert(sizeof(StepOp) % 16 == 0, "StepOp travels in 16-byte cp.async pieces");
 
 struct StepParams {
     const StepOp* ops;
@@ -36,7 +49,6 @@ struct StepParams {
     int* ids_next;
     const void* embed;
     int vocab, hidden;
-    void* hidden_buf;     // [B, H] residual stream
     void* qkv;            // [B, h+2hk, d]
     void* attn;           // [B, h*d]  (splits == 1 only)
     void* logits;         // [B, V]
@@ -46,8 +58,9 @@ struct StepParams {
     unsigned* sync;       // [0] arrival counter (monotonic), [1] base of the current launch, [2] error flag
     int stages;
     size_t xs_bytes;
-    long long l2_ahead_bytes;    // per-CTA distance of the L2 prefetch cursor in front of the smem ring (0 = off)
-    unsigned long long* trace;   // optional [2*n_ops] %globaltimer stamps of CTA 0 (op done, barrier passed)
+    unsigned long long* trace;   // optional (B200_STEP_TRACE=1): [0,2n) CTA 0 (op done, barrier passed) %globaltimer stamps, [2n,3n) x staged,
+                                 // [3n,4n) ring stages landed at GEMV start, [4n] L2 prefetches, [4n+1,5n+1) / [5n+1,6n+1) cycles warp 0 of the
+                                 // first / last CTA waited for weights, [6n+1 + op*grid + cta] op-done stamp of every CTA
 };
 
 struct StepProgram {

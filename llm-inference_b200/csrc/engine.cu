@@ -86,6 +86,11 @@ struct b200_engine {
     bool ragged = false;
     std::map<int, cudaGraphExec_t> graphs;  // key: split-KV count
     b200::StepProgram* program = nullptr;   // persistent whole-step kernel (fp16, batch <= 4, tp 1)
+    // fused FFN of the persistent kernel: down weights stored TRANSPOSED [I, H] per layer (the K-split form streams
+    // rows of it), refreshed lazily whenever a down weight changes; two fp32 accumulators [batch, H] (layer parity)
+    char* down_t = nullptr;
+    float* ffn_acc = nullptr;
+    bool down_t_dirty = true;
     int launches_per_step = 0;
 };
 
@@ -157,6 +162,22 @@ __global__ void fill_uniform_rows_kernel(T* cache, size_t rows_total, int max_se
     }
 }
 
+// dst [cols, rows] = src [rows, cols]^T, 32 x 32 tiles through shared memory (load-time weight packing)
+template <typename T>
+__global__ void transpose_kernel(const T* __restrict__ src, T* __restrict__ dst, int rows, int cols) {
+    __shared__ T tile[32][33];
+    const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+    for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+        const int r = r0 + j, c = c0 + threadIdx.x;
+        if (r < rows && c < cols) tile[j][threadIdx.x] = src[(size_t)r * cols + c];
+    }
+    __syncthreads();
+    for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+        const int c = c0 + j, r = r0 + threadIdx.x;
+        if (r < rows && c < cols) dst[(size_t)c * rows + r] = tile[threadIdx.x][j];
+    }
+}
+
 __global__ void advance_kernel(int* ids_cur, const int* ids_next, int* step, int batch) {
     pdl_wait();
     if (threadIdx.x < batch) ids_cur[threadIdx.x] = ids_next[threadIdx.x];
@@ -181,32 +202,110 @@ static void build_program(b200_engine* e) {
     const b200_model_config& c = e->cfg;
     if (c.dtype != B200_F16 || c.tp_size != 1 || e->batch > 4) return;
     std::vector<StepOp> ops;
-    const int H = e->H;
-    for (int l = 0; l < c.num_layers; ++l) {
+    const int H = e->H, L = c.num_layers;
+    // Fused FFN (gate_up + SwiGLU + K-split down in one op): needs whole W2 rows per ring stage
+    // (H a power of two <= 16384) and the per-thread accumulators in registers (batch tile x packets per thread <= 8)
+    const int nb_t = e->batch <= 1 ? 1 : e->batch <= 2 ? 2 : 4;
+    const int ppt = (H / 8 + 255) / 256;
+    bool fuse_ffn = L >= 1 && H >= 256 && (H & (H - 1)) == 0 && H <= 16384 && nb_t * ppt <= 8;
+    {
+        const char* env = getenv("B200_STEP_NO_FFN_FUSION");
+        if (env && env[0] == '1') fuse_ffn = false;
+    }
+    if (fuse_ffn) {
+        const size_t wt = (size_t)L * e->I * H * e->esz, ab = (size_t)2 * e->batch * H * sizeof(float);
+        if (cudaMalloc(&e->down_t, wt) != cudaSuccess || cudaMalloc(&e->ffn_acc, ab) != cudaSuccess) {
+            cudaGetLastError();
+            cudaFree(e->down_t);
+            e->down_t = nullptr;
+            fuse_ffn = false;
+        } else {
+            cudaMemset(e->ffn_acc, 0, ab);
+            e->down_t_dirty = true;
+        }
+    }
+    // residual stream: layer l works in buf[l % 2] (the K-split down's residual add is formed in the next op's x
+    // staging, which publishes it to the OTHER buffer - other CTAs may still be reading the old one); the decoder
+    // output of the step ends up in e->hidden either way
+    void* buf[2] = {e->hidden, e->hidden};
+    if (fuse_ffn) {
+        buf[L % 2] = e->hidden;
+        buf[(L + 1) % 2] = e->residual;
+    }
+    auto acc = [&](int l) { return e->ffn_acc + (size_t)(l % 2) * e->batch * H; };
+    const int n_acc = e->batch * H;
+    for (int l = 0; l < L; ++l) {
         LayerW& w = e->layers[l];
         void* kc = e->k_cache + (size_t)l * e->layer_kv_elems * e->esz;
         void* vc = e->v_cache + (size_t)l * e->layer_kv_elems * e->esz;
-        StepOp qkv{kOpGemv, kEpiRopeKV, l == 0 ? kXEmbed : kXPlain, 1, e->qkv_n, H, e->qkv_n / 2,
-                   w.qkv, e->hidden, e->qkv, w.attn_norm, kc, vc};
-        StepOp att{kOpAttn, 0, 0, 0, 0, 0, 0, nullptr, nullptr, nullptr, nullptr, kc, vc};
-        StepOp o{kOpGemv, kEpiResidual, kXCombine, 0, H, e->h * e->d, (H + 1) / 2,
-                 w.o, e->attn, e->hidden, nullptr, nullptr, nullptr};
-        StepOp gu{kOpGemv, kEpiSwiglu, kXPlain, 2, e->I, H, e->I, w.gate_up, e->hidden, e->act, w.ffn_norm, nullptr, nullptr};
-        StepOp dn{kOpGemv, kEpiResidual, kXPlain, 0, H, e->I, (H + 1) / 2, w.down, e->act, e->hidden, nullptr, nullptr, nullptr};
-        ops.push_back(qkv); ops.push_back(att); ops.push_back(o); ops.push_back(gu); ops.push_back(dn);
+        void* hid = buf[l % 2];
+        StepOp qkv{};
+        qkv.type = kOpGemv; qkv.epi = kEpiRopeKV; qkv.norm = 1; qkv.N = e->qkv_n; qkv.K = H; qkv.units = e->qkv_n / 2;
+        qkv.W = w.qkv; qkv.y = e->qkv; qkv.gamma = w.attn_norm; qkv.k_cache = kc; qkv.v_cache = vc;
+        if (l == 0) { qkv.xsrc = kXEmbed; qkv.xout = hid; qkv.x = hid; }
+        else if (fuse_ffn) { qkv.xsrc = kXResidAcc; qkv.x = buf[(l - 1) % 2]; qkv.acc_in = acc(l - 1); qkv.xout = hid; }
+        else { qkv.xsrc = kXPlain; qkv.x = hid; }
+        StepOp att{};
+        att.type = kOpAttn; att.k_cache = kc; att.v_cache = vc;
+        if (fuse_ffn && l >= 1) { att.zero = acc(l - 1); att.n_zero = n_acc; }   // consumed by this layer's qkv staging
+        StepOp o{};
+        o.type = kOpGemv; o.epi = kEpiResidual; o.xsrc = kXCombine; o.N = H; o.K = e->h * e->d; o.units = (H + 1) / 2;
+        o.W = w.o; o.x = e->attn; o.y = hid;
+        StepOp gu{};
+        gu.type = kOpGemv; gu.xsrc = kXPlain; gu.norm = 2; gu.N = e->I; gu.K = H; gu.units = e->I;
+        gu.W = w.gate_up; gu.x = hid; gu.gamma = w.ffn_norm;
+        ops.push_back(qkv); ops.push_back(att); ops.push_back(o);
+        if (fuse_ffn) {
+            gu.epi = kEpiSwigluDown;
+            gu.act_stride = (((e->I + sm_count() - 1) / sm_count()) + 8) & ~7;
+            gu.W2 = e->down_t + (size_t)l * e->I * H * e->esz;
+            gu.acc_out = acc(l);
+            ops.push_back(gu);
+        } else {
+            gu.epi = kEpiSwiglu;
+            gu.y = e->act;
+            StepOp dn{};
+            dn.type = kOpGemv; dn.epi = kEpiResidual; dn.xsrc = kXPlain; dn.N = H; dn.K = e->I; dn.units = (H + 1) / 2;
+            dn.W = w.down; dn.x = e->act; dn.y = hid;
+            ops.push_back(gu); ops.push_back(dn);
+        }
     }
-    StepOp head{kOpGemv, kEpiPlain, c.num_layers == 0 ? kXEmbed : kXPlain, 1, e->V, H, (e->V + 1) / 2,
-                e->lm_head, e->hidden, e->logits, e->final_norm, nullptr, nullptr};
-    StepOp fin{kOpFinal, 0, 0, 0, 0, 0, 0, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    StepOp head{};
+    head.type = kOpGemv; head.epi = kEpiPlain; head.norm = 1; head.N = e->V; head.K = H; head.units = (e->V + 1) / 2;
+    head.W = e->lm_head; head.y = e->logits; head.gamma = e->final_norm;
+    if (L == 0) { head.xsrc = kXEmbed; head.x = e->hidden; head.xout = e->hidden; }
+    else if (fuse_ffn) { head.xsrc = kXResidAcc; head.x = buf[(L - 1) % 2]; head.acc_in = acc(L - 1); head.xout = buf[L % 2]; }
+    else { head.xsrc = kXPlain; head.x = e->hidden; }
+    StepOp fin{};
+    fin.type = kOpFinal;
+    if (fuse_ffn) { fin.zero = acc(L - 1); fin.n_zero = n_acc; }
     ops.push_back(head); ops.push_back(fin);
     StepParams p{};
     p.head_num = e->h; p.kv_head_num = e->hk; p.head_size = e->d; p.max_seq_len = c.max_seq_len;
     p.rotary_dim = c.rotary_dim; p.eps = c.rms_eps; p.rope_den = e->rope_den;
     p.step_dev = e->step_dev; p.ids_cur = e->ids_cur; p.ids_next = e->ids_next;
     p.embed = e->embed; p.vocab = e->V; p.hidden = H;
-    p.hidden_buf = e->hidden; p.qkv = e->qkv; p.attn = e->attn; p.logits = e->logits;
-    const int k_max = std::max(std::max(H, e->I), e->h * e->d);
+    p.qkv = e->qkv; p.attn = e->attn; p.logits = e->logits;
+    const int k_max = fuse_ffn ? std::max(H, e->h * e->d) : std::max(std::max(H, e->I), e->h * e->d);
     e->program = step_program_create(ops, p, e->batch, e->h, e->hk, e->d, k_max, e->attn_ws);
+    if (!e->program && e->down_t) {
+        cudaFree(e->down_t);
+        cudaFree(e->ffn_acc);
+        e->down_t = nullptr;
+        e->ffn_acc = nullptr;
+    }
+}
+
+// the persistent kernel's transposed copy of the down weights follows every change of them
+static int refresh_down_t(b200_engine* e) {
+    if (!e->down_t || !e->down_t_dirty) return 0;
+    const dim3 blk(32, 8), grd((e->I + 31) / 32, (e->H + 31) / 32);
+    for (int l = 0; l < e->cfg.num_layers; ++l)
+        transpose_kernel<__half><<<grd, blk, 0, e->stream>>>((const __half*)e->layers[l].down,
+                                                             (__half*)e->down_t + (size_t)l * e->I * e->H, e->H, e->I);
+    CU(cudaGetLastError());
+    e->down_t_dirty = false;
+    return 0;
 }
 
 extern "C" const char* b200_engine_last_error(void) { return g_err.c_str(); }
@@ -329,6 +428,8 @@ extern "C" void b200_engine_destroy(b200_engine* e) {
     if (e->pf_pinned) cudaFreeHost(e->pf_pinned);
     if (e->pf_copied) cudaEventDestroy(e->pf_copied);
     cudaFree(e->pf_arena);
+    cudaFree(e->down_t);
+    cudaFree(e->ffn_acc);
     cudaFree(e->arena);
     cudaFree(e->k_cache);
     cudaFree(e->v_cache);
@@ -366,6 +467,7 @@ extern "C" int b200_engine_set_mode(b200_engine* e, unsigned flags) {
     if (!e) return B200_EINVAL;
     cudaStreamSynchronize(e->stream);
     drop_graphs(e);
+    e->down_t_dirty = true;   // also the hook for callers that wrote weights through b200_engine_weight_ptr
     e->mode = flags;
     return B200_OK;
 }
@@ -423,6 +525,7 @@ extern "C" int b200_engine_init_random(b200_engine* e, uint64_t seed, float std)
     fill(e->embed, B200_W_EMBED, 0.f);
     fill(e->final_norm, B200_W_FINAL_NORM, 1.f);
     fill(e->lm_head, B200_W_LM_HEAD, 0.f);
+    e->down_t_dirty = true;
     CU(cudaStreamSynchronize(e->stream));
     CU(cudaGetLastError());
     return B200_OK;
@@ -433,6 +536,7 @@ extern "C" int b200_engine_set_weight(b200_engine* e, int slot, int layer, const
     void* p = slot_ptr(e, slot, layer);
     if (!p || bytes != slot_elems(e, slot) * e->esz) return fail("set_weight: bad slot / size");
     CU(cudaMemcpy(p, src, bytes, cudaMemcpyHostToDevice));
+    if (slot == B200_W_DOWN) e->down_t_dirty = true;
     return B200_OK;
 }
 extern "C" int b200_engine_get_weight(b200_engine* e, int slot, int layer, void* dst, size_t bytes) {
@@ -631,6 +735,7 @@ static void stepped(b200_engine* e) {
 static int run_step(b200_engine* e) {
     if (e->step + 1 > e->cfg.max_seq_len) return fail("KV cache full (step == max_seq_len)");
     if (e->program && !e->ragged && (e->mode & B200_ENGINE_FUSED) && (e->mode & B200_ENGINE_PERSISTENT)) {
+        RC(refresh_down_t(e));
         RC(step_program_launch(e->program, e->step + 1, e->stream));
         e->launches_per_step = 1;
         stepped(e);

@@ -144,13 +144,20 @@ class Engine:
 
     # ---- control
     def step_trace(self):
-        """numpy uint64 [n_ops, 4]: %globaltimer stamps (op done, barrier passed, x staged) + ring stages landed at GEMV start, or None"""
-        buf = np.zeros(4096, np.uint64)
+        """numpy uint64 [n_ops, 4]: %globaltimer stamps (op done, barrier passed, x staged) + ring stages landed at GEMV
+        start, or None (B200_STEP_TRACE=1). Also sets self.trace_starved [2, n_ops] (cycles warp 0 of the first / last CTA
+        waited for weights) and self.trace_done [n_ops, grid] (op-done stamp of every CTA)."""
+        import torch
+        grid = torch.cuda.get_device_properties(torch.cuda.current_device()).multi_processor_count
+        kmax = 5 * self.cfg.num_layers + 2
+        buf = np.zeros(6 * kmax + 1 + kmax * grid, np.uint64)
         n = self.lib.b200_engine_step_trace(self.h, buf.ctypes.data_as(C.c_void_p), buf.size)
         if not n:
             return None
-        k = n // 4
-        self.prefetch_stages = int(buf[4 * k]) if n > 4 * k else 0
+        k = (n - 1) // (6 + grid)   # ops of the program: 4 per layer + 2 with the fused FFN op, else 5 per layer + 2
+        self.prefetch_stages = int(buf[4 * k])
+        self.trace_starved = buf[4 * k + 1:6 * k + 1].reshape(2, k).astype(np.int64)
+        self.trace_done = buf[6 * k + 1:6 * k + 1 + k * grid].reshape(k, grid).astype(np.int64)
         return np.concatenate([buf[:2 * k].reshape(k, 2), buf[2 * k:3 * k].reshape(k, 1),
                                buf[3 * k:4 * k].reshape(k, 1)], axis=1)
 

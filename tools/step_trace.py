@@ -22,13 +22,15 @@ ids = np.zeros(B, np.int32)
 for _ in range(5):
     ids = eng.decode_step_host(ids)
 t = eng.step_trace().astype(np.int64)
-names = ["qkv", "attn", "o", "gate_up", "down"]
+per_layer = (len(t) - 2) // 32
+names = ["qkv", "attn", "o", "gate_up", "down"] if per_layer == 5 else ["qkv", "attn", "o", "ffn"]
+n_layer_ops = 32 * per_layer
 start = t[0, 0]
 print("kernel start -> first op done: n/a; total ns:", t[-1, 0] - (t[0, 0]), "ops:", len(t))
 prev = None
 acc = {}
 for i in range(len(t)):
-    kind = names[i % 5] if i < 160 else ("lm_head" if i == 160 else "final")
+    kind = names[i % per_layer] if i < n_layer_ops else ("lm_head" if i == n_layer_ops else "final")
     op_ns = t[i, 0] - (t[i - 1, 1] if i else t[i, 0])
     bar_ns = t[i, 1] - t[i, 0]
     x_ns = (t[i, 2] - t[i - 1, 1]) if (i and t[i, 2] > 0) else 0
@@ -42,4 +44,20 @@ for k, (o, b, n, x, ld) in acc.items():
     print(f"{k:8s} n={n:3d} op avg {o / n / 1e3:8.2f} us (x staging {x / n / 1e3:6.2f} us, ring stages landed at start "
           f"{ld / n:4.1f})   barrier wait avg {b / n / 1e3:8.2f} us")
 print("L2 prefetch stages issued by CTA 0:", eng.prefetch_stages)
+# starvation: cycles warp 0 of the first / last CTA spent waiting for weights, per op kind, and as a share of the GEMV
+st, dn = eng.trace_starved, eng.trace_done
+for which, row in (("first CTA", st[0]), ("last CTA", st[1])):
+    for j, kname in enumerate(names):
+        if kname == "attn":
+            continue
+        cyc = row[j:n_layer_ops:per_layer].mean()
+        print(f"{which}: {kname:8s} warp 0 starved {cyc / 1.965e3:7.2f} us per op")
+# skew: op-done stamps over all CTAs
+for j, kname in enumerate(names):
+    d = dn[j:n_layer_ops:per_layer]                                   # [32 layers, grid]
+    spread = d.max(axis=1) - d.min(axis=1)
+    late = d.max(axis=1)[:, None] - d
+    print(f"skew {kname:8s}: last-first CTA {spread.mean() / 1e3:6.2f} us, mean CTA finishes {late.mean() / 1e3:6.2f} us before the last; "
+          f"slowest CTA ids (mode) {np.bincount(d.argmax(axis=1)).argmax()}")
+
 print("first rows:", (t[:12] - start).tolist())
