@@ -91,8 +91,12 @@ template <> struct Unpack<__half> {
 // half: mixed-precision fma.rn.f32.f16 (SASS FHFMA) -> products are exact in fp32,
 // bit-identical to convert-then-FFMA but without the conversions.
 __device__ __forceinline__ float fma_h(uint16_t a, uint16_t b, float c) {
+#ifdef B200_NO_FHFMA
+    return fmaf(__half2float(__ushort_as_half(a)), __half2float(__ushort_as_half(b)), c);
+#else
     asm("fma.rn.f32.f16 %0, %1, %2, %0;" : "+f"(c) : "h"(a), "h"(b));
     return c;
+#endif
 }
 template <typename T>
 __device__ __forceinline__ float dot16(const Pack16& a, const Pack16& b, float acc);
@@ -104,6 +108,16 @@ __device__ __forceinline__ float dot16<float>(const Pack16& a, const Pack16& b, 
 }
 template <>
 __device__ __forceinline__ float dot16<__half>(const Pack16& a, const Pack16& b, float acc) {
+#ifdef B200_NO_FHFMA
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const float2 x = __half22float2(*reinterpret_cast<const __half2*>(&a.w[i]));
+        const float2 y = __half22float2(*reinterpret_cast<const __half2*>(&b.w[i]));
+        acc = fmaf(x.x, y.x, acc);
+        acc = fmaf(x.y, y.y, acc);
+    }
+    return acc;
+#endif
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
         acc = fma_h((uint16_t)(a.w[i] & 0xffffu), (uint16_t)(b.w[i] & 0xffffu), acc);

@@ -15,6 +15,7 @@
 // barrier the ring (up to ~190 KB per SM, ~28 MB chip-wide) keeps HBM busy.
 //
 // HBM-bound: algorithmic bytes per step = all weights once + KV cache rows [0, step) once.
+#include <cstdio>
 #include <vector>
 
 #include "common.cuh"
@@ -120,6 +121,12 @@ struct StepSmem {
     }
 };
 
+// a copy of v the compiler cannot merge with other copies (see the call sites in decode_step_kernel)
+__device__ __forceinline__ int opaque_i32(int v) {
+    asm volatile("" : "+r"(v));
+    return v;
+}
+
 struct Ring {
     unsigned char* base;
     uint64_t* full;
@@ -161,6 +168,13 @@ struct OpSlice {
     int epi, N, K, u0, u1, ngroups;
 };
 __device__ __forceinline__ bool load_slice(const StepOp* ops, int oi, OpSlice& sl) {
+    if (ops[oi].type == kOpAttnO) {   // no row phase; W2 block of item blockIdx.x, K = bytes / 2 of the whole block
+        sl.W = nullptr;
+        sl.epi = -1; sl.N = ops[oi].N; sl.K = (ops[oi].N / ops[oi].act_stride) * (ops[oi].K / (ops[oi].units / ops[oi].act_stride));
+        sl.W2 = (int)blockIdx.x < ops[oi].units ? reinterpret_cast<const unsigned char*>(ops[oi].W2) : nullptr;
+        sl.u0 = blockIdx.x; sl.u1 = blockIdx.x + 1; sl.ngroups = 0;
+        return sl.W2 != nullptr;
+    }
     if (ops[oi].type != kOpGemv) return false;
     sl.W = reinterpret_cast<const unsigned char*>(ops[oi].W);
     sl.epi = ops[oi].epi; sl.N = ops[oi].N; sl.K = ops[oi].K;
@@ -206,7 +220,7 @@ __device__ __forceinline__ void cursor_seek(Cursor& c, const StepOp* ops, int n_
     c.valid = false;
     c.phase2 = false;
     while (c.oi < n_ops) {
-        if (load_slice(ops, c.oi, c.sl) && c.sl.ngroups > 0) {
+        if (load_slice(ops, c.oi, c.sl) && (c.sl.ngroups > 0 || c.sl.epi < 0)) {
             constexpr int KSEG = kSegB / 2;
             c.nseg = (c.sl.K + KSEG - 1) / KSEG;
             c.last_seg_bytes = (uint32_t)(c.sl.K - (c.nseg - 1) * KSEG) * 2u;
@@ -217,6 +231,7 @@ __device__ __forceinline__ void cursor_seek(Cursor& c, const StepOp* ops, int n_
             c.s2 = 0;
             c.bytes2 = c.sl.W2 ? (long long)(c.sl.u1 - c.sl.u0) * c.sl.K * 2 : 0;
             c.n2 = (int)((c.bytes2 + kStageB - 1) / kStageB);
+            c.phase2 = c.sl.ngroups == 0;   // kOpAttnO: straight to the contiguous phase
             c.valid = true;
             return;
         }
@@ -501,23 +516,25 @@ __device__ __forceinline__ void red_add_v4(float* gptr, float a, float b, float 
     asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(gptr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
+// y[b][0, K) += sum_r xv[b][r] * row_r[0, K) over the n_rows rows (K halves each) this CTA streams through the ring;
+// xv = [nb][x_stride] halves in shared memory, out = fp32 [nb][out_stride] in global memory (red.add)
 template <int NB, int PPT>
-__device__ __forceinline__ uint32_t down_consume(const StepOp& op, const StepParams& p, uint32_t state, const int n_rows) {
+__device__ __forceinline__ uint32_t down_consume(const StepParams& p, uint32_t state, const int K, const int n_rows,
+                                                 const __half* const act_s, const int act_stride, float* const out,
+                                                 const int out_stride, unsigned long long* const stamp = nullptr) {
     extern __shared__ __align__(128) unsigned char smem[];
     const StepSmem<NB> sm(smem, p.stages, p.xs_bytes);
     unsigned char* const r_base = sm.ring;
     uint64_t* const r_full = sm.full;
     uint64_t* const r_empty = sm.empty;
     const int r_stages = p.stages;
-    const __half* const act_s = reinterpret_cast<const __half*>(sm.scratch);
-    const int act_stride = op.act_stride;
 #ifdef B200_STEP_STARVE_TRACE
     long long* const starved = sm.starved;
     const bool traced = p.trace != nullptr && threadIdx.x < 32 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1);
 #endif
     int slot = (int)(state & 0xffu);
     uint32_t phase = state >> 8;
-    const int K = op.K, nb = p.nb;
+    const int nb = p.nb;
     const int PR = K / 8;                                              // packets per row
     const int tid = threadIdx.x, lane = tid & 31;
     const int PRc = PR < kStepConsumers ? PR : kStepConsumers;
@@ -532,6 +549,10 @@ __device__ __forceinline__ uint32_t down_consume(const StepOp& op, const StepPar
         for (int i = 0; i < PPT; ++i)
 #pragma unroll
             for (int e = 0; e < 8; ++e) acc[b][i][e] = 0.f;
+#ifdef B200_DBG_STAGES
+    long long dbg_t[16], dbg_c[16];
+    const long long dbg_entry = clock64();
+#endif
 
     for (int s2 = 0; s2 < n2; ++s2) {
 #ifdef B200_STEP_STARVE_TRACE
@@ -542,30 +563,52 @@ __device__ __forceinline__ uint32_t down_consume(const StepOp& op, const StepPar
         } else
 #endif
             mbar_wait(&r_full[slot], phase);
+#ifdef B200_DBG_STAGES
+        if (stamp && s2 < 16) dbg_t[s2] = clock64();
+#endif
         const int r0 = s2 * rows_per_stage;
         const int r1 = min(n_rows, r0 + rows_per_stage);
         const unsigned char* st = r_base + (size_t)slot * kStageB;
-        for (int r = r0 + rg; r < r1; r += nrg) {
-            uint16_t a[NB];
+        // four rows per trip: all their shared-memory loads are issued before the first FMA (8 warps per SM cannot hide
+        // the load latency of a one-row-at-a-time loop: 150 cycles per row measured)
+        constexpr int UR = PPT == 1 ? 4 : 2;
+        for (int r = r0 + rg; r < r1; r += UR * nrg) {
+            uint16_t a[UR][NB];
+            Pack16 w[UR][PPT];
 #pragma unroll
-            for (int b = 0; b < NB; ++b) a[b] = (b < nb) ? __half_as_ushort(act_s[b * act_stride + r]) : (uint16_t)0;
-            const unsigned char* row = st + (size_t)(r - r0) * K * 2;
+            for (int u = 0; u < UR; ++u) {
+                const int rr = min(r + u * nrg, r1 - 1);   // rows past the end re-read the last row; their FMAs are skipped
 #pragma unroll
-            for (int i = 0; i < PPT; ++i) {
-                const int pk = p0 + i * kStepConsumers;
-                if (pk < PR) {
-                    const Pack16 w = ld16(row + (size_t)pk * 16);
+                for (int b = 0; b < NB; ++b) a[u][b] = __half_as_ushort(act_s[(b < nb ? b : 0) * act_stride + rr]);
+                const unsigned char* row = st + (size_t)(rr - r0) * K * 2;
 #pragma unroll
-                    for (int b = 0; b < NB; ++b) {
+                for (int i = 0; i < PPT; ++i) {
+                    const int pk = min(p0 + i * kStepConsumers, PR - 1);
+                    w[u][i] = ld16(row + (size_t)pk * 16);
+                }
+            }
 #pragma unroll
-                        for (int e = 0; e < 4; ++e) {
-                            acc[b][i][2 * e] = fma_h((uint16_t)(w.w[e] & 0xffffu), a[b], acc[b][i][2 * e]);
-                            acc[b][i][2 * e + 1] = fma_h((uint16_t)(w.w[e] >> 16), a[b], acc[b][i][2 * e + 1]);
+            for (int u = 0; u < UR; ++u) {
+                if (r + u * nrg < r1) {
+#pragma unroll
+                    for (int i = 0; i < PPT; ++i) {
+                        if (p0 + i * kStepConsumers < PR) {
+#pragma unroll
+                            for (int b = 0; b < NB; ++b) {
+#pragma unroll
+                                for (int e = 0; e < 4; ++e) {
+                                    acc[b][i][2 * e] = fma_h((uint16_t)(w[u][i].w[e] & 0xffffu), a[u][b], acc[b][i][2 * e]);
+                                    acc[b][i][2 * e + 1] = fma_h((uint16_t)(w[u][i].w[e] >> 16), a[u][b], acc[b][i][2 * e + 1]);
+                                }
+                            }
                         }
                     }
                 }
             }
         }
+#ifdef B200_DBG_STAGES
+        if (stamp && s2 < 16) dbg_c[s2] = clock64();
+#endif
         __syncwarp();
         if (lane == 0) mbar_arrive(&r_empty[slot]);
         if (++slot == r_stages) {
@@ -573,6 +616,14 @@ __device__ __forceinline__ uint32_t down_consume(const StepOp& op, const StepPar
             phase ^= 1;
         }
     }
+    if (stamp) *stamp = global_timer_ns();   // trace: all stages consumed
+#ifdef B200_DBG_STAGES
+    if (stamp) {
+        printf("entry->first data %d, total %d; stages (cycles: compute, then gap to the next stage's data):", (int)(dbg_t[0] - dbg_entry), (int)(clock64() - dbg_entry));
+        for (int i = 0; i < n2 && i < 16; ++i) printf(" %d/%d", (int)(dbg_c[i] - dbg_t[i]), i + 1 < n2 ? (int)(dbg_t[i + 1] - dbg_c[i]) : 0);
+        printf("\n");
+    }
+#endif
     // the CTA's partial sums -> the fp32 accumulator (L2 adds; order over the CTAs is not fixed)
     if (rg < n_rows) {
 #pragma unroll
@@ -582,7 +633,7 @@ __device__ __forceinline__ uint32_t down_consume(const StepOp& op, const StepPar
                 for (int i = 0; i < PPT; ++i) {
                     const int pk = p0 + i * kStepConsumers;
                     if (pk < PR) {
-                        float* dst = op.acc_out + (size_t)b * K + (size_t)pk * 8;
+                        float* dst = out + (size_t)b * out_stride + (size_t)pk * 8;
                         red_add_v4(dst, acc[b][i][0], acc[b][i][1], acc[b][i][2], acc[b][i][3]);
                         red_add_v4(dst + 4, acc[b][i][4], acc[b][i][5], acc[b][i][6], acc[b][i][7]);
                     }
@@ -598,10 +649,16 @@ __device__ __forceinline__ uint32_t down_consume(const StepOp& op, const StepPar
 // Epilogues are those of gemv.cu (same rounding points as the unfused launch sequence).
 // ------------------------------------------------------------------------------------------
 template <int NB>
-__device__ __forceinline__ uint32_t gemv_consume(const StepOp& op, const StepParams& p, unsigned char* const r_base,
-                                                 uint64_t* const r_full, uint64_t* const r_empty, const int r_stages,
-                                                 uint32_t state, const __half* xs, const int step, const int op_index,
-                                                 float* scratch) {
+__device__ __noinline__ uint32_t gemv_consume(const StepOp& op, const StepParams& p, uint32_t state, const int step,
+                                              const int op_index) {
+    extern __shared__ __align__(128) unsigned char smem_dyn[];
+    const StepSmem<NB> lay(smem_dyn, p.stages, p.xs_bytes);
+    unsigned char* const r_base = lay.ring;
+    uint64_t* const r_full = lay.full;
+    uint64_t* const r_empty = lay.empty;
+    const int r_stages = p.stages;
+    const __half* const xs = lay.xs;
+    float* const scratch = lay.scratch;
     constexpr int KSEG = kSegB / 2;
 #ifdef B200_STEP_STARVE_TRACE   // build with -DB200_STEP_STARVE_TRACE: cycles warp 0 waited for weights, per op, into the trace
     long long* const starved = reinterpret_cast<long long*>(
@@ -613,11 +670,14 @@ __device__ __forceinline__ uint32_t gemv_consume(const StepOp& op, const StepPar
     uint32_t phase = state >> 8;
     const int epi = op.epi;
     const int nb = p.nb, N = op.N, K = op.K, units = op.units, head_size = p.head_size;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // opaque copies: nothing derived from the thread / block indices may be hoisted out of the kernel's op loop, where it
+    // would stay live across every out-of-line call (see decode_step_kernel)
+    const int tid_o = opaque_i32((int)threadIdx.x), bid_o = opaque_i32((int)blockIdx.x), grid_o = opaque_i32((int)gridDim.x);
+    const int warp = tid_o >> 5, lane = tid_o & 31;
     const int nseg = (K + KSEG - 1) / KSEG;
     const int last_seg_pk = (K - (nseg - 1) * KSEG) / 8;
-    const int u0 = (int)(((long long)units * blockIdx.x) / gridDim.x);
-    const int u1 = (int)(((long long)units * (blockIdx.x + 1)) / gridDim.x);
+    const int u0 = (int)(((long long)units * bid_o) / grid_o);
+    const int u1 = (int)(((long long)units * (bid_o + 1)) / grid_o);
     const int ngroups = (u1 - u0 + kStepWarps - 1) / kStepWarps;
     __half* const y = reinterpret_cast<__half*>(op.y);
 #ifdef B200_STEP_STARVE_TRACE
@@ -770,9 +830,11 @@ __device__ __noinline__ uint32_t down_phase(const StepOp& op, const StepParams& 
     const int u0 = (int)(((long long)units * blockIdx.x) / gridDim.x);
     const int u1 = (int)(((long long)units * (blockIdx.x + 1)) / gridDim.x);
     const int ppt = (op.K / 8 + kStepConsumers - 1) / kStepConsumers;   // 16-byte packets of a W2 row per thread
-    if (ppt <= 1) state = down_consume<NB, 1>(op, p, state, u1 - u0);
-    else if (ppt == 2) state = down_consume<NB, 2>(op, p, state, u1 - u0);
-    else state = down_consume<NB, (NB <= 2 ? 4 : 2)>(op, p, state, u1 - u0);
+    extern __shared__ __align__(128) unsigned char smem_dyn[];
+    const StepSmem<NB> lay(smem_dyn, p.stages, p.xs_bytes);
+    const __half* act_s = reinterpret_cast<const __half*>(lay.scratch);
+    if (ppt <= 1) state = down_consume<NB, 1>(p, state, op.K, u1 - u0, act_s, op.act_stride, op.acc_out, op.K);
+    else state = down_consume<NB, 2>(p, state, op.K, u1 - u0, act_s, op.act_stride, op.acc_out, op.K);   // K <= 4096 (builder)
 #ifdef B200_STEP_STARVE_TRACE
     if (p.trace != nullptr && threadIdx.x == 0 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) {
         extern __shared__ __align__(128) unsigned char smem[];
@@ -941,8 +1003,101 @@ __device__ __noinline__ void attn_consume(const StepOp& op, const StepParams& p,
                 if (e == 0) { p.part_ml[slot * 2] = M; p.part_ml[slot * 2 + 1] = L; }
             }
         }
-        consumers_sync();   // sm is reused by the next item
+        consumers_sync();   // sm is reused by the next item; every thread's partial stores precede thread 0's release
+        if (op.type == kOpAttnO && threadIdx.x == 0)
+            asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(reinterpret_cast<unsigned*>(op.y) + bh) : "memory");
     }
+}
+
+// second half of a kOpAttnO op: o-projection item (head, part) of this CTA. Waits for the attention items of its
+// (sequence, kv head) pairs, merges the head's split partials (fused_decoder_self_attention.cu:203-221,272-287; the
+// attention output is rounded to T as the unfused path stores it before o_proj), then streams its block of the
+// packed o weights: rows = the head's d input columns, N / parts output values each.
+template <int NB>
+__device__ __noinline__ uint32_t attn_o_phase(const StepOp& op, const StepParams& p, uint32_t state, const int op_index) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    const int item = blockIdx.x;
+    if (item >= op.units) return state;   // no o item (and no ring stages) for this CTA
+    const StepSmem<NB> sm(smem, p.stages, p.xs_bytes);
+    const int parts = op.act_stride, d = p.head_size, nb = p.nb, S = p.splits;
+    const int head = item / parts, part = item - head * parts;
+    const int kvh = head / (p.head_num / p.kv_head_num);
+    const int tid = threadIdx.x;
+    const bool tr = p.trace != nullptr && blockIdx.x == 0 && tid == 0;
+    if (tr) p.trace[4 * p.n_ops + 1 + op_index] = global_timer_ns();   // attention items of this CTA done
+    if (tid == 0) {
+        const unsigned* cnt = reinterpret_cast<const unsigned*>(op.y);
+        const unsigned long long t0 = global_timer_ns();
+        for (int b = 0; b < nb; ++b) {
+            while (ld_acquire_u32(cnt + b * p.kv_head_num + kvh) < (unsigned)S) {
+                if (global_timer_ns() - t0 > 2000000000ull) {
+                    atomicExch(&p.sync[2], 2u);
+                    __trap();
+                }
+            }
+        }
+    }
+    consumers_sync();
+    __half* xh = sm.xs;   // [nb][d]: the head's attention output
+    for (int idx = tid; idx < nb * d; idx += kStepConsumers) {
+        const int b = idx / d, j = idx - b * d;
+        const size_t bh = (size_t)b * p.head_num + head;
+        __half v;
+        if (S == 1) {
+            v = ldh_cg(reinterpret_cast<const __half*>(p.attn) + bh * d + j);
+        } else {
+            // online merge over the splits, four at a time: the eight loads of a group are independent (one L2
+            // round trip per group instead of one per load)
+            const float2* ml = reinterpret_cast<const float2*>(p.part_ml) + bh * S;
+            const float* po = p.part_o + bh * S * d + j;
+            float M = -INFINITY, L = 0.f, O = 0.f;
+            for (int s0 = 0; s0 < S; s0 += 4) {
+                float2 t[4];
+                float o4[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const bool in = s0 + u < S;
+                    t[u] = in ? __ldcg(ml + s0 + u) : make_float2(-INFINITY, 0.f);
+                    o4[u] = in ? __ldcg(po + (size_t)(s0 + u) * d) : 0.f;
+                }
+                float Mn = M;
+#pragma unroll
+                for (int u = 0; u < 4; ++u) Mn = fmaxf(Mn, t[u].x);
+                if (Mn != -INFINITY) {
+                    const float c = (M == -INFINITY) ? 0.f : expf(M - Mn);
+                    L *= c;
+                    O *= c;
+                    M = Mn;
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const float a = (t[u].x == -INFINITY) ? 0.f : expf(t[u].x - M);
+                        L += t[u].y * a;
+                        O += o4[u] * a;
+                    }
+                }
+            }
+            v = __float2half_rn(O * (1.f / (L + 1e-6f)));
+        }
+        xh[b * d + j] = v;
+    }
+    consumers_sync();
+    if (tr) {
+        p.trace[5 * p.n_ops + 1 + op_index] = global_timer_ns();   // dependencies met, head output merged
+        int sl = (int)(state & 0xffu), landed = 0;                 // ring stages of the o block already landed
+        uint32_t ph = state >> 8;
+        for (int i = 0; i < p.stages; ++i) {
+            landed += mbar_test(&sm.full[sl], ph) ? 1 : 0;
+            if (++sl == p.stages) { sl = 0; ph ^= 1; }
+        }
+        p.trace[2 * p.n_ops + op_index] = (unsigned long long)landed;
+    }
+    const int row_len = op.N / parts;
+    const int ppt = (row_len / 8 + kStepConsumers - 1) / kStepConsumers;
+    float* out = op.acc_out + (size_t)part * row_len;
+    unsigned long long* stamp = tr ? p.trace + 3 * p.n_ops + op_index : nullptr;
+    if (ppt <= 1) state = down_consume<NB, 1>(p, state, row_len, d, xh, d, out, op.N, stamp);
+    else state = down_consume<NB, 2>(p, state, row_len, d, xh, d, out, op.N, stamp);
+    return state;
 }
 
 // greedy pick (topK.cu:147 with K = 1; ties -> lower index) + advance (ids_cur <- ids_next, step+1)
@@ -1020,11 +1175,8 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const __gr
     __shared__ StepParams p;
     __shared__ __align__(16) StepOp opbuf[2];   // current op / next op (fetched while the current one runs)
     unsigned char* ring = smem;
-    __half* xs = reinterpret_cast<__half*>(smem + (size_t)gp.stages * kStageB);
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + (size_t)gp.stages * kStageB + gp.xs_bytes);
     uint64_t* empty_bar = full_bar + kStepMaxStages;
-    float* red = reinterpret_cast<float*>(empty_bar + kStepMaxStages);   // [NB*8 + NB + 32] floats, also argmax scratch
-    float* scratch = red + (NB * kStepWarps + NB + 32);                  // split-KV merge weights / act slice
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x == 0) {
@@ -1044,6 +1196,10 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const __gr
     }
 
     // ---- consumers
+#ifdef B200_DBG_STAGES
+    const long long dbg_c0 = clock64();
+    const unsigned long long dbg_g0 = global_timer_ns();
+#endif
     const int step = *gp.step_dev;
     const unsigned base = gp.sync[1];
     const int n_ops = gp.n_ops;
@@ -1069,14 +1225,24 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const __gr
                 *reinterpret_cast<float4*>(op.zero + i) = make_float4(0.f, 0.f, 0.f, 0.f);
         }
         if (type == kOpGemv) {
-            stage_x<NB>(op, p, xs, red, scratch);
+            // the shared-memory pointers are re-derived at every call site from an opaque copy of the two layout
+            // parameters: kept live across the out-of-line calls they (and whatever else is live) compete with the
+            // callees for the 168 registers a 9-warp CTA can have, and anything pushed to local memory is an L2 trip
+            {
+                const StepSmem<NB> L(smem, opaque_i32(gp.stages), (size_t)opaque_i32((int)gp.xs_bytes));
+                stage_x<NB>(op, p, L.xs, L.red, L.scratch);
+            }
             if (gp.trace && blockIdx.x == 0 && threadIdx.x == 0) trace_gemv_start(p, ring_state, oi);
-            ring_state = gemv_consume<NB>(op, p, ring, full_bar, empty_bar, gp.stages, ring_state, xs, step, oi, scratch);
+            ring_state = gemv_consume<NB>(op, p, ring_state, step, oi);
             if (op.epi == kEpiSwigluDown) ring_state = down_phase<NB>(op, p, ring_state, oi);
         } else if (type == kOpAttn) {
-            attn_consume<G>(op, p, reinterpret_cast<float*>(xs), step);
+            attn_consume<G>(op, p, reinterpret_cast<float*>(smem + (size_t)opaque_i32(gp.stages) * kStageB), step);
+        } else if (type == kOpAttnO) {
+            attn_consume<G>(op, p, reinterpret_cast<float*>(smem + (size_t)opaque_i32(gp.stages) * kStageB), step);
+            ring_state = attn_o_phase<NB>(op, p, ring_state, oi);
         } else {
-            final_consume(p, red, reinterpret_cast<int*>(red + 16));
+            const StepSmem<NB> L(smem, opaque_i32(gp.stages), (size_t)opaque_i32((int)gp.xs_bytes));
+            final_consume(p, L.red, reinterpret_cast<int*>(L.red + 16));
         }
         if (gp.trace && blockIdx.x == 0 && threadIdx.x == 0) gp.trace[2 * oi] = global_timer_ns();
         if (gp.trace && threadIdx.x == 0) gp.trace[6 * n_ops + 1 + (size_t)oi * gridDim.x + blockIdx.x] = global_timer_ns();
@@ -1087,11 +1253,16 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const __gr
             // while the other CTAs arrive: warm L2 with what the next op reads first and that does not
             // depend on this step (the KV rows of this CTA's attention item)
             const StepOp& nop = opbuf[(oi + 1) & 1];
-            if (nop.type == kOpAttn) attn_prefetch<G>(nop, p, step);
+            if (nop.type == kOpAttn || nop.type == kOpAttnO) attn_prefetch<G>(nop, p, step);
             grid_barrier_wait(gp.sync, base + epoch * gridDim.x);
         }
         if (gp.trace && blockIdx.x == 0 && threadIdx.x == 0) gp.trace[2 * oi + 1] = global_timer_ns();
     }
+#ifdef B200_DBG_STAGES
+    if (blockIdx.x == 0 && threadIdx.x == 0)
+        printf("kernel: %lld cycles in %llu ns -> %.3f GHz\n", clock64() - dbg_c0, global_timer_ns() - dbg_g0,
+               (double)(clock64() - dbg_c0) / (double)(global_timer_ns() - dbg_g0));
+#endif
     // last op done by this CTA: the final arrival advances the launch base and the step
     consumers_sync();
     if (threadIdx.x == 0) {

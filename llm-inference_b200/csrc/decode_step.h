@@ -6,7 +6,12 @@
 
 namespace b200 {
 
-enum { kOpGemv = 0, kOpAttn = 1, kOpFinal = 2 };
+// kOpAttnO: split-KV attention items, then - without a grid barrier - the o projection split along K into (head, part)
+// items: the CTA of item (head, part) waits on the (sequence, kv head) counters of the attention items it depends on,
+// merges that head's split partials, multiplies the head's d outputs by ITS block of the packed o weights
+// (W2: [head_num * parts][d][N / parts], rows = input columns) and adds the partial rows into acc_out (red.add).
+// Fields: N = hidden size, K = head_num * head_size, units = head_num * parts, act_stride = parts, y = counters.
+enum { kOpGemv = 0, kOpAttn = 1, kOpFinal = 2, kOpAttnO = 3 };
 // kEpiSwigluDown: gate_up GEMV + SwiGLU, then - without a grid barrier - the CTA multiplies the slice of `act` it has
 // just produced by ITS rows of the transposed down weights W2 [I, H] and adds the partial [H] into acc_out with
 // red.global.add.v4.f32 (the down projection split along K over the CTAs; L2 does the cross-CTA sum)
@@ -21,7 +26,7 @@ struct StepOp {
     int norm;        // 0 none, 1 (x*inv)*gamma, 2 (gamma*x)*inv   (gemv prologue)
     int N, K, units;
     int n_zero;      // floats of `zero` cleared (split over the CTAs) when this op starts
-    int act_stride;  // kEpiSwigluDown: halves between the batch rows of the CTA's act slice in shared memory
+    int act_stride;  // kEpiSwigluDown: halves between the batch rows of the CTA's act slice in shared memory; kOpAttnO: parts
     int pad1;
     const void* W;
     const void* x;

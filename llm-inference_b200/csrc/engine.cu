@@ -91,6 +91,11 @@ struct b200_engine {
     char* down_t = nullptr;
     float* ffn_acc = nullptr;
     bool down_t_dirty = true;
+    // attention -> o projection without a grid barrier (kOpAttnO): o weights packed per (head, part) item, one fp32
+    // accumulator [batch, H] and the (sequence, kv head) arrival counters behind it
+    char* o_packed = nullptr;
+    float* o_acc = nullptr;     // [batch*H floats][counters: batch*hk unsigned, padded to 4]
+    int o_parts = 0;
     int launches_per_step = 0;
 };
 
@@ -178,6 +183,20 @@ __global__ void transpose_kernel(const T* __restrict__ src, T* __restrict__ dst,
     }
 }
 
+// o weights [H, h*d] -> blocks of item (head, part): [d input columns][H / parts output rows] (load-time packing)
+__global__ void pack_o_kernel(const __half* __restrict__ W, __half* __restrict__ dst, int H, int heads, int d, int parts) {
+    const int hp = H / parts;
+    const size_t total = (size_t)H * heads * d;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const int r = (int)(i % hp);
+        size_t t = i / hp;
+        const int j = (int)(t % d);
+        t /= d;
+        const int part = (int)(t % parts), head = (int)(t / parts);
+        dst[i] = W[(size_t)(part * hp + r) * ((size_t)heads * d) + (size_t)head * d + j];
+    }
+}
+
 __global__ void advance_kernel(int* ids_cur, const int* ids_next, int* step, int batch) {
     pdl_wait();
     if (threadIdx.x < batch) ids_cur[threadIdx.x] = ids_next[threadIdx.x];
@@ -207,7 +226,7 @@ static void build_program(b200_engine* e) {
     // (H a power of two <= 16384) and the per-thread accumulators in registers (batch tile x packets per thread <= 8)
     const int nb_t = e->batch <= 1 ? 1 : e->batch <= 2 ? 2 : 4;
     const int ppt = (H / 8 + 255) / 256;
-    bool fuse_ffn = L >= 1 && H >= 256 && (H & (H - 1)) == 0 && H <= 16384 && nb_t * ppt <= 8;
+    bool fuse_ffn = L >= 1 && H >= 256 && (H & (H - 1)) == 0 && ppt <= 2 && nb_t * ppt <= 8;   // H <= 4096
     {
         const char* env = getenv("B200_STEP_NO_FFN_FUSION");
         if (env && env[0] == '1') fuse_ffn = false;
@@ -224,37 +243,81 @@ static void build_program(b200_engine* e) {
             e->down_t_dirty = true;
         }
     }
-    // residual stream: layer l works in buf[l % 2] (the K-split down's residual add is formed in the next op's x
-    // staging, which publishes it to the OTHER buffer - other CTAs may still be reading the old one); the decoder
-    // output of the step ends up in e->hidden either way
+    // attention -> o projection as one op (no grid barrier in between): parts = the largest power of two with
+    // head_num * parts <= CTAs and >= 64 output rows per part; needs the fused FFN's residual plumbing
+    int parts = 0;
+    if (fuse_ffn && e->d == 128) {
+        parts = 1;
+        while (e->h * parts * 2 <= sm_count() && H / (parts * 2) >= 64) parts *= 2;
+        const int row_len = H / parts;
+        const char* env = getenv("B200_STEP_NO_ATTN_O_FUSION");
+        if ((env && env[0] == '1') || H % parts || row_len % 8 || (32768 % (row_len * 2)) || (row_len / 8 + 255) / 256 > 2 ||
+            nb_t * ((row_len / 8 + 255) / 256) > 8)
+            parts = 0;
+    }
+    if (parts) {
+        const size_t wb = (size_t)L * H * e->h * e->d * e->esz;
+        const size_t cnt = ((size_t)e->batch * e->hk + 3) & ~(size_t)3;
+        const size_t ab = (size_t)e->batch * H * sizeof(float) + cnt * sizeof(unsigned);
+        if (cudaMalloc(&e->o_packed, wb) != cudaSuccess || cudaMalloc(&e->o_acc, ab) != cudaSuccess) {
+            cudaGetLastError();
+            cudaFree(e->o_packed);
+            e->o_packed = nullptr;
+            parts = 0;
+        } else {
+            cudaMemset(e->o_acc, 0, ab);
+            e->o_parts = parts;
+        }
+    }
+    // Residual stream with K-split projections: the residual add of a projection is formed in the NEXT op's x staging
+    // (T(x + T(sum))), which publishes the result to the OTHER buffer - CTAs of the same staging still read the old one.
+    //   FFN only fused : layer l works in buf[l % 2] (o_proj adds in place), the decoder output lands in e->hidden
+    //   attn-o fused too: A = e->hidden holds h_l, B = e->residual holds h_l + o_proj; A again after the FFN
     void* buf[2] = {e->hidden, e->hidden};
-    if (fuse_ffn) {
+    if (fuse_ffn && !parts) {
         buf[L % 2] = e->hidden;
         buf[(L + 1) % 2] = e->residual;
     }
+    void* const bufA = e->hidden;
+    void* const bufB = e->residual;
     auto acc = [&](int l) { return e->ffn_acc + (size_t)(l % 2) * e->batch * H; };
     const int n_acc = e->batch * H;
+    unsigned* counters = parts ? reinterpret_cast<unsigned*>(e->o_acc + n_acc) : nullptr;
+    const int n_cnt = (e->batch * e->hk + 3) & ~3;
     for (int l = 0; l < L; ++l) {
         LayerW& w = e->layers[l];
         void* kc = e->k_cache + (size_t)l * e->layer_kv_elems * e->esz;
         void* vc = e->v_cache + (size_t)l * e->layer_kv_elems * e->esz;
-        void* hid = buf[l % 2];
+        void* hid = parts ? bufA : buf[l % 2];
         StepOp qkv{};
         qkv.type = kOpGemv; qkv.epi = kEpiRopeKV; qkv.norm = 1; qkv.N = e->qkv_n; qkv.K = H; qkv.units = e->qkv_n / 2;
         qkv.W = w.qkv; qkv.y = e->qkv; qkv.gamma = w.attn_norm; qkv.k_cache = kc; qkv.v_cache = vc;
         if (l == 0) { qkv.xsrc = kXEmbed; qkv.xout = hid; qkv.x = hid; }
-        else if (fuse_ffn) { qkv.xsrc = kXResidAcc; qkv.x = buf[(l - 1) % 2]; qkv.acc_in = acc(l - 1); qkv.xout = hid; }
+        else if (fuse_ffn) { qkv.xsrc = kXResidAcc; qkv.x = parts ? bufB : buf[(l - 1) % 2]; qkv.acc_in = acc(l - 1); qkv.xout = hid; }
         else { qkv.xsrc = kXPlain; qkv.x = hid; }
+        if (parts && l >= 1) { qkv.zero = e->o_acc; qkv.n_zero = n_acc; }   // consumed by the previous layer's FFN staging
         StepOp att{};
         att.type = kOpAttn; att.k_cache = kc; att.v_cache = vc;
         if (fuse_ffn && l >= 1) { att.zero = acc(l - 1); att.n_zero = n_acc; }   // consumed by this layer's qkv staging
-        StepOp o{};
-        o.type = kOpGemv; o.epi = kEpiResidual; o.xsrc = kXCombine; o.N = H; o.K = e->h * e->d; o.units = (H + 1) / 2;
-        o.W = w.o; o.x = e->attn; o.y = hid;
         StepOp gu{};
         gu.type = kOpGemv; gu.xsrc = kXPlain; gu.norm = 2; gu.N = e->I; gu.K = H; gu.units = e->I;
         gu.W = w.gate_up; gu.x = hid; gu.gamma = w.ffn_norm;
-        ops.push_back(qkv); ops.push_back(att); ops.push_back(o);
+        ops.push_back(qkv);
+        if (parts) {
+            att.type = kOpAttnO;
+            att.N = H; att.K = e->h * e->d; att.units = e->h * parts; att.act_stride = parts;
+            att.W2 = e->o_packed + (size_t)l * H * e->h * e->d * e->esz;
+            att.acc_out = e->o_acc;
+            att.y = counters;
+            ops.push_back(att);
+            gu.xsrc = kXResidAcc; gu.x = bufA; gu.acc_in = e->o_acc; gu.xout = bufB;
+            gu.zero = reinterpret_cast<float*>(counters); gu.n_zero = n_cnt;   // all o items have passed their waits
+        } else {
+            StepOp o{};
+            o.type = kOpGemv; o.epi = kEpiResidual; o.xsrc = kXCombine; o.N = H; o.K = e->h * e->d; o.units = (H + 1) / 2;
+            o.W = w.o; o.x = e->attn; o.y = hid;
+            ops.push_back(att); ops.push_back(o);
+        }
         if (fuse_ffn) {
             gu.epi = kEpiSwigluDown;
             gu.act_stride = (((e->I + sm_count() - 1) / sm_count()) + 8) & ~7;
@@ -274,7 +337,11 @@ static void build_program(b200_engine* e) {
     head.type = kOpGemv; head.epi = kEpiPlain; head.norm = 1; head.N = e->V; head.K = H; head.units = (e->V + 1) / 2;
     head.W = e->lm_head; head.y = e->logits; head.gamma = e->final_norm;
     if (L == 0) { head.xsrc = kXEmbed; head.x = e->hidden; head.xout = e->hidden; }
-    else if (fuse_ffn) { head.xsrc = kXResidAcc; head.x = buf[(L - 1) % 2]; head.acc_in = acc(L - 1); head.xout = buf[L % 2]; }
+    else if (fuse_ffn) {
+        head.xsrc = kXResidAcc; head.x = parts ? bufB : buf[(L - 1) % 2]; head.acc_in = acc(L - 1);
+        head.xout = parts ? bufA : buf[L % 2];
+        if (parts) { head.zero = e->o_acc; head.n_zero = n_acc; }
+    }
     else { head.xsrc = kXPlain; head.x = e->hidden; }
     StepOp fin{};
     fin.type = kOpFinal;
@@ -291,8 +358,12 @@ static void build_program(b200_engine* e) {
     if (!e->program && e->down_t) {
         cudaFree(e->down_t);
         cudaFree(e->ffn_acc);
+        cudaFree(e->o_packed);
+        cudaFree(e->o_acc);
         e->down_t = nullptr;
         e->ffn_acc = nullptr;
+        e->o_packed = nullptr;
+        e->o_acc = nullptr;
     }
 }
 
@@ -303,6 +374,11 @@ static int refresh_down_t(b200_engine* e) {
     for (int l = 0; l < e->cfg.num_layers; ++l)
         transpose_kernel<__half><<<grd, blk, 0, e->stream>>>((const __half*)e->layers[l].down,
                                                              (__half*)e->down_t + (size_t)l * e->I * e->H, e->H, e->I);
+    if (e->o_packed)
+        for (int l = 0; l < e->cfg.num_layers; ++l)
+            pack_o_kernel<<<148 * 8, 256, 0, e->stream>>>((const __half*)e->layers[l].o,
+                                                          (__half*)e->o_packed + (size_t)l * e->H * e->h * e->d, e->H,
+                                                          e->h, e->d, e->o_parts);
     CU(cudaGetLastError());
     e->down_t_dirty = false;
     return 0;
@@ -430,6 +506,8 @@ extern "C" void b200_engine_destroy(b200_engine* e) {
     cudaFree(e->pf_arena);
     cudaFree(e->down_t);
     cudaFree(e->ffn_acc);
+    cudaFree(e->o_packed);
+    cudaFree(e->o_acc);
     cudaFree(e->arena);
     cudaFree(e->k_cache);
     cudaFree(e->v_cache);
@@ -536,7 +614,7 @@ extern "C" int b200_engine_set_weight(b200_engine* e, int slot, int layer, const
     void* p = slot_ptr(e, slot, layer);
     if (!p || bytes != slot_elems(e, slot) * e->esz) return fail("set_weight: bad slot / size");
     CU(cudaMemcpy(p, src, bytes, cudaMemcpyHostToDevice));
-    if (slot == B200_W_DOWN) e->down_t_dirty = true;
+    if (slot == B200_W_DOWN || slot == B200_W_O) e->down_t_dirty = true;
     return B200_OK;
 }
 extern "C" int b200_engine_get_weight(b200_engine* e, int slot, int layer, void* dst, size_t bytes) {

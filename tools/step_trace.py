@@ -23,7 +23,7 @@ for _ in range(5):
     ids = eng.decode_step_host(ids)
 t = eng.step_trace().astype(np.int64)
 per_layer = (len(t) - 2) // 32
-names = ["qkv", "attn", "o", "gate_up", "down"] if per_layer == 5 else ["qkv", "attn", "o", "ffn"]
+names = {5: ["qkv", "attn", "o", "gate_up", "down"], 4: ["qkv", "attn", "o", "ffn"], 3: ["qkv", "attn_o", "ffn"]}[per_layer]
 n_layer_ops = 32 * per_layer
 start = t[0, 0]
 print("kernel start -> first op done: n/a; total ns:", t[-1, 0] - (t[0, 0]), "ops:", len(t))
@@ -48,7 +48,7 @@ print("L2 prefetch stages issued by CTA 0:", eng.prefetch_stages)
 st, dn = eng.trace_starved, eng.trace_done
 for which, row in (("first CTA", st[0]), ("last CTA", st[1])):
     for j, kname in enumerate(names):
-        if kname == "attn":
+        if kname.startswith("attn"):
             continue
         cyc = row[j:n_layer_ops:per_layer].mean()
         print(f"{which}: {kname:8s} warp 0 starved {cyc / 1.965e3:7.2f} us per op")
@@ -61,3 +61,11 @@ for j, kname in enumerate(names):
           f"slowest CTA ids (mode) {np.bincount(d.argmax(axis=1)).argmax()}")
 
 print("first rows:", (t[:12] - start).tolist())
+
+if per_layer == 3:   # anatomy of the attention + o projection op (CTA 0): attention items | wait + merge | o block
+    idx = np.arange(1, n_layer_ops, 3)
+    a_done, merged = eng.trace_starved[0][idx], eng.trace_starved[1][idx]
+    start = t[idx - 1, 1]
+    print("o block stages landed at the start of the o phase:", t[idx, 2].mean())
+    print(f"attn_o anatomy: attention {np.mean(a_done - start) / 1e3:.2f} us, wait + merge {np.mean(merged - a_done) / 1e3:.2f} us, "
+          f"o block stages {np.mean(t[idx, 3] - merged) / 1e3:.2f} us, reds + return {np.mean(t[idx, 0] - t[idx, 3]) / 1e3:.2f} us")
