@@ -161,18 +161,23 @@ __device__ __forceinline__ void op_rows_rt(const StepOp& op, int head_size, int 
     else op_unit_rows<kEpiPlain>(op, head_size, u, ra, rb);
 }
 
+// Row pairs of a CTA are walked in ngroups = ceil(n / 8) groups of EQUAL size ceil(n / ngroups) <= 8 (one row pair per
+// consumer warp and stage): 42 pairs are 6 groups of 7, not 5 of 8 and a tail of 2 whose four nearly empty stages
+// each still cost the consumers a full stage hand-over. Producer and consumers use the same rule.
+__device__ __forceinline__ int group_size(int n_units, int ngroups) { return ngroups > 0 ? (n_units + ngroups - 1) / ngroups : 0; }
+
 // this CTA's slice of one GEMV op, as the producer sees it
 struct OpSlice {
     const unsigned char* W;
     const unsigned char* W2;   // kEpiSwigluDown: transposed down weights (rows [u0, u1) are this CTA's), else nullptr
-    int epi, N, K, u0, u1, ngroups;
+    int epi, N, K, u0, u1, ngroups, gsz;
 };
 __device__ __forceinline__ bool load_slice(const StepOp* ops, int oi, OpSlice& sl) {
     if (ops[oi].type == kOpAttnO) {   // no row phase; W2 block of item blockIdx.x, K = bytes / 2 of the whole block
         sl.W = nullptr;
         sl.epi = -1; sl.N = ops[oi].N; sl.K = (ops[oi].N / ops[oi].act_stride) * (ops[oi].K / (ops[oi].units / ops[oi].act_stride));
         sl.W2 = (int)blockIdx.x < ops[oi].units ? reinterpret_cast<const unsigned char*>(ops[oi].W2) : nullptr;
-        sl.u0 = blockIdx.x; sl.u1 = blockIdx.x + 1; sl.ngroups = 0;
+        sl.u0 = blockIdx.x; sl.u1 = blockIdx.x + 1; sl.ngroups = 0; sl.gsz = 0;
         return sl.W2 != nullptr;
     }
     if (ops[oi].type != kOpGemv) return false;
@@ -183,12 +188,13 @@ __device__ __forceinline__ bool load_slice(const StepOp* ops, int oi, OpSlice& s
     sl.u0 = (int)(((long long)units * blockIdx.x) / gridDim.x);
     sl.u1 = (int)(((long long)units * (blockIdx.x + 1)) / gridDim.x);
     sl.ngroups = (sl.u1 - sl.u0 + kStepWarps - 1) / kStepWarps;
+    sl.gsz = group_size(sl.u1 - sl.u0, sl.ngroups);
     return true;
 }
 // source row of this lane (lane l -> row (l & 1) of unit (l >> 1)) in group g; nullptr if none
 __device__ __forceinline__ const unsigned char* slice_lane_row(const OpSlice& sl, int g, int lane, int head_size) {
-    const int ubase = sl.u0 + g * kStepWarps;
-    const int nu = min(kStepWarps, sl.u1 - ubase);
+    const int ubase = sl.u0 + g * sl.gsz;
+    const int nu = min(sl.gsz, sl.u1 - ubase);
     if (lane >= 2 * nu) return nullptr;
     const int u = ubase + (lane >> 1);
     int ra, rb;
@@ -679,6 +685,7 @@ __device__ __noinline__ uint32_t gemv_consume(const StepOp& op, const StepParams
     const int u0 = (int)(((long long)units * bid_o) / grid_o);
     const int u1 = (int)(((long long)units * (bid_o + 1)) / grid_o);
     const int ngroups = (u1 - u0 + kStepWarps - 1) / kStepWarps;
+    const int gsz = group_size(u1 - u0, ngroups);
     __half* const y = reinterpret_cast<__half*>(op.y);
 #ifdef B200_STEP_STARVE_TRACE
     const bool traced = p.trace != nullptr && warp == 0 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1);
@@ -686,8 +693,8 @@ __device__ __noinline__ uint32_t gemv_consume(const StepOp& op, const StepParams
 #endif
 
     for (int g = 0; g < ngroups; ++g) {
-        const int unit = u0 + g * kStepWarps + warp;
-        const bool active = unit < u1;
+        const int unit = u0 + g * gsz + warp;
+        const bool active = warp < gsz && unit < u1;
         int ra = 0, rb = -1;
         if (active) {
             if (epi == kEpiSwiglu || epi == kEpiSwigluDown) { ra = unit; rb = N + unit; }
