@@ -825,6 +825,18 @@ __device__ __noinline__ uint32_t gemv_consume(const StepOp& op, const StepParams
 #ifdef B200_STEP_STARVE_TRACE
     if (traced && lane == 0) p.trace[4 * p.n_ops + 1 + (blockIdx.x == 0 ? 0 : p.n_ops) + op_index] = (unsigned long long)*starved;
 #endif
+    if (epi == kEpiRopeKV && op.head_cnt != nullptr) {
+        // this CTA's rows of q / k / v (and the cache rows appended with them) are complete: credit every qkv head
+        // it covers with the number of row pairs it contributed; attention items wait for head_size / 2 per head
+        consumers_sync();
+        if (threadIdx.x == 0 && u1 > u0) {
+            const int hd = head_size >> 1;
+            for (int head = u0 / hd; head <= (u1 - 1) / hd; ++head) {
+                const int n = min(u1, (head + 1) * hd) - max(u0, head * hd);
+                asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(op.head_cnt + head), "r"((unsigned)n) : "memory");
+            }
+        }
+    }
     return (uint32_t)slot | (phase << 8);
 }
 
@@ -900,6 +912,22 @@ __device__ __noinline__ void attn_consume(const StepOp& op, const StepParams& p,
         const __half* kc = reinterpret_cast<const __half*>(op.k_cache) + ((size_t)b * p.kv_head_num + kvh) * p.max_seq_len * D;
         const __half* vc = reinterpret_cast<const __half*>(op.v_cache) + ((size_t)b * p.kv_head_num + kvh) * p.max_seq_len * D;
         const int k0 = split * per, k1 = min(step, k0 + per);
+        if (op.head_cnt != nullptr) {
+            // no grid barrier after the qkv op: wait until the CTAs that own the rows of this item's q heads, k head and
+            // v head have released them (D / 2 row pairs per head)
+            if (threadIdx.x < G + 2) {
+                const int head = (int)threadIdx.x < G ? kvh * G + (int)threadIdx.x
+                                                      : ((int)threadIdx.x == G ? p.head_num + kvh : p.head_num + p.kv_head_num + kvh);
+                const unsigned long long t0 = global_timer_ns();
+                while (ld_acquire_u32(op.head_cnt + head) < (unsigned)(D / 2)) {
+                    if (global_timer_ns() - t0 > 2000000000ull) {
+                        atomicExch(&p.sync[2], 3u);
+                        __trap();
+                    }
+                }
+            }
+            consumers_sync();
+        }
 
         Pack16 q[G];
 #pragma unroll
@@ -1231,6 +1259,12 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const __gr
             for (int i = z0 + 4 * (int)threadIdx.x; i < z1; i += 4 * kStepConsumers)
                 *reinterpret_cast<float4*>(op.zero + i) = make_float4(0.f, 0.f, 0.f, 0.f);
         }
+        if (op.zero2) {
+            const int per = (((op.n_zero2 + (int)gridDim.x - 1) / (int)gridDim.x) + 3) & ~3;
+            const int z0 = per * blockIdx.x, z1 = min(op.n_zero2, z0 + per);
+            for (int i = z0 + 4 * (int)threadIdx.x; i < z1; i += 4 * kStepConsumers)
+                *reinterpret_cast<float4*>(op.zero2 + i) = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
         if (type == kOpGemv) {
             // the shared-memory pointers are re-derived at every call site from an opaque copy of the two layout
             // parameters: kept live across the out-of-line calls they (and whatever else is live) compete with the
@@ -1253,7 +1287,7 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const __gr
         }
         if (gp.trace && blockIdx.x == 0 && threadIdx.x == 0) gp.trace[2 * oi] = global_timer_ns();
         if (gp.trace && threadIdx.x == 0) gp.trace[6 * n_ops + 1 + (size_t)oi * gridDim.x + blockIdx.x] = global_timer_ns();
-        if (oi + 1 < n_ops) {
+        if (oi + 1 < n_ops && !op.no_barrier) {
             ++epoch;
             asm volatile("cp.async.wait_group 0;" ::: "memory");   // the next op's descriptor has landed
             grid_barrier_arrive(gp.sync);
@@ -1262,6 +1296,13 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const __gr
             const StepOp& nop = opbuf[(oi + 1) & 1];
             if (nop.type == kOpAttn || nop.type == kOpAttnO) attn_prefetch<G>(nop, p, step);
             grid_barrier_wait(gp.sync, base + epoch * gridDim.x);
+        } else if (oi + 1 < n_ops) {
+            // no grid barrier: the next op's consumers wait on the counters this op released. The next descriptor
+            // still has to be in shared memory for every thread of the CTA.
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+            consumers_sync();
+            const StepOp& nop = opbuf[(oi + 1) & 1];
+            if (nop.type == kOpAttnO) attn_prefetch<G>(nop, p, step);
         }
         if (gp.trace && blockIdx.x == 0 && threadIdx.x == 0) gp.trace[2 * oi + 1] = global_timer_ns();
     }

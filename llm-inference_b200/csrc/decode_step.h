@@ -27,7 +27,9 @@ struct StepOp {
     int N, K, units;
     int n_zero;      // floats of `zero` cleared (split over the CTAs) when this op starts
     int act_stride;  // kEpiSwigluDown: halves between the batch rows of the CTA's act slice in shared memory; kOpAttnO: parts
-    int pad1;
+    int no_barrier;  // 1: no grid barrier after this op (its consumers wait on finer-grained counters instead)
+    int n_zero2;     // floats of `zero2` cleared when this op starts
+    int pad2, pad3, pad4;
     const void* W;
     const void* x;
     void* y;
@@ -39,6 +41,9 @@ struct StepOp {
     float* acc_out;        // kEpiSwigluDown: fp32 accumulator [nb, K]
     void* xout;            // kXEmbed / kXResidAcc: CTA 0 stores the new residual stream [nb, K] here
     float* zero;           // accumulator to clear for its next use (consumed one op earlier), or nullptr
+    float* zero2;          // a second range to clear (the arrival counters), or nullptr
+    unsigned* head_cnt;    // kEpiRopeKV: per qkv head, row pairs finished (released by the producing CTAs);
+                           // kOpAttnO: the same array - an attention item waits for its q, k and v heads
 };
 static_assert(sizeof(StepOp) % 16 == 0, "StepOp travels in 16-byte cp.async pieces");
 

@@ -257,7 +257,8 @@ static void build_program(b200_engine* e) {
     }
     if (parts) {
         const size_t wb = (size_t)L * H * e->h * e->d * e->esz;
-        const size_t cnt = ((size_t)e->batch * e->hk + 3) & ~(size_t)3;
+        // arrival counters: [batch * hk attention items done][h + 2 hk qkv heads done], each block padded to 4
+        const size_t cnt = (((size_t)e->batch * e->hk + 3) & ~(size_t)3) + (((size_t)e->h + 2 * e->hk + 3) & ~(size_t)3);
         const size_t ab = (size_t)e->batch * H * sizeof(float) + cnt * sizeof(unsigned);
         if (cudaMalloc(&e->o_packed, wb) != cudaSuccess || cudaMalloc(&e->o_acc, ab) != cudaSuccess) {
             cudaGetLastError();
@@ -283,7 +284,13 @@ static void build_program(b200_engine* e) {
     auto acc = [&](int l) { return e->ffn_acc + (size_t)(l % 2) * e->batch * H; };
     const int n_acc = e->batch * H;
     unsigned* counters = parts ? reinterpret_cast<unsigned*>(e->o_acc + n_acc) : nullptr;
-    const int n_cnt = (e->batch * e->hk + 3) & ~3;
+    const int n_cnt_attn = (e->batch * e->hk + 3) & ~3;
+    const int n_cnt = n_cnt_attn + ((e->h + 2 * e->hk + 3) & ~3);
+    unsigned* head_cnt = parts ? counters + n_cnt_attn : nullptr;
+    {
+        const char* env = getenv("B200_STEP_QKV_BARRIER");   // 1: keep the grid barrier between qkv and attention
+        if (env && env[0] == '1') head_cnt = nullptr;
+    }
     for (int l = 0; l < L; ++l) {
         LayerW& w = e->layers[l];
         void* kc = e->k_cache + (size_t)l * e->layer_kv_elems * e->esz;
@@ -298,7 +305,9 @@ static void build_program(b200_engine* e) {
         if (parts && l >= 1) { qkv.zero = e->o_acc; qkv.n_zero = n_acc; }   // consumed by the previous layer's FFN staging
         StepOp att{};
         att.type = kOpAttn; att.k_cache = kc; att.v_cache = vc;
-        if (fuse_ffn && l >= 1) { att.zero = acc(l - 1); att.n_zero = n_acc; }   // consumed by this layer's qkv staging
+        // acc(l - 1) was consumed by this layer's qkv staging: cleared one barrier later - at the attention op, or at
+        // the FFN op when no grid barrier separates qkv and attention
+        if (fuse_ffn && l >= 1 && !head_cnt) { att.zero = acc(l - 1); att.n_zero = n_acc; }
         StepOp gu{};
         gu.type = kOpGemv; gu.xsrc = kXPlain; gu.norm = 2; gu.N = e->I; gu.K = H; gu.units = e->I;
         gu.W = w.gate_up; gu.x = hid; gu.gamma = w.ffn_norm;
@@ -311,7 +320,13 @@ static void build_program(b200_engine* e) {
             att.y = counters;
             ops.push_back(att);
             gu.xsrc = kXResidAcc; gu.x = bufA; gu.acc_in = e->o_acc; gu.xout = bufB;
-            gu.zero = reinterpret_cast<float*>(counters); gu.n_zero = n_cnt;   // all o items have passed their waits
+            gu.zero2 = reinterpret_cast<float*>(counters); gu.n_zero2 = n_cnt;   // all waits on them have been passed
+            if (head_cnt) {
+                ops[ops.size() - 2].head_cnt = head_cnt;   // the qkv op pushed above releases, ...
+                ops[ops.size() - 2].no_barrier = 1;
+                ops.back().head_cnt = head_cnt;            // ... the kOpAttnO op's attention items wait
+                if (l >= 1) { gu.zero = acc(l - 1); gu.n_zero = n_acc; }
+            }
         } else {
             StepOp o{};
             o.type = kOpGemv; o.epi = kEpiResidual; o.xsrc = kXCombine; o.N = H; o.K = e->h * e->d; o.units = (H + 1) / 2;
