@@ -692,6 +692,17 @@ __device__ __noinline__ uint32_t gemv_consume(const StepOp& op, const StepParams
     if (traced && lane == 0) *starved = 0;
 #endif
 
+    if (epi == kEpiRopeKV) {
+        // cos / sin of this step's rotary angles, once per CTA into shared memory (qkv_bias_and_RoPE.cu:29-46): the
+        // epilogue used to fetch rope_den[i] from global memory on lane 0 of every row pair - an L2 round trip with
+        // the warp's next stage waiting behind it
+        for (int i = tid_o; i < (p.rotary_dim >> 1); i += kStepConsumers) {
+            const float ang = (float)(step - 1) / p.rope_den[i];
+            scratch[2 * i] = cosf(ang);
+            scratch[2 * i + 1] = sinf(ang);
+        }
+        consumers_sync();
+    }
     for (int g = 0; g < ngroups; ++g) {
         const int unit = u0 + g * gsz + warp;
         const bool active = warp < gsz && unit < u1;
@@ -781,9 +792,8 @@ __device__ __noinline__ uint32_t gemv_consume(const StepOp& op, const StepParams
                     const int qkv_heads = p.head_num + 2 * p.kv_head_num;
                     float c = 1.f, sn = 0.f;
                     if (head < p.head_num + p.kv_head_num && i < (p.rotary_dim >> 1)) {
-                        const float ang = (float)(step - 1) / p.rope_den[i];
-                        c = cosf(ang);
-                        sn = sinf(ang);
+                        c = scratch[2 * i];   // staged once per op, below (scratch is only 4-byte aligned)
+                        sn = scratch[2 * i + 1];
                     }
 #pragma unroll
                     for (int b = 0; b < NB; ++b) {

@@ -69,3 +69,18 @@ if per_layer == 3:   # anatomy of the attention + o projection op (CTA 0): atten
     print("o block stages landed at the start of the o phase:", t[idx, 2].mean())
     print(f"attn_o anatomy: attention {np.mean(a_done - start) / 1e3:.2f} us, wait + merge {np.mean(merged - a_done) / 1e3:.2f} us, "
           f"o block stages {np.mean(t[idx, 3] - merged) / 1e3:.2f} us, reds + return {np.mean(t[idx, 0] - t[idx, 3]) / 1e3:.2f} us")
+
+# per-CTA lateness (mean over layers of: op-done stamp minus the earliest CTA's), to see whether the skew is systematic
+if len(sys.argv) > 3 and sys.argv[3] == "cta":
+    for j, kname in enumerate(names):
+        d = dn[j:n_layer_ops:per_layer].astype(np.float64)
+        late = (d - d.min(axis=1, keepdims=True)).mean(axis=0) / 1e3
+        order = np.argsort(-late)
+        print(f"{kname}: lateness us by CTA, worst 12:", [(int(c), round(float(late[c]), 2)) for c in order[:12]])
+        print(f"{kname}: best 8:", [(int(c), round(float(late[c]), 2)) for c in order[-8:]])
+        print(f"{kname}: mean {late.mean():.2f} max {late.max():.2f}; by CTA index block of 16:",
+              [round(float(late[i:i + 16].mean()), 2) for i in range(0, len(late), 16)])
+        units = [(6144 * (c + 1)) // 148 - (6144 * c) // 148 for c in range(148)] if kname == "qkv" else None
+        if units:
+            print("qkv: mean lateness of CTAs with 42 row pairs:", round(float(np.mean([late[c] for c in range(148) if units[c] == 42])), 2),
+                  "with 41:", round(float(np.mean([late[c] for c in range(148) if units[c] == 41])), 2))
