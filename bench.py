@@ -1057,12 +1057,12 @@ def main():
         achieved = step_bytes / (per_launch_ms * 1e-3) / 1e9
         traffic = None
         try:   # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the committed ncu capture
-            traffic = float(json.load(open(os.path.join(ROOT, "profiles", "r01_decode_step_traffic.json")))["dram_bytes_per_launch"])
+            traffic = float(json.load(open(os.path.join(ROOT, "profiles", "r02_decode_step_traffic.json")))["dram_bytes_per_launch"])
         except Exception:
             pass
         roof = {"bound": "hbm", "kernel": "decode_step_kernel", "achieved": round(achieved, 1), "peak": peak,
                 "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": traffic,
-                "traffic_unit": "bytes/launch (ncu --set full, profiles/r01_decode_step_full.md)" if traffic else None,
+                "traffic_unit": "bytes/launch (ncu --set full, profiles/r02_decode_step_full.md)" if traffic else None,
                 "per_launch_us": round(per_launch_ms * 1e3, 1), "algorithmic_bytes_per_launch": int(step_bytes),
                 "peak_source": peak_src,
                 "note": "persistent whole-step kernel: one cooperative launch per token; per-launch time = the "
