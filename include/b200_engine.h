@@ -67,6 +67,14 @@ enum {
     B200_W_LM_HEAD = 8
 };
 
+/* creation flags for b200_engine_create_ex */
+#define B200_ENGINE_KV_FP8 1u  /* KV cache in fp8 e4m3 with one fp32 scale per cached row (replaces the T-typed
+                                * [layers,B,hk,max_seq,d] caches of llama.cpp:77-78). fp16 models, head size 128,
+                                * head_num / kv_head_num in {1,2,4}. A row is rounded once, when it enters the cache; decode
+                                * runs the reference launch order (RoPE -> b200_kv_append_fp8 -> b200_decode_attention_fp8);
+                                * only the FIRST prompt pass of a sequence is supported. Not bit-compatible with the fp16
+                                * cache: tests/test_kv_fp8_gpu.py pins it to the oracle run on the same rounded rows. */
+
 /* mode flags for b200_engine_set_mode */
 #define B200_ENGINE_FUSED 1u   /* fused GEMV prologues/epilogues (default)                    */
 #define B200_ENGINE_GRAPH 2u   /* CUDA-graph replay of the whole step (default)               */
@@ -107,6 +115,11 @@ size_t b200_p2p_max_message_bytes(const b200_p2p* c);
 void b200_p2p_destroy(b200_p2p* c);
 
 b200_engine* b200_engine_create(const b200_model_config* cfg, int batch);
+/* the same with B200_ENGINE_KV_* creation flags (0 = b200_engine_create) */
+b200_engine* b200_engine_create_ex(const b200_model_config* cfg, int batch, unsigned flags);
+int b200_engine_kv_is_fp8(const b200_engine* e);
+/* fp8 cache only: K and V dequantised to fp16 into caller DEVICE buffers [layers, B, hk, max_seq, d] (tests) */
+int b200_engine_kv_dequant(b200_engine* e, void* k_dst, void* v_dst);
 void b200_engine_destroy(b200_engine* e);
 const char* b200_engine_last_error(void);
 

@@ -259,6 +259,30 @@ int b200_decode_attention_static(const void* qkv, void* k_cache_layer, void* v_c
                                  int batch, int head_num, int kv_head_num, int head_size,
                                  int max_seq_len, int step, int append_kv, int dtype, void* stream);
 
+/* ------------------------------------------------------------------------------------
+ * fp8 (e4m3) KV cache, SURVEY 8 f4 - the evolution of the reference's T-typed cache
+ * [layers,B,hk,max_seq,d] (src/models/llama/llama.cpp:77-78,102-103): one byte per element + one fp32 scale
+ * per cached row ([B, hk, max_seq] per layer), value = scale * e4m3, scale = amax(row) / 448 fixed at append.
+ * fp16 models, head size 128, head_num / kv_head_num in {1,2,4}.
+ *   b200_kv_append_fp8       the new token's rotated k, v (qkv [batch, h+2hk, d]) -> cache row step-1
+ *   b200_decode_attention_fp8 launchDecoderMaskedMHA (fused_decoder_self_attention.cu:317) over rows [0, step) of
+ *                            that cache; the new row must already be there; workspace as b200_decode_attention
+ *   b200_kv_quantize_fp8     rows t < n_rows[b] of an fp16 slice [batch, hk, src_seq, d] -> cache rows dst_row0[b] + t
+ *                            (the prompt pass: launchConcatKVCache concat_past_kv.cu:103 with quantisation)
+ *   b200_kv_dequant_fp8      slice back to fp16 (tests)
+ * step_dev (DEVICE int, may be NULL) overrides step; step_stride 1 = one entry per sequence (ragged batch).
+ * ------------------------------------------------------------------------------------ */
+int b200_kv_append_fp8(const void* qkv, void* k_cache8, void* v_cache8, float* k_scale, float* v_scale, int batch,
+                       int head_num, int kv_head_num, int head_size, int max_seq_len, int step, const int* step_dev,
+                       int step_stride, void* stream);
+int b200_decode_attention_fp8(const void* qkv, const void* k_cache8, const void* v_cache8, const float* k_scale,
+                              const float* v_scale, void* out, void* workspace, size_t workspace_bytes, int batch,
+                              int head_num, int kv_head_num, int head_size, int max_seq_len, int step,
+                              const int* step_dev, int step_stride, void* stream);
+int b200_kv_quantize_fp8(const void* src, void* dst8, float* scale, const int* n_rows, const int* dst_row0, int batch,
+                         int kv_head_num, int src_seq, int max_seq_len, int head_size, int max_rows, void* stream);
+int b200_kv_dequant_fp8(const void* src8, const float* scale, void* dst, size_t rows, int head_size, void* stream);
+
 /* Prefill attention without materialising scores / mask / repeated KV (replaces
  * context_attention.cpp:136-161: RepeatKV + QK^T + ScaleMaskSoftmax + PV + transpose):
  * q [batch, head_num, seq_len, head_size]; cache layer slice as above;

@@ -13,6 +13,8 @@
 //    kUnroll loads in flight per lane; dot products reduce with warp shuffles across the PR lanes;
 //  * every lane group runs its own online softmax (m, l, o[]) in fp32, merged by shuffles, then
 //    across warps through shared memory, then across splits by the combine kernel.
+#include <cuda_fp8.h>
+
 #include "common.cuh"
 #include "launch_count.h"
 
@@ -32,6 +34,8 @@ struct AttnParams {
     const int* step_dev;
     int step_stride;  // 0: *step_dev is the one step all sequences share; 1: step_dev[b] (ragged batch)
     int append_kv;
+    const float* k_scale;   // fp8 cache only: one scale per cached row, [B, hk, max_seq]
+    const float* v_scale;
 };
 
 // fp32 data keeps the accurate expf (1e-5 tolerance); half data uses the MUFU fast path
@@ -199,6 +203,197 @@ decode_attn_split_kernel(const AttnParams p) {
         if (splits == 1) {
             reinterpret_cast<T*>(p.out)[((size_t)b * p.head_num + head) * D + e] =
                 DT<T>::from_f(O / (L + 1e-6f));
+        } else {
+            const size_t slot = ((size_t)b * p.head_num + head) * splits + blockIdx.y;
+            p.part_o[slot * D + e] = O;
+            if (e == 0) { p.part_ml[slot * 2] = M; p.part_ml[slot * 2 + 1] = L; }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// The same split-KV kernel over an fp8 (e4m3) cache with one fp32 scale per row (kv_fp8.cu): head size 128, a key row
+// is 128 B = eight 16-byte packets of 16 elements, eight lanes own a row, four rows per warp-wide load. q stays fp16;
+// a cache element is widened to half exactly (e4m3 is a subset of fp16) and enters the same fp32 FMA; the row scale
+// multiplies the finished dot product (K) or the softmax weight (V). No append here: kv_append_fp8 runs before it.
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t fp8x2_to_half2(unsigned short v) {
+    const __half2_raw h = __nv_cvt_fp8x2_to_halfraw2((__nv_fp8x2_storage_t)v, __NV_E4M3);
+    return *reinterpret_cast<const uint32_t*>(&h);
+}
+
+template <int G, bool FULL>
+__device__ __forceinline__ void fp8_tile(const unsigned char* kc, const unsigned char* vc, const float* ksc, const float* vsc,
+                                         const Pack16 (&q)[G][2], float (&m)[G], float (&l)[G], float (&o)[G][16], const int base,
+                                         const int k1, const int pi, const int ks, const float scale) {
+    constexpr int D = 128, PR = 8, E = 16, KPI = 32 / PR;
+        Pack16 kp[kUnroll], vp[kUnroll];
+        float ks_[kUnroll], vs_[kUnroll];
+        bool ok[kUnroll];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            const int key = FULL ? base + u * KPI + ks : min(base + u * KPI + ks, k1 - 1);   // rows past the end re-read the last row
+            ok[u] = FULL || base + u * KPI + ks < k1;
+            kp[u] = ld16_stream(kc + (size_t)key * D + pi * E);
+            ks_[u] = __ldg(ksc + key);
+        }
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            const int key = FULL ? base + u * KPI + ks : min(base + u * KPI + ks, k1 - 1);
+            vp[u] = ld16_stream(vc + (size_t)key * D + pi * E);
+            vs_[u] = __ldg(vsc + key);
+        }
+        float s[G][kUnroll];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            uint32_t kh[8];   // the packet as eight half2
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                kh[2 * i] = fp8x2_to_half2((unsigned short)(kp[u].w[i] & 0xffffu));
+                kh[2 * i + 1] = fp8x2_to_half2((unsigned short)(kp[u].w[i] >> 16));
+            }
+#pragma unroll
+            for (int g = 0; g < G; ++g) {
+                float d = 0.f;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const uint32_t qw = q[g][i >> 2].w[i & 3];
+                    d = fma_h((uint16_t)(kh[i] & 0xffffu), (uint16_t)(qw & 0xffffu), d);
+                    d = fma_h((uint16_t)(kh[i] >> 16), (uint16_t)(qw >> 16), d);
+                }
+#pragma unroll
+                for (int off = PR >> 1; off > 0; off >>= 1) d += __shfl_xor_sync(0xffffffffu, d, off);
+                s[g][u] = (FULL || ok[u]) ? d * ks_[u] * scale : -INFINITY;
+            }
+        }
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+            float mn = m[g];
+#pragma unroll
+            for (int u = 0; u < kUnroll; ++u) mn = fmaxf(mn, s[g][u]);
+            if (FULL || mn != -INFINITY) {
+                const float corr = exp_guard(m[g], mn);
+                l[g] *= corr;
+#pragma unroll
+                for (int e = 0; e < E; ++e) o[g][e] *= corr;
+                m[g] = mn;
+#pragma unroll
+                for (int u = 0; u < kUnroll; ++u) {
+                    if (FULL || ok[u]) {
+                        const float pr = __expf(s[g][u] - mn);
+                        l[g] += pr;
+                        // the softmax weight times the row scale enters the mixed-precision FMA as a half (11 bits: far
+                        // below the cache's own 4-bit rounding); the e4m3 element widens to half exactly
+                        const uint16_t pv = __half_as_ushort(__float2half_rn(pr * vs_[u]));
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const uint32_t lo = fp8x2_to_half2((unsigned short)(vp[u].w[i] & 0xffffu));
+                            const uint32_t hi = fp8x2_to_half2((unsigned short)(vp[u].w[i] >> 16));
+                            o[g][4 * i] = fma_h((uint16_t)(lo & 0xffffu), pv, o[g][4 * i]);
+                            o[g][4 * i + 1] = fma_h((uint16_t)(lo >> 16), pv, o[g][4 * i + 1]);
+                            o[g][4 * i + 2] = fma_h((uint16_t)(hi & 0xffffu), pv, o[g][4 * i + 2]);
+                            o[g][4 * i + 3] = fma_h((uint16_t)(hi >> 16), pv, o[g][4 * i + 3]);
+                        }
+                    }
+                }
+            }
+        }
+}
+
+template <int G>
+__global__ void __launch_bounds__(kAttnWarps * 32)
+decode_attn_split_fp8_kernel(const AttnParams p) {
+    constexpr int D = 128, PR = 8, E = 16, KPI = 32 / PR;
+    extern __shared__ float sm[];  // [kAttnWarps][G][2 + D]
+
+    pdl_wait();
+    const int bh = blockIdx.x;
+    const int b = bh / p.kv_head_num, kvh = bh - b * p.kv_head_num;
+    const int step = p.step_dev ? p.step_dev[b * p.step_stride] : p.step;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int pi = lane % PR, ks = lane / PR;
+    const int qkv_heads = p.head_num + 2 * p.kv_head_num;
+    const __half* tok = reinterpret_cast<const __half*>(p.qkv) + (size_t)b * qkv_heads * D;
+    const size_t head_rows = ((size_t)b * p.kv_head_num + kvh) * p.max_seq_len;
+    const unsigned char* kc = reinterpret_cast<const unsigned char*>(p.k_cache) + head_rows * D;
+    const unsigned char* vc = reinterpret_cast<const unsigned char*>(p.v_cache) + head_rows * D;
+    const float* ksc = p.k_scale + head_rows;
+    const float* vsc = p.v_scale + head_rows;
+
+    const int splits = gridDim.y;
+    const int per = (step + splits - 1) / splits;
+    const int k0 = blockIdx.y * per;
+    const int k1 = min(step, k0 + per);
+
+    Pack16 q[G][2];   // the lane's 16 elements of every query head of the group
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+        q[g][0] = ld16(tok + (size_t)(kvh * G + g) * D + pi * E);
+        q[g][1] = ld16(tok + (size_t)(kvh * G + g) * D + pi * E + 8);
+    }
+    const float scale = rsqrtf((float)D);
+
+    float m[G], l[G], o[G][E];
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+        m[g] = -INFINITY;
+        l[g] = 0.f;
+#pragma unroll
+        for (int e = 0; e < E; ++e) o[g][e] = 0.f;
+    }
+
+    for (int base = k0 + warp * KPI * kUnroll; base < k1; base += kAttnWarps * KPI * kUnroll) {
+        // whole tiles (every row of the 16 this warp loads exists) take a branch-free path: no per-row predicates, and
+        // the shuffles stay plain SHFLs instead of divergence-safe collectives
+        if (base + KPI * kUnroll <= k1) fp8_tile<G, true>(kc, vc, ksc, vsc, q, m, l, o, base, k1, pi, ks, scale);
+        else fp8_tile<G, false>(kc, vc, ksc, vsc, q, m, l, o, base, k1, pi, ks, scale);
+    }
+
+    // merge the KPI lane groups of the warp
+#pragma unroll
+    for (int off = PR; off < 32; off <<= 1) {
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+            const float mo = __shfl_xor_sync(0xffffffffu, m[g], off);
+            const float lo = __shfl_xor_sync(0xffffffffu, l[g], off);
+            const float M = fmaxf(m[g], mo);
+            const float a = exp_guard(m[g], M), bb = exp_guard(mo, M);
+            l[g] = l[g] * a + lo * bb;
+#pragma unroll
+            for (int e = 0; e < E; ++e) {
+                const float oo = __shfl_xor_sync(0xffffffffu, o[g][e], off);
+                o[g][e] = o[g][e] * a + oo * bb;
+            }
+            m[g] = M;
+        }
+    }
+    if (ks == 0) {
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+            float* dst = sm + ((size_t)warp * G + g) * (2 + D);
+            if (pi == 0) { dst[0] = m[g]; dst[1] = l[g]; }
+#pragma unroll
+            for (int e = 0; e < E; ++e) dst[2 + pi * E + e] = o[g][e];
+        }
+    }
+    __syncthreads();
+    pdl_launch_dependents();
+    for (int idx = threadIdx.x; idx < G * D; idx += blockDim.x) {
+        const int g = idx / D, e = idx - g * D;
+        float M = -INFINITY;
+#pragma unroll
+        for (int w = 0; w < kAttnWarps; ++w) M = fmaxf(M, sm[((size_t)w * G + g) * (2 + D)]);
+        float L = 0.f, O = 0.f;
+#pragma unroll
+        for (int w = 0; w < kAttnWarps; ++w) {
+            const float* src = sm + ((size_t)w * G + g) * (2 + D);
+            const float a = exp_guard(src[0], M);
+            L += src[1] * a;
+            O += src[2 + e] * a;
+        }
+        const int head = kvh * G + g;
+        if (splits == 1) {
+            reinterpret_cast<__half*>(p.out)[((size_t)b * p.head_num + head) * D + e] = __float2half_rn(O / (L + 1e-6f));
         } else {
             const size_t slot = ((size_t)b * p.head_num + head) * splits + blockIdx.y;
             p.part_o[slot * D + e] = O;
@@ -522,4 +717,49 @@ extern "C" int b200_decode_attention_static(const void* qkv, void* k_cache_layer
     return decode_attention_impl(qkv, k_cache_layer, v_cache_layer, out, scratch,
                                  (size_t)B200_DECODE_ATTENTION_STATIC_MAX_BYTES, batch, head_num, kv_head_num,
                                  head_size, max_seq_len, step, nullptr, 0, append_kv, dtype, stream);
+}
+
+// ------------------------------------------------------------------------------------------
+// fp8 KV cache (kv_fp8.cu): attention over rows [0, step) of an e4m3 cache with one fp32 scale per row. fp16 q / out,
+// head size 128, h/hk in {1, 2, 4}. The new token's row must already be in the cache (b200_kv_append_fp8).
+// ------------------------------------------------------------------------------------------
+extern "C" int b200_decode_attention_fp8(const void* qkv, const void* k_cache8, const void* v_cache8, const float* k_scale,
+                                         const float* v_scale, void* out, void* workspace, size_t workspace_bytes,
+                                         int batch, int head_num, int kv_head_num, int head_size, int max_seq_len,
+                                         int step, const int* step_dev, int step_stride, void* stream) {
+    B200_RETURN_IF(!qkv || !k_cache8 || !v_cache8 || !k_scale || !v_scale || !out, B200_EINVAL);
+    B200_RETURN_IF(batch <= 0 || head_num <= 0 || kv_head_num <= 0 || max_seq_len <= 0 || head_num % kv_head_num != 0,
+                   B200_EINVAL);
+    B200_RETURN_IF(step < 1 || step > max_seq_len, B200_EINVAL);
+    const int G = head_num / kv_head_num;
+    B200_RETURN_IF(head_size != 128 || (G != 1 && G != 2 && G != 4), B200_EUNSUPPORTED);
+    auto al = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15u) == 0; };
+    B200_RETURN_IF(!al(qkv) || !al(k_cache8) || !al(v_cache8), B200_EINVAL);
+    AttnParams p{};
+    p.qkv = qkv; p.k_cache = const_cast<void*>(k_cache8); p.v_cache = const_cast<void*>(v_cache8); p.out = out;
+    p.k_scale = k_scale; p.v_scale = v_scale;
+    p.batch = batch; p.head_num = head_num; p.kv_head_num = kv_head_num; p.head_size = head_size;
+    p.max_seq_len = max_seq_len; p.step = step; p.step_dev = step_dev; p.step_stride = step_stride; p.append_kv = 0;
+    const int splits = attn_pick_splits(batch, kv_head_num, step, G);
+    if (splits > 1) {
+        const size_t ml = (size_t)batch * head_num * splits * 2 * sizeof(float);
+        const size_t need = ((ml + 255) & ~(size_t)255) + (size_t)batch * head_num * splits * head_size * sizeof(float);
+        B200_RETURN_IF(!workspace || workspace_bytes < need, B200_EWORKSPACE);
+        p.part_ml = reinterpret_cast<float*>(workspace);
+        p.part_o = reinterpret_cast<float*>((char*)workspace + ((ml + 255) & ~(size_t)255));
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    const dim3 grid(batch * kv_head_num, splits), block(kAttnWarps * 32);
+    cudaError_t e;
+    if (G == 1) e = launch_k(decode_attn_split_fp8_kernel<1>, grid, block, (size_t)kAttnWarps * 1 * (2 + 128) * sizeof(float), s, true, p);
+    else if (G == 2) e = launch_k(decode_attn_split_fp8_kernel<2>, grid, block, (size_t)kAttnWarps * 2 * (2 + 128) * sizeof(float), s, true, p);
+    else e = launch_k(decode_attn_split_fp8_kernel<4>, grid, block, (size_t)kAttnWarps * 4 * (2 + 128) * sizeof(float), s, true, p);
+    count_launch();
+    if (e != cudaSuccess) return (int)e;
+    if (splits > 1) {
+        e = launch_k(decode_attn_combine_kernel<__half>, dim3(batch * head_num), dim3(128), 0, s, true,
+                     (const float*)p.part_ml, (const float*)p.part_o, (__half*)p.out, splits, head_size);
+        count_launch();
+    }
+    return (int)e;
 }

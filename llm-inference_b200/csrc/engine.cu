@@ -35,6 +35,9 @@ static int fail(const std::string& m, int code = B200_EINVAL) {
         if (rc_ != 0) return fail(std::string(#call) + " failed", rc_); \
     } while (0)
 
+int kv_fill_fp8(void* cache8, float* scale, size_t rows_total, int max_seq, int len, int d, uint64_t seed, float amp,
+                cudaStream_t s);   // kv_fp8.cu
+
 struct LayerW {
     void *attn_norm, *qkv, *o, *ffn_norm, *gate_up, *down;
 };
@@ -56,6 +59,11 @@ struct b200_engine {
     void *embed = nullptr, *final_norm = nullptr, *lm_head = nullptr;
     char *k_cache = nullptr, *v_cache = nullptr;
     size_t kv_bytes_each = 0, layer_kv_elems = 0;
+    // fp8 KV cache (B200_ENGINE_KV_FP8, kv_fp8.cu): one byte per cached element + one fp32 scale per cached row
+    bool kv_fp8 = false;
+    size_t kv_esz = 0;            // bytes per cached element (esz, or 1)
+    float *k_scale = nullptr, *v_scale = nullptr;   // [layers, B, hk, max_seq]
+    size_t layer_kv_rows = 0;
     char* act_arena = nullptr;
     void *hidden, *residual, *qkv, *attn, *act, *gate_up, *logits, *partial;
     int *ids_cur, *ids_next, *step_dev;
@@ -402,7 +410,18 @@ static int refresh_down_t(b200_engine* e) {
 extern "C" const char* b200_engine_last_error(void) { return g_err.c_str(); }
 
 extern "C" b200_engine* b200_engine_create(const b200_model_config* c, int batch) {
+    return b200_engine_create_ex(c, batch, 0u);
+}
+
+extern "C" b200_engine* b200_engine_create_ex(const b200_model_config* c, int batch, unsigned flags) {
     if (!c || batch < 1 || batch > c->max_batch) { fail("bad config / batch"); return nullptr; }
+    if (flags & B200_ENGINE_KV_FP8) {
+        const int G = c->kv_head_num > 0 ? c->head_num / c->kv_head_num : 0;
+        if (c->dtype != B200_F16 || c->head_size != 128 || (G != 1 && G != 2 && G != 4)) {
+            fail("B200_ENGINE_KV_FP8 needs fp16, head size 128 and head_num / kv_head_num in {1, 2, 4}");
+            return nullptr;
+        }
+    }
     if (c->tp_size < 1 || c->head_num % c->tp_size || c->kv_head_num % c->tp_size ||
         c->inter_size % c->tp_size || c->head_num % c->kv_head_num) {
         fail("heads / inter size not divisible by tp_size");
@@ -455,8 +474,18 @@ extern "C" b200_engine* b200_engine_create(const b200_model_config* c, int batch
     e->final_norm = e->arena + o_fnorm;
     e->lm_head = e->arena + o_head;
     // ---- KV cache [layers, B, hk, max_seq, d] x2, 64-bit sizes (reference D21)
+    e->kv_fp8 = (flags & B200_ENGINE_KV_FP8) != 0;
+    e->kv_esz = e->kv_fp8 ? 1 : es;
     e->layer_kv_elems = (size_t)batch * e->hk * c->max_seq_len * e->d;
-    e->kv_bytes_each = e->layer_kv_elems * c->num_layers * es;
+    e->layer_kv_rows = (size_t)batch * e->hk * c->max_seq_len;
+    e->kv_bytes_each = e->layer_kv_elems * c->num_layers * e->kv_esz;
+    if (e->kv_fp8) {
+        const size_t sb = e->layer_kv_rows * c->num_layers * sizeof(float);
+        if ((err = cudaMalloc(&e->k_scale, sb)) != cudaSuccess) return fail_free("cudaMalloc(K scales)", err);
+        if ((err = cudaMalloc(&e->v_scale, sb)) != cudaSuccess) return fail_free("cudaMalloc(V scales)", err);
+        cudaMemset(e->k_scale, 0, sb);
+        cudaMemset(e->v_scale, 0, sb);
+    }
     if ((err = cudaMalloc(&e->k_cache, e->kv_bytes_each)) != cudaSuccess) return fail_free("cudaMalloc(K)", err);
     if ((err = cudaMalloc(&e->v_cache, e->kv_bytes_each)) != cudaSuccess) return fail_free("cudaMalloc(V)", err);
     cudaMemset(e->k_cache, 0, e->kv_bytes_each);
@@ -497,7 +526,7 @@ extern "C" b200_engine* b200_engine_create(const b200_model_config* c, int batch
     const int ref_step0 = 1;  // reference `step` of the first token (tokens in cache + 1)
     cudaMemcpy(e->step_dev, &ref_step0, sizeof(int), cudaMemcpyHostToDevice);
     cudaDeviceSynchronize();
-    build_program(e);
+    if (!e->kv_fp8) build_program(e);   // the persistent step kernel reads and appends an fp16 cache
     // default launch order by batch (measured, tools/order_sweep.sh + route_sweep.sh, 7B fp16, ms per step at
     // context 512 / 4096; GEMV = the tensor-core consumer, gemv.cu):
     //   batch 2: persistent 3.53 / 4.72, fused GEMV graph 3.30 / 4.24, reference launch order graph 3.49 / 4.42
@@ -526,6 +555,8 @@ extern "C" void b200_engine_destroy(b200_engine* e) {
     cudaFree(e->arena);
     cudaFree(e->k_cache);
     cudaFree(e->v_cache);
+    cudaFree(e->k_scale);
+    cudaFree(e->v_scale);
     cudaFree(e->act_arena);
     delete e;
 }
@@ -534,7 +565,9 @@ extern "C" void b200_engine_destroy(b200_engine* e) {
 // accessors / weights
 // ------------------------------------------------------------------------------------------
 extern "C" size_t b200_engine_weight_bytes(const b200_engine* e) { return e ? e->arena_bytes : 0; }
-extern "C" size_t b200_engine_kv_bytes(const b200_engine* e) { return e ? 2 * e->kv_bytes_each : 0; }
+extern "C" size_t b200_engine_kv_bytes(const b200_engine* e) {
+    return e ? 2 * e->kv_bytes_each + (e->kv_fp8 ? 2 * e->layer_kv_rows * e->cfg.num_layers * sizeof(float) : 0) : 0;
+}
 extern "C" size_t b200_engine_weight_elems(const b200_engine* e, int slot) { return e ? slot_elems(e, slot) : 0; }
 extern "C" void* b200_engine_stream(b200_engine* e) { return e ? (void*)e->stream : nullptr; }
 extern "C" void* b200_engine_logits(b200_engine* e) { return e->logits; }
@@ -543,6 +576,16 @@ extern "C" void* b200_engine_hidden(b200_engine* e) { return e->hidden; }
 extern "C" void* b200_engine_k_cache(b200_engine* e) { return e->k_cache; }
 extern "C" void* b200_engine_v_cache(b200_engine* e) { return e->v_cache; }
 extern "C" int b200_engine_get_step(const b200_engine* e) { return e->step; }
+extern "C" int b200_engine_kv_is_fp8(const b200_engine* e) { return e && e->kv_fp8 ? 1 : 0; }
+/* fp8 cache only: the whole K and V caches dequantised to fp16 into caller DEVICE buffers [layers, B, hk, max_seq, d] */
+extern "C" int b200_engine_kv_dequant(b200_engine* e, void* k_dst, void* v_dst) {
+    if (!e || !e->kv_fp8 || !k_dst || !v_dst) return B200_EINVAL;
+    const size_t rows = e->layer_kv_rows * e->cfg.num_layers;
+    RC(b200_kv_dequant_fp8(e->k_cache, e->k_scale, k_dst, rows, e->d, e->stream));
+    RC(b200_kv_dequant_fp8(e->v_cache, e->v_scale, v_dst, rows, e->d, e->stream));
+    CU(cudaStreamSynchronize(e->stream));
+    return B200_OK;
+}
 extern "C" void* b200_engine_weight_ptr(b200_engine* e, int slot, int layer) { return e ? slot_ptr(e, slot, layer) : nullptr; }
 extern "C" int b200_engine_launches_per_step(const b200_engine* e) { return e->launches_per_step; }
 extern "C" int b200_engine_step_trace(b200_engine* e, unsigned long long* host_dst, int max_entries) {
@@ -643,7 +686,10 @@ extern "C" int b200_engine_get_weight(b200_engine* e, int slot, int layer, void*
 extern "C" int b200_engine_fill_kv_random(b200_engine* e, int len, uint64_t seed, float amp) {
     if (!e || len < 0 || len >= e->cfg.max_seq_len) return fail("fill_kv: len out of range");
     const size_t rows = (size_t)e->cfg.num_layers * e->batch * e->hk;
-    if (len > 0) {
+    if (len > 0 && e->kv_fp8) {
+        RC(kv_fill_fp8(e->k_cache, e->k_scale, rows, e->cfg.max_seq_len, len, e->d, seed * 2 + 1, amp, e->stream));
+        RC(kv_fill_fp8(e->v_cache, e->v_scale, rows, e->cfg.max_seq_len, len, e->d, seed * 2 + 2, amp, e->stream));
+    } else if (len > 0) {
         const size_t n = rows * (size_t)len * e->d;
         size_t blocks = (n + 255) / 256;
         if (blocks > 148 * 32) blocks = 148 * 32;
@@ -738,15 +784,16 @@ static int enqueue_step(b200_engine* e) {
     // step instead of once per 8-token tile).
     // fp16 batches of 5..8 also take the tensor-core path: eight x-rows of K = 11008 crowd the GEMV's weight ring out
     // of shared memory (measured at batch 8 x KV 4096: 12.0 ms per step fused vs the figure in DESIGN §4c)
-    const bool fused = (e->mode & B200_ENGINE_FUSED) && B <= (dt == B200_F16 && !tp ? 4 : B200_GEMV_MAX_TOKENS);
+    // (the fused qkv GEMV appends fp16 rows in its epilogue: an fp8 cache takes the reference launch order)
+    const bool fused = (e->mode & B200_ENGINE_FUSED) && B <= (dt == B200_F16 && !tp ? 4 : B200_GEMV_MAX_TOKENS) && !e->kv_fp8;
     auto linear = [&](const void* x, const void* W, void* y, int N, int K) {
         return b200_linear(x, W, nullptr, y, B, N, K, 1, dt, e->lin_ws, e->lin_ws_bytes, s);
     };
     RC(b200_embedding(e->ids_cur, e->embed, e->hidden, B, H, e->V, dt, s));
     for (int l = 0; l < e->cfg.num_layers; ++l) {
         LayerW& w = e->layers[l];
-        void* kc = e->k_cache + (size_t)l * e->layer_kv_elems * e->esz;
-        void* vc = e->v_cache + (size_t)l * e->layer_kv_elems * e->esz;
+        void* kc = e->k_cache + (size_t)l * e->layer_kv_elems * e->kv_esz;
+        void* vc = e->v_cache + (size_t)l * e->layer_kv_elems * e->kv_esz;
         if (fused) {
             RC(gemv(e, e->hidden, w.qkv, e->qkv, e->qkv_n, H, B200_GEMV_NORM | B200_GEMV_ROPE_KV, w.attn_norm, l));
             if (e->ragged)
@@ -780,7 +827,21 @@ static int enqueue_step(b200_engine* e) {
             // the reference's launch sequence, one kernel per launch* (self_decoder.cpp:53-85)
             RC(b200_rmsnorm(e->hidden, e->residual, w.attn_norm, B, H, e->cfg.rms_eps, dt, s));
             RC(linear(e->hidden, w.qkv, e->qkv, e->qkv_n, H));
-            if (e->ragged) {   // per-sequence positions and key counts; ref_step (the longest) only sizes the launch
+            if (e->kv_fp8) {   // RoPE, then the new rows enter the fp8 cache (quantised once), then attention over the cache
+                float* ksc = e->k_scale + (size_t)l * e->layer_kv_rows;
+                float* vsc = e->v_scale + (size_t)l * e->layer_kv_rows;
+                const int* sd = e->ragged ? e->seq_steps : e->step_dev;
+                const int stride = e->ragged ? 1 : 0;
+                if (e->ragged)
+                    RC(b200_rope_decode_ragged(e->qkv, B, e->h, e->hk, e->d, e->seq_steps, e->cfg.rotary_dim,
+                                               e->cfg.rotary_base, e->rope_den, dt, s));
+                else
+                    RC(b200_rope_decode_tab(e->qkv, B, e->h, e->hk, e->d, ref_step, e->step_dev, e->cfg.rotary_dim,
+                                            e->cfg.rotary_base, e->rope_den, dt, s));
+                RC(b200_kv_append_fp8(e->qkv, kc, vc, ksc, vsc, B, e->h, e->hk, e->d, e->cfg.max_seq_len, ref_step, sd, stride, s));
+                RC(b200_decode_attention_fp8(e->qkv, kc, vc, ksc, vsc, e->attn, e->attn_ws, e->attn_ws_bytes, B, e->h, e->hk,
+                                             e->d, e->cfg.max_seq_len, ref_step, sd, stride, s));
+            } else if (e->ragged) {   // per-sequence positions and key counts; ref_step (the longest) only sizes the launch
                 RC(b200_rope_decode_ragged(e->qkv, B, e->h, e->hk, e->d, e->seq_steps, e->cfg.rotary_dim,
                                            e->cfg.rotary_base, e->rope_den, dt, s));
                 RC(b200_decode_attention_ragged(e->qkv, kc, vc, e->attn, e->attn_ws, e->attn_ws_bytes, B, e->h, e->hk,
@@ -954,6 +1015,13 @@ static int prefill_impl(b200_engine* e, const int* ids_host, const int* lens_hos
     }
     const size_t o_lws = take(lin_ws + 256);
     const bool flash = dt == B200_F16 && e->d == 128 && !(getenv("B200_NO_TCGEN05") && getenv("B200_NO_TCGEN05")[0] == '1');
+    if (e->kv_fp8) {
+        if (!flash) return fail("fp8 KV cache: the prompt pass needs the flash context attention", B200_EUNSUPPORTED);
+        for (int b = 0; b < B; ++b)
+            if (hist_b[b] != 0)
+                return fail("fp8 KV cache: a prompt pass over an existing history is not supported (first pass only)",
+                            B200_EUNSUPPORTED);
+    }
     size_t o_mask = 0, o_kr = 0, o_vr = 0, o_sc = 0, o_pv = 0;
     if (!flash) {   // reference-order attention: dense mask, repeated KV, materialised scores
         o_mask = take((size_t)B * len * ctx * es);
@@ -1018,6 +1086,17 @@ static int prefill_impl(b200_engine* e, const int* ids_host, const int* lens_hos
         const size_t layer_off = (size_t)l * e->layer_kv_elems;
         RC(b200_rmsnorm(x, res, w.attn_norm, Nt, H, e->cfg.rms_eps, dt, s));
         RC(linear(x, w.qkv, qkv, e->qkv_n, H));
+        if (e->kv_fp8) {
+            // fp8 cache: this pass's k, v go to an fp16 scratch slice [B, hk, len, d] (history is empty, checked above), the
+            // flash kernel attends over it, and the rows enter the fp8 cache quantised once
+            RC(b200_qkv_bias_rope_to_cache(q, k, v, qkv, nullptr, pad, hists, B, len, Nt, e->h, e->hk, e->d, len,
+                                           e->cfg.rotary_dim, e->cfg.rotary_base, dt, s));
+            RC(b200_context_attention(q, k, v, att, pad, lens, hists, B, len, Nt, e->h, e->hk, e->d, len, dt, s));
+            RC(b200_kv_quantize_fp8(k, e->k_cache + layer_off, e->k_scale + (size_t)l * e->layer_kv_rows, lens, hists, B, e->hk,
+                                    len, e->cfg.max_seq_len, e->d, len, s));
+            RC(b200_kv_quantize_fp8(v, e->v_cache + layer_off, e->v_scale + (size_t)l * e->layer_kv_rows, lens, hists, B, e->hk,
+                                    len, e->cfg.max_seq_len, e->d, len, s));
+        } else {
         // bias/RoPE/transpose with ConcatKV folded in: k, v land in the cache rows directly
         RC(b200_qkv_bias_rope_to_cache(q, e->k_cache + layer_off * es, e->v_cache + layer_off * es, qkv, nullptr, pad, hists,
                                        B, len, Nt, e->h, e->hk, e->d, e->cfg.max_seq_len, e->cfg.rotary_dim,
@@ -1032,6 +1111,7 @@ static int prefill_impl(b200_engine* e, const int* ids_host, const int* lens_hos
             RC(b200_scale_mask_softmax(a + o_sc, a + o_mask, a + o_sc, B, e->h, len, ctx, 1.0f / sqrtf((float)e->d), dt, s));
             RC(b200_batched_gemm(a + o_sc, a + o_vr, a + o_pv, B * e->h, len, e->d, ctx, 0, dt, s));
             RC(b200_transpose_remove_padding(a + o_pv, att, pad, Nt, B, len, e->h, e->d, dt, s));
+        }
         }
         RC(linear(att, w.o, x, H, e->h * e->d));
         if (tp) RC(tp_sum(e, x, (size_t)Nt * H));

@@ -8,6 +8,7 @@ from . import capi
 W_ATTN_NORM, W_QKV, W_O, W_FFN_NORM, W_GATE_UP, W_DOWN, W_EMBED, W_FINAL_NORM, W_LM_HEAD = range(9)
 LAYER_SLOTS = (W_ATTN_NORM, W_QKV, W_O, W_FFN_NORM, W_GATE_UP, W_DOWN)
 MODE_FUSED, MODE_GRAPH, MODE_PERSISTENT = 1, 2, 4
+KV_FP8 = 1   # creation flag B200_ENGINE_KV_FP8
 
 
 class ModelConfig(C.Structure):
@@ -23,6 +24,9 @@ ALLREDUCE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p,
 _vp, _i = C.c_void_p, C.c_int
 ENGINE_PROTOTYPES = {
     "b200_engine_create": (_vp, [C.POINTER(ModelConfig), _i]),
+    "b200_engine_create_ex": (_vp, [C.POINTER(ModelConfig), _i, C.c_uint]),
+    "b200_engine_kv_is_fp8": (_i, [_vp]),
+    "b200_engine_kv_dequant": (_i, [_vp, _vp, _vp]),
     "b200_engine_destroy": (None, [_vp]),
     "b200_engine_last_error": (C.c_char_p, []),
     "b200_engine_weight_bytes": (C.c_size_t, [_vp]),
@@ -90,7 +94,7 @@ class Engine:
     """Owns one b200_engine on the current CUDA device."""
 
     def __init__(self, batch, max_seq_len, dtype=capi.F16, rms_eps=1e-5, rotary_base=10000.0,
-                 rotary_dim=None, tp_size=1, tp_rank=0, **shape):
+                 rotary_dim=None, tp_size=1, tp_rank=0, kv_fp8=False, **shape):
         cfg = ModelConfig()
         for k, v in shape.items():
             setattr(cfg, k, v)
@@ -101,7 +105,8 @@ class Engine:
         self.cfg, self.batch, self.dtype = cfg, batch, dtype
         self.np_dtype = np.float16 if dtype == capi.F16 else np.float32
         self.lib = _lib()
-        self.h = self.lib.b200_engine_create(C.byref(cfg), batch)
+        self.kv_fp8 = bool(kv_fp8)
+        self.h = self.lib.b200_engine_create_ex(C.byref(cfg), batch, KV_FP8 if kv_fp8 else 0)
         if not self.h:
             raise RuntimeError("[b200][ERROR] engine_create: " + self.lib.b200_engine_last_error().decode())
         self._cb = None
@@ -307,11 +312,16 @@ class Engine:
         return self._view(self.lib.b200_engine_weight_ptr(self.h, slot, layer), self.weight_shape(slot), td)
 
     def kv_caches(self):
-        """torch views [layers, batch, kv_heads(local), max_seq, d] of K and V"""
+        """torch views [layers, batch, kv_heads(local), max_seq, d] of K and V (fp8 cache: dequantised fp16 COPIES)"""
         import torch
         td = torch.float16 if self.dtype == capi.F16 else torch.float32
         c = self.cfg
         shape = (c.num_layers, self.batch, c.kv_head_num // c.tp_size, c.max_seq_len, c.head_size)
+        if self.kv_fp8:
+            k = torch.empty(shape, dtype=torch.float16, device="cuda")
+            v = torch.empty(shape, dtype=torch.float16, device="cuda")
+            self._ck(self.lib.b200_engine_kv_dequant(self.h, C.c_void_p(k.data_ptr()), C.c_void_p(v.data_ptr())), "kv_dequant")
+            return k, v
         return (self._view(self.lib.b200_engine_k_cache(self.h), shape, td),
                 self._view(self.lib.b200_engine_v_cache(self.h), shape, td))
 

@@ -28,6 +28,7 @@ class OracleModel:
         self.k = np.zeros((L, batch, hk, max_seq_len, d), np.float32)
         self.v = np.zeros((L, batch, hk, max_seq_len, d), np.float32)
         self.step = 0   # tokens already cached
+        self.kv_round = None   # optional rows [..., d] -> rows: the rounding a cache applies to a row when it is appended
 
     def _ffn(self, w, o, resid, I):
         """gate_up GEMM -> SwiGLU -> down GEMM -> + residual (ffn.cpp:53-93, self_decoder.cpp:79-81)"""
@@ -70,7 +71,14 @@ class OracleModel:
             cpu.rope_decode(qkv, h, hk, ref_step, rot, base)
             qkv = rt(qkv)
             att = np.zeros((B, Hl), np.float32)
-            cpu.decode_attention(qkv, self.k[l], self.v[l], att, h, hk, ref_step, True)
+            if self.kv_round is not None:
+                # a cache that rounds rows on entry (fp8 KV): the new token's k, v are rounded, stored, and THEN attended
+                # over with everything else - the step that appends a row already sees the rounded row
+                self.k[l][:, :, ref_step - 1] = self.kv_round(qkv[:, h:h + hk])
+                self.v[l][:, :, ref_step - 1] = self.kv_round(qkv[:, h + hk:h + 2 * hk])
+                cpu.decode_attention(qkv, self.k[l], self.v[l], att, h, hk, ref_step, False)
+            else:
+                cpu.decode_attention(qkv, self.k[l], self.v[l], att, h, hk, ref_step, True)
             att = rt(att)
             o = np.zeros((B, H), np.float32)
             cpu.linear(att, w["o"], o, True)
