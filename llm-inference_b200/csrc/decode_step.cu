@@ -744,17 +744,37 @@ __device__ __noinline__ uint32_t gemv_consume(const StepOp& op, const StepParams
                 const unsigned char* sa = r_base + (size_t)slot * kStageB + (2 * warp) * kSegB;
                 const unsigned char* sb = sa + kSegB;   // row b's slot (stale data when rb < 0: result unused)
                 const __half* xseg = xs + (size_t)seg * KSEG;
+                if (seg_pk == KSEG / 8) {
+                    // whole segment (all but a row's last one): branch-free, every weight packet is loaded before the
+                    // first FMA; same summation order as the guarded loop below
+                    Pack16 wa[kJS], wb[kJS];
 #pragma unroll
-                for (int j = 0; j < kJS; ++j) {
-                    const int pkt = lane + 32 * j;
-                    if (pkt < seg_pk) {
-                        const Pack16 wa = ld16(sa + pkt * 16);
-                        const Pack16 wb = ld16(sb + pkt * 16);
+                    for (int j = 0; j < kJS; ++j) {
+                        wa[j] = ld16(sa + (lane + 32 * j) * 16);
+                        wb[j] = ld16(sb + (lane + 32 * j) * 16);
+                    }
 #pragma unroll
-                        for (int b = 0; b < NB; ++b) {
-                            const Pack16 xv = ld16(xseg + (size_t)b * K + (size_t)pkt * 8);
-                            acc_a[b] = dot16<__half>(wa, xv, acc_a[b]);
-                            acc_b[b] = dot16<__half>(wb, xv, acc_b[b]);
+                    for (int b = 0; b < NB; ++b) {
+#pragma unroll
+                        for (int j = 0; j < kJS; ++j) {
+                            const Pack16 xv = ld16(xseg + (size_t)b * K + (size_t)(lane + 32 * j) * 8);
+                            acc_a[b] = dot16<__half>(wa[j], xv, acc_a[b]);
+                            acc_b[b] = dot16<__half>(wb[j], xv, acc_b[b]);
+                        }
+                    }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < kJS; ++j) {
+                        const int pkt = lane + 32 * j;
+                        if (pkt < seg_pk) {
+                            const Pack16 wa = ld16(sa + pkt * 16);
+                            const Pack16 wb = ld16(sb + pkt * 16);
+#pragma unroll
+                            for (int b = 0; b < NB; ++b) {
+                                const Pack16 xv = ld16(xseg + (size_t)b * K + (size_t)pkt * 8);
+                                acc_a[b] = dot16<__half>(wa, xv, acc_a[b]);
+                                acc_b[b] = dot16<__half>(wb, xv, acc_b[b]);
+                            }
                         }
                     }
                 }
