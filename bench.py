@@ -805,30 +805,43 @@ def extras_multi_gpu(pkg, args, rank, world, local_rank, peak):
         eng.set_mode(fused=True, graph=True, persistent=False)
         comm = sh.P2PComm(B * 8192 * 2)
         logits = {}
-        for kind in ("p2p", "nccl"):
+        for kind in ("p2p", "p2p_persistent", "nccl"):
             eng.fill_kv_random(ctx, seed=7 + rank, amp=0.5)
             if kind == "p2p":
                 eng.set_p2p(comm)
+                eng.set_mode(fused=True, graph=True, persistent=False)
+            elif kind == "p2p_persistent":   # ONE launch per token: the exchange ops inside decode_step_kernel
+                eng.set_p2p(comm)
+                eng.set_mode(fused=True, graph=True, persistent=True)
             else:
                 eng.set_p2p(None)
+                eng.set_mode(fused=True, graph=True, persistent=False)
                 eng.set_allreduce(sh.make_allreduce())
             ms = timed(eng, B)
+            # agreement probe: four steps on FIXED token ids from the same cache state (a free-running greedy chain on
+            # random weights forks at the first near-tie, so its last logits say nothing about agreement)
+            eng.fill_kv_random(ctx, seed=7 + rank, amp=0.5)
+            for s_ in range(4):
+                eng.decode_step_host(np.full(B, 11 + s_, np.int32))
             logits[kind] = eng.logits().float().clone()
             bytes_ = tp_step_bytes(eng, B, ctx + W + K // 2, world, cfg["num_layers"])
             ach = bytes_ / (ms * 1e-3) / 1e9
             out["tp_" + kind] = {"workload": f"LLaMA-2-70B-shaped GQA fp16 decode, tp{world}, batch 1, context 512 (configs[4])",
-                                 "comm": "GEMV epilogue pushes partial rows to the peers + one-shot NVLink reduce+residual kernel"
-                                         if kind == "p2p" else "ncclAllReduce + AddResidual",
+                                 "comm": {"p2p": "GEMV epilogue pushes partial rows to the peers + one-shot NVLink reduce+residual kernel",
+                                          "p2p_persistent": "persistent step kernel: K-split accumulators exchanged as low-latency "
+                                                            "lines over NVLink inside the kernel (kOpExchange), 1 launch per token",
+                                          "nccl": "ncclAllReduce + AddResidual"}[kind],
                                  "value": round(B / (ms * 1e-3), 2), "unit": "tok/s", "ms_per_step": round(ms, 4),
                                  "steps": K, "warmup": W, "layers": cfg["num_layers"],
                                  "launches_per_step": eng.launches_per_step,
                                  "roofline": {"bound": "hbm", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s",
                                               "frac": round(ach / peak, 4), "algorithmic_bytes_per_gpu_per_step": int(bytes_)}}
         # both variants decoded the same tokens from the same cache: their last logits must agree
-        d = (logits["p2p"] - logits["nccl"]).abs().max() / logits["nccl"].abs().max().clamp_min(1e-30)
-        t = torch.tensor([float(d)], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        out["tp_p2p_vs_nccl_logits_rel"] = round(float(t[0]), 6)
+        for name, a_ in (("tp_p2p_vs_nccl_logits_rel", "p2p"), ("tp_p2p_persistent_vs_nccl_logits_rel", "p2p_persistent")):
+            d = (logits[a_] - logits["nccl"]).abs().max() / logits["nccl"].abs().max().clamp_min(1e-30)
+            t = torch.tensor([float(d)], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            out[name] = round(float(t[0]), 6)
         eng.close()
         comm.close()
     except Exception as ex:   # never take the main line down

@@ -577,7 +577,7 @@ __device__ __forceinline__ uint32_t down_consume(const StepParams& p, uint32_t s
         const unsigned char* st = r_base + (size_t)slot * kStageB;
         // four rows per trip: all their shared-memory loads are issued before the first FMA (8 warps per SM cannot hide
         // the load latency of a one-row-at-a-time loop: 150 cycles per row measured)
-        constexpr int UR = PPT == 1 ? 4 : 2;
+        constexpr int UR = PPT == 1 ? 4 : (PPT == 2 ? 2 : 1);
         for (int r = r0 + rg; r < r1; r += UR * nrg) {
             uint16_t a[UR][NB];
             Pack16 w[UR][PPT];
@@ -883,7 +883,8 @@ __device__ __noinline__ uint32_t down_phase(const StepOp& op, const StepParams& 
     const StepSmem<NB> lay(smem_dyn, p.stages, p.xs_bytes);
     const __half* act_s = reinterpret_cast<const __half*>(lay.scratch);
     if (ppt <= 1) state = down_consume<NB, 1>(p, state, op.K, u1 - u0, act_s, op.act_stride, op.acc_out, op.K);
-    else state = down_consume<NB, 2>(p, state, op.K, u1 - u0, act_s, op.act_stride, op.acc_out, op.K);   // K <= 4096 (builder)
+    else if (ppt == 2) state = down_consume<NB, 2>(p, state, op.K, u1 - u0, act_s, op.act_stride, op.acc_out, op.K);
+    else state = down_consume<NB, (NB <= 2 ? 4 : 2)>(p, state, op.K, u1 - u0, act_s, op.act_stride, op.acc_out, op.K);   // K = 8192: batch <= 2 (builder)
 #ifdef B200_STEP_STARVE_TRACE
     if (p.trace != nullptr && threadIdx.x == 0 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) {
         extern __shared__ __align__(128) unsigned char smem[];
@@ -1165,6 +1166,61 @@ __device__ __noinline__ uint32_t attn_o_phase(const StepOp& op, const StepParams
     return state;
 }
 
+// kOpExchange: see decode_step.h. One thread per 16-byte line of this CTA's slice; the push of a line and the wait for
+// the same line of every rank are done by the same thread, so no intra-CTA synchronisation is needed. fp16 only.
+template <int NB>
+__device__ __noinline__ void exchange_op(const StepOp& op, const StepParams& p, const unsigned call_base) {
+    const int world = p.wire.world, me = p.wire.rank;
+    const unsigned call = call_base + (unsigned)op.units + 1u;
+    const size_t buf_off = kP2PHeader + (size_t)(call & 1u) * world * p.wire.slot_bytes;
+    const int lines = p.nb * op.N / 4;
+    const int per = (lines + (int)gridDim.x - 1) / (int)gridDim.x;
+    const int l0 = per * blockIdx.x, l1 = min(lines, l0 + per);
+    float4* acc4 = reinterpret_cast<float4*>(op.acc_out);
+    uint2* hid2 = reinterpret_cast<uint2*>(op.y);
+    for (int i = l0 + (int)threadIdx.x; i < l1; i += kStepConsumers) {
+        // ---- push: T(partial) of line i into slot `me` of every rank (its own included), then clear the accumulator
+        const float4 a = __ldcg(acc4 + i);
+        const __half2 h0 = __floats2half2_rn(a.x, a.y), h1 = __floats2half2_rn(a.z, a.w);
+        const unsigned d0 = *reinterpret_cast<const unsigned*>(&h0), d1 = *reinterpret_cast<const unsigned*>(&h1);
+#pragma unroll 1
+        for (int r = 0; r < world; ++r)
+            asm volatile("st.volatile.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p.wire.peer[r] + buf_off + (size_t)me * p.wire.slot_bytes + (size_t)i * 16),
+                         "r"(d0), "r"(call), "r"(d1), "r"(call)
+                         : "memory");
+        acc4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        // ---- receive: the same line from every rank, summed in rank order (identical on all ranks), + residual
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+        const unsigned long long t0 = global_timer_ns();
+        for (int r = 0; r < world; ++r) {
+            const unsigned char* src = p.wire.peer[me] + buf_off + (size_t)r * p.wire.slot_bytes + (size_t)i * 16;
+            unsigned w0, w1, w2, w3;
+            for (;;) {
+                asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(w0), "=r"(w1), "=r"(w2), "=r"(w3) : "l"(src) : "memory");
+                if (w1 == call && w3 == call) break;
+                if (global_timer_ns() - t0 > 2000000000ull) {   // a peer never arrived: fail instead of hanging
+                    atomicExch(&p.sync[2], 4u);
+                    __trap();
+                }
+            }
+            const float2 x = __half22float2(*reinterpret_cast<const __half2*>(&w0));
+            const float2 y = __half22float2(*reinterpret_cast<const __half2*>(&w2));
+            s0 += x.x; s1 += x.y; s2 += y.x; s3 += y.y;
+        }
+        // hidden <- T(hidden + T(sum)): "allreduce, then launchAddResidual" (oracle/model.py _ffn)
+        const uint2 hv = __ldcg(hid2 + i);   // written by another CTA earlier in this launch (embedding row): L2, not L1
+        const float2 ha = __half22float2(*reinterpret_cast<const __half2*>(&hv.x));
+        const float2 hb = __half22float2(*reinterpret_cast<const __half2*>(&hv.y));
+        auto rnd = [](float v) { return __half2float(__float2half_rn(v)); };
+        const __half2 o0 = __floats2half2_rn(ha.x + rnd(s0), ha.y + rnd(s1));
+        const __half2 o1 = __floats2half2_rn(hb.x + rnd(s2), hb.y + rnd(s3));
+        uint2 ov;
+        ov.x = *reinterpret_cast<const unsigned*>(&o0);
+        ov.y = *reinterpret_cast<const unsigned*>(&o1);
+        hid2[i] = ov;
+    }
+}
+
 // greedy pick (topK.cu:147 with K = 1; ties -> lower index) + advance (ids_cur <- ids_next, step+1)
 __device__ __noinline__ void final_consume(const StepParams& p, float* sv, int* si) {
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -1267,6 +1323,8 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const __gr
 #endif
     const int step = *gp.step_dev;
     const unsigned base = gp.sync[1];
+    // tensor parallel: the communicator's call counter as every CTA of this launch finds it (advanced by the last CTA)
+    const unsigned call_base = gp.wire.world > 0 ? *reinterpret_cast<volatile unsigned*>(gp.wire.peer[gp.wire.rank]) : 0u;
     const int n_ops = gp.n_ops;
     unsigned epoch = 0;
     uint32_t ring_state = 0;   // slot | phase << 8
@@ -1308,6 +1366,8 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const __gr
             if (op.epi == kEpiSwigluDown) ring_state = down_phase<NB>(op, p, ring_state, oi);
         } else if (type == kOpAttn) {
             attn_consume<G>(op, p, reinterpret_cast<float*>(smem + (size_t)opaque_i32(gp.stages) * kStageB), step);
+        } else if (type == kOpExchange) {
+            exchange_op<NB>(op, p, call_base);
         } else if (type == kOpAttnO) {
             attn_consume<G>(op, p, reinterpret_cast<float*>(smem + (size_t)opaque_i32(gp.stages) * kStageB), step);
             ring_state = attn_o_phase<NB>(op, p, ring_state, oi);
@@ -1350,6 +1410,8 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const __gr
         if (prev + 1 == base + total) {   // every CTA has finished its final op
             gp.sync[1] = base + total;
             *gp.step_dev = step + 1;
+            if (gp.wire.world > 0)
+                *reinterpret_cast<volatile unsigned*>(gp.wire.peer[gp.wire.rank]) = call_base + (unsigned)gp.n_exchanges;
         }
     }
 }

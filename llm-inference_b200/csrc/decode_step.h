@@ -4,6 +4,8 @@
 #include <stddef.h>
 #include <vector>
 
+#include "p2p_internal.h"
+
 namespace b200 {
 
 // kOpAttnO: split-KV attention items, then - without a grid barrier - the o projection split along K into (head, part)
@@ -11,7 +13,13 @@ namespace b200 {
 // merges that head's split partials, multiplies the head's d outputs by ITS block of the packed o weights
 // (W2: [head_num * parts][d][N / parts], rows = input columns) and adds the partial rows into acc_out (red.add).
 // Fields: N = hidden size, K = head_num * head_size, units = head_num * parts, act_stride = parts, y = counters.
-enum { kOpGemv = 0, kOpAttn = 1, kOpFinal = 2, kOpAttnO = 3 };
+// kOpExchange (tensor parallel): the fp32 accumulator of a K-split projection holds THIS RANK's partial sums. CTA c
+// rounds its slice to T and pushes it as 16-byte low-latency lines {data, call, data, call} into slot `rank` of every
+// rank's receive buffer (p2p_allreduce.cu's wire format, peer stores over NVLink), clears the slice, then spins on the
+// lines of all ranks for the same slice, sums them in rank order, adds the residual and stores `hidden` - the
+// allreduce after o_proj / down_proj and launchAddResidual in one op. Fields: acc_out = accumulator, y = hidden
+// (in place), N = hidden size, units = index of the exchange within the step (call tag = base + units + 1).
+enum { kOpGemv = 0, kOpAttn = 1, kOpFinal = 2, kOpAttnO = 3, kOpExchange = 4 };
 // kEpiSwigluDown: gate_up GEMV + SwiGLU, then - without a grid barrier - the CTA multiplies the slice of `act` it has
 // just produced by ITS rows of the transposed down weights W2 [I, H] and adds the partial [H] into acc_out with
 // red.global.add.v4.f32 (the down projection split along K over the CTAs; L2 does the cross-CTA sum)
@@ -68,6 +76,8 @@ struct StepParams {
     unsigned* sync;       // [0] arrival counter (monotonic), [1] base of the current launch, [2] error flag
     int stages;
     size_t xs_bytes;
+    P2PWire wire;         // tensor parallel: the ranks' receive buffers (wire.world == 0: single GPU)
+    int n_exchanges;      // kOpExchange ops per step (the communicator's call counter advances by this per launch)
     unsigned long long* trace;   // optional (B200_STEP_TRACE=1): [0,2n) CTA 0 (op done, barrier passed) %globaltimer stamps, [2n,3n) x staged,
                                  // [3n,4n) ring stages landed at GEMV start, [4n] L2 prefetches, [4n+1,5n+1) / [5n+1,6n+1) cycles warp 0 of the
                                  // first / last CTA waited for weights, [6n+1 + op*grid + cta] op-done stamp of every CTA

@@ -227,18 +227,23 @@ __global__ void advance_ragged_kernel(int* ids_cur, const int* ids_next, int* st
 // branch, one entry per GEMV / attention phase.
 static void build_program(b200_engine* e) {
     const b200_model_config& c = e->cfg;
-    if (c.dtype != B200_F16 || c.tp_size != 1 || e->batch > 4) return;
+    // tensor parallel: only with the peer-memory communicator attached (b200_engine_set_p2p rebuilds the program)
+    // (a communicator attached to a tp_size = 1 engine gives the same exchange form with one rank: one-GPU test coverage)
+    if (c.tp_size > 1 && !(e->p2p && e->p2p->connected)) return;
+    const bool tp = e->p2p != nullptr && e->p2p->connected;
+    if (c.dtype != B200_F16 || e->batch > 4) return;
     std::vector<StepOp> ops;
     const int H = e->H, L = c.num_layers;
     // Fused FFN (gate_up + SwiGLU + K-split down in one op): needs whole W2 rows per ring stage
     // (H a power of two <= 16384) and the per-thread accumulators in registers (batch tile x packets per thread <= 8)
     const int nb_t = e->batch <= 1 ? 1 : e->batch <= 2 ? 2 : 4;
     const int ppt = (H / 8 + 255) / 256;
-    bool fuse_ffn = L >= 1 && H >= 256 && (H & (H - 1)) == 0 && ppt <= 2 && nb_t * ppt <= 8;   // H <= 4096
+    bool fuse_ffn = L >= 1 && H >= 256 && (H & (H - 1)) == 0 && ppt <= 4 && nb_t * ppt <= 8;   // H <= 8192; 8192: batch <= 2
     {
         const char* env = getenv("B200_STEP_NO_FFN_FUSION");
-        if (env && env[0] == '1') fuse_ffn = false;
+        if (env && env[0] == '1' && !tp) fuse_ffn = false;
     }
+    if (tp && !fuse_ffn) return;   // the tensor-parallel program exists only in the K-split form (its accumulators ARE the partials)
     if (fuse_ffn) {
         const size_t wt = (size_t)L * e->I * H * e->esz, ab = (size_t)2 * e->batch * H * sizeof(float);
         if (cudaMalloc(&e->down_t, wt) != cudaSuccess || cudaMalloc(&e->ffn_acc, ab) != cudaSuccess) {
@@ -262,6 +267,11 @@ static void build_program(b200_engine* e) {
         if ((env && env[0] == '1') || H % parts || row_len % 8 || (32768 % (row_len * 2)) || (row_len / 8 + 255) / 256 > 2 ||
             nb_t * ((row_len / 8 + 255) / 256) > 8)
             parts = 0;
+    }
+    if (tp && !parts) {
+        cudaFree(e->down_t); cudaFree(e->ffn_acc);
+        e->down_t = nullptr; e->ffn_acc = nullptr;
+        return;
     }
     if (parts) {
         const size_t wb = (size_t)L * H * e->h * e->d * e->esz;
@@ -303,19 +313,20 @@ static void build_program(b200_engine* e) {
         LayerW& w = e->layers[l];
         void* kc = e->k_cache + (size_t)l * e->layer_kv_elems * e->esz;
         void* vc = e->v_cache + (size_t)l * e->layer_kv_elems * e->esz;
-        void* hid = parts ? bufA : buf[l % 2];
+        void* hid = parts ? bufA : buf[l % 2];   // (tensor parallel: always e->hidden = bufA)
         StepOp qkv{};
         qkv.type = kOpGemv; qkv.epi = kEpiRopeKV; qkv.norm = 1; qkv.N = e->qkv_n; qkv.K = H; qkv.units = e->qkv_n / 2;
         qkv.W = w.qkv; qkv.y = e->qkv; qkv.gamma = w.attn_norm; qkv.k_cache = kc; qkv.v_cache = vc;
         if (l == 0) { qkv.xsrc = kXEmbed; qkv.xout = hid; qkv.x = hid; }
+        else if (tp) { qkv.xsrc = kXPlain; qkv.x = hid; }   // the exchange op has already formed the residual sum in `hidden`
         else if (fuse_ffn) { qkv.xsrc = kXResidAcc; qkv.x = parts ? bufB : buf[(l - 1) % 2]; qkv.acc_in = acc(l - 1); qkv.xout = hid; }
         else { qkv.xsrc = kXPlain; qkv.x = hid; }
-        if (parts && l >= 1) { qkv.zero = e->o_acc; qkv.n_zero = n_acc; }   // consumed by the previous layer's FFN staging
+        if (parts && l >= 1 && !tp) { qkv.zero = e->o_acc; qkv.n_zero = n_acc; }   // consumed by the previous layer's FFN staging
         StepOp att{};
         att.type = kOpAttn; att.k_cache = kc; att.v_cache = vc;
         // acc(l - 1) was consumed by this layer's qkv staging: cleared one barrier later - at the attention op, or at
         // the FFN op when no grid barrier separates qkv and attention
-        if (fuse_ffn && l >= 1 && !head_cnt) { att.zero = acc(l - 1); att.n_zero = n_acc; }
+        if (fuse_ffn && l >= 1 && !head_cnt && !tp) { att.zero = acc(l - 1); att.n_zero = n_acc; }
         StepOp gu{};
         gu.type = kOpGemv; gu.xsrc = kXPlain; gu.norm = 2; gu.N = e->I; gu.K = H; gu.units = e->I;
         gu.W = w.gate_up; gu.x = hid; gu.gamma = w.ffn_norm;
@@ -333,7 +344,15 @@ static void build_program(b200_engine* e) {
                 ops[ops.size() - 2].head_cnt = head_cnt;   // the qkv op pushed above releases, ...
                 ops[ops.size() - 2].no_barrier = 1;
                 ops.back().head_cnt = head_cnt;            // ... the kOpAttnO op's attention items wait
-                if (l >= 1) { gu.zero = acc(l - 1); gu.n_zero = n_acc; }
+                if (l >= 1 && !tp) { gu.zero = acc(l - 1); gu.n_zero = n_acc; }
+            }
+            if (tp) {
+                // tensor parallel: o_acc holds this rank's partial; the exchange op sums it over the ranks, adds the
+                // residual into `hidden` and clears it; the FFN then reads `hidden` like any other op
+                StepOp ex{};
+                ex.type = kOpExchange; ex.N = H; ex.units = 2 * l; ex.acc_out = e->o_acc; ex.y = e->hidden;
+                ops.push_back(ex);
+                gu.xsrc = kXPlain; gu.x = e->hidden; gu.acc_in = nullptr; gu.xout = nullptr;
             }
         } else {
             StepOp o{};
@@ -345,8 +364,13 @@ static void build_program(b200_engine* e) {
             gu.epi = kEpiSwigluDown;
             gu.act_stride = (((e->I + sm_count() - 1) / sm_count()) + 8) & ~7;
             gu.W2 = e->down_t + (size_t)l * e->I * H * e->esz;
-            gu.acc_out = acc(l);
+            gu.acc_out = tp ? acc(0) : acc(l);
             ops.push_back(gu);
+            if (tp) {
+                StepOp ex{};
+                ex.type = kOpExchange; ex.N = H; ex.units = 2 * l + 1; ex.acc_out = acc(0); ex.y = e->hidden;
+                ops.push_back(ex);
+            }
         } else {
             gu.epi = kEpiSwiglu;
             gu.y = e->act;
@@ -360,6 +384,7 @@ static void build_program(b200_engine* e) {
     head.type = kOpGemv; head.epi = kEpiPlain; head.norm = 1; head.N = e->V; head.K = H; head.units = (e->V + 1) / 2;
     head.W = e->lm_head; head.y = e->logits; head.gamma = e->final_norm;
     if (L == 0) { head.xsrc = kXEmbed; head.x = e->hidden; head.xout = e->hidden; }
+    else if (tp) { head.xsrc = kXPlain; head.x = e->hidden; }
     else if (fuse_ffn) {
         head.xsrc = kXResidAcc; head.x = parts ? bufB : buf[(L - 1) % 2]; head.acc_in = acc(L - 1);
         head.xout = parts ? bufA : buf[L % 2];
@@ -368,7 +393,7 @@ static void build_program(b200_engine* e) {
     else { head.xsrc = kXPlain; head.x = e->hidden; }
     StepOp fin{};
     fin.type = kOpFinal;
-    if (fuse_ffn) { fin.zero = acc(L - 1); fin.n_zero = n_acc; }
+    if (fuse_ffn && !tp) { fin.zero = acc(L - 1); fin.n_zero = n_acc; }
     ops.push_back(head); ops.push_back(fin);
     StepParams p{};
     p.head_num = e->h; p.kv_head_num = e->hk; p.head_size = e->d; p.max_seq_len = c.max_seq_len;
@@ -376,6 +401,10 @@ static void build_program(b200_engine* e) {
     p.step_dev = e->step_dev; p.ids_cur = e->ids_cur; p.ids_next = e->ids_next;
     p.embed = e->embed; p.vocab = e->V; p.hidden = H;
     p.qkv = e->qkv; p.attn = e->attn; p.logits = e->logits;
+    if (tp) {
+        p.wire = p2p_wire(e->p2p);
+        p.n_exchanges = 2 * L;
+    }
     const int k_max = fuse_ffn ? std::max(H, e->h * e->d) : std::max(std::max(H, e->I), e->h * e->d);
     e->program = step_program_create(ops, p, e->batch, e->h, e->hk, e->d, k_max, e->attn_ws);
     if (!e->program && e->down_t) {
@@ -620,6 +649,14 @@ extern "C" int b200_engine_set_p2p(b200_engine* e, b200_p2p* comm) {
     cudaStreamSynchronize(e->stream);
     drop_graphs(e);
     e->p2p = comm;
+    {
+        // the persistent step program carries the communicator's peer pointers (exchange form): rebuild it
+        b200::step_program_destroy(e->program);
+        e->program = nullptr;
+        cudaFree(e->down_t); cudaFree(e->ffn_acc); cudaFree(e->o_packed); cudaFree(e->o_acc);
+        e->down_t = nullptr; e->ffn_acc = nullptr; e->o_packed = nullptr; e->o_acc = nullptr;
+        if (!e->kv_fp8) build_program(e);
+    }
     return B200_OK;
 }
 

@@ -198,3 +198,82 @@ def test_persistent_step_kernel_vs_oracle_with_context(pkg, cfg_name, B, ctx):
     assert_close(kc[:, :, :, ctx:ctx + steps].float().cpu().numpy(), ora.k[:, :, :, ctx:ctx + steps], "fp16", "K rows")
     assert_close(vc[:, :, :, ctx:ctx + steps].float().cpu().numpy(), ora.v[:, :, :, ctx:ctx + steps], "fp16", "V rows")
     eng.close()
+
+
+@pytest.mark.parametrize("B,ctx", [(1, 0), (1, 300), (2, 130)])
+def test_persistent_step_kernel_exchange_form_single_rank(pkg, B, ctx):
+    """The tensor-parallel form of the persistent step kernel (kOpExchange: the K-split accumulators are pushed as
+    low-latency lines into the ranks' receive buffers, summed, and the residual added) on ONE GPU: a world = 1
+    communicator attached to an unsharded engine exercises the wire format, call tags, buffer parity and the device
+    call counter over several steps; the result must match the oracle like the plain form does."""
+    import ctypes as C
+    E = pkg.engine
+    lib = E._lib()
+    max_seq, steps = ctx + 16, 6
+    eng = E.Engine(B, max_seq, dtype=pkg.F16, **SMALL)
+    eng.init_random(seed=33, std=0.05)
+    H = SMALL["head_num"] * SMALL["head_size"]
+    comm = lib.b200_p2p_create(1, 0, B * H * 2)
+    assert comm
+    hnd = C.create_string_buffer(int(lib.b200_p2p_handle_bytes()))
+    assert lib.b200_p2p_local_handle(comm, hnd) == 0
+    assert lib.b200_p2p_connect(comm, hnd.raw) == 0
+    assert lib.b200_engine_set_p2p(eng.h, comm) == 0
+    eng.set_mode(fused=True, graph=True, persistent=True)
+    if ctx:
+        eng.fill_kv_random(ctx, seed=5, amp=0.5)
+    ora = omodel.OracleModel(download_weights(E, eng, SMALL["num_layers"]), SMALL, B, max_seq, "fp16")
+    kc, vc = eng.kv_caches()
+    ora.k[:] = kc.float().cpu().numpy()
+    ora.v[:] = vc.float().cpu().numpy()
+    ora.step = ctx
+    ids = np.random.default_rng(2).integers(0, SMALL["vocab_size"], B).astype(np.int32)
+    for s in range(steps):
+        eng.decode_step_host(ids)
+        want_logits, want_ids = ora.decode_step(ids)
+        assert_close(eng.logits().float().cpu().numpy(), want_logits, "fp16", f"exchange form: logits step {s}")
+        ids = want_ids
+    assert eng.launches_per_step == 1
+    kc, vc = eng.kv_caches()
+    assert_close(kc[:, :, :, ctx:ctx + steps].float().cpu().numpy(), ora.k[:, :, :, ctx:ctx + steps], "fp16", "K rows")
+    assert lib.b200_engine_set_p2p(eng.h, None) == 0
+    eng.close()
+    lib.b200_p2p_destroy(comm)
+
+
+def test_persistent_step_kernel_70b_geometry(pkg):
+    """hidden 8192 (four 16-byte packets per thread in the K-split consumer), 64 q / 8 kv heads (groups of 8): the
+    geometry of BASELINE configs[4], two layers with a narrow FFN, plain and exchange form, vs the oracle."""
+    import ctypes as C
+    E = pkg.engine
+    lib = E._lib()
+    cfg = dict(num_layers=2, head_num=64, kv_head_num=8, head_size=128, inter_size=2368, vocab_size=1000)
+    B, ctx, steps = 1, 200, 3
+    for form in ("plain", "exchange"):
+        eng = E.Engine(B, ctx + 8, dtype=pkg.F16, **cfg)
+        eng.init_random(seed=3, std=0.02)
+        comm = None
+        if form == "exchange":
+            comm = lib.b200_p2p_create(1, 0, B * 8192 * 2)
+            hnd = C.create_string_buffer(int(lib.b200_p2p_handle_bytes()))
+            assert lib.b200_p2p_local_handle(comm, hnd) == 0 and lib.b200_p2p_connect(comm, hnd.raw) == 0
+            assert lib.b200_engine_set_p2p(eng.h, comm) == 0
+        eng.set_mode(fused=True, graph=True, persistent=True)
+        eng.fill_kv_random(ctx, seed=5, amp=0.5)
+        ora = omodel.OracleModel(download_weights(E, eng, 2), cfg, B, ctx + 8, "fp16")
+        kc, vc = eng.kv_caches()
+        ora.k[:] = kc.float().cpu().numpy()
+        ora.v[:] = vc.float().cpu().numpy()
+        ora.step = ctx
+        ids = np.array([17], np.int32)
+        for s in range(steps):
+            eng.decode_step_host(ids)
+            want_logits, want_ids = ora.decode_step(ids)
+            assert_close(eng.logits().float().cpu().numpy(), want_logits, "fp16", f"70B geometry ({form}): logits step {s}")
+            ids = want_ids
+        assert eng.launches_per_step == 1
+        if comm:
+            assert lib.b200_engine_set_p2p(eng.h, None) == 0
+        eng.close()
+        if comm:
+            lib.b200_p2p_destroy(comm)

@@ -72,9 +72,11 @@ def _worker(rank, world, port, kind, fused, out_dir, comm="hook"):
             return inner(ptr, count, dtype, stream)
 
         p2p = None
-        if comm == "p2p":   # the fused one-shot NVLink allreduce + residual add (csrc/p2p_allreduce.cu)
+        if comm in ("p2p", "p2p_persistent"):   # the fused one-shot NVLink allreduce + residual add (csrc/p2p_allreduce.cu)
             p2p = sh.P2PComm(B * CFG["head_num"] * CFG["head_size"] * 4)
             eng.set_p2p(p2p)
+            if comm == "p2p_persistent":   # ONE launch per token: the exchange ops of decode_step_kernel do the allreduce
+                eng.set_mode(fused=True, graph=True, persistent=True)
         else:
             eng.set_allreduce(hook)
         ids = np.array([7, 1000], np.int32)
@@ -85,6 +87,8 @@ def _worker(rank, world, port, kind, fused, out_dir, comm="hook"):
             picked.append(ids.copy())
         if not multi and comm == "hook":
             assert n_calls[0] == STEPS * CFG["num_layers"] * 2, "two allreduces per layer per step"
+        if comm == "p2p_persistent":
+            assert eng.launches_per_step == 1, "tensor-parallel persistent step kernel not selected"
         kc, vc = eng.kv_caches()
         np.savez(os.path.join(out_dir, f"rank{rank}.npz"), logits=np.stack(logits), ids=np.stack(picked),
                  k=kc.float().cpu().numpy(), v=vc.float().cpu().numpy())
@@ -158,14 +162,16 @@ def test_p2p_oneshot_allreduce_two_gpus(tmp_path):
         assert open(os.path.join(tmp_path, f"p2p{r}.txt")).read() == "ok"
 
 
-@pytest.mark.parametrize("comm", ["hook", "p2p"])
+@pytest.mark.parametrize("comm", ["hook", "p2p", "p2p_persistent"])
 @pytest.mark.parametrize("fused", [True, False])
 @pytest.mark.parametrize("kind", ["fp32", "fp16"])
 def test_engine_tensor_parallel_two_ranks_vs_unsharded_oracle(tmp_path, kind, fused, comm):
     import torch.multiprocessing as mp
     world = 2
-    if comm == "p2p" and torch.cuda.device_count() < world:
+    if comm in ("p2p", "p2p_persistent") and torch.cuda.device_count() < world:
         pytest.skip("the one-shot NVLink allreduce needs one GPU per rank")
+    if comm == "p2p_persistent" and (kind != "fp16" or not fused):
+        pytest.skip("the persistent step kernel is fp16 and has one launch order")
     mp.spawn(_worker, args=(world, free_port(), kind, fused, str(tmp_path), comm), nprocs=world, join=True)
     full = make_weights(CFG, kind, 33)
     om = omodel.OracleModel(full, CFG, B, MAX_SEQ, kind)
