@@ -117,6 +117,12 @@ void b200_p2p_destroy(b200_p2p* c);
 b200_engine* b200_engine_create(const b200_model_config* cfg, int batch);
 /* the same with B200_ENGINE_KV_* creation flags (0 = b200_engine_create) */
 b200_engine* b200_engine_create_ex(const b200_model_config* cfg, int batch, unsigned flags);
+/* Sequence retirement, the reference's `finished` flags (src/kernels/sampling.cu:46,81-83, llama.cpp:189,327):
+ * with eos_id >= 0 a sequence that has produced eos_id is marked on the DEVICE, keeps emitting eos_id, and from the
+ * next step on neither appends to nor reads its KV cache (the attention kernels skip it). -1 = off (default).
+ * Flags are cleared by reset / fill_kv_random / every prompt pass. */
+int b200_engine_set_eos(b200_engine* e, int eos_id);
+int b200_engine_get_finished(b200_engine* e, unsigned char* flags_host /* [batch] */);
 int b200_engine_kv_is_fp8(const b200_engine* e);
 /* fp8 cache only: K and V dequantised to fp16 into caller DEVICE buffers [layers, B, hk, max_seq, d] (tests) */
 int b200_engine_kv_dequant(b200_engine* e, void* k_dst, void* v_dst);

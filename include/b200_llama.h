@@ -243,6 +243,11 @@ int b200_decode_attention_ragged(const void* qkv, void* k_cache_layer, void* v_c
                                  int max_step, const int* seq_steps_dev, int append_kv, int dtype,
                                  void* stream);
 
+/* `finished` of launchDecoderMaskedMHA (fused_decoder_self_attention.h:10-19; the reference passes it and never reads
+ * it): DEVICE flags [batch] applied to every b200_decode_attention* / b200_kv_append_fp8 launch issued afterwards
+ * from this host thread (NULL = off). A set flag retires the sequence: no K/V append, no cache reads, zero output. */
+void b200_decode_attention_set_finished(const unsigned char* finished_dev);
+
 /* Allocation-free variant of b200_decode_attention. No counterpart in the reference: added
  * for callers that cannot call cudaMalloc (CUDA-graph capture, tight
  * serving loops, harnesses that forbid it). Same arguments minus the workspace: the split-KV partials

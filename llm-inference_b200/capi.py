@@ -58,6 +58,7 @@ PROTOTYPES = {
     "b200_decode_attention_ex": (_i, [_vp, _vp, _vp, _vp, _vp, _sz] + [_i] * 6 + [_vp, _i, _i, _vp]),
     "b200_decode_attention_ragged": (_i, [_vp, _vp, _vp, _vp, _vp, _sz] + [_i] * 6 + [_vp, _i, _i, _vp]),
     "b200_decode_attention_static": (_i, [_vp, _vp, _vp, _vp] + [_i] * 8 + [_vp]),
+    "b200_decode_attention_set_finished": (None, [_vp]),
     "b200_kv_append_fp8": (_i, [_vp] * 5 + [_i] * 6 + [_vp, _i, _vp]),
     "b200_decode_attention_fp8": (_i, [_vp] * 7 + [_sz] + [_i] * 6 + [_vp, _i, _vp]),
     "b200_kv_quantize_fp8": (_i, [_vp] * 5 + [_i] * 6 + [_vp]),

@@ -36,7 +36,13 @@ struct AttnParams {
     int append_kv;
     const float* k_scale;   // fp8 cache only: one scale per cached row, [B, hk, max_seq]
     const float* v_scale;
+    const unsigned char* finished;   // optional [B]: a retired sequence neither appends nor reads its cache (output 0)
 };
+
+// `finished` flags for the launches that follow on this host thread (NULL = off): the reference passes a
+// TensorWrapper<bool>* finished to launchDecoderMaskedMHA (fused_decoder_self_attention.h:10-19) and never reads it;
+// here a set flag retires the sequence - no K/V append, no cache reads, zero output row.
+static thread_local const unsigned char* g_attn_finished = nullptr;
 
 // fp32 data keeps the accurate expf (1e-5 tolerance); half data uses the MUFU fast path
 template <typename T> __device__ __forceinline__ float fexp(float x);
@@ -69,7 +75,8 @@ decode_attn_split_kernel(const AttnParams p) {
     const int splits = gridDim.y;
     const int per = (step + splits - 1) / splits;
     const int k0 = blockIdx.y * per;
-    const int k1 = min(step, k0 + per);
+    const bool retired = p.finished != nullptr && p.finished[b] != 0;
+    const int k1 = retired ? k0 : min(step, k0 + per);   // a retired sequence: empty key range -> (m, l, o) = (-inf, 0, 0)
 
     // append the new token's k,v (reference :170-172, :274-276) - only the CTA that will read it
     if (p.append_kv && k0 <= step - 1 && step - 1 < k1) {
@@ -323,7 +330,8 @@ decode_attn_split_fp8_kernel(const AttnParams p) {
     const int splits = gridDim.y;
     const int per = (step + splits - 1) / splits;
     const int k0 = blockIdx.y * per;
-    const int k1 = min(step, k0 + per);
+    const bool retired = p.finished != nullptr && p.finished[b] != 0;
+    const int k1 = retired ? k0 : min(step, k0 + per);
 
     Pack16 q[G][2];   // the lane's 16 elements of every query head of the group
 #pragma unroll
@@ -447,6 +455,12 @@ decode_attn_generic_kernel(const AttnParams p, float* __restrict__ scores) {
     float* sc = scores + (size_t)blockIdx.x * p.max_seq_len;
     const float scale = rsqrtf((float)d);
     const bool use_new = p.append_kv != 0;
+    if (p.finished != nullptr && p.finished[b] != 0) {   // retired sequence: no append, no reads, zero output
+        for (int e = threadIdx.x; e < d; e += blockDim.x)
+            reinterpret_cast<T*>(p.out)[((size_t)b * p.head_num + head) * d + e] = DT<T>::from_f(0.f);
+        pdl_launch_dependents();
+        return;
+    }
 
     float mx = -INFINITY;
     for (int j = threadIdx.x; j < step; j += blockDim.x) {
@@ -501,6 +515,8 @@ static int attn_pick_splits(int batch, int kv_head_num, int step, int group) {
     if (splits > 64) splits = 64;
     return splits;
 }
+
+const unsigned char* attn_finished_ptr() { return g_attn_finished; }   // kv_fp8.cu's append honours the same flags
 
 int attn_pick_splits_public(int batch, int kv_head_num, int step, int group) {
     return attn_pick_splits(batch, kv_head_num, step, group);
@@ -575,6 +591,7 @@ static int decode_attention_impl(const void* qkv, void* k_cache_layer, void* v_c
     p.qkv = qkv; p.k_cache = k_cache_layer; p.v_cache = v_cache_layer; p.out = out;
     p.batch = batch; p.head_num = head_num; p.kv_head_num = kv_head_num; p.head_size = head_size;
     p.max_seq_len = max_seq_len; p.step = step; p.step_dev = step_dev; p.step_stride = step_stride; p.append_kv = append_kv;
+    p.finished = g_attn_finished;
     auto al = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15u) == 0; };
     const bool fast = attn_fast_shape(head_num, kv_head_num, head_size, esz) && al(qkv) &&
                       al(k_cache_layer) && al(v_cache_layer);
@@ -740,6 +757,7 @@ extern "C" int b200_decode_attention_fp8(const void* qkv, const void* k_cache8, 
     p.k_scale = k_scale; p.v_scale = v_scale;
     p.batch = batch; p.head_num = head_num; p.kv_head_num = kv_head_num; p.head_size = head_size;
     p.max_seq_len = max_seq_len; p.step = step; p.step_dev = step_dev; p.step_stride = step_stride; p.append_kv = 0;
+    p.finished = g_attn_finished;
     const int splits = attn_pick_splits(batch, kv_head_num, step, G);
     if (splits > 1) {
         const size_t ml = (size_t)batch * head_num * splits * 2 * sizeof(float);
@@ -763,3 +781,7 @@ extern "C" int b200_decode_attention_fp8(const void* qkv, const void* k_cache8, 
     }
     return (int)e;
 }
+
+/* DEVICE flags [batch] (0 / 1) applied to every decode-attention launch issued afterwards from this host thread; NULL
+ * switches it off. A set flag retires the sequence: no K/V append, no cache reads, zero output row. */
+extern "C" void b200_decode_attention_set_finished(const unsigned char* finished_dev) { g_attn_finished = finished_dev; }

@@ -67,6 +67,8 @@ struct b200_engine {
     char* act_arena = nullptr;
     void *hidden, *residual, *qkv, *attn, *act, *gate_up, *logits, *partial;
     int *ids_cur, *ids_next, *step_dev;
+    unsigned char* finished = nullptr;   // [batch] device flags (b200_engine_set_eos); part of the activation arena
+    int eos_id = -1;                      // -1: no retirement
     float* rope_den;
     void* attn_ws;
     size_t attn_ws_bytes;
@@ -205,18 +207,31 @@ __global__ void pack_o_kernel(const __half* __restrict__ W, __half* __restrict__
     }
 }
 
-__global__ void advance_kernel(int* ids_cur, const int* ids_next, int* step, int batch) {
+// `finished` retirement (sampling.cu:46,81-83: finished[b] = (id == end_id)): once a sequence has produced eos_id it
+// keeps emitting eos_id, and the attention / append kernels skip it (b200_decode_attention_set_finished)
+__device__ __forceinline__ int retire(int* ids_next, unsigned char* finished, int eos_id, int b) {
+    int id = ids_next[b];
+    if (finished != nullptr && eos_id >= 0) {
+        if (finished[b]) { id = eos_id; ids_next[b] = id; }
+        else if (id == eos_id) finished[b] = 1;
+    }
+    return id;
+}
+
+__global__ void advance_kernel(int* ids_cur, int* ids_next, int* step, int batch, unsigned char* finished, int eos_id) {
     pdl_wait();
-    if (threadIdx.x < batch) ids_cur[threadIdx.x] = ids_next[threadIdx.x];
+    for (int b = threadIdx.x; b < batch; b += blockDim.x) ids_cur[b] = retire(ids_next, finished, eos_id, b);
     if (threadIdx.x == 0) *step += 1;
 }
 
 // ragged batch: every sequence moves on by one token from its own length
-__global__ void advance_ragged_kernel(int* ids_cur, const int* ids_next, int* step, int* seq_steps, int batch) {
+__global__ void advance_ragged_kernel(int* ids_cur, int* ids_next, int* step, int* seq_steps, int batch,
+                                      unsigned char* finished, int eos_id) {
     pdl_wait();
     for (int b = threadIdx.x; b < batch; b += blockDim.x) {
-        ids_cur[b] = ids_next[b];
-        seq_steps[b] += 1;
+        const bool was = finished != nullptr && eos_id >= 0 && finished[b];
+        ids_cur[b] = retire(ids_next, finished, eos_id, b);
+        if (!was) seq_steps[b] += 1;   // a retired sequence stays where it ended
     }
     if (threadIdx.x == 0) *step += 1;
 }
@@ -527,6 +542,7 @@ extern "C" b200_engine* b200_engine_create_ex(const b200_model_config* c, int ba
                  o_attn = take(B * e->h * e->d), o_act = take(B * e->I),
                  o_gu = take(B * 2 * e->I), o_logits = take(B * e->V), o_part = take(B * e->H);
     const size_t o_ids = off; off += align256(3 * B * sizeof(int) + sizeof(int) + 64);
+    const size_t o_fin = off; off += align256(B);
     const size_t o_den = off; off += align256((size_t)c->rotary_dim / 2 * sizeof(float) + 64);
     const size_t o_ws = off; off += align256(e->attn_ws_bytes);
     e->lin_ws_bytes = 0;
@@ -545,6 +561,7 @@ extern "C" b200_engine* b200_engine_create_ex(const b200_model_config* c, int ba
     e->act = a + o_act; e->gate_up = a + o_gu; e->logits = a + o_logits; e->partial = a + o_part;
     e->ids_cur = (int*)(a + o_ids); e->ids_next = e->ids_cur + B; e->step_dev = e->ids_next + B;
     e->seq_steps = e->step_dev + 1;
+    e->finished = (unsigned char*)(a + o_fin);
     e->seq_cached.assign(B, 0);
     e->attn_ws = a + o_ws;
     e->lin_ws = a + o_lws;
@@ -666,11 +683,30 @@ static int set_step(b200_engine* e, int n) {
     e->ragged = false;
     const int ref_step = n + 1;  // reference `step`: tokens in the cache including the new one
     CU(cudaMemcpyAsync(e->step_dev, &ref_step, sizeof(int), cudaMemcpyHostToDevice, e->stream));
+    CU(cudaMemsetAsync(e->finished, 0, e->batch, e->stream));   // a new position: nobody is retired
     CU(cudaStreamSynchronize(e->stream));
     return B200_OK;
 }
 
 extern "C" int b200_engine_reset(b200_engine* e) { return e ? set_step(e, 0) : B200_EINVAL; }
+
+/* eos_id >= 0 switches sequence retirement on (sampling.cu:81-83: finished[b] = (id == end_id)); -1 off. The flags are
+ * cleared by reset / fill_kv / every prompt pass. The persistent whole-step kernel does not look at them (its default use
+ * is batch 1, where the generation loop simply stops): engines with retirement on run the multi-kernel orders. */
+extern "C" int b200_engine_set_eos(b200_engine* e, int eos_id) {
+    if (!e) return B200_EINVAL;
+    CU(cudaStreamSynchronize(e->stream));
+    drop_graphs(e);   // the advance kernel's arguments are baked into the graphs
+    e->eos_id = eos_id < 0 ? -1 : eos_id;
+    CU(cudaMemsetAsync(e->finished, 0, e->batch, e->stream));
+    return B200_OK;
+}
+extern "C" int b200_engine_get_finished(b200_engine* e, unsigned char* flags_host) {
+    if (!e || !flags_host) return B200_EINVAL;
+    CU(cudaMemcpyAsync(flags_host, e->finished, e->batch, cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaStreamSynchronize(e->stream));
+    return B200_OK;
+}
 
 template <typename T>
 static void fill_normal(void* p, size_t n, uint64_t seed, float mean, float std, cudaStream_t s) {
@@ -811,7 +847,14 @@ static int tp_sum(b200_engine* e, void* buf, size_t count) {
     return 0;
 }
 
+static int enqueue_step_body(b200_engine* e);
 static int enqueue_step(b200_engine* e) {
+    b200_decode_attention_set_finished(e->eos_id >= 0 ? e->finished : nullptr);
+    const int rc = enqueue_step_body(e);
+    b200_decode_attention_set_finished(nullptr);
+    return rc;
+}
+static int enqueue_step_body(b200_engine* e) {
     const int dt = e->cfg.dtype, B = e->batch, H = e->H;
     const int ref_step = e->step + 1;
     cudaStream_t s = e->stream;
@@ -910,10 +953,11 @@ static int enqueue_step(b200_engine* e) {
     }
     RC(b200_argmax(e->logits, e->ids_next, B, e->V, dt, s));
     if (e->ragged)
-        CU(launch_k(advance_ragged_kernel, dim3(1), dim3(1024), 0, s, true, e->ids_cur, (const int*)e->ids_next,
-                    e->step_dev, e->seq_steps, B));
+        CU(launch_k(advance_ragged_kernel, dim3(1), dim3(1024), 0, s, true, e->ids_cur, e->ids_next,
+                    e->step_dev, e->seq_steps, B, e->eos_id >= 0 ? e->finished : nullptr, e->eos_id));
     else
-        CU(launch_k(advance_kernel, dim3(1), dim3(1024), 0, s, true, e->ids_cur, (const int*)e->ids_next, e->step_dev, B));
+        CU(launch_k(advance_kernel, dim3(1), dim3(1024), 0, s, true, e->ids_cur, e->ids_next, e->step_dev, B,
+                    e->eos_id >= 0 ? e->finished : nullptr, e->eos_id));
     count_launch();
     return 0;
 }
@@ -925,7 +969,8 @@ static void stepped(b200_engine* e) {
 
 static int run_step(b200_engine* e) {
     if (e->step + 1 > e->cfg.max_seq_len) return fail("KV cache full (step == max_seq_len)");
-    if (e->program && !e->ragged && (e->mode & B200_ENGINE_FUSED) && (e->mode & B200_ENGINE_PERSISTENT)) {
+    if (e->program && !e->ragged && (e->mode & B200_ENGINE_FUSED) && (e->mode & B200_ENGINE_PERSISTENT) &&
+        !(e->eos_id >= 0 && e->batch > 1)) {
         RC(refresh_down_t(e));
         RC(step_program_launch(e->program, e->step + 1, e->stream));
         e->launches_per_step = 1;
@@ -1106,6 +1151,7 @@ static int prefill_impl(b200_engine* e, const int* ids_host, const int* lens_hos
     CU(cudaMemcpyAsync(ctxs, e->pf_pinned + Nt + 2 * B, (size_t)B * sizeof(int), cudaMemcpyHostToDevice, s));
     CU(cudaMemcpyAsync(e->seq_steps, e->pf_pinned + Nt + 3 * B, (size_t)B * sizeof(int), cudaMemcpyHostToDevice, s));
     CU(cudaEventRecord(e->pf_copied, s));
+    CU(cudaMemsetAsync(e->finished, 0, B, s));   // a prompt pass starts every sequence afresh
     auto linear = [&](const void* in, const void* W, void* out, int N, int K) {
         return b200_linear(in, W, nullptr, out, Nt, N, K, 1, dt, lws, lin_ws + 256, s);
     };
@@ -1323,6 +1369,14 @@ static int generate_impl(b200_engine* e, const int* prompt_ids_host, const int* 
     if (!e || !prompt_ids_host || !out_ids || max_new_tokens < 1) return B200_EINVAL;
     const int B = e->batch;
     std::vector<int> cur(B), done(B, 0), count(B, 0);
+    // batches: a sequence that has produced eos_id is retired on the device (no more KV traffic for it) while the others
+    // go on - the reference's `finished` flags; restored to the caller's setting on the way out
+    const int eos_before = e->eos_id;
+    struct Restore {
+        b200_engine* e; int eos;
+        ~Restore() { if (e->eos_id != eos) b200_engine_set_eos(e, eos); }
+    } restore{e, eos_before};
+    if (B > 1 && eos_id >= 0 && e->eos_id != eos_id) b200_engine_set_eos(e, eos_id);
     int rc = lens_host ? b200_engine_prefill_ragged(e, prompt_ids_host, lens_host, cur.data())
                        : b200_engine_prefill(e, prompt_ids_host, prompt_len, cur.data());
     if (rc != 0) return rc > 0 ? -1000 - rc : rc;

@@ -40,9 +40,14 @@ __device__ __forceinline__ void quantize_row(const __half* __restrict__ src, uns
 // new token of every sequence: k, v of qkv [B, h+2hk, d] (already rotated) -> cache row step-1. grid = B*hk, 64 threads.
 __global__ void __launch_bounds__(64)
 kv_append_fp8_kernel(const __half* __restrict__ qkv, unsigned char* k8, unsigned char* v8, float* k_scale, float* v_scale,
-                     int head_num, int kv_head_num, int d, int max_seq, int step, const int* step_dev, int step_stride) {
+                     int head_num, int kv_head_num, int d, int max_seq, int step, const int* step_dev, int step_stride,
+                     const unsigned char* finished) {
     pdl_wait();
     const int b = blockIdx.x / kv_head_num, kvh = blockIdx.x - b * kv_head_num;
+    if (finished != nullptr && finished[b] != 0) {   // retired sequence: nothing enters its cache any more
+        pdl_launch_dependents();
+        return;
+    }
     const int st = step_dev ? step_dev[b * step_stride] : step;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const __half* tok = qkv + (size_t)b * (head_num + 2 * kv_head_num) * d;
@@ -99,6 +104,9 @@ kv_fill_fp8_kernel(unsigned char* cache, float* scale, size_t rows_total, int ma
 
 }  // namespace b200
 
+namespace b200 {
+const unsigned char* attn_finished_ptr();   // decode_attention.cu
+}
 using namespace b200;
 
 /* the new token's k, v (qkv [batch, h+2hk, d], after RoPE) -> row step-1 of the fp8 cache layer slice, quantised per row */
@@ -110,7 +118,7 @@ extern "C" int b200_kv_append_fp8(const void* qkv, void* k_cache8, void* v_cache
     B200_RETURN_IF(step < 1 || step > max_seq_len, B200_EINVAL);
     cudaError_t e = launch_k(kv_append_fp8_kernel, dim3(batch * kv_head_num), dim3(64), 0, (cudaStream_t)stream, true,
                              (const __half*)qkv, (unsigned char*)k_cache8, (unsigned char*)v_cache8, k_scale, v_scale,
-                             head_num, kv_head_num, head_size, max_seq_len, step, step_dev, step_stride);
+                             head_num, kv_head_num, head_size, max_seq_len, step, step_dev, step_stride, attn_finished_ptr());
     count_launch();
     return (int)e;
 }

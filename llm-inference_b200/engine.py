@@ -26,6 +26,8 @@ ENGINE_PROTOTYPES = {
     "b200_engine_create": (_vp, [C.POINTER(ModelConfig), _i]),
     "b200_engine_create_ex": (_vp, [C.POINTER(ModelConfig), _i, C.c_uint]),
     "b200_engine_kv_is_fp8": (_i, [_vp]),
+    "b200_engine_set_eos": (_i, [_vp, _i]),
+    "b200_engine_get_finished": (_i, [_vp, _vp]),
     "b200_engine_kv_dequant": (_i, [_vp, _vp, _vp]),
     "b200_engine_destroy": (None, [_vp]),
     "b200_engine_last_error": (C.c_char_p, []),
@@ -182,6 +184,15 @@ class Engine:
         """pyfunc(buf_ptr:int, count:int, dtype:int, stream_ptr:int) -> int"""
         self._cb = ALLREDUCE_FN(lambda buf, n, dt, st, user: int(pyfunc(buf, n, dt, st) or 0))
         self._ck(self.lib.b200_engine_set_allreduce(self.h, self._cb, None), "set_allreduce")
+
+    def set_eos(self, eos_id):
+        """sequence retirement (the reference's `finished` flags): -1 switches it off"""
+        self._ck(self.lib.b200_engine_set_eos(self.h, int(eos_id)), "set_eos")
+
+    def finished(self):
+        out = np.zeros(self.batch, np.uint8)
+        self._ck(self.lib.b200_engine_get_finished(self.h, out.ctypes.data_as(C.c_void_p)), "get_finished")
+        return out.astype(bool)
 
     def init_random(self, seed=1234, std=0.02):
         self._ck(self.lib.b200_engine_init_random(self.h, seed, std), "init_random")
