@@ -27,8 +27,16 @@ namespace b200 {
 constexpr int kStepWarps = 8;                         // consumer warps
 constexpr int kStepThreads = (kStepWarps + 1) * 32;   // + producer warp
 constexpr int kStepConsumers = kStepWarps * 32;
-constexpr int kSegB = 2048;                           // K-segment bytes per row per stage
-constexpr int kStageB = kStepWarps * 2 * kSegB;       // 32 KB: 8 row pairs
+// K-segment bytes per row per stage = the size of one bulk copy. 4 KB (round 2; was 2 KB): a stage is 64 KB, the ring
+// 3 stages. The SM's copy engine costs ~27 ns + bytes / 124 GB/s per copy, so 2 KB copies cap an SM at 47.8 GB/s - just
+// under its fair share of HBM - and 4 KB copies at 68 GB/s; the consumers pay their ~200-cycle hand-over once per 64 KB
+// instead of once per 32 KB. Round 1 measured 4 KB copies SLOWER (HBM saturated -> uneven service -> every one of the 5
+// grid barriers per layer waits for the slowest CTA); with 2 barriers per layer the balance flips: 2.70 -> 2.53 ms.
+#ifndef B200_STEP_SEG_KB
+#define B200_STEP_SEG_KB 4
+#endif
+constexpr int kSegB = B200_STEP_SEG_KB * 1024;
+constexpr int kStageB = kStepWarps * 2 * kSegB;       // 64 KB: 8 row pairs x 4 KB
 constexpr int kStepMaxStages = 6;
 constexpr int kStepScratchBytes = 6 * 1024;            // split-KV merge weights: nb*h*(splits+1) floats
 constexpr int kJS = kSegB / 16 / 32;                  // 16-byte packets per lane per segment
@@ -747,19 +755,23 @@ __device__ __noinline__ uint32_t gemv_consume(const StepOp& op, const StepParams
                 if (seg_pk == KSEG / 8) {
                     // whole segment (all but a row's last one): branch-free, every weight packet is loaded before the
                     // first FMA; same summation order as the guarded loop below
-                    Pack16 wa[kJS], wb[kJS];
+                    constexpr int CH = 4;   // packets per lane loaded before their FMAs (register budget)
 #pragma unroll
-                    for (int j = 0; j < kJS; ++j) {
-                        wa[j] = ld16(sa + (lane + 32 * j) * 16);
-                        wb[j] = ld16(sb + (lane + 32 * j) * 16);
-                    }
+                    for (int j0 = 0; j0 < kJS; j0 += CH) {
+                        Pack16 wa[CH], wb[CH];
 #pragma unroll
-                    for (int b = 0; b < NB; ++b) {
+                        for (int j = 0; j < CH; ++j) {
+                            wa[j] = ld16(sa + (lane + 32 * (j0 + j)) * 16);
+                            wb[j] = ld16(sb + (lane + 32 * (j0 + j)) * 16);
+                        }
 #pragma unroll
-                        for (int j = 0; j < kJS; ++j) {
-                            const Pack16 xv = ld16(xseg + (size_t)b * K + (size_t)(lane + 32 * j) * 8);
-                            acc_a[b] = dot16<__half>(wa[j], xv, acc_a[b]);
-                            acc_b[b] = dot16<__half>(wb[j], xv, acc_b[b]);
+                        for (int b = 0; b < NB; ++b) {
+#pragma unroll
+                            for (int j = 0; j < CH; ++j) {
+                                const Pack16 xv = ld16(xseg + (size_t)b * K + (size_t)(lane + 32 * (j0 + j)) * 8);
+                                acc_a[b] = dot16<__half>(wa[j], xv, acc_a[b]);
+                                acc_b[b] = dot16<__half>(wb[j], xv, acc_b[b]);
+                            }
                         }
                     }
                 } else {
