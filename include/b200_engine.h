@@ -79,9 +79,10 @@ enum {
 #define B200_ENGINE_FUSED 1u   /* fused GEMV prologues/epilogues (default)                    */
 #define B200_ENGINE_GRAPH 2u   /* CUDA-graph replay of the whole step (default)               */
 #define B200_ENGINE_PERSISTENT 4u /* with FUSED: ONE persistent cooperative kernel per step     */
-/* Default: all three for fp16 batch 1 (and fp32 / tensor-parallel engines, where PERSISTENT is
- * ignored); FUSED | GRAPH for fp16 batches >= 2 (the measured best): fused tensor-core
- * GEMVs up to 4 token rows; above, the reference launch order on the tcgen05 weight-streaming GEMM. */
+/* Default: all three for fp16 batches 1-2 (and fp32 / tensor-parallel engines, where PERSISTENT only applies once a
+ * b200_p2p communicator is attached and the mode asks for it); FUSED | GRAPH for fp16 batches >= 3 (the measured best,
+ * DESIGN 4c): fused tensor-core GEMVs up to 4 token rows; above, the reference launch order on the tcgen05
+ * weight-streaming GEMM. */
                                   /* (fp16, batch <= 4, tp_size 1; default where it applies)   */
 /* without FUSED the engine issues the reference's kernel sequence one launch* at a time
  * (rmsnorm, linear, rope, masked MHA, linear, fused add+norm, linear, act, linear, add) */

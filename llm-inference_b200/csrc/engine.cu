@@ -581,7 +581,9 @@ extern "C" b200_engine* b200_engine_create_ex(const b200_model_config* c, int ba
     // (the persistent kernel still runs the scalar FHFMA loop, issue-bound from 2 token rows on). So batch 1 keeps the
     // persistent kernel, fp16 batches 2-4 default to the graphed fused-GEMV order; batches >= 5 run the reference
     // launch order on the tcgen05 weight-streaming GEMM whatever the FUSED flag says (enqueue_step).
-    if (c->dtype == B200_F16 && c->tp_size == 1 && batch >= 2) e->mode = B200_ENGINE_FUSED | B200_ENGINE_GRAPH;
+    // Round 2 (2 grid barriers per layer, K-split o / down, 4 KB copies): batch 2 persistent 3.13 / 4.37 ms vs fused GEMV
+    // graph 3.31 / 4.38; batch 3 persistent 4.01 / 6.51 vs 3.71 / 5.08 -> the persistent kernel is the default up to batch 2.
+    if (c->dtype == B200_F16 && c->tp_size == 1 && batch >= 3) e->mode = B200_ENGINE_FUSED | B200_ENGINE_GRAPH;
     return e;
 }
 

@@ -169,8 +169,8 @@ class Engine:
                                buf[3 * k:4 * k].reshape(k, 1)], axis=1)
 
     def set_mode(self, fused=True, graph=True, persistent=False):
-        """A fresh engine runs the persistent whole-step kernel for fp16 batch 1 and the CUDA-graphed launch
-        fused-GEMV sequence for fp16 batches >= 2 (the measured best, engine.cu b200_engine_create);
+        """A fresh engine runs the persistent whole-step kernel for fp16 batches 1-2 and the CUDA-graphed
+        fused-GEMV sequence for fp16 batches >= 3 (the measured best, engine.cu b200_engine_create);
         an explicit set_mode() selects the multi-kernel paths unless persistent=True (which applies up to batch 4)."""
         flags = (MODE_FUSED if fused else 0) | (MODE_GRAPH if graph else 0) | (MODE_PERSISTENT if persistent else 0)
         self._ck(self.lib.b200_engine_set_mode(self.h, flags), "set_mode")
