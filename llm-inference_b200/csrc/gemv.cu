@@ -26,8 +26,11 @@ namespace b200 {
 
 constexpr int kGemvWarps = 8;                       // consumer warps == units per stage
 constexpr int kGemvThreads = (kGemvWarps + 1) * 32; // + producer warp
-constexpr int kSegBytes = 2048;                     // K-segment per row per stage
-constexpr int kStageBytes = kGemvWarps * 2 * kSegBytes;  // 32 KB
+#ifndef B200_GEMV_SEG_KB
+#define B200_GEMV_SEG_KB 2
+#endif
+constexpr int kSegBytes = B200_GEMV_SEG_KB * 1024;  // K-segment per row per stage = the size of one bulk copy
+constexpr int kStageBytes = kGemvWarps * 2 * kSegBytes;  // 32 KB at 2 KB segments
 constexpr int kMaxStages = 4;
 constexpr int kJ = kSegBytes / 16 / 32;  // 16B packets per lane per row-segment (=4)
 // Tensor-core consumer (fp16, 2..8 token rows): one FHFMA per weight element PER TOKEN makes the scalar loop
@@ -264,9 +267,10 @@ __global__ void __launch_bounds__(kGemvThreads, 1) gemv_stream_kernel(const Gemv
             const unsigned char* ar1 = st + (size_t)(gq + 8) * PITCH;
             const T* xr = xs + (size_t)gq * xp + (size_t)seg * KSEG;   // token gq (zero fragment when gq >= nb)
             const bool tok = gq < p.nb;
+            constexpr int KW = KSEG / kGemvWarps;   // this warp's k slice of the segment
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const int kk = warp * 128 + i * 16;
+            for (int i = 0; i < KW / 16; ++i) {
+                const int kk = warp * KW + i * 16;
                 if (kk < seg_len) {
                     const int o = (kk + 2 * tq) * 2;
                     const uint32_t a0 = *reinterpret_cast<const uint32_t*>(ar0 + o);
@@ -286,24 +290,27 @@ __global__ void __launch_bounds__(kGemvThreads, 1) gemv_stream_kernel(const Gemv
             const unsigned char* sa = ring + (size_t)slot * kStageBytes + (2 * warp) * kSegBytes;
             const unsigned char* sb = sa + kSegBytes;
             const T* xseg = xs + (size_t)seg * KSEG;
-            Pack16 wa[kJ], wb[kJ];
 #pragma unroll
-            for (int j = 0; j < kJ; ++j) {
-                const int pkt = lane + 32 * j;
-                if (pkt < seg_pk) {
-                    wa[j] = ld16(sa + pkt * 16);
-                    if (rb >= 0) wb[j] = ld16(sb + pkt * 16);
+            for (int j0 = 0; j0 < kJ; j0 += 4) {   // four packets per lane in flight (register budget)
+                Pack16 wa[4], wb[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int pkt = lane + 32 * (j0 + j);
+                    if (pkt < seg_pk) {
+                        wa[j] = ld16(sa + pkt * 16);
+                        if (rb >= 0) wb[j] = ld16(sb + pkt * 16);
+                    }
                 }
-            }
 #pragma unroll
-            for (int j = 0; j < kJ; ++j) {
-                const int pkt = lane + 32 * j;
-                if (pkt < seg_pk) {
+                for (int j = 0; j < 4; ++j) {
+                    const int pkt = lane + 32 * (j0 + j);
+                    if (pkt < seg_pk) {
 #pragma unroll
-                    for (int b = 0; b < NB; ++b) {
-                        const Pack16 xv = ld16(xseg + (size_t)b * xp + (size_t)pkt * E);
-                        acc_a[b] = dot16<T>(wa[j], xv, acc_a[b]);
-                        if (rb >= 0) acc_b[b] = dot16<T>(wb[j], xv, acc_b[b]);
+                        for (int b = 0; b < NB; ++b) {
+                            const Pack16 xv = ld16(xseg + (size_t)b * xp + (size_t)pkt * E);
+                            acc_a[b] = dot16<T>(wa[j], xv, acc_a[b]);
+                            if (rb >= 0) acc_b[b] = dot16<T>(wb[j], xv, acc_b[b]);
+                        }
                     }
                 }
             }
