@@ -192,6 +192,7 @@ def cpu_baseline_hf(wl, n_layers=8, n_decode=12):
     steps and not scaled)."""
     import torch
     from transformers import LlamaConfig, LlamaForCausalLM
+    torch.set_num_threads(os.cpu_count() or 1)   # torchrun exports OMP_NUM_THREADS=1: this leg uses all host cores
     ctx = min(wl["context"], 512)
     cfg = LlamaConfig(hidden_size=4096, intermediate_size=11008, num_hidden_layers=n_layers, num_attention_heads=32,
                       num_key_value_heads=32, vocab_size=32000, max_position_embeddings=4096, rms_norm_eps=1e-5)
