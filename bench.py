@@ -56,6 +56,9 @@ def parse():
     ap.add_argument("--kv-fp8", action="store_true",
                     help="cfg4: fp8 (e4m3) KV cache with one scale per cached row (B200_ENGINE_KV_FP8); an engine option, "
                          "not the reference's cache type - the line says so in config.kv_cache")
+    ap.add_argument("--kv-paged", action="store_true",
+                    help="cfg4: paged KV cache (B200_ENGINE_KV_PAGED: page pools [n_pages, hk, 128, d] + one page list per "
+                         "sequence); same arithmetic and results as the dense cache, the line says so in config.kv_cache")
     return ap.parse_args()
 
 
@@ -730,10 +733,20 @@ def verify_decode(pkg, eng, model_shape, weight_seed, ctx, kv_seed, ids0, n_step
     chk.set_mode(fused=False, graph=False)
     chk.fill_kv_random(ctx, seed=kv_seed, amp=0.5)
     eng.fill_kv_random(ctx, seed=kv_seed, amp=0.5)
-    kc, vc = eng.kv_caches()
     kc2, vc2 = chk.kv_caches()
-    kc2[:, :, :, :ctx].copy_(kc[:, :nb, :, :ctx])
-    vc2[:, :, :, :ctx].copy_(vc[:, :nb, :, :ctx])
+    if getattr(eng, "kv_paged", False):   # rows of the first nb sequences straight out of their pages
+        kp, vp = eng.kv_pools()
+        tab = eng.kv_page_table().cpu()
+        npg = (ctx + 127) // 128
+        for b in range(nb):
+            pages = tab[b, :npg].long().cuda()
+            for pool, dst in ((kp, kc2), (vp, vc2)):
+                rows = pool[:, pages].permute(0, 2, 1, 3, 4).reshape(pool.shape[0], pool.shape[2], npg * 128, pool.shape[4])
+                dst[:, b, :, :ctx].copy_(rows[:, :, :ctx])
+    else:
+        kc, vc = eng.kv_caches()
+        kc2[:, :, :, :ctx].copy_(kc[:, :nb, :, :ctx])
+        vc2[:, :, :, :ctx].copy_(vc[:, :nb, :, :ctx])
     ids = np.ascontiguousarray(ids0, dtype=np.int32)
     worst, same, compared = 0.0, 0, 0
     for _ in range(n_steps):
@@ -923,7 +936,7 @@ def main():
     ctx, K, W = wl["context"], args.steps, args.warmup
     W = max(W, 3)
     max_seq = ctx + 2 * (W + K) + 8
-    eng = E.Engine(B_local, max_seq, dtype=capi.F16, kv_fp8=args.kv_fp8, **L7B)
+    eng = E.Engine(B_local, max_seq, dtype=capi.F16, kv_fp8=args.kv_fp8, kv_paged=args.kv_paged, **L7B)
     eng.init_random(seed=1234 + rank, std=0.02)
     eng.fill_kv_random(ctx, seed=7 + rank, amp=0.5)   # context already in the cache (prefill is not the metric)
     kv_row_bytes = (128 + 4) if args.kv_fp8 else 256   # one cached K or V row of one head
@@ -975,7 +988,7 @@ def main():
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_src = "MEASURED_PEAKS.json hbm_gbs (burst copy)" if peaks else "fallback 6650 GB/s"
-    if rank == 0 and B_local > 8 and not args.kv_fp8:
+    if rank == 0 and B_local > 8 and not args.kv_fp8 and not args.kv_paged:
         # batched decode at long context: the split-KV decode attention moves 84% of the step's bytes
         kc, vc = eng.kv_caches()
         L_now = eng.step
@@ -1009,7 +1022,7 @@ def main():
                 "per_launch_us": round(g_ms * 1e3 / 64, 2), "algorithmic_bytes_per_launch": per_launch,
                 "peak_source": peak_src,
                 "note": f"32 layers of split-KV decode attention at batch {B_local} x KV {L_now}, CUDA-graph replay"}
-    elif rank == 0 and not args.kv_fp8:
+    elif rank == 0 and not args.kv_fp8 and not args.kv_paged:
         H, I, V = 4096, 11008, 32000
         nb = min(B_local, 8)
         x_h = torch.randn(nb, H, device="cuda").half() * 0.1
@@ -1065,12 +1078,13 @@ def main():
     tok_s = B_total * K / (ms_max * 1e-3)
     e2e_tok_s = B_total * K / (e2e_ms_max * 1e-3)
     step_bytes = eng.weight_bytes - 2 * 32000 * 4096 + 0 + B_local * 2 * 32 * 32 * kv_row_bytes * (ctx + W + K // 2)
-    if rank == 0 and args.kv_fp8:
+    if rank == 0 and (args.kv_fp8 or args.kv_paged):
         achieved = step_bytes / (ms / K * 1e-3) / 1e9
-        roof = {"bound": "hbm", "kernel": "whole decode step (decode_attn_split_fp8_kernel moves the cache)", "achieved": round(achieved, 1),
+        kern = "decode_attn_split_fp8_kernel" if args.kv_fp8 else "decode_attn_split_kernel<.., PAGED>"
+        roof = {"bound": "hbm", "kernel": f"whole decode step ({kern} moves the cache)", "achieved": round(achieved, 1),
                 "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": None,
                 "algorithmic_bytes_per_launch": int(step_bytes), "peak_source": peak_src,
-                "note": "bytes of one step with the fp8 cache (weights once + 132 B per cached K / V row) / step time"}
+                "note": f"bytes of one step (weights once + {kv_row_bytes} B per cached K / V row) / step time"}
     roof_aux = None
     if rank == 0 and eng.launches_per_step == 1:
         # the whole step is ONE launch of decode_step_kernel: that kernel is the dominant (only) one, its
@@ -1098,7 +1112,9 @@ def main():
                "scaling": wl["scaling"], "vs_baseline": None, "dtype": "f16", "data": "synthetic",
                "config": {"workload": wl["name"], "batch_total": B_total, "batch_per_gpu": B_local, "context": ctx,
                           "weights": "random-init N(0,0.02^2) fp16, 13.2 GB per GPU", "accumulate": "fp32",
-                          "kv_cache": "fp8 e4m3 + one fp32 scale per cached row (engine option)" if args.kv_fp8 else "fp16 (the reference's cache type)",
+                          "kv_cache": ("fp8 e4m3 + one fp32 scale per cached row (engine option)" if args.kv_fp8 else
+                                       f"fp16 in pages of 128 rows, {eng.kv_pages_total} pages per layer pool (engine option; bit-identical "
+                                       "results to the dense cache)" if args.kv_paged else "fp16 (the reference's cache type)"),
                           "l2": "inputs larger than L2 (13.2 GB of weights streamed per step vs 126 MB L2)",
                           "parallelism": f"dp{world} (independent requests, no collective)"},
                "e2e": {"value": round(e2e_tok_s, 2), "unit": "tok/s", "h2d_bytes_per_step": 4 * B_local,

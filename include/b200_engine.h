@@ -75,6 +75,16 @@ enum {
                                 * only the FIRST prompt pass of a sequence is supported. Not bit-compatible with the fp16
                                 * cache: tests/test_kv_fp8_gpu.py pins it to the oracle run on the same rounded rows. */
 
+#define B200_ENGINE_KV_PAGED 2u /* KV cache as page pools [layers][n_pages, hk, 128 rows, d] + one page list per sequence
+                                * (SURVEY 8 f4 "paged blocks"; b200_llama.h, csrc/kv_paged.cu) instead of max_seq rows
+                                * reserved per sequence slot. fp16 models, head size 128, head_num / kv_head_num in
+                                * {1,2,4,8}; not combinable with KV_FP8 yet. Bit-identical results to the dense cache on
+                                * the same launch order (tests/test_kv_paged_gpu.py). Decode runs the reference launch order
+                                * with b200_decode_attention_paged; a prompt pass attends over a dense scratch slice and
+                                * scatters its rows into pages (FIRST prompt pass of a sequence only). Pages are taken
+                                * when a sequence grows into them, returned by reset / a new prompt pass /
+                                * b200_engine_release_finished; an empty pool fails the call with B200_ENOMEM. */
+
 /* mode flags for b200_engine_set_mode */
 #define B200_ENGINE_FUSED 1u   /* fused GEMV prologues/epilogues (default)                    */
 #define B200_ENGINE_GRAPH 2u   /* CUDA-graph replay of the whole step (default)               */
@@ -124,6 +134,19 @@ b200_engine* b200_engine_create_ex(const b200_model_config* cfg, int batch, unsi
  * Flags are cleared by reset / fill_kv_random / every prompt pass. */
 int b200_engine_set_eos(b200_engine* e, int eos_id);
 int b200_engine_get_finished(b200_engine* e, unsigned char* flags_host /* [batch] */);
+/* create_ex with the size of each layer's page pool (B200_ENGINE_KV_PAGED; 0 = batch * ceil(max_seq_len / 128)) */
+b200_engine* b200_engine_create_paged(const b200_model_config* cfg, int batch, unsigned flags, int n_pages);
+int b200_engine_kv_is_paged(const b200_engine* e);
+/* paged cache: pool size / pages currently free / DEVICE page lists [batch, ceil(max_seq_len / 128)] */
+int b200_engine_kv_pages_total(const b200_engine* e);
+int b200_engine_kv_pages_free(const b200_engine* e);
+const int* b200_engine_kv_page_table(const b200_engine* e);
+/* paged cache: the pages of every sequence whose `finished` flag is set (b200_engine_set_eos) go back to the pool;
+ * returns the number of pages released (>= 0). Synchronises the engine's stream. */
+int b200_engine_release_finished(b200_engine* e);
+/* paged cache: rows [0, cached rows of sequence b) of K and V gathered into caller DEVICE buffers laid out as the
+ * reference's dense cache [layers, B, hk, max_seq, d] (tests; rows beyond a sequence's length are left untouched) */
+int b200_engine_kv_gather(b200_engine* e, void* k_dst, void* v_dst);
 int b200_engine_kv_is_fp8(const b200_engine* e);
 /* fp8 cache only: K and V dequantised to fp16 into caller DEVICE buffers [layers, B, hk, max_seq, d] (tests) */
 int b200_engine_kv_dequant(b200_engine* e, void* k_dst, void* v_dst);

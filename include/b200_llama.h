@@ -34,6 +34,7 @@ extern "C" {
 #define B200_EINVAL (-1)       /* bad shape / null pointer / misalignment */
 #define B200_EUNSUPPORTED (-2) /* shape outside what the kernel covers */
 #define B200_EWORKSPACE (-3)   /* workspace missing or too small */
+#define B200_ENOMEM (-4)       /* a fixed-size pool (the KV page pool of a paged engine) is exhausted */
 
 /* library identity; b200_abi_version() bumps when a signature changes */
 int b200_abi_version(void);
@@ -287,6 +288,32 @@ int b200_decode_attention_fp8(const void* qkv, const void* k_cache8, const void*
 int b200_kv_quantize_fp8(const void* src, void* dst8, float* scale, const int* n_rows, const int* dst_row0, int batch,
                          int kv_head_num, int src_seq, int max_seq_len, int head_size, int max_rows, void* stream);
 int b200_kv_dequant_fp8(const void* src8, const float* scale, void* dst, size_t rows, int head_size, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * Paged KV cache, SURVEY 8 f4 - the other evolution of [layers,B,hk,max_seq,d] (src/models/llama/llama.cpp:77-78):
+ * a layer's K (V) is a pool of pages [n_pages, hk, B200_KV_PAGE_ROWS, d]; sequence b owns the pages listed in
+ * page_table[b * max_pages + i] (DEVICE int, one list for all layers), cache row r of the sequence = row r % 128 of
+ * page r / 128. No reference counterpart: the reference reserves max_seq rows per sequence slot.
+ *   b200_decode_attention_paged  launchDecoderMaskedMHA (fused_decoder_self_attention.cu:317) over the pages: same
+ *                            kernel, split / combine and semantics as b200_decode_attention_ragged (append_kv writes
+ *                            the new row into the page that holds row step-1, which the list must already name);
+ *                            fp16, head size 128, head_num / kv_head_num in {1,2,4,8}. seq_steps_dev NULL: every
+ *                            sequence is at max_step; step_stride 0: one shared device step, 1: one per sequence.
+ *   b200_kv_scatter_pages    rows t < n_rows[b] of a dense slice [batch, hk, src_seq, d] -> rows dst_row0[b] + t of the
+ *                            sequence's pages (the prompt pass: launchConcatKVCache concat_past_kv.cu:103 into pages)
+ *   b200_kv_gather_pages     rows [0, n_rows[b]) of the pages -> the dense slice [batch, hk, dst_seq, d] (tests)
+ * elem_bytes: 2 (fp16), 4 (fp32) or 1; n_rows / dst_row0: DEVICE int [batch]; max_rows >= every n_rows[b].
+ * ------------------------------------------------------------------------------------ */
+#define B200_KV_PAGE_ROWS 128
+int b200_decode_attention_paged(const void* qkv, void* k_pool_layer, void* v_pool_layer, const int* page_table,
+                                int max_pages, void* out, void* workspace, size_t workspace_bytes, int batch,
+                                int head_num, int kv_head_num, int head_size, int max_step, const int* seq_steps_dev,
+                                int step_stride, int append_kv, void* stream);
+int b200_kv_scatter_pages(const void* src, void* pool, const int* page_table, int max_pages, const int* n_rows,
+                          const int* dst_row0, int batch, int kv_head_num, int src_seq, int head_size, int elem_bytes,
+                          int max_rows, void* stream);
+int b200_kv_gather_pages(const void* pool, void* dst, const int* page_table, int max_pages, const int* n_rows, int batch,
+                         int kv_head_num, int dst_seq, int head_size, int elem_bytes, int max_rows, void* stream);
 
 /* Prefill attention without materialising scores / mask / repeated KV (replaces
  * context_attention.cpp:136-161: RepeatKV + QK^T + ScaleMaskSoftmax + PV + transpose):

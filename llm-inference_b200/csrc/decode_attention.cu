@@ -37,7 +37,14 @@ struct AttnParams {
     const float* k_scale;   // fp8 cache only: one scale per cached row, [B, hk, max_seq]
     const float* v_scale;
     const unsigned char* finished;   // optional [B]: a retired sequence neither appends nor reads its cache (output 0)
+    // paged cache (b200_decode_attention_paged): k_cache / v_cache are page pools [n_pages, hk, kPageRows, d] and row
+    // `key` of sequence b lives in page page_table[b * max_pages + key / kPageRows]
+    const int* page_table;
+    int max_pages;
 };
+constexpr int kPageRows = B200_KV_PAGE_ROWS;
+constexpr int kPageShift = 7;
+static_assert(kPageRows == 1 << kPageShift, "page size");
 
 // `finished` flags for the launches that follow on this host thread (NULL = off): the reference passes a
 // TensorWrapper<bool>* finished to launchDecoderMaskedMHA (fused_decoder_self_attention.h:10-19) and never reads it;
@@ -52,7 +59,7 @@ __device__ __forceinline__ float exp_guard(float m, float M) {
     return (m == -INFINITY) ? 0.f : expf(m - M);
 }
 
-template <typename T, int G, int PR>
+template <typename T, int G, int PR, bool PAGED = false>
 __global__ void __launch_bounds__(kAttnWarps * 32)
 decode_attn_split_kernel(const AttnParams p) {
     constexpr int E = DT<T>::kPer16B;
@@ -68,8 +75,17 @@ decode_attn_split_kernel(const AttnParams p) {
     const int pi = lane % PR, ks = lane / PR;
     const int qkv_heads = p.head_num + 2 * p.kv_head_num;
     const T* tok = reinterpret_cast<const T*>(p.qkv) + (size_t)b * qkv_heads * D;
-    T* kc = reinterpret_cast<T*>(p.k_cache) + ((size_t)b * p.kv_head_num + kvh) * p.max_seq_len * D;
-    T* vc = reinterpret_cast<T*>(p.v_cache) + ((size_t)b * p.kv_head_num + kvh) * p.max_seq_len * D;
+    // dense: the (b, kvh) slice of [B, hk, max_seq, d]; paged: the pool, rows found through the sequence's page list
+    T* kc = reinterpret_cast<T*>(p.k_cache) + (PAGED ? (size_t)0 : ((size_t)b * p.kv_head_num + kvh) * p.max_seq_len * D);
+    T* vc = reinterpret_cast<T*>(p.v_cache) + (PAGED ? (size_t)0 : ((size_t)b * p.kv_head_num + kvh) * p.max_seq_len * D);
+    const int* pages = PAGED ? p.page_table + (size_t)b * p.max_pages : nullptr;
+    auto row_off = [&](int key) -> size_t {   // element offset of cache row `key` from kc / vc
+        if (PAGED) {
+            const int pg = __ldg(pages + (key >> kPageShift));
+            return (((size_t)pg * p.kv_head_num + kvh) * kPageRows + (size_t)(key & (kPageRows - 1))) * D;
+        }
+        return (size_t)key * D;
+    };
 
     // keys of this split
     const int splits = gridDim.y;
@@ -81,11 +97,11 @@ decode_attn_split_kernel(const AttnParams p) {
     // append the new token's k,v (reference :170-172, :274-276) - only the CTA that will read it
     if (p.append_kv && k0 <= step - 1 && step - 1 < k1) {
         if (threadIdx.x < PR) {
-            st16(kc + (size_t)(step - 1) * D + threadIdx.x * E,
+            st16(kc + row_off(step - 1) + threadIdx.x * E,
                  ld16(tok + (size_t)(p.head_num + kvh) * D + threadIdx.x * E));
         } else if (threadIdx.x >= 32 && threadIdx.x < 32 + PR) {
             const int t = threadIdx.x - 32;
-            st16(vc + (size_t)(step - 1) * D + t * E,
+            st16(vc + row_off(step - 1) + t * E,
                  ld16(tok + (size_t)(p.head_num + p.kv_head_num + kvh) * D + t * E));
         }
     }
@@ -113,18 +129,24 @@ decode_attn_split_kernel(const AttnParams p) {
     for (int base = k0 + warp * KPI * kUnroll; base < k1; base += kAttnWarps * KPI * kUnroll) {
         Pack16 kp[kUnroll], vp[kUnroll];
         bool ok[kUnroll];
+        size_t ro[kUnroll];
 #pragma unroll
         for (int u = 0; u < kUnroll; ++u) {
             const int key = base + u * KPI + ks;
             ok[u] = key < k1;
-            // the row this kernel appended is taken from qkv, never re-read from the cache through the
-            // read-only (.nc) path: .nc is only defined for data no thread of the kernel writes
-            if (ok[u]) kp[u] = ld16_stream((key == new_row ? knew : kc + (size_t)key * D) + pi * E);
+            ro[u] = (PAGED && ok[u]) ? row_off(key) : 0;   // dense: recomputed from `key` below, nothing kept
         }
 #pragma unroll
         for (int u = 0; u < kUnroll; ++u) {
             const int key = base + u * KPI + ks;
-            if (ok[u]) vp[u] = ld16_stream((key == new_row ? vnew : vc + (size_t)key * D) + pi * E);
+            // the row this kernel appended is taken from qkv, never re-read from the cache through the
+            // read-only (.nc) path: .nc is only defined for data no thread of the kernel writes
+            if (ok[u]) kp[u] = ld16_stream((key == new_row ? knew : kc + (PAGED ? ro[u] : (size_t)key * D)) + pi * E);
+        }
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            const int key = base + u * KPI + ks;
+            if (ok[u]) vp[u] = ld16_stream((key == new_row ? vnew : vc + (PAGED ? ro[u] : (size_t)key * D)) + pi * E);
         }
         float s[G][kUnroll];
 #pragma unroll
@@ -651,6 +673,59 @@ extern "C" int b200_decode_attention(const void* qkv, void* k_cache_layer, void*
     return b200_decode_attention_ex(qkv, k_cache_layer, v_cache_layer, out, workspace,
                                     workspace_bytes, batch, head_num, kv_head_num, head_size,
                                     max_seq_len, step, nullptr, append_kv, dtype, stream);
+}
+
+// ------------------------------------------------------------------------------------------
+// Paged cache (SURVEY 8 f4 "paged blocks"): the reference's dense [layers, B, hk, max_seq, d] (llama.cpp:77-78) reserves
+// max_seq rows for every sequence slot; here a layer's K (V) is a pool of pages [n_pages, hk, 128 rows, d] and a
+// sequence owns the pages its page list names ([batch, max_pages] int, shared by all layers). Same kernel, same
+// split / combine, same semantics as b200_decode_attention_ragged; the only difference is the row address. fp16,
+// head size 128 (a 256-byte row), head_num / kv_head_num in {1, 2, 4, 8}.
+// ------------------------------------------------------------------------------------------
+extern "C" int b200_decode_attention_paged(const void* qkv, void* k_pool_layer, void* v_pool_layer, const int* page_table,
+                                           int max_pages, void* out, void* workspace, size_t workspace_bytes, int batch,
+                                           int head_num, int kv_head_num, int head_size, int max_step,
+                                           const int* seq_steps_dev, int step_stride, int append_kv, void* stream) {
+    B200_RETURN_IF(!qkv || !k_pool_layer || !v_pool_layer || !page_table || !out, B200_EINVAL);
+    B200_RETURN_IF(batch <= 0 || head_num <= 0 || kv_head_num <= 0 || max_pages <= 0 || head_num % kv_head_num != 0, B200_EINVAL);
+    B200_RETURN_IF(max_step < 1 || max_step > max_pages * kPageRows, B200_EINVAL);
+    B200_RETURN_IF(step_stride != 0 && step_stride != 1, B200_EINVAL);
+    const int G = head_num / kv_head_num;
+    B200_RETURN_IF(head_size != 128 || (G != 1 && G != 2 && G != 4 && G != 8), B200_EUNSUPPORTED);
+    auto al = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15u) == 0; };
+    B200_RETURN_IF(!al(qkv) || !al(k_pool_layer) || !al(v_pool_layer), B200_EINVAL);
+    cudaStream_t s = (cudaStream_t)stream;
+    AttnParams p{};
+    p.qkv = qkv; p.k_cache = k_pool_layer; p.v_cache = v_pool_layer; p.out = out;
+    p.batch = batch; p.head_num = head_num; p.kv_head_num = kv_head_num; p.head_size = head_size;
+    p.max_seq_len = max_pages * kPageRows; p.step = max_step; p.step_dev = seq_steps_dev; p.step_stride = step_stride;
+    p.append_kv = append_kv;
+    p.finished = g_attn_finished;
+    p.page_table = page_table; p.max_pages = max_pages;
+    const int splits = attn_pick_splits(batch, kv_head_num, max_step, G);
+    if (splits > 1) {
+        const size_t ml = (size_t)batch * head_num * splits * 2 * sizeof(float);
+        const size_t need = ((ml + 255) & ~(size_t)255) + (size_t)batch * head_num * splits * head_size * sizeof(float);
+        B200_RETURN_IF(!workspace || workspace_bytes < need, B200_EWORKSPACE);
+        p.part_ml = reinterpret_cast<float*>(workspace);
+        p.part_o = reinterpret_cast<float*>((char*)workspace + ((ml + 255) & ~(size_t)255));
+    }
+    constexpr int PR = 16, D = 128;
+    cudaError_t e = cudaErrorInvalidValue;
+#define CASE(g)                                                                                                   \
+    if (G == g)                                                                                                   \
+        e = launch_k(decode_attn_split_kernel<__half, g, PR, true>, dim3(batch * kv_head_num, splits),            \
+                     dim3(kAttnWarps * 32), (size_t)kAttnWarps * g * (2 + D) * sizeof(float), s, true, p);
+    CASE(1) CASE(2) CASE(4) CASE(8)
+#undef CASE
+    count_launch();
+    if (e != cudaSuccess) return (int)e;
+    if (splits > 1) {
+        e = launch_k(decode_attn_combine_kernel<__half>, dim3(batch * head_num), dim3(128), 0, s, true,
+                     (const float*)p.part_ml, (const float*)p.part_o, (__half*)p.out, splits, head_size);
+        count_launch();
+    }
+    return (int)e;
 }
 
 // ------------------------------------------------------------------------------------------

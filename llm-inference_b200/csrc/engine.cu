@@ -64,6 +64,17 @@ struct b200_engine {
     size_t kv_esz = 0;            // bytes per cached element (esz, or 1)
     float *k_scale = nullptr, *v_scale = nullptr;   // [layers, B, hk, max_seq]
     size_t layer_kv_rows = 0;
+    // paged KV cache (B200_ENGINE_KV_PAGED, kv_paged.cu): k_cache / v_cache are [layers][n_pages, hk, 128, d] pools; one
+    // page list per sequence, shared by all layers. The host owns the allocator (free stack + pinned mirror of the lists);
+    // the device only ever reads the lists.
+    bool kv_paged = false;
+    int n_pages = 0, max_pages = 0;        // pool size; list length = ceil(max_seq / 128)
+    int* page_table = nullptr;             // device [batch, max_pages]
+    int* page_table_host = nullptr;        // pinned mirror (entries are only appended while a sequence lives)
+    int* page_rows_dev = nullptr;          // device [batch]: rows per sequence, for gather (tests)
+    std::vector<int> free_pages, seq_pages;
+    std::vector<char> seq_released;        // retired sequences whose pages went back (b200_engine_release_finished)
+    bool pages_dirty = false;              // the host lists hold entries the device copy does not have yet
     char* act_arena = nullptr;
     void *hidden, *residual, *qkv, *attn, *act, *gate_up, *logits, *partial;
     int *ids_cur, *ids_next, *step_dev;
@@ -458,7 +469,20 @@ extern "C" b200_engine* b200_engine_create(const b200_model_config* c, int batch
 }
 
 extern "C" b200_engine* b200_engine_create_ex(const b200_model_config* c, int batch, unsigned flags) {
+    return b200_engine_create_paged(c, batch, flags, 0);
+}
+
+/* n_pages: size of each layer's K (V) page pool with B200_ENGINE_KV_PAGED (0 = batch * ceil(max_seq_len / 128), the
+ * capacity of the dense cache); ignored without the flag */
+extern "C" b200_engine* b200_engine_create_paged(const b200_model_config* c, int batch, unsigned flags, int n_pages) {
     if (!c || batch < 1 || batch > c->max_batch) { fail("bad config / batch"); return nullptr; }
+    if (flags & B200_ENGINE_KV_PAGED) {
+        const int G = c->kv_head_num > 0 ? c->head_num / c->kv_head_num : 0;
+        if (c->dtype != B200_F16 || c->head_size != 128 || (G != 1 && G != 2 && G != 4 && G != 8) || (flags & B200_ENGINE_KV_FP8)) {
+            fail("B200_ENGINE_KV_PAGED needs fp16, head size 128, head_num / kv_head_num in {1, 2, 4, 8} and an fp16 cache");
+            return nullptr;
+        }
+    }
     if (flags & B200_ENGINE_KV_FP8) {
         const int G = c->kv_head_num > 0 ? c->head_num / c->kv_head_num : 0;
         if (c->dtype != B200_F16 || c->head_size != 128 || (G != 1 && G != 2 && G != 4)) {
@@ -522,6 +546,24 @@ extern "C" b200_engine* b200_engine_create_ex(const b200_model_config* c, int ba
     e->kv_esz = e->kv_fp8 ? 1 : es;
     e->layer_kv_elems = (size_t)batch * e->hk * c->max_seq_len * e->d;
     e->layer_kv_rows = (size_t)batch * e->hk * c->max_seq_len;
+    e->kv_paged = (flags & B200_ENGINE_KV_PAGED) != 0;
+    if (e->kv_paged) {
+        e->max_pages = (c->max_seq_len + B200_KV_PAGE_ROWS - 1) / B200_KV_PAGE_ROWS;
+        if (n_pages < 0) { fail("n_pages < 0"); b200_engine_destroy(e); return nullptr; }
+        e->n_pages = n_pages > 0 ? n_pages : batch * e->max_pages;
+        e->layer_kv_rows = (size_t)e->n_pages * e->hk * B200_KV_PAGE_ROWS;
+        e->layer_kv_elems = e->layer_kv_rows * e->d;
+        const size_t tb = (size_t)batch * e->max_pages * sizeof(int);
+        if ((err = cudaMalloc(&e->page_table, tb + (size_t)batch * sizeof(int))) != cudaSuccess) return fail_free("cudaMalloc(page lists)", err);
+        cudaMemset(e->page_table, 0, tb + (size_t)batch * sizeof(int));
+        e->page_rows_dev = e->page_table + (size_t)batch * e->max_pages;
+        if ((err = cudaMallocHost(&e->page_table_host, tb + (size_t)batch * sizeof(int))) != cudaSuccess) return fail_free("cudaMallocHost(page lists)", err);
+        memset(e->page_table_host, 0, tb + (size_t)batch * sizeof(int));
+        e->seq_pages.assign(batch, 0);
+        e->seq_released.assign(batch, 0);
+        e->free_pages.resize(e->n_pages);
+        for (int i = 0; i < e->n_pages; ++i) e->free_pages[i] = e->n_pages - 1 - i;   // page 0 is handed out first
+    }
     e->kv_bytes_each = e->layer_kv_elems * c->num_layers * e->kv_esz;
     if (e->kv_fp8) {
         const size_t sb = e->layer_kv_rows * c->num_layers * sizeof(float);
@@ -572,7 +614,7 @@ extern "C" b200_engine* b200_engine_create_ex(const b200_model_config* c, int ba
     const int ref_step0 = 1;  // reference `step` of the first token (tokens in cache + 1)
     cudaMemcpy(e->step_dev, &ref_step0, sizeof(int), cudaMemcpyHostToDevice);
     cudaDeviceSynchronize();
-    if (!e->kv_fp8) build_program(e);   // the persistent step kernel reads and appends an fp16 cache
+    if (!e->kv_fp8 && !e->kv_paged) build_program(e);   // the persistent step kernel reads and appends a dense fp16 cache
     // default launch order by batch (measured, tools/order_sweep.sh + route_sweep.sh, 7B fp16, ms per step at
     // context 512 / 4096; GEMV = the tensor-core consumer, gemv.cu):
     //   batch 2: persistent 3.53 / 4.72, fused GEMV graph 3.30 / 4.24, reference launch order graph 3.49 / 4.42
@@ -605,6 +647,8 @@ extern "C" void b200_engine_destroy(b200_engine* e) {
     cudaFree(e->v_cache);
     cudaFree(e->k_scale);
     cudaFree(e->v_scale);
+    cudaFree(e->page_table);
+    if (e->page_table_host) cudaFreeHost(e->page_table_host);
     cudaFree(e->act_arena);
     delete e;
 }
@@ -625,6 +669,32 @@ extern "C" void* b200_engine_k_cache(b200_engine* e) { return e->k_cache; }
 extern "C" void* b200_engine_v_cache(b200_engine* e) { return e->v_cache; }
 extern "C" int b200_engine_get_step(const b200_engine* e) { return e->step; }
 extern "C" int b200_engine_kv_is_fp8(const b200_engine* e) { return e && e->kv_fp8 ? 1 : 0; }
+extern "C" int b200_engine_kv_is_paged(const b200_engine* e) { return e && e->kv_paged ? 1 : 0; }
+extern "C" int b200_engine_kv_pages_total(const b200_engine* e) { return e && e->kv_paged ? e->n_pages : 0; }
+extern "C" int b200_engine_kv_pages_free(const b200_engine* e) { return e && e->kv_paged ? (int)e->free_pages.size() : 0; }
+extern "C" const int* b200_engine_kv_page_table(const b200_engine* e) { return e && e->kv_paged ? e->page_table : nullptr; }
+/* paged cache only: K and V rows of every sequence gathered into dense [layers, B, hk, max_seq, d] DEVICE buffers */
+extern "C" int b200_engine_kv_gather(b200_engine* e, void* k_dst, void* v_dst) {
+    if (!e || !e->kv_paged || !k_dst || !v_dst) return B200_EINVAL;
+    CU(cudaStreamSynchronize(e->stream));
+    int* rows_host = e->page_table_host + (size_t)e->batch * e->max_pages;
+    int max_rows = 0;
+    for (int b = 0; b < e->batch; ++b) {
+        rows_host[b] = std::min(e->seq_cached[b], e->seq_pages[b] * B200_KV_PAGE_ROWS);
+        max_rows = std::max(max_rows, rows_host[b]);
+    }
+    CU(cudaMemcpyAsync(e->page_rows_dev, rows_host, (size_t)e->batch * sizeof(int), cudaMemcpyHostToDevice, e->stream));
+    const size_t dense_layer = (size_t)e->batch * e->hk * e->cfg.max_seq_len * e->d * e->esz;
+    for (int l = 0; l < e->cfg.num_layers; ++l) {
+        const size_t po = (size_t)l * e->layer_kv_elems * e->esz;
+        RC(b200_kv_gather_pages(e->k_cache + po, (char*)k_dst + l * dense_layer, e->page_table, e->max_pages, e->page_rows_dev,
+                                e->batch, e->hk, e->cfg.max_seq_len, e->d, (int)e->esz, max_rows, e->stream));
+        RC(b200_kv_gather_pages(e->v_cache + po, (char*)v_dst + l * dense_layer, e->page_table, e->max_pages, e->page_rows_dev,
+                                e->batch, e->hk, e->cfg.max_seq_len, e->d, (int)e->esz, max_rows, e->stream));
+    }
+    CU(cudaStreamSynchronize(e->stream));
+    return B200_OK;
+}
 /* fp8 cache only: the whole K and V caches dequantised to fp16 into caller DEVICE buffers [layers, B, hk, max_seq, d] */
 extern "C" int b200_engine_kv_dequant(b200_engine* e, void* k_dst, void* v_dst) {
     if (!e || !e->kv_fp8 || !k_dst || !v_dst) return B200_EINVAL;
@@ -679,7 +749,57 @@ extern "C" int b200_engine_set_p2p(b200_engine* e, b200_p2p* comm) {
     return B200_OK;
 }
 
+// ------------------------------------------------------------------------------------------
+// page allocator of the paged KV cache (host side; the device only reads the lists)
+// ------------------------------------------------------------------------------------------
+// Entries of a living sequence's list are only ever APPENDED, so a queued list upload that runs late and picks up newer
+// entries is harmless (kernels ahead of it never look past their own row count). Pages change owner only through
+// release_pages, which callers run behind a stream synchronisation.
+static void release_pages(b200_engine* e, int b) {
+    int* list = e->page_table_host + (size_t)b * e->max_pages;
+    for (int i = e->seq_pages[b] - 1; i >= 0; --i) e->free_pages.push_back(list[i]);
+    e->seq_pages[b] = 0;
+}
+// make sure sequence b owns the pages of rows [0, rows); returns 1 if its list grew, 0 if not, < 0 on exhaustion
+static int ensure_pages(b200_engine* e, int b, int rows) {
+    const int need = (rows + B200_KV_PAGE_ROWS - 1) / B200_KV_PAGE_ROWS;
+    if (need > e->max_pages) return fail("paged KV: sequence longer than max_seq_len");
+    if (need <= e->seq_pages[b]) return 0;
+    if ((size_t)(need - e->seq_pages[b]) > e->free_pages.size())
+        return fail("paged KV: page pool exhausted (" + std::to_string(e->n_pages) + " pages of 128 rows)", B200_ENOMEM);
+    int* list = e->page_table_host + (size_t)b * e->max_pages;
+    while (e->seq_pages[b] < need) {
+        list[e->seq_pages[b]++] = e->free_pages.back();
+        e->free_pages.pop_back();
+    }
+    e->pages_dirty = true;
+    return 1;
+}
+static int upload_pages(b200_engine* e) {
+    CU(cudaMemcpyAsync(e->page_table, e->page_table_host, (size_t)e->batch * e->max_pages * sizeof(int),
+                       cudaMemcpyHostToDevice, e->stream));
+    e->pages_dirty = false;
+    return 0;
+}
+// pages for `rows_b[b]` rows of every sequence (rows_b[b] < 0: leave sequence b alone)
+static int ensure_all_pages(b200_engine* e, const int* rows_b) {
+    for (int b = 0; b < e->batch; ++b) {
+        if (rows_b[b] < 0) continue;
+        const int r = ensure_pages(e, b, rows_b[b]);
+        if (r < 0) return r;   // lists that grew before the failure stay marked dirty and go up with the next call
+    }
+    return e->pages_dirty ? upload_pages(e) : 0;
+}
+
 static int set_step(b200_engine* e, int n) {
+    if (e->kv_paged) {   // a new position for everybody: hand every page back, then take what n rows need
+        CU(cudaStreamSynchronize(e->stream));
+        for (int b = 0; b < e->batch; ++b) release_pages(e, b);
+        e->seq_released.assign(e->batch, 0);
+        std::vector<int> rows(e->batch, n);
+        const int rc = ensure_all_pages(e, rows.data());
+        if (rc != 0) return rc;
+    }
     e->step = n;
     e->seq_cached.assign(e->batch, n);
     e->ragged = false;
@@ -758,8 +878,38 @@ extern "C" int b200_engine_get_weight(b200_engine* e, int slot, int layer, void*
     return B200_OK;
 }
 
+/* paged cache: pages of the sequences the device has retired go back to the pool (they are never read again: the
+ * attention kernels skip a finished sequence). Returns the number of pages released. */
+extern "C" int b200_engine_release_finished(b200_engine* e) {
+    if (!e) return B200_EINVAL;
+    if (!e->kv_paged || e->eos_id < 0) return 0;
+    std::vector<unsigned char> flags(e->batch);
+    const int rc = b200_engine_get_finished(e, flags.data());   // synchronises the stream
+    if (rc != 0) return rc > 0 ? -1000 - rc : rc;
+    int released = 0;
+    for (int b = 0; b < e->batch; ++b)
+        if (flags[b] && e->seq_pages[b] > 0) {
+            released += e->seq_pages[b];
+            release_pages(e, b);
+            e->seq_released[b] = 1;
+        }
+    return released;
+}
+
 extern "C" int b200_engine_fill_kv_random(b200_engine* e, int len, uint64_t seed, float amp) {
     if (!e || len < 0 || len >= e->cfg.max_seq_len) return fail("fill_kv: len out of range");
+    if (e->kv_paged) {   // every page of every pool gets synthetic rows; set_step hands out the pages of `len` rows
+        const size_t prow = (size_t)e->cfg.num_layers * e->n_pages * e->hk;
+        const size_t n = prow * B200_KV_PAGE_ROWS * e->d;
+        size_t blocks = (n + 255) / 256;
+        if (blocks > 148 * 32) blocks = 148 * 32;
+        fill_uniform_rows_kernel<__half><<<(unsigned)blocks, 256, 0, e->stream>>>(
+            (__half*)e->k_cache, prow, B200_KV_PAGE_ROWS, B200_KV_PAGE_ROWS, e->d, seed * 2 + 1, amp);
+        fill_uniform_rows_kernel<__half><<<(unsigned)blocks, 256, 0, e->stream>>>(
+            (__half*)e->v_cache, prow, B200_KV_PAGE_ROWS, B200_KV_PAGE_ROWS, e->d, seed * 2 + 2, amp);
+        CU(cudaGetLastError());
+        return set_step(e, len);
+    }
     const size_t rows = (size_t)e->cfg.num_layers * e->batch * e->hk;
     if (len > 0 && e->kv_fp8) {
         RC(kv_fill_fp8(e->k_cache, e->k_scale, rows, e->cfg.max_seq_len, len, e->d, seed * 2 + 1, amp, e->stream));
@@ -867,7 +1017,8 @@ static int enqueue_step_body(b200_engine* e) {
     // fp16 batches of 5..8 also take the tensor-core path: eight x-rows of K = 11008 crowd the GEMV's weight ring out
     // of shared memory (measured at batch 8 x KV 4096: 12.0 ms per step fused vs the figure in DESIGN §4c)
     // (the fused qkv GEMV appends fp16 rows in its epilogue: an fp8 cache takes the reference launch order)
-    const bool fused = (e->mode & B200_ENGINE_FUSED) && B <= (dt == B200_F16 && !tp ? 4 : B200_GEMV_MAX_TOKENS) && !e->kv_fp8;
+    const bool fused = (e->mode & B200_ENGINE_FUSED) && B <= (dt == B200_F16 && !tp ? 4 : B200_GEMV_MAX_TOKENS) && !e->kv_fp8 &&
+                       !e->kv_paged;
     auto linear = [&](const void* x, const void* W, void* y, int N, int K) {
         return b200_linear(x, W, nullptr, y, B, N, K, 1, dt, e->lin_ws, e->lin_ws_bytes, s);
     };
@@ -923,6 +1074,16 @@ static int enqueue_step_body(b200_engine* e) {
                 RC(b200_kv_append_fp8(e->qkv, kc, vc, ksc, vsc, B, e->h, e->hk, e->d, e->cfg.max_seq_len, ref_step, sd, stride, s));
                 RC(b200_decode_attention_fp8(e->qkv, kc, vc, ksc, vsc, e->attn, e->attn_ws, e->attn_ws_bytes, B, e->h, e->hk,
                                              e->d, e->cfg.max_seq_len, ref_step, sd, stride, s));
+            } else if (e->kv_paged) {   // RoPE, then the attention appends the new row into / reads the rows out of the pages
+                if (e->ragged)
+                    RC(b200_rope_decode_ragged(e->qkv, B, e->h, e->hk, e->d, e->seq_steps, e->cfg.rotary_dim,
+                                               e->cfg.rotary_base, e->rope_den, dt, s));
+                else
+                    RC(b200_rope_decode_tab(e->qkv, B, e->h, e->hk, e->d, ref_step, e->step_dev, e->cfg.rotary_dim,
+                                            e->cfg.rotary_base, e->rope_den, dt, s));
+                RC(b200_decode_attention_paged(e->qkv, kc, vc, e->page_table, e->max_pages, e->attn, e->attn_ws, e->attn_ws_bytes,
+                                               B, e->h, e->hk, e->d, ref_step, e->ragged ? e->seq_steps : e->step_dev,
+                                               e->ragged ? 1 : 0, 1, s));
             } else if (e->ragged) {   // per-sequence positions and key counts; ref_step (the longest) only sizes the launch
                 RC(b200_rope_decode_ragged(e->qkv, B, e->h, e->hk, e->d, e->seq_steps, e->cfg.rotary_dim,
                                            e->cfg.rotary_base, e->rope_den, dt, s));
@@ -971,6 +1132,13 @@ static void stepped(b200_engine* e) {
 
 static int run_step(b200_engine* e) {
     if (e->step + 1 > e->cfg.max_seq_len) return fail("KV cache full (step == max_seq_len)");
+    if (e->kv_paged) {   // the row this step appends may open a new page (a retired sequence with no pages stays without)
+        std::vector<int> rows(e->batch);
+        for (int b = 0; b < e->batch; ++b)
+            rows[b] = e->seq_released[b] ? -1 : e->seq_cached[b] + 1;
+        const int rc = ensure_all_pages(e, rows.data());
+        if (rc != 0) return rc;
+    }
     if (e->program && !e->ragged && (e->mode & B200_ENGINE_FUSED) && (e->mode & B200_ENGINE_PERSISTENT) &&
         !(e->eos_id >= 0 && e->batch > 1)) {
         RC(refresh_down_t(e));
@@ -1106,6 +1274,26 @@ static int prefill_impl(b200_engine* e, const int* ids_host, const int* lens_hos
                 return fail("fp8 KV cache: a prompt pass over an existing history is not supported (first pass only)",
                             B200_EUNSUPPORTED);
     }
+    if (e->kv_paged) {
+        if (!flash) return fail("paged KV cache: the prompt pass needs the flash context attention", B200_EUNSUPPORTED);
+        for (int b = 0; b < B; ++b)
+            if (hist_b[b] != 0)
+                return fail("paged KV cache: a prompt pass over an existing history is not supported (first pass only)",
+                            B200_EUNSUPPORTED);
+        // every sequence starts afresh: its old pages go back, then it takes the pages of its prompt
+        CU(cudaStreamSynchronize(s));
+        for (int b = 0; b < B; ++b) release_pages(e, b);
+        e->seq_released.assign(B, 0);
+        for (int b = 0; b < B; ++b) {
+            const int r = ensure_pages(e, b, len_b[b]);
+            if (r < 0) {   // the pool cannot hold these prompts: leave an empty, consistent engine behind
+                const std::string why = g_err;
+                set_step(e, 0);
+                return fail(why, r);
+            }
+        }
+        RC(upload_pages(e));
+    }
     size_t o_mask = 0, o_kr = 0, o_vr = 0, o_sc = 0, o_pv = 0;
     if (!flash) {   // reference-order attention: dense mask, repeated KV, materialised scores
         o_mask = take((size_t)B * len * ctx * es);
@@ -1181,6 +1369,16 @@ static int prefill_impl(b200_engine* e, const int* ids_host, const int* lens_hos
                                     len, e->cfg.max_seq_len, e->d, len, s));
             RC(b200_kv_quantize_fp8(v, e->v_cache + layer_off, e->v_scale + (size_t)l * e->layer_kv_rows, lens, hists, B, e->hk,
                                     len, e->cfg.max_seq_len, e->d, len, s));
+        } else if (e->kv_paged) {
+            // paged cache: k, v of this pass go to a dense scratch slice [B, hk, len, d] (history is empty, checked above), the
+            // flash kernel attends over it, and the rows are scattered into the sequences' pages
+            RC(b200_qkv_bias_rope_to_cache(q, k, v, qkv, nullptr, pad, hists, B, len, Nt, e->h, e->hk, e->d, len,
+                                           e->cfg.rotary_dim, e->cfg.rotary_base, dt, s));
+            RC(b200_context_attention(q, k, v, att, pad, lens, hists, B, len, Nt, e->h, e->hk, e->d, len, dt, s));
+            RC(b200_kv_scatter_pages(k, e->k_cache + layer_off * es, e->page_table, e->max_pages, lens, hists, B, e->hk, len,
+                                     e->d, (int)es, len, s));
+            RC(b200_kv_scatter_pages(v, e->v_cache + layer_off * es, e->page_table, e->max_pages, lens, hists, B, e->hk, len,
+                                     e->d, (int)es, len, s));
         } else {
         // bias/RoPE/transpose with ConcatKV folded in: k, v land in the cache rows directly
         RC(b200_qkv_bias_rope_to_cache(q, e->k_cache + layer_off * es, e->v_cache + layer_off * es, qkv, nullptr, pad, hists,
@@ -1386,13 +1584,15 @@ static int generate_impl(b200_engine* e, const int* prompt_ids_host, const int* 
     int steps = 0;
     for (int t = 0; t < max_new_tokens; ++t) {
         int alive = 0;
+        bool newly_done = false;
         for (int b = 0; b < B; ++b) {
             // the first token (from the prompt pass) is emitted unconditionally, as llama.cpp:410-413 does
-            if (!done[b] && t > 0 && cur[b] == eos_id) done[b] = 1;
+            if (!done[b] && t > 0 && cur[b] == eos_id) { done[b] = 1; newly_done = true; }
             if (!done[b]) { out_ids[(size_t)b * max_new_tokens + t] = cur[b]; count[b] = t + 1; ++alive; }
         }
         if (!alive || t == max_new_tokens - 1) break;
         if (e->step + 1 >= e->cfg.max_seq_len) break;   // cache full
+        if (newly_done && e->kv_paged) b200_engine_release_finished(e);   // retired sequences give their pages back
         rc = b200_engine_decode_step_host(e, nullptr, cur.data());   // continues from the ids the engine holds
         if (rc != 0) return rc > 0 ? -1000 - rc : rc;
         ++steps;

@@ -9,6 +9,7 @@ W_ATTN_NORM, W_QKV, W_O, W_FFN_NORM, W_GATE_UP, W_DOWN, W_EMBED, W_FINAL_NORM, W
 LAYER_SLOTS = (W_ATTN_NORM, W_QKV, W_O, W_FFN_NORM, W_GATE_UP, W_DOWN)
 MODE_FUSED, MODE_GRAPH, MODE_PERSISTENT = 1, 2, 4
 KV_FP8 = 1   # creation flag B200_ENGINE_KV_FP8
+KV_PAGED = 2   # creation flag B200_ENGINE_KV_PAGED
 
 
 class ModelConfig(C.Structure):
@@ -25,6 +26,13 @@ _vp, _i = C.c_void_p, C.c_int
 ENGINE_PROTOTYPES = {
     "b200_engine_create": (_vp, [C.POINTER(ModelConfig), _i]),
     "b200_engine_create_ex": (_vp, [C.POINTER(ModelConfig), _i, C.c_uint]),
+    "b200_engine_create_paged": (_vp, [C.POINTER(ModelConfig), _i, C.c_uint, _i]),
+    "b200_engine_kv_is_paged": (_i, [_vp]),
+    "b200_engine_kv_pages_total": (_i, [_vp]),
+    "b200_engine_kv_pages_free": (_i, [_vp]),
+    "b200_engine_kv_page_table": (_vp, [_vp]),
+    "b200_engine_release_finished": (_i, [_vp]),
+    "b200_engine_kv_gather": (_i, [_vp, _vp, _vp]),
     "b200_engine_kv_is_fp8": (_i, [_vp]),
     "b200_engine_set_eos": (_i, [_vp, _i]),
     "b200_engine_get_finished": (_i, [_vp, _vp]),
@@ -96,7 +104,7 @@ class Engine:
     """Owns one b200_engine on the current CUDA device."""
 
     def __init__(self, batch, max_seq_len, dtype=capi.F16, rms_eps=1e-5, rotary_base=10000.0,
-                 rotary_dim=None, tp_size=1, tp_rank=0, kv_fp8=False, **shape):
+                 rotary_dim=None, tp_size=1, tp_rank=0, kv_fp8=False, kv_paged=False, kv_pages=0, **shape):
         cfg = ModelConfig()
         for k, v in shape.items():
             setattr(cfg, k, v)
@@ -108,7 +116,9 @@ class Engine:
         self.np_dtype = np.float16 if dtype == capi.F16 else np.float32
         self.lib = _lib()
         self.kv_fp8 = bool(kv_fp8)
-        self.h = self.lib.b200_engine_create_ex(C.byref(cfg), batch, KV_FP8 if kv_fp8 else 0)
+        self.kv_paged = bool(kv_paged)
+        flags = (KV_FP8 if kv_fp8 else 0) | (KV_PAGED if kv_paged else 0)
+        self.h = self.lib.b200_engine_create_paged(C.byref(cfg), batch, flags, int(kv_pages))
         if not self.h:
             raise RuntimeError("[b200][ERROR] engine_create: " + self.lib.b200_engine_last_error().decode())
         self._cb = None
@@ -328,6 +338,11 @@ class Engine:
         td = torch.float16 if self.dtype == capi.F16 else torch.float32
         c = self.cfg
         shape = (c.num_layers, self.batch, c.kv_head_num // c.tp_size, c.max_seq_len, c.head_size)
+        if self.kv_paged:   # gathered COPIES laid out as the dense cache; rows beyond a sequence's length are zero
+            k = torch.zeros(shape, dtype=td, device="cuda")
+            v = torch.zeros(shape, dtype=td, device="cuda")
+            self._ck(self.lib.b200_engine_kv_gather(self.h, C.c_void_p(k.data_ptr()), C.c_void_p(v.data_ptr())), "kv_gather")
+            return k, v
         if self.kv_fp8:
             k = torch.empty(shape, dtype=torch.float16, device="cuda")
             v = torch.empty(shape, dtype=torch.float16, device="cuda")
@@ -335,6 +350,36 @@ class Engine:
             return k, v
         return (self._view(self.lib.b200_engine_k_cache(self.h), shape, td),
                 self._view(self.lib.b200_engine_v_cache(self.h), shape, td))
+
+    # ---- paged cache
+    @property
+    def kv_pages_total(self):
+        return self.lib.b200_engine_kv_pages_total(self.h)
+
+    @property
+    def kv_pages_free(self):
+        return self.lib.b200_engine_kv_pages_free(self.h)
+
+    def kv_page_table(self):
+        """torch view [batch, ceil(max_seq_len / 128)] int32 of the DEVICE page lists"""
+        import torch
+        n = (self.cfg.max_seq_len + 127) // 128
+        return self._view(self.lib.b200_engine_kv_page_table(self.h), (self.batch, n), torch.int32)
+
+    def kv_pools(self):
+        """torch views [layers, n_pages, kv_heads(local), 128, d] of the K and V page pools"""
+        import torch
+        c = self.cfg
+        shape = (c.num_layers, self.kv_pages_total, c.kv_head_num // c.tp_size, 128, c.head_size)
+        return (self._view(self.lib.b200_engine_k_cache(self.h), shape, torch.float16),
+                self._view(self.lib.b200_engine_v_cache(self.h), shape, torch.float16))
+
+    def release_finished(self):
+        """pages of the sequences the device has retired go back to the pool; returns the number released"""
+        n = self.lib.b200_engine_release_finished(self.h)
+        if n < 0:
+            self._ck(n, "release_finished")
+        return n
 
     def ids_out(self):
         import torch
