@@ -11,6 +11,7 @@
 //   warps 2-5 epilogue (both CTAs): own 128 rows from own TMEM, then a remote arrive on the leader's
 //             accumulator-empty barrier
 // GLU: as in gemm_tcgen05.cu — the leader's B half is 128 gate rows, the peer's the matching 128 up rows.
+#include <cstdio>
 #include "common.cuh"
 #include "launch_count.h"
 #include "tc_common.cuh"
@@ -32,9 +33,28 @@ struct Gemm2Params {
     int tokens, n_out;  // valid rows of A; valid output features (GLU: inter)
     int ldc, k_blocks;
     int m_tiles, n_tiles;   // tiles of 256 rows x (256 features | GLU: 128 features)
+    int group_m;            // tile order: bands of group_m row tiles swept over all column tiles (0: column-major over all rows)
 };
 
-template <bool GLU>
+// unit u -> (row tile, column tile). The clusters resident at one time work on ~74 consecutive units: with bands of
+// group_m row tiles they share group_m A tiles (L2-resident for the whole sweep of the band) and ~74 / group_m B tiles,
+// instead of ALL row tiles x 2 column tiles (A = 64 MB at 8192 tokens re-streamed for every pair of column tiles).
+__device__ __forceinline__ void tile_of_unit(const Gemm2Params& p, int n_tiles, int u, int& mt, int& nt) {
+    if (p.group_m <= 0) { mt = u % p.m_tiles; nt = u / p.m_tiles; return; }
+    const int per_band = p.group_m * n_tiles;
+    const int band = u / per_band, r = u - band * per_band;
+    const int rows = min(p.group_m, p.m_tiles - band * p.group_m);
+    nt = r / rows;
+    mt = band * p.group_m + (r - nt * rows);
+}
+
+// QUAD: a cluster of FOUR CTAs = two MMA pairs on the same 256 rows of A and two neighbouring column tiles. Every CTA
+// loads a 64-row box of A and multicasts it to its counterpart in the other pair, so a cluster reads A from L2 once
+// instead of twice: 48 KB instead of 64 KB per pair and K step (the cuBLAS kernel of this shape, nvjet ..._2x2_2cta, moves
+// the same 4.83 GB against the pair kernel's 6.44 GB at 8192 x 12288 x 4096). On a power-capped B200 the bytes moved set
+// the clock. A stage is free when BOTH pairs' MMAs have read it (empty barriers count two commits); each pair
+// keeps its own full barriers, accumulators and epilogue.
+template <bool GLU, bool QUAD>
 __global__ void __launch_bounds__(k2Threads, 1)
 gemm2_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const Gemm2Params p) {
     extern __shared__ __align__(1024) unsigned char smem[];
@@ -44,12 +64,16 @@ gemm2_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
     uint64_t* acc_empty = acc_full + 2;          // [2], used in the leader only
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + k2OffSlot);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint32_t rank = cluster_ctarank();     // 0 = leader
+    const uint32_t crank = cluster_ctarank();
+    const uint32_t rank = crank & 1u;            // position in the MMA pair, 0 = pair leader
+    const uint32_t pair = QUAD ? crank >> 1 : 0u;
+    const uint32_t leader = crank & ~1u;         // cluster rank of this pair's leader
+    constexpr int CS = QUAD ? 4 : 2;
     if (threadIdx.x == 0) {
         if (smem_u32(smem) & 1023u) __trap();
         for (int s = 0; s < k2Stages; ++s) {
             mbar_init(&full_bar[s], 1);
-            mbar_init(&empty_bar[s], 1);
+            mbar_init(&empty_bar[s], QUAD ? 2 : 1);   // one commit per pair that reads the stage
         }
         for (int a = 0; a < 2; ++a) {
             mbar_init(&acc_full[a], 1);
@@ -68,24 +92,31 @@ gemm2_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
     pdl_launch_dependents();
     pdl_wait();
 
-    const int units = p.m_tiles * p.n_tiles;
-    const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
+    const int n_tiles = QUAD ? p.n_tiles >> 1 : p.n_tiles;   // QUAD: a unit is two neighbouring column tiles
+    const int units = p.m_tiles * n_tiles;
+    const int cluster_id = blockIdx.x / CS, n_clusters = gridDim.x / CS;
 
     if (warp == 0) {
         // ================= TMA producer (both CTAs) =================
         int stage = 0;
         uint32_t phase = 0;
         for (int u = cluster_id; u < units; u += n_clusters) {
-            const int mt = u % p.m_tiles, nt = u / p.m_tiles;
-            const int a_row = mt * 256 + (int)rank * 128;
+            int mt, nt;
+            tile_of_unit(p, n_tiles, u, mt, nt);
+            if (QUAD) nt = 2 * nt + (int)pair;
+            const int a_row = mt * 256 + (int)rank * 128 + (QUAD ? (int)pair * 64 : 0);
             const int b_row = GLU ? (rank == 0 ? nt * 128 : p.n_out + nt * 128) : nt * 256 + (int)rank * 128;
             for (int kb = 0; kb < p.k_blocks; ++kb) {
                 mbar_wait_bounded(&empty_bar[stage], phase ^ 1);
                 if (lane == 0) {
                     unsigned char* sa = smem + (size_t)stage * k2StageBytes;
-                    const uint32_t leader_full = mapa_shared(smem_u32(&full_bar[stage]), 0);
+                    const uint32_t leader_full = mapa_shared(smem_u32(&full_bar[stage]), leader);
                     if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * k2StageBytes);   // both CTAs' boxes
-                    tma_load_2d_pair(sa, &map_a, kb * k2BK, a_row, leader_full);
+                    if (QUAD)   // my 64 rows of this position's A half, to me and to my counterpart in the other pair
+                        tma_load_2d_pair_multicast(sa + pair * (k2ABytes / 2), &map_a, kb * k2BK, a_row, leader_full,
+                                                   (uint16_t)((1u << rank) | (1u << (rank + 2))));
+                    else
+                        tma_load_2d_pair(sa, &map_a, kb * k2BK, a_row, leader_full);
                     tma_load_2d_pair(sa + k2ABytes, &map_b, kb * k2BK, b_row, leader_full);
                 }
                 __syncwarp();
@@ -112,8 +143,8 @@ gemm2_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
 #pragma unroll
                         for (int k = 0; k < k2BK / kUmmaK; ++k)
                             umma_f16_pair(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb > 0 || k > 0) ? 1u : 0u);
-                        umma_commit_pair(&empty_bar[stage], 3);                      // both producers may refill
-                        if (kb == p.k_blocks - 1) umma_commit_pair(&acc_full[acc], 3);   // both epilogues may read
+                        umma_commit_pair(&empty_bar[stage], QUAD ? 0xF : 3);         // the producers may refill
+                        if (kb == p.k_blocks - 1) umma_commit_pair(&acc_full[acc], (uint16_t)(3u << (2 * pair)));   // both epilogues of the pair may read
                     }
                     __syncwarp();
                     if (++stage == k2Stages) { stage = 0; phase ^= 1; }
@@ -128,7 +159,9 @@ gemm2_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
         int acc = 0;
         uint32_t acc_phase = 0;
         for (int u = cluster_id; u < units; u += n_clusters) {
-            const int mt = u % p.m_tiles, nt = u / p.m_tiles;
+            int mt, nt;
+            tile_of_unit(p, n_tiles, u, mt, nt);
+            if (QUAD) nt = 2 * nt + (int)pair;
             mbar_wait_bounded(&acc_full[acc], acc_phase);
             tc_fence_after();
             const int row = mt * 256 + (int)rank * 128 + quarter * 32 + lane;
@@ -194,7 +227,7 @@ gemm2_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive_cluster(mapa_shared(smem_u32(&acc_empty[acc]), 0));
+            if (lane == 0) mbar_arrive_cluster(mapa_shared(smem_u32(&acc_empty[acc]), leader));
             acc ^= 1;
             if (acc == 0) acc_phase ^= 1;
         }
@@ -208,9 +241,67 @@ gemm2_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_con
     }
 }
 
+static void fill_cluster_cfg(cudaLaunchConfig_t& cfg, cudaLaunchAttribute* attr, int grid, int cluster, cudaStream_t s, bool pdl) {
+    cfg = cudaLaunchConfig_t{};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(k2Threads);
+    cfg.dynamicSmemBytes = k2Smem;
+    cfg.stream = s;
+    int na = 0;
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = cluster;
+    attr[na].val.clusterDim.y = 1;
+    attr[na].val.clusterDim.z = 1;
+    ++na;
+    if (pdl) {
+        attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[na].val.programmaticStreamSerializationAllowed = 1;
+        ++na;
+    }
+    cfg.attrs = attr;
+    cfg.numAttrs = na;
+}
+
+// clusters of four CTAs that can be resident at once (a cluster lives inside one GPC: fewer than sm_count / 4 where a GPC's
+// SM count is not a multiple of 4), asked from the runtime once per device and instantiation; 0 = not launchable
+template <bool GLU>
+static int quad_clusters() {
+    static int cached[64];
+    static bool have[64];
+    const int dev = current_device();
+    if (dev < 0 || dev >= 64) return 0;
+    if (!have[dev]) {
+        auto kern = gemm2_tcgen05_kernel<GLU, true>;
+        static unsigned long long attr_done = 0;
+        int n = 0;
+        if (ensure_max_dynamic_smem(reinterpret_cast<const void*>(kern), (int)k2Smem, attr_done) == cudaSuccess) {
+            prefer_max_smem_carveout(reinterpret_cast<const void*>(kern));
+            cudaLaunchConfig_t cfg;
+            cudaLaunchAttribute attr[2];
+            fill_cluster_cfg(cfg, attr, 4 * (sm_count() / 4), 4, nullptr, false);
+            if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess) { n = 0; cudaGetLastError(); }
+        }
+        if (getenv("B200_GEMM2_VERBOSE")) fprintf(stderr, "[b200] gemm2 quad: %d clusters of 4 CTAs resident (of %d SMs)\n", n, sm_count());
+        cached[dev] = n;
+        have[dev] = true;
+    }
+    return cached[dev];
+}
+
+template <bool GLU>
+static int gemm2_launch_quad(const CUtensorMap& ma, const CUtensorMap& mb, const Gemm2Params& p, int clusters, cudaStream_t s) {
+    auto kern = gemm2_tcgen05_kernel<GLU, true>;
+    cudaLaunchConfig_t cfg;
+    cudaLaunchAttribute attr[2];
+    fill_cluster_cfg(cfg, attr, 4 * clusters, 4, s, pdl_enabled());
+    cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ma, mb, p);
+    count_launch();
+    return (int)e;
+}
+
 template <bool GLU>
 static int gemm2_launch(const CUtensorMap& ma, const CUtensorMap& mb, const Gemm2Params& p, int grid, cudaStream_t s) {
-    auto kern = gemm2_tcgen05_kernel<GLU>;
+    auto kern = gemm2_tcgen05_kernel<GLU, false>;
     static unsigned long long attr_done = 0;   // per instantiation, one bit per device
     {
         cudaError_t e = ensure_max_dynamic_smem(reinterpret_cast<const void*>(kern), (int)k2Smem, attr_done);
@@ -248,7 +339,9 @@ int gemm2_tcgen05_f16(const void* x, const void* W, const void* bias, void* y, i
     static int mode = -1;   // B200_GEMM_PAIR=0 keeps the one-CTA kernel
     if (mode < 0) { const char* e = getenv("B200_GEMM_PAIR"); mode = (e && e[0] == '0') ? 0 : 1; }
     if (!mode) return B200_EUNSUPPORTED;
-    if (M < 512 || N < 256 || K < 64 || (K & 7)) return B200_EUNSUPPORTED;
+    // below 512 token rows only the one case the caller has measured (gemm_tcgen05.cu: one row tile x >= 60 column tiles)
+    const bool one_row_tile = !glu && M > 160 && M <= 256 && (N + 255) / 256 >= 60;
+    if ((M < 512 && !one_row_tile) || N < 256 || K < 64 || (K & 7)) return B200_EUNSUPPORTED;
     if (glu && ((N & 127) || bias || residual)) return B200_EUNSUPPORTED;
     Gemm2Params p{};
     p.C = reinterpret_cast<__half*>(y);
@@ -258,7 +351,30 @@ int gemm2_tcgen05_f16(const void* x, const void* W, const void* bias, void* y, i
     p.k_blocks = (K + k2BK - 1) / k2BK;
     p.m_tiles = (M + 255) / 256;
     p.n_tiles = glu ? N / 128 : (N + 255) / 256;
+    {   // bands of 16 row tiles (measured at 8192 x 12288 x 4096, power-capped: 1108 -> 1191 TFLOP/s sustained; 8: 1150, 32 = the
+        // old column-major order). B200_GEMM2_GROUP_M overrides (0 = column-major over all row tiles).
+        static int group_env = -2;
+        if (group_env == -2) { const char* g = getenv("B200_GEMM2_GROUP_M"); group_env = g ? atoi(g) : -1; }
+        p.group_m = group_env >= 0 ? group_env : 16;
+    }
     CUtensorMap ma, mb;
+    // Opt-in (B200_GEMM2_QUAD=1, read per call so that tests can switch it): four-CTA clusters with the A tile multicast
+    // between two MMA pairs. Needs an even number of column tiles and >= 2 units per cluster. Measured on the B200 at
+    // 8192 x 12288 x 4096 (tools/gemm_power.py, 3 s back to back, board at its 1 kW cap): L2 -> SM bytes 6.44 -> 4.83 GB and
+    // the SM clock rises 1335 -> 1455 MHz (cuBLAS' clock), but only 33 clusters of 4 are resident (132 of 148 SMs: a cluster
+    // lives inside one GPC) and the throughput per clock drops 891 -> 782 TFLOP/s/GHz: 1137 vs 1190 TFLOP/s sustained, 1262
+    // vs 1305 burst. The pair kernel stays the default.
+    const char* quad_s = getenv("B200_GEMM2_QUAD");
+    const int quad_env = (quad_s && quad_s[0] == '1') ? 1 : 0;
+    if (quad_env && M >= 512 && (p.n_tiles & 1) == 0) {
+        int clusters = glu ? quad_clusters<true>() : quad_clusters<false>();
+        const int units4 = p.m_tiles * (p.n_tiles / 2);
+        if (clusters > units4) clusters = units4;
+        if (clusters >= 8 && units4 >= 2 * clusters) {
+            if (!make_tma_map_2d(&ma, x, M, K, 64) || !make_tma_map_2d(&mb, W, glu ? 2ll * N : (long long)N, K, 128)) return B200_EUNSUPPORTED;
+            return glu ? gemm2_launch_quad<true>(ma, mb, p, clusters, s) : gemm2_launch_quad<false>(ma, mb, p, clusters, s);
+        }
+    }
     if (!make_tma_map_2d(&ma, x, M, K, 128) || !make_tma_map_2d(&mb, W, glu ? 2ll * N : (long long)N, K, 128)) return B200_EUNSUPPORTED;
     const int units = p.m_tiles * p.n_tiles;
     int clusters = sm_count() / 2;

@@ -396,6 +396,14 @@ int gemm_tcgen05_f16(const void* x, const void* W, const void* bias, void* y, in
     p.C = y; p.bias = bias; p.K = K; p.ldc = N; p.tokens = M;
     p.k_blocks = (K + kBK - 1) / kBK;
     CUtensorMap ma, mb;
+    // 161..256 token rows against a wide weight matrix (>= 60 column tiles of 256: most of the 74 cluster slots busy): one row
+    // tile of the two-CTA kernel beats the swapped kernel's 2 waves of 128 x 256 tiles (measured, us: 22016 x 4096 at 192 /
+    // 256 rows: 60.9 / 61.4 vs 75.8 / 87.6; 12288 x 4096 at 256: 35.5 vs 44.0; narrow outputs stay swapped: 4096 x 11008 at
+    // 256: 38.4 vs 65.5)
+    if (M > 160 && M <= 256 && (N + 255) / 256 >= 60) {
+        const int rc2 = gemm2_tcgen05_f16(x, W, bias, y, M, N, K, false, s);
+        if (rc2 != B200_EUNSUPPORTED) return rc2;
+    }
     if (M <= 256) {
         // swapped: weights stream through the M axis, tokens are the N extent
         const int BN = M <= 32 ? 32 : M <= 64 ? 64 : M <= 128 ? 128 : 256;

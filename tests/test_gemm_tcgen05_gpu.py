@@ -43,11 +43,32 @@ def test_swapped_weight_streaming_mode(ops, m, n, k):
 
 
 @pytest.mark.parametrize("m,n,k", [(257, 256, 64), (512, 4096, 4096), (1000, 520, 264), (2048, 12288, 4096),
-                                   (384, 96, 128), (300, 40, 2048), (4096, 4096, 11008)])
+                                   (384, 96, 128), (300, 40, 2048), (4096, 4096, 11008),
+                                   # ragged rows / columns / K across several bands of the banded tile order
+                                   (4000, 2504, 328), (4100, 2500, 72), (8192, 1024, 512)])
 def test_normal_prefill_mode(ops, m, n, k):
     got, want = case(ops, m, n, k, m + n * 3)
     assert_close(got, want, "fp16", f"tcgen05 normal {m}x{n}x{k}")
     assert rel_err(got, want) < 4e-3
+
+
+@pytest.mark.parametrize("m,n,k", [(200, 15400, 264), (161, 15364, 72), (256, 22016, 4096)])
+def test_one_row_tile_of_the_pair_kernel(ops, m, n, k):
+    """161..256 token rows against >= 60 column tiles: routed to the two-CTA kernel with one (partly empty) row tile"""
+    got, want = case(ops, m, n, k, m + n)
+    assert_close(got, want, "fp16", f"tcgen05 pair, one row tile {m}x{n}x{k}")
+    assert rel_err(got, want) < 4e-3
+
+
+@pytest.mark.parametrize("m,n,k", [(2048, 12288, 4096), (4000, 2504, 328), (4100, 2500, 72), (8192, 1024, 512)])
+def test_quad_cluster_multicast_variant(ops, m, n, k, monkeypatch):
+    """B200_GEMM2_QUAD=1: clusters of four CTAs, the A tile multicast between the two MMA pairs (opt-in, gemm2_tcgen05.cu);
+    must give the pair kernel's result bit for bit (same MMAs in the same order) and match the oracle"""
+    got0, want = case(ops, m, n, k, m + n * 3)
+    monkeypatch.setenv("B200_GEMM2_QUAD", "1")
+    got1, _ = case(ops, m, n, k, m + n * 3)
+    assert_close(got1, want, "fp16", f"tcgen05 quad {m}x{n}x{k}")
+    assert np.array_equal(got0, got1)
 
 
 @pytest.mark.parametrize("m", [24, 700])

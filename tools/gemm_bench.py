@@ -35,7 +35,9 @@ def timed(fn, reps):
 def main():
     shapes = [(8192, 12288, 4096), (8192, 4096, 4096), (8192, 22016, 4096), (8192, 4096, 11008),
               (32, 12288, 4096), (32, 4096, 4096), (32, 22016, 4096), (32, 4096, 11008), (32, 32000, 4096),
-              (16, 22016, 4096), (64, 22016, 4096), (128, 22016, 4096), (256, 22016, 4096)]
+              (16, 22016, 4096), (64, 22016, 4096), (128, 22016, 4096), (256, 22016, 4096), (512, 22016, 4096)]
+    if len(sys.argv) > 1:   # e.g. 128,22016,4096 256,12288,4096
+        shapes = [tuple(int(v) for v in a.split(',')) for a in sys.argv[1:]]
     out = []
     for m, n, k in shapes:
         nw = max(1, int(300e6 // (n * k * 2)) + 1)   # cycle through > 300 MB of weights so HBM, not L2, is measured
