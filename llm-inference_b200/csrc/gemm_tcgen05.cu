@@ -220,7 +220,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
                                 st16(dst + q * 8, Unpack<__half>::put(f));
                             }
                         } else {
-                            for (int j = 0; j < 32 && col0 + j < p.rows_b; ++j) {
+                            // unrolled with a predicate: a run-time index would move v[] to local memory (no L1 behind
+                            // it with the 227 KB carve-out) for EVERY path of the epilogue
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) {
+                                if (col0 + j >= p.rows_b) continue;
                                 float f = __uint_as_float(v[j]);
                                 if (bias) f += __half2float(bias[col0 + j]);
                                 dst[j] = __float2half_rn(f);

@@ -71,6 +71,18 @@ def test_quad_cluster_multicast_variant(ops, m, n, k, monkeypatch):
     assert np.array_equal(got0, got1)
 
 
+@pytest.mark.parametrize("m,n,k", [(8192, 12288, 512), (5000, 5120, 328), (19000, 1024, 72), (2048, 12288, 4096)])
+def test_wide_pair_tile_equals_the_256x256_tile(ops, m, n, k, monkeypatch):
+    """B200_GEMM2_WIDE=1: the 256 x 512 pair tile (gemm2w_tcgen05_kernel, opt-in), incl. shapes whose last wave is split
+    into single column tiles; same MMAs in the same K order as the default 256 x 256 tile, so bit-identical, and both
+    match the oracle"""
+    got_p, want = case(ops, m, n, k, m + n * 3)
+    monkeypatch.setenv("B200_GEMM2_WIDE", "1")
+    got_w, _ = case(ops, m, n, k, m + n * 3)
+    assert_close(got_w, want, "fp16", f"tcgen05 wide {m}x{n}x{k}")
+    assert np.array_equal(got_w, got_p)
+
+
 @pytest.mark.parametrize("m", [24, 700])
 def test_bias_epilogue(ops, m):
     got, want = case(ops, m, 1024, 512, 5, bias=True)

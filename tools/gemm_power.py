@@ -1,5 +1,6 @@
 #!/usr/bin/env python
-"""SM clock and board power while one GEMM runs back to back for a few seconds: gemm2_tcgen05_kernel vs the cuBLAS kernel
+"""usage: gemm_power.py [N] [VARIANT ...], VARIANT = comma-separated B200_GEMM2_* knobs without the prefix, e.g. WIDE=1 or QUAD=1,GROUP_M=8
+SM clock and board power while one GEMM runs back to back for a few seconds: gemm2_tcgen05_kernel vs the cuBLAS kernel
 on the same 7B prefill shape (both are power-capped on a B200: the clock they settle at is part of the comparison)."""
 import os
 import subprocess
@@ -56,23 +57,36 @@ def run(name, fn, secs=4.0):
           f"  -> {2 * m * n * k / ms / 1e9 / med(0) * 1000:7.1f} TFLOP/s per GHz", flush=True)
 
 
-def mine(group_m, quiet):
-    def fn(i):
-        ops.launchLinearGemm(x, ws[i % 4], y, trans_b=True)
-    def go(secs=3.0):
-        os.environ["B200_GEMM2_GROUP_M"] = str(group_m)
-        os.environ["B200_GEMM2_QUIET"] = str(quiet)
-        run(f"gemm2 group_m={group_m} quiet={quiet}", fn, secs)
-    return go
+variants = [dict(kv.split("=") for kv in a.split(",") if kv) for a in sys.argv[2:]] or [{}, {"WIDE": "1"}, {"QUAD": "1"}]
+variants = [{("B200_GEMM2_" + k_): v for k_, v in d.items()} for d in variants]
+# the board drifts (temperature, power-cap controller): every variant is timed in ROUNDS interleaved rounds, means are printed last
+ROUNDS, SECS = 3, 2.0
+names = ["cuBLAS"] + [(" ".join(f"{k_[11:]}={v}" for k_, v in env.items()) or "default") for env in variants]
+acc = {nm: [] for nm in names}
+_run = run
 
 
-ref = torch.nn.functional.linear(x, ws[0]).float()
-for gm, q in ((16, 7), (16, 22), (8, 10)):
-    os.environ["B200_GEMM2_GROUP_M"], os.environ["B200_GEMM2_QUIET"] = str(gm), str(q)
-    ops.launchLinearGemm(x, ws[0], y, trans_b=True)
-    torch.cuda.synchronize()
-    print("check", gm, q, float((y.float() - ref).abs().max()), flush=True)
-run("cuBLAS (torch linear)", lambda i: torch.nn.functional.linear(x, ws[i % 4]), 3.0)
-for gm, q in ((16, 0), (16, 1), (16, 16), (16, 2), (16, 4), (16, 8 + 2), (16, 1 + 2 + 4), (16, 16 + 2 + 4), (8, 0), (32, 0)):
-    mine(gm, q)()
-run("cuBLAS (torch linear)", lambda i: torch.nn.functional.linear(x, ws[i % 4]), 3.0)
+def run(name, fn, secs=3.0):   # noqa: F811 - keeps the one-line report, collects TFLOP/s and clock
+    import io, contextlib
+    buf = io.StringIO()
+    with contextlib.redirect_stdout(buf):
+        _run(name, fn, secs)
+    line = buf.getvalue().strip()
+    print(line, flush=True)
+    parts = line.split()
+    return float(parts[parts.index("TFLOP/s") - 1]), float(parts[parts.index("MHz") - 1])
+
+
+for r in range(ROUNDS):
+    acc["cuBLAS"].append(run("cuBLAS (torch linear)", lambda i: torch.nn.functional.linear(x, ws[i % 4]), SECS))
+    for env, nm in zip(variants, names[1:]):
+        for k_ in ("B200_GEMM2_WIDE", "B200_GEMM2_QUAD", "B200_GEMM2_GROUP_M"):
+            os.environ.pop(k_, None)
+        os.environ.update(env)
+        acc[nm].append(run("gemm2 " + nm, lambda i: ops.launchLinearGemm(x, ws[i % 4], y, trans_b=True), SECS))
+print("---- means over", ROUNDS, "interleaved rounds")
+base = sum(t for t, _ in acc["cuBLAS"]) / ROUNDS
+for nm in names:
+    t = sum(v[0] for v in acc[nm]) / ROUNDS
+    c = sum(v[1] for v in acc[nm]) / ROUNDS
+    print(f"{nm:32s} {t:7.1f} TFLOP/s  {c:6.0f} MHz  {t / base:5.3f} x cuBLAS", flush=True)
