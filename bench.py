@@ -725,6 +725,7 @@ def verify_decode(pkg, eng, model_shape, weight_seed, ctx, kv_seed, ids0, n_step
     identical wherever the check engine's top-2 margin exceeds that band. Both orders are pinned to the CPU
     oracle at these shapes by tests/test_7b_shapes_gpu.py; this run-time check is about the timed run itself."""
     import numpy as np
+    import torch
     E, capi = pkg.engine, pkg.capi
     B = eng.batch
     nb = min(B, 2)
@@ -747,6 +748,7 @@ def verify_decode(pkg, eng, model_shape, weight_seed, ctx, kv_seed, ids0, n_step
         kc, vc = eng.kv_caches()
         kc2[:, :, :, :ctx].copy_(kc[:, :nb, :, :ctx])
         vc2[:, :, :, :ctx].copy_(vc[:, :nb, :, :ctx])
+    torch.cuda.synchronize()   # the copies ran on torch's stream, the engines step on their own
     ids = np.ascontiguousarray(ids0, dtype=np.int32)
     worst, same, compared = 0.0, 0, 0
     for _ in range(n_steps):

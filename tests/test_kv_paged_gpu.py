@@ -228,6 +228,7 @@ def test_cfg4_shape_paged_equals_dense(pkg):
     kp, vp = pe.kv_caches()
     kd, vd = de.kv_caches()
     kd.copy_(kp), vd.copy_(vp)
+    torch.cuda.synchronize()   # torch's stream, not the engines': the copies must have landed before the first step
     del kp, vp
     ids = np.random.default_rng(3).integers(0, 32000, B).astype(np.int32)
     for s in range(3):
