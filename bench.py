@@ -795,6 +795,7 @@ def extras_multi_gpu(pkg, args, rank, world, local_rank, peak):
 
     def timed(eng, B):
         stream = torch.cuda.ExternalStream(eng.stream)
+        dist.barrier(); torch.cuda.synchronize()   # the ranks' first kernels wait for one another on the device: start together
         eng.decode_step_host(np.full(B, 11, np.int32))
         for _ in range(W - 1):
             eng.decode_step()
@@ -837,6 +838,7 @@ def extras_multi_gpu(pkg, args, rank, world, local_rank, peak):
             # agreement probe: four steps on FIXED token ids from the same cache state (a free-running greedy chain on
             # random weights forks at the first near-tie, so its last logits say nothing about agreement)
             eng.fill_kv_random(ctx, seed=7 + rank, amp=0.5)
+            dist.barrier(); torch.cuda.synchronize()
             for s_ in range(4):
                 eng.decode_step_host(np.full(B, 11 + s_, np.int32))
             logits[kind] = eng.logits().float().clone()

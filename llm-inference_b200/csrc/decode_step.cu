@@ -1224,7 +1224,9 @@ __device__ __noinline__ void exchange_op(const StepOp& op, const StepParams& p, 
             for (;;) {
                 asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(w0), "=r"(w1), "=r"(w2), "=r"(w3) : "l"(src) : "memory");
                 if (w1 == call && w3 == call) break;
-                if (global_timer_ns() - t0 > 2000000000ull) {   // a peer never arrived: fail instead of hanging
+                // a peer never arrived: fail instead of hanging. 10 s, not the 2 s of the intra-GPU waits: the other rank is
+                // another PROCESS, whose host thread may be late by a scheduling hiccup or a lazy weight re-pack
+                if (global_timer_ns() - t0 > 10000000000ull) {
                     atomicExch(&p.sync[2], 4u);
                     __trap();
                 }

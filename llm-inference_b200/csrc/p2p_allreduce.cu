@@ -100,7 +100,7 @@ p2p_allreduce_add_kernel(const P2PParams p, const T* partial, T* hidden, size_t 
                     unsigned long long now;
                     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
                     if (t0 == 0) t0 = now;
-                    else if (now - t0 > 5000000000ull) __trap();   // a peer never arrived: fail instead of hanging
+                    else if (now - t0 > 10000000000ull) __trap();   // a peer never arrived: fail instead of hanging
                 }
                 v = ld16_volatile(src);
             }
