@@ -153,3 +153,33 @@ def test_linear_with_residual_epilogue(ops, m, n, k):
                         torch.from_numpy(res).cuda().half(), out)
     torch.cuda.synchronize()
     assert_close(out.float().cpu().numpy(), want, "fp16", f"linear + residual {m}x{n}x{k}")
+
+
+@pytest.mark.parametrize("knob", ["B200_GEMM2_WIDE", "B200_GEMM2_QUAD"])
+def test_opt_in_tile_shapes_with_swiglu_and_residual_epilogues(ops, knob, monkeypatch):
+    """the opt-in 256 x 512 pair tile / four-CTA multicast cluster also carry the SwiGLU and the residual epilogue: their
+    outputs must equal the default 256 x 256 tile's bit for bit (same MMAs, same K order, same rounding points); the default
+    is pinned to the oracle by the tests above"""
+    g = torch.Generator(device="cpu").manual_seed(3)
+    m, inter, k = 2048, 11008, 1024      # 86 GLU column tiles: 344 wide units / quad units
+    x = (torch.rand(m, k, generator=g) * 2 - 1).half().cuda()
+    w = (torch.randn(2 * inter, k, generator=g) * 0.05).half().cuda()
+    m2, n2, k2 = 4096, 4096, 520          # 16 x 8 units, ragged K
+    x2 = (torch.rand(m2, k2, generator=g) * 2 - 1).half().cuda()
+    w2 = (torch.randn(n2, k2, generator=g) * 0.05).half().cuda()
+    res = (torch.rand(m2, n2, generator=g) * 4 - 2).half().cuda()
+
+    def run():
+        o1 = torch.full((m, inter), float("nan"), dtype=torch.float16, device="cuda")
+        o2 = torch.full((m2, n2), float("nan"), dtype=torch.float16, device="cuda")
+        ops.linear_swiglu(x, w, o1)
+        ops.linear_residual(x2, w2, res, o2)
+        torch.cuda.synchronize()
+        return o1, o2
+
+    a1, a2 = run()
+    monkeypatch.setenv(knob, "1")
+    b1, b2 = run()
+    assert not torch.isnan(b1).any() and not torch.isnan(b2).any()
+    assert torch.equal(a1, b1), f"{knob}: SwiGLU epilogue differs from the default tile"
+    assert torch.equal(a2, b2), f"{knob}: residual epilogue differs from the default tile"
