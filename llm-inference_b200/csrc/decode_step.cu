@@ -912,6 +912,9 @@ __device__ __noinline__ uint32_t down_phase(const StepOp& op, const StepParams& 
 // the persistent kernel). Work item = (sequence, kv head, split); head_size 128 (16 packets / row).
 // The new token's k,v were written to cache row step-1 by the qkv op's epilogue.
 // ------------------------------------------------------------------------------------------
+#ifndef B200_STEP_ATTN_GC
+#define B200_STEP_ATTN_GC 2   // query heads of one kv head that a work item handles at once (see attn_consume)
+#endif
 __device__ __forceinline__ float exp_guard_s(float m, float M) { return (m == -INFINITY) ? 0.f : expf(m - M); }
 
 // L2 prefetch of the cache rows [k0, min(k1, step-1)) of this CTA's first attention item (one
@@ -919,10 +922,11 @@ __device__ __forceinline__ float exp_guard_s(float m, float M) { return (m == -I
 template <int G>
 __device__ __forceinline__ void attn_prefetch(const StepOp& op, const StepParams& p, int step) {
     constexpr int D = 128;
+    constexpr int NP = G > B200_STEP_ATTN_GC ? G / B200_STEP_ATTN_GC : 1;
     const int splits = p.splits;
-    const int items = p.nb * p.kv_head_num * splits;
-    const int item = blockIdx.x;
-    if (item >= items) return;
+    const int items = p.nb * p.kv_head_num * splits * NP;
+    if ((int)blockIdx.x >= items) return;
+    const int item = blockIdx.x / NP;   // (sequence, kv head, split) of this CTA's first work item
     const int per = (step + splits - 1) / splits;
     const int split = item % splits, bh = item / splits;
     const int b = bh / p.kv_head_num, kvh = bh - b * p.kv_head_num;
@@ -940,20 +944,19 @@ __device__ __forceinline__ void attn_prefetch(const StepOp& op, const StepParams
 template <int G>
 __device__ __noinline__ void attn_consume(const StepOp& op, const StepParams& p, float* sm, int step) {
     constexpr int PR = 16, E = 8, D = 128, KPI = 2, UN = 4;
-#ifndef B200_STEP_ATTN_GC
-#define B200_STEP_ATTN_GC 2
-#endif
-    constexpr int GC = G > B200_STEP_ATTN_GC ? B200_STEP_ATTN_GC : G;   // heads per pass over the keys
+    constexpr int GC = G > B200_STEP_ATTN_GC ? B200_STEP_ATTN_GC : G;   // heads per work item
+    constexpr int NP = G / GC;                                            // head groups per (sequence, kv head, split)
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int pi = lane % PR, ks = lane / PR;
     const int splits = p.splits;
-    const int items = p.nb * p.kv_head_num * splits;
+    const int items = p.nb * p.kv_head_num * splits * NP;
     const int qkv_heads = p.head_num + 2 * p.kv_head_num;
     const float scale = rsqrtf((float)D);
     const int per = (step + splits - 1) / splits;
 
     for (int item = blockIdx.x; item < items; item += gridDim.x) {
-        const int split = item % splits, bh = item / splits;
+        const int g0 = (item % NP) * GC, rest = item / NP;
+        const int split = rest % splits, bh = rest / splits;
         const int b = bh / p.kv_head_num, kvh = bh - b * p.kv_head_num;
         const __half* tok = reinterpret_cast<const __half*>(p.qkv) + (size_t)b * qkv_heads * D;
         const __half* kc = reinterpret_cast<const __half*>(op.k_cache) + ((size_t)b * p.kv_head_num + kvh) * p.max_seq_len * D;
@@ -962,9 +965,9 @@ __device__ __noinline__ void attn_consume(const StepOp& op, const StepParams& p,
         if (op.head_cnt != nullptr) {
             // no grid barrier after the qkv op: wait until the CTAs that own the rows of this item's q heads, k head and
             // v head have released them (D / 2 row pairs per head)
-            if (threadIdx.x < G + 2) {
-                const int head = (int)threadIdx.x < G ? kvh * G + (int)threadIdx.x
-                                                      : ((int)threadIdx.x == G ? p.head_num + kvh : p.head_num + p.kv_head_num + kvh);
+            if (threadIdx.x < GC + 2) {
+                const int head = (int)threadIdx.x < GC ? kvh * G + g0 + (int)threadIdx.x
+                                                       : ((int)threadIdx.x == GC ? p.head_num + kvh : p.head_num + p.kv_head_num + kvh);
                 const unsigned long long t0 = global_timer_ns();
                 while (ld_acquire_u32(op.head_cnt + head) < (unsigned)(D / 2)) {
                     if (global_timer_ns() - t0 > 2000000000ull) {
@@ -977,13 +980,13 @@ __device__ __noinline__ void attn_consume(const StepOp& op, const StepParams& p,
         }
 
         // G = 4 / 8 (8 = the 70B-shaped tensor-parallel ranks): eight heads' q, (m, l) and 64 fp32 outputs per lane do not fit
-        // the 168-register cap (G = 8: 472 bytes of stack, 319 local loads / stores in the SASS; G = 4: 136 / 106). Passes of
-        // GC = 2 heads over the item's keys instead: later passes re-read K / V rows the first one has just pulled into L2 (a
-        // few hundred KB per layer against ~100 MB of weights). Per-head arithmetic and its order are unchanged. Measured on
-        // an 8-layer 70B-shaped slice, one GPU, batch 1, context 512 / 4096: 2.350 / 2.484 ms per step with all eight heads at
-        // once, 2.310 / 2.443 with GC = 4, 2.278 / 2.430 with GC = 2 (tools/g8_step_bench.py).
-#pragma unroll 1
-        for (int g0 = 0; g0 < G; g0 += GC) {
+        // the 168-register cap (G = 8: 472 bytes of stack, 319 local loads / stores in the SASS; G = 4: 136 / 106). A work item
+        // therefore covers GC = 2 query heads of its (sequence, kv head, split); the NP = G / GC head groups are separate items
+        // that other CTAs take (each re-reads the split's K / V rows, from L2 after the first: a few hundred KB per layer
+        // against ~100 MB of weights). Per-head arithmetic and its order are unchanged. Measured on an 8-layer 70B-shaped
+        // slice, one GPU, batch 1, context 512 / 4096 (tools/g8_step_bench.py): 2.350 / 2.484 ms per step with all eight heads
+        // in one item, 2.310 / 2.443 with passes of four, 2.278 / 2.430 with passes of two inside the item.
+        {
             Pack16 q[GC];
 #pragma unroll
             for (int g = 0; g < GC; ++g) q[g] = ld16_cg(tok + (size_t)(kvh * G + g0 + g) * D + pi * E);
@@ -1093,7 +1096,6 @@ __device__ __noinline__ void attn_consume(const StepOp& op, const StepParams& p,
                     if (e == 0) { p.part_ml[slot * 2] = M; p.part_ml[slot * 2 + 1] = L; }
                 }
             }
-            if (g0 + GC < G) consumers_sync();   // sm is reused by the next pass
         }
         consumers_sync();   // sm is reused by the next item; every thread's partial stores precede thread 0's release
         if (op.type == kOpAttnO && threadIdx.x == 0)
@@ -1117,11 +1119,13 @@ __device__ __noinline__ uint32_t attn_o_phase(const StepOp& op, const StepParams
     const int tid = threadIdx.x;
     const bool tr = p.trace != nullptr && blockIdx.x == 0 && tid == 0;
     if (tr) p.trace[4 * p.n_ops + 1 + op_index] = global_timer_ns();   // attention items of this CTA done
+    const int gq = p.head_num / p.kv_head_num;
+    const int np = gq > B200_STEP_ATTN_GC ? gq / B200_STEP_ATTN_GC : 1;   // attention work items per (sequence, kv head, split)
     if (tid == 0) {
         const unsigned* cnt = reinterpret_cast<const unsigned*>(op.y);
         const unsigned long long t0 = global_timer_ns();
         for (int b = 0; b < nb; ++b) {
-            while (ld_acquire_u32(cnt + b * p.kv_head_num + kvh) < (unsigned)S) {
+            while (ld_acquire_u32(cnt + b * p.kv_head_num + kvh) < (unsigned)(S * np)) {
                 if (global_timer_ns() - t0 > 2000000000ull) {
                     atomicExch(&p.sync[2], 2u);
                     __trap();
