@@ -466,6 +466,7 @@ def bench_prefill(args, wl, rank, world, local_rank):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     def barrier():
+        torch.cuda.synchronize()   # no collective kernel may slip in between queued cooperative step kernels (see extras_multi_gpu)
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
@@ -624,6 +625,7 @@ def bench_tp(args, wl, rank, world, local_rank):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     def barrier():
+        torch.cuda.synchronize()   # no collective kernel may slip in between queued cooperative step kernels (see extras_multi_gpu)
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
@@ -793,20 +795,24 @@ def extras_multi_gpu(pkg, args, rank, world, local_rank, peak):
     K, W = min(args.steps, 24), 3
     out = {}
 
+    # Every cross-rank barrier below is bracketed by device synchronisations. The persistent TP step is a cooperative launch that
+    # needs EVERY SM (211 KB of shared memory per CTA) and waits on the device for its peers' exchange lines: an NCCL kernel
+    # (dist.barrier) that slips in between two queued steps on one rank but not on the other deadlocks the two GPUs until the
+    # kernel's peer time-out traps (seen once in a while as "unspecified launch failure" before this was added).
     def timed(eng, B):
         stream = torch.cuda.ExternalStream(eng.stream)
-        dist.barrier(); torch.cuda.synchronize()   # the ranks' first kernels wait for one another on the device: start together
+        torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()   # the ranks' first kernels wait for one another on the device: start together
         eng.decode_step_host(np.full(B, 11, np.int32))
         for _ in range(W - 1):
             eng.decode_step()
-        dist.barrier(); torch.cuda.synchronize()
+        torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         with torch.cuda.stream(stream):
             e0.record()
             for _ in range(K):
                 eng.decode_step()
             e1.record()
-        dist.barrier(); torch.cuda.synchronize()
+        torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
         t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t[0]) / K
@@ -838,7 +844,7 @@ def extras_multi_gpu(pkg, args, rank, world, local_rank, peak):
             # agreement probe: four steps on FIXED token ids from the same cache state (a free-running greedy chain on
             # random weights forks at the first near-tie, so its last logits say nothing about agreement)
             eng.fill_kv_random(ctx, seed=7 + rank, amp=0.5)
-            dist.barrier(); torch.cuda.synchronize()
+            torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
             for s_ in range(4):
                 eng.decode_step_host(np.full(B, 11 + s_, np.int32))
             logits[kind] = eng.logits().float().clone()
@@ -864,7 +870,7 @@ def extras_multi_gpu(pkg, args, rank, world, local_rank, peak):
         comm.close()
     except Exception as ex:   # never take the main line down
         out["tp_error"] = f"{type(ex).__name__}: {ex}"
-    dist.barrier(); torch.cuda.synchronize()
+    torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
 
     # ---- (ii) cfg4 split over the GPUs (no collective on the data path)
     try:
@@ -885,7 +891,7 @@ def extras_multi_gpu(pkg, args, rank, world, local_rank, peak):
         eng.close()
     except Exception as ex:
         out["cfg4_shard_error"] = f"{type(ex).__name__}: {ex}"
-    dist.barrier(); torch.cuda.synchronize()
+    torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
     return out
 
 
@@ -931,6 +937,7 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     def barrier():
+        torch.cuda.synchronize()   # no collective kernel may slip in between queued cooperative step kernels (see extras_multi_gpu)
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
