@@ -1125,7 +1125,8 @@ def main():
                           "weights": "random-init N(0,0.02^2) fp16, 13.2 GB per GPU", "accumulate": "fp32",
                           "kv_cache": ("fp8 e4m3 + one fp32 scale per cached row (engine option)" if args.kv_fp8 else
                                        f"fp16 in pages of 128 rows, {eng.kv_pages_total} pages per layer pool (engine option; bit-identical "
-                                       "results to the dense cache)" if args.kv_paged else "fp16 (the reference's cache type)"),
+                                       "results to the dense cache)" if args.kv_paged else "fp16 (the reference's cache type)")
+                                      + (f", in pages of 128 rows ({eng.kv_pages_total} per layer pool)" if args.kv_fp8 and args.kv_paged else ""),
                           "l2": "inputs larger than L2 (13.2 GB of weights streamed per step vs 126 MB L2)",
                           "parallelism": f"dp{world} (independent requests, no collective)"},
                "e2e": {"value": round(e2e_tok_s, 2), "unit": "tok/s", "h2d_bytes_per_step": 4 * B_local,

@@ -78,8 +78,9 @@ enum {
 #define B200_ENGINE_KV_PAGED 2u /* KV cache as page pools [layers][n_pages, hk, 128 rows, d] + one page list per sequence
                                 * (SURVEY 8 f4 "paged blocks"; b200_llama.h, csrc/kv_paged.cu) instead of max_seq rows
                                 * reserved per sequence slot. fp16 models, head size 128, head_num / kv_head_num in
-                                * {1,2,4,8}; not combinable with KV_FP8 yet. Bit-identical results to the dense cache on
-                                * the same launch order (tests/test_kv_paged_gpu.py). Decode runs the reference launch order
+                                * {1,2,4,8}. Bit-identical results to the dense cache on the same launch order
+                                * (tests/test_kv_paged_gpu.py). With KV_FP8 as well: fp8 pages + scale pools
+                                * (head_num / kv_head_num in {1,2,4}), bit-identical to the dense fp8 cache. Decode runs the reference launch order
                                 * with b200_decode_attention_paged; a prompt pass attends over a dense scratch slice and
                                 * scatters its rows into pages (FIRST prompt pass of a sequence only). Pages are taken
                                 * when a sequence grows into them, returned by reset / a new prompt pass /

@@ -314,6 +314,22 @@ int b200_kv_scatter_pages(const void* src, void* pool, const int* page_table, in
                           int max_rows, void* stream);
 int b200_kv_gather_pages(const void* pool, void* dst, const int* page_table, int max_pages, const int* n_rows, int batch,
                          int kv_head_num, int dst_seq, int head_size, int elem_bytes, int max_rows, void* stream);
+/* fp8 pages: the four fp8 entries above over pools [n_pages, hk, 128, d] of e4m3 bytes + scale pools [n_pages, hk, 128]
+ * (one fp32 per cached row) and the same page lists; arguments as their dense counterparts, max_seq_len replaced by
+ * (page_table, max_pages). b200_kv_dequant_fp8_paged writes rows [0, n_rows[b]) as fp16 into a dense slice (tests). */
+int b200_kv_append_fp8_paged(const void* qkv, void* k_pool8, void* v_pool8, float* k_scale_pool, float* v_scale_pool,
+                             const int* page_table, int max_pages, int batch, int head_num, int kv_head_num, int head_size,
+                             int step, const int* step_dev, int step_stride, void* stream);
+int b200_decode_attention_fp8_paged(const void* qkv, const void* k_pool8, const void* v_pool8, const float* k_scale_pool,
+                                    const float* v_scale_pool, const int* page_table, int max_pages, void* out,
+                                    void* workspace, size_t workspace_bytes, int batch, int head_num, int kv_head_num,
+                                    int head_size, int step, const int* step_dev, int step_stride, void* stream);
+int b200_kv_quantize_fp8_paged(const void* src, void* pool8, float* scale_pool, const int* page_table, int max_pages,
+                               const int* n_rows, const int* dst_row0, int batch, int kv_head_num, int src_seq, int head_size,
+                               int max_rows, void* stream);
+int b200_kv_dequant_fp8_paged(const void* pool8, const float* scale_pool, void* dst, const int* page_table, int max_pages,
+                              const int* n_rows, int batch, int kv_head_num, int dst_seq, int head_size, int max_rows,
+                              void* stream);
 
 /* Prefill attention without materialising scores / mask / repeated KV (replaces
  * context_attention.cpp:136-161: RepeatKV + QK^T + ScaleMaskSoftmax + PV + transpose):

@@ -66,6 +66,10 @@ PROTOTYPES = {
     "b200_decode_attention_paged": (_i, [_vp] * 4 + [_i] + [_vp, _vp, _sz] + [_i] * 5 + [_vp, _i, _i, _vp]),
     "b200_kv_scatter_pages": (_i, [_vp] * 3 + [_i] + [_vp, _vp] + [_i] * 6 + [_vp]),
     "b200_kv_gather_pages": (_i, [_vp] * 3 + [_i] + [_vp] + [_i] * 6 + [_vp]),
+    "b200_kv_append_fp8_paged": (_i, [_vp] * 6 + [_i] * 6 + [_vp, _i, _vp]),
+    "b200_decode_attention_fp8_paged": (_i, [_vp] * 6 + [_i] + [_vp, _vp, _sz] + [_i] * 5 + [_vp, _i, _vp]),
+    "b200_kv_quantize_fp8_paged": (_i, [_vp] * 4 + [_i] + [_vp, _vp] + [_i] * 5 + [_vp]),
+    "b200_kv_dequant_fp8_paged": (_i, [_vp] * 4 + [_i] + [_vp] + [_i] * 5 + [_vp]),
     "b200_rope_decode_ragged": (_i, [_vp, _i, _i, _i, _i, _vp, _i, C.c_float, _vp, _i, _vp]),
     "b200_context_attention": (_i, [_vp] * 7 + [_i] * 8 + [_vp]),
     "b200_embedding": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp]),

@@ -251,26 +251,31 @@ __device__ __forceinline__ uint32_t fp8x2_to_half2(unsigned short v) {
     return *reinterpret_cast<const uint32_t*>(&h);
 }
 
-template <int G, bool FULL>
+// PAGED: kc / vc / ksc / vsc are the POOLS and row `key` of this (sequence, kv head) is row
+// (pages[key / 128] * kv_heads + kvh) * 128 + key % 128 of them (data x d, scales x 1)
+template <int G, bool FULL, bool PAGED>
 __device__ __forceinline__ void fp8_tile(const unsigned char* kc, const unsigned char* vc, const float* ksc, const float* vsc,
                                          const Pack16 (&q)[G][2], float (&m)[G], float (&l)[G], float (&o)[G][16], const int base,
-                                         const int k1, const int pi, const int ks, const float scale) {
+                                         const int k1, const int pi, const int ks, const float scale, const int* pages,
+                                         const int kv_heads, const int kvh) {
     constexpr int D = 128, PR = 8, E = 16, KPI = 32 / PR;
         Pack16 kp[kUnroll], vp[kUnroll];
         float ks_[kUnroll], vs_[kUnroll];
+        size_t rid[kUnroll];
         bool ok[kUnroll];
 #pragma unroll
         for (int u = 0; u < kUnroll; ++u) {
             const int key = FULL ? base + u * KPI + ks : min(base + u * KPI + ks, k1 - 1);   // rows past the end re-read the last row
             ok[u] = FULL || base + u * KPI + ks < k1;
-            kp[u] = ld16_stream(kc + (size_t)key * D + pi * E);
-            ks_[u] = __ldg(ksc + key);
+            rid[u] = PAGED ? ((size_t)__ldg(pages + (key >> kPageShift)) * kv_heads + kvh) * kPageRows + (size_t)(key & (kPageRows - 1))
+                           : (size_t)key;
+            kp[u] = ld16_stream(kc + rid[u] * D + pi * E);
+            ks_[u] = __ldg(ksc + rid[u]);
         }
 #pragma unroll
         for (int u = 0; u < kUnroll; ++u) {
-            const int key = FULL ? base + u * KPI + ks : min(base + u * KPI + ks, k1 - 1);
-            vp[u] = ld16_stream(vc + (size_t)key * D + pi * E);
-            vs_[u] = __ldg(vsc + key);
+            vp[u] = ld16_stream(vc + rid[u] * D + pi * E);
+            vs_[u] = __ldg(vsc + rid[u]);
         }
         float s[G][kUnroll];
 #pragma unroll
@@ -329,7 +334,7 @@ __device__ __forceinline__ void fp8_tile(const unsigned char* kc, const unsigned
         }
 }
 
-template <int G>
+template <int G, bool PAGED = false>
 __global__ void __launch_bounds__(kAttnWarps * 32)
 decode_attn_split_fp8_kernel(const AttnParams p) {
     constexpr int D = 128, PR = 8, E = 16, KPI = 32 / PR;
@@ -343,7 +348,8 @@ decode_attn_split_fp8_kernel(const AttnParams p) {
     const int pi = lane % PR, ks = lane / PR;
     const int qkv_heads = p.head_num + 2 * p.kv_head_num;
     const __half* tok = reinterpret_cast<const __half*>(p.qkv) + (size_t)b * qkv_heads * D;
-    const size_t head_rows = ((size_t)b * p.kv_head_num + kvh) * p.max_seq_len;
+    const size_t head_rows = PAGED ? (size_t)0 : ((size_t)b * p.kv_head_num + kvh) * p.max_seq_len;
+    const int* pages = PAGED ? p.page_table + (size_t)b * p.max_pages : nullptr;
     const unsigned char* kc = reinterpret_cast<const unsigned char*>(p.k_cache) + head_rows * D;
     const unsigned char* vc = reinterpret_cast<const unsigned char*>(p.v_cache) + head_rows * D;
     const float* ksc = p.k_scale + head_rows;
@@ -375,8 +381,8 @@ decode_attn_split_fp8_kernel(const AttnParams p) {
     for (int base = k0 + warp * KPI * kUnroll; base < k1; base += kAttnWarps * KPI * kUnroll) {
         // whole tiles (every row of the 16 this warp loads exists) take a branch-free path: no per-row predicates, and
         // the shuffles stay plain SHFLs instead of divergence-safe collectives
-        if (base + KPI * kUnroll <= k1) fp8_tile<G, true>(kc, vc, ksc, vsc, q, m, l, o, base, k1, pi, ks, scale);
-        else fp8_tile<G, false>(kc, vc, ksc, vsc, q, m, l, o, base, k1, pi, ks, scale);
+        if (base + KPI * kUnroll <= k1) fp8_tile<G, true, PAGED>(kc, vc, ksc, vsc, q, m, l, o, base, k1, pi, ks, scale, pages, p.kv_head_num, kvh);
+        else fp8_tile<G, false, PAGED>(kc, vc, ksc, vsc, q, m, l, o, base, k1, pi, ks, scale, pages, p.kv_head_num, kvh);
     }
 
     // merge the KPI lane groups of the warp
@@ -815,10 +821,11 @@ extern "C" int b200_decode_attention_static(const void* qkv, void* k_cache_layer
 // fp8 KV cache (kv_fp8.cu): attention over rows [0, step) of an e4m3 cache with one fp32 scale per row. fp16 q / out,
 // head size 128, h/hk in {1, 2, 4}. The new token's row must already be in the cache (b200_kv_append_fp8).
 // ------------------------------------------------------------------------------------------
-extern "C" int b200_decode_attention_fp8(const void* qkv, const void* k_cache8, const void* v_cache8, const float* k_scale,
-                                         const float* v_scale, void* out, void* workspace, size_t workspace_bytes,
-                                         int batch, int head_num, int kv_head_num, int head_size, int max_seq_len,
-                                         int step, const int* step_dev, int step_stride, void* stream) {
+static int decode_attention_fp8_impl(const void* qkv, const void* k_cache8, const void* v_cache8, const float* k_scale,
+                                     const float* v_scale, void* out, void* workspace, size_t workspace_bytes,
+                                     int batch, int head_num, int kv_head_num, int head_size, int max_seq_len,
+                                     int step, const int* step_dev, int step_stride, const int* page_table, int max_pages,
+                                     void* stream) {
     B200_RETURN_IF(!qkv || !k_cache8 || !v_cache8 || !k_scale || !v_scale || !out, B200_EINVAL);
     B200_RETURN_IF(batch <= 0 || head_num <= 0 || kv_head_num <= 0 || max_seq_len <= 0 || head_num % kv_head_num != 0,
                    B200_EINVAL);
@@ -833,6 +840,7 @@ extern "C" int b200_decode_attention_fp8(const void* qkv, const void* k_cache8, 
     p.batch = batch; p.head_num = head_num; p.kv_head_num = kv_head_num; p.head_size = head_size;
     p.max_seq_len = max_seq_len; p.step = step; p.step_dev = step_dev; p.step_stride = step_stride; p.append_kv = 0;
     p.finished = g_attn_finished;
+    p.page_table = page_table; p.max_pages = max_pages;
     const int splits = attn_pick_splits(batch, kv_head_num, step, G);
     if (splits > 1) {
         const size_t ml = (size_t)batch * head_num * splits * 2 * sizeof(float);
@@ -844,9 +852,14 @@ extern "C" int b200_decode_attention_fp8(const void* qkv, const void* k_cache8, 
     cudaStream_t s = (cudaStream_t)stream;
     const dim3 grid(batch * kv_head_num, splits), block(kAttnWarps * 32);
     cudaError_t e;
-    if (G == 1) e = launch_k(decode_attn_split_fp8_kernel<1>, grid, block, (size_t)kAttnWarps * 1 * (2 + 128) * sizeof(float), s, true, p);
-    else if (G == 2) e = launch_k(decode_attn_split_fp8_kernel<2>, grid, block, (size_t)kAttnWarps * 2 * (2 + 128) * sizeof(float), s, true, p);
-    else e = launch_k(decode_attn_split_fp8_kernel<4>, grid, block, (size_t)kAttnWarps * 4 * (2 + 128) * sizeof(float), s, true, p);
+    const size_t sm1 = (size_t)kAttnWarps * (2 + 128) * sizeof(float);
+    if (page_table) {
+        if (G == 1) e = launch_k(decode_attn_split_fp8_kernel<1, true>, grid, block, sm1, s, true, p);
+        else if (G == 2) e = launch_k(decode_attn_split_fp8_kernel<2, true>, grid, block, 2 * sm1, s, true, p);
+        else e = launch_k(decode_attn_split_fp8_kernel<4, true>, grid, block, 4 * sm1, s, true, p);
+    } else if (G == 1) e = launch_k(decode_attn_split_fp8_kernel<1>, grid, block, sm1, s, true, p);
+    else if (G == 2) e = launch_k(decode_attn_split_fp8_kernel<2>, grid, block, 2 * sm1, s, true, p);
+    else e = launch_k(decode_attn_split_fp8_kernel<4>, grid, block, 4 * sm1, s, true, p);
     count_launch();
     if (e != cudaSuccess) return (int)e;
     if (splits > 1) {
@@ -855,6 +868,27 @@ extern "C" int b200_decode_attention_fp8(const void* qkv, const void* k_cache8, 
         count_launch();
     }
     return (int)e;
+}
+
+extern "C" int b200_decode_attention_fp8(const void* qkv, const void* k_cache8, const void* v_cache8, const float* k_scale,
+                                         const float* v_scale, void* out, void* workspace, size_t workspace_bytes,
+                                         int batch, int head_num, int kv_head_num, int head_size, int max_seq_len,
+                                         int step, const int* step_dev, int step_stride, void* stream) {
+    return decode_attention_fp8_impl(qkv, k_cache8, v_cache8, k_scale, v_scale, out, workspace, workspace_bytes, batch, head_num,
+                                     kv_head_num, head_size, max_seq_len, step, step_dev, step_stride, nullptr, 0, stream);
+}
+
+/* the same over a paged fp8 cache (pools [n_pages, kv_heads, 128, d] + scale pools [n_pages, kv_heads, 128], page lists
+ * DEVICE int [batch, max_pages]); the new row must already be in its page (b200_kv_append_fp8_paged) */
+extern "C" int b200_decode_attention_fp8_paged(const void* qkv, const void* k_pool8, const void* v_pool8, const float* k_scale_pool,
+                                               const float* v_scale_pool, const int* page_table, int max_pages, void* out,
+                                               void* workspace, size_t workspace_bytes, int batch, int head_num,
+                                               int kv_head_num, int head_size, int step, const int* step_dev, int step_stride,
+                                               void* stream) {
+    B200_RETURN_IF(!page_table || max_pages <= 0, B200_EINVAL);
+    return decode_attention_fp8_impl(qkv, k_pool8, v_pool8, k_scale_pool, v_scale_pool, out, workspace, workspace_bytes, batch,
+                                     head_num, kv_head_num, head_size, max_pages * kPageRows, step, step_dev, step_stride,
+                                     page_table, max_pages, stream);
 }
 
 /* DEVICE flags [batch] (0 / 1) applied to every decode-attention launch issued afterwards from this host thread; NULL

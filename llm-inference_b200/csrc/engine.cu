@@ -478,8 +478,8 @@ extern "C" b200_engine* b200_engine_create_paged(const b200_model_config* c, int
     if (!c || batch < 1 || batch > c->max_batch) { fail("bad config / batch"); return nullptr; }
     if (flags & B200_ENGINE_KV_PAGED) {
         const int G = c->kv_head_num > 0 ? c->head_num / c->kv_head_num : 0;
-        if (c->dtype != B200_F16 || c->head_size != 128 || (G != 1 && G != 2 && G != 4 && G != 8) || (flags & B200_ENGINE_KV_FP8)) {
-            fail("B200_ENGINE_KV_PAGED needs fp16, head size 128, head_num / kv_head_num in {1, 2, 4, 8} and an fp16 cache");
+        if (c->dtype != B200_F16 || c->head_size != 128 || (G != 1 && G != 2 && G != 4 && G != 8)) {
+            fail("B200_ENGINE_KV_PAGED needs fp16, head size 128 and head_num / kv_head_num in {1, 2, 4, 8} ({1, 2, 4} with KV_FP8)");
             return nullptr;
         }
     }
@@ -686,6 +686,14 @@ extern "C" int b200_engine_kv_gather(b200_engine* e, void* k_dst, void* v_dst) {
     CU(cudaMemcpyAsync(e->page_rows_dev, rows_host, (size_t)e->batch * sizeof(int), cudaMemcpyHostToDevice, e->stream));
     const size_t dense_layer = (size_t)e->batch * e->hk * e->cfg.max_seq_len * e->d * e->esz;
     for (int l = 0; l < e->cfg.num_layers; ++l) {
+        if (e->kv_fp8) {   // fp8 pages: dequantised on the way out
+            const size_t po8 = (size_t)l * e->layer_kv_elems, so = (size_t)l * e->layer_kv_rows;
+            RC(b200_kv_dequant_fp8_paged(e->k_cache + po8, e->k_scale + so, (char*)k_dst + l * dense_layer, e->page_table, e->max_pages,
+                                         e->page_rows_dev, e->batch, e->hk, e->cfg.max_seq_len, e->d, max_rows, e->stream));
+            RC(b200_kv_dequant_fp8_paged(e->v_cache + po8, e->v_scale + so, (char*)v_dst + l * dense_layer, e->page_table, e->max_pages,
+                                         e->page_rows_dev, e->batch, e->hk, e->cfg.max_seq_len, e->d, max_rows, e->stream));
+            continue;
+        }
         const size_t po = (size_t)l * e->layer_kv_elems * e->esz;
         RC(b200_kv_gather_pages(e->k_cache + po, (char*)k_dst + l * dense_layer, e->page_table, e->max_pages, e->page_rows_dev,
                                 e->batch, e->hk, e->cfg.max_seq_len, e->d, (int)e->esz, max_rows, e->stream));
@@ -698,6 +706,7 @@ extern "C" int b200_engine_kv_gather(b200_engine* e, void* k_dst, void* v_dst) {
 /* fp8 cache only: the whole K and V caches dequantised to fp16 into caller DEVICE buffers [layers, B, hk, max_seq, d] */
 extern "C" int b200_engine_kv_dequant(b200_engine* e, void* k_dst, void* v_dst) {
     if (!e || !e->kv_fp8 || !k_dst || !v_dst) return B200_EINVAL;
+    if (e->kv_paged) return b200_engine_kv_gather(e, k_dst, v_dst);
     const size_t rows = e->layer_kv_rows * e->cfg.num_layers;
     RC(b200_kv_dequant_fp8(e->k_cache, e->k_scale, k_dst, rows, e->d, e->stream));
     RC(b200_kv_dequant_fp8(e->v_cache, e->v_scale, v_dst, rows, e->d, e->stream));
@@ -900,6 +909,11 @@ extern "C" int b200_engine_fill_kv_random(b200_engine* e, int len, uint64_t seed
     if (!e || len < 0 || len >= e->cfg.max_seq_len) return fail("fill_kv: len out of range");
     if (e->kv_paged) {   // every page of every pool gets synthetic rows; set_step hands out the pages of `len` rows
         const size_t prow = (size_t)e->cfg.num_layers * e->n_pages * e->hk;
+        if (e->kv_fp8) {
+            RC(kv_fill_fp8(e->k_cache, e->k_scale, prow, B200_KV_PAGE_ROWS, B200_KV_PAGE_ROWS, e->d, seed * 2 + 1, amp, e->stream));
+            RC(kv_fill_fp8(e->v_cache, e->v_scale, prow, B200_KV_PAGE_ROWS, B200_KV_PAGE_ROWS, e->d, seed * 2 + 2, amp, e->stream));
+            return set_step(e, len);
+        }
         const size_t n = prow * B200_KV_PAGE_ROWS * e->d;
         size_t blocks = (n + 255) / 256;
         if (blocks > 148 * 32) blocks = 148 * 32;
@@ -1071,9 +1085,16 @@ static int enqueue_step_body(b200_engine* e) {
                 else
                     RC(b200_rope_decode_tab(e->qkv, B, e->h, e->hk, e->d, ref_step, e->step_dev, e->cfg.rotary_dim,
                                             e->cfg.rotary_base, e->rope_den, dt, s));
-                RC(b200_kv_append_fp8(e->qkv, kc, vc, ksc, vsc, B, e->h, e->hk, e->d, e->cfg.max_seq_len, ref_step, sd, stride, s));
-                RC(b200_decode_attention_fp8(e->qkv, kc, vc, ksc, vsc, e->attn, e->attn_ws, e->attn_ws_bytes, B, e->h, e->hk,
-                                             e->d, e->cfg.max_seq_len, ref_step, sd, stride, s));
+                if (e->kv_paged) {
+                    RC(b200_kv_append_fp8_paged(e->qkv, kc, vc, ksc, vsc, e->page_table, e->max_pages, B, e->h, e->hk, e->d, ref_step,
+                                                sd, stride, s));
+                    RC(b200_decode_attention_fp8_paged(e->qkv, kc, vc, ksc, vsc, e->page_table, e->max_pages, e->attn, e->attn_ws,
+                                                       e->attn_ws_bytes, B, e->h, e->hk, e->d, ref_step, sd, stride, s));
+                } else {
+                    RC(b200_kv_append_fp8(e->qkv, kc, vc, ksc, vsc, B, e->h, e->hk, e->d, e->cfg.max_seq_len, ref_step, sd, stride, s));
+                    RC(b200_decode_attention_fp8(e->qkv, kc, vc, ksc, vsc, e->attn, e->attn_ws, e->attn_ws_bytes, B, e->h, e->hk,
+                                                 e->d, e->cfg.max_seq_len, ref_step, sd, stride, s));
+                }
             } else if (e->kv_paged) {   // RoPE, then the attention appends the new row into / reads the rows out of the pages
                 if (e->ragged)
                     RC(b200_rope_decode_ragged(e->qkv, B, e->h, e->hk, e->d, e->seq_steps, e->cfg.rotary_dim,
@@ -1365,10 +1386,17 @@ static int prefill_impl(b200_engine* e, const int* ids_host, const int* lens_hos
             RC(b200_qkv_bias_rope_to_cache(q, k, v, qkv, nullptr, pad, hists, B, len, Nt, e->h, e->hk, e->d, len,
                                            e->cfg.rotary_dim, e->cfg.rotary_base, dt, s));
             RC(b200_context_attention(q, k, v, att, pad, lens, hists, B, len, Nt, e->h, e->hk, e->d, len, dt, s));
+            if (e->kv_paged) {
+                RC(b200_kv_quantize_fp8_paged(k, e->k_cache + layer_off, e->k_scale + (size_t)l * e->layer_kv_rows, e->page_table,
+                                              e->max_pages, lens, hists, B, e->hk, len, e->d, len, s));
+                RC(b200_kv_quantize_fp8_paged(v, e->v_cache + layer_off, e->v_scale + (size_t)l * e->layer_kv_rows, e->page_table,
+                                              e->max_pages, lens, hists, B, e->hk, len, e->d, len, s));
+            } else {
             RC(b200_kv_quantize_fp8(k, e->k_cache + layer_off, e->k_scale + (size_t)l * e->layer_kv_rows, lens, hists, B, e->hk,
                                     len, e->cfg.max_seq_len, e->d, len, s));
             RC(b200_kv_quantize_fp8(v, e->v_cache + layer_off, e->v_scale + (size_t)l * e->layer_kv_rows, lens, hists, B, e->hk,
                                     len, e->cfg.max_seq_len, e->d, len, s));
+            }
         } else if (e->kv_paged) {
             // paged cache: k, v of this pass go to a dense scratch slice [B, hk, len, d] (history is empty, checked above), the
             // flash kernel attends over it, and the rows are scattered into the sequences' pages

@@ -371,8 +371,9 @@ class Engine:
         import torch
         c = self.cfg
         shape = (c.num_layers, self.kv_pages_total, c.kv_head_num // c.tp_size, 128, c.head_size)
-        return (self._view(self.lib.b200_engine_k_cache(self.h), shape, torch.float16),
-                self._view(self.lib.b200_engine_v_cache(self.h), shape, torch.float16))
+        dt = torch.uint8 if self.kv_fp8 else torch.float16   # fp8 pages: raw e4m3 bytes (scales are not exposed here)
+        return (self._view(self.lib.b200_engine_k_cache(self.h), shape, dt),
+                self._view(self.lib.b200_engine_v_cache(self.h), shape, dt))
 
     def release_finished(self):
         """pages of the sequences the device has retired go back to the pool; returns the number released"""

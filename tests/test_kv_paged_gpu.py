@@ -237,3 +237,37 @@ def test_cfg4_shape_paged_equals_dense(pkg):
         assert np.array_equal(a, b)
     assert pe.kv_pages_total - pe.kv_pages_free == B * 33
     pe.close(), de.close()
+
+
+@pytest.mark.parametrize("B,lens", [(2, [120, 120]), (5, [130, 5, 128, 64, 127])])
+def test_fp8_pages_equal_the_dense_fp8_cache(pkg, B, lens):
+    """B200_ENGINE_KV_FP8 | B200_ENGINE_KV_PAGED: e4m3 pages + scale pools. Same rounding, same kernels, same order as the
+    dense fp8 cache (which tests/test_kv_fp8_gpu.py pins to the oracle on equally rounded rows): prompt pass + decode steps
+    across a page boundary must give bit-identical logits, ids and (dequantised) cached rows; the pool is half the bytes."""
+    E = pkg.engine
+    max_seq, steps = 300, 10
+    pe = E.Engine(B, max_seq, dtype=pkg.F16, kv_paged=True, kv_fp8=True, **SMALL)
+    de = E.Engine(B, max_seq, dtype=pkg.F16, kv_fp8=True, **SMALL)
+    fp16_paged = E.Engine(B, max_seq, dtype=pkg.F16, kv_paged=True, **SMALL)
+    assert pe.kv_bytes < 0.53 * fp16_paged.kv_bytes
+    fp16_paged.close()
+    for eng in (pe, de):
+        eng.init_random(seed=21, std=0.05)
+    rng = np.random.default_rng(sum(lens))
+    prompts = [rng.integers(0, SMALL["vocab_size"], n).astype(np.int32) for n in lens]
+    if len(set(lens)) == 1:
+        ip, idd = pe.prefill(np.stack(prompts)), de.prefill(np.stack(prompts))
+    else:
+        ip, idd = pe.prefill_ragged(prompts), de.prefill_ragged(prompts)
+    assert np.array_equal(ip, idd)
+    assert torch.equal(pe.logits(), de.logits()), "prefill logits"
+    for s in range(steps):
+        ip, idd = pe.decode_step_host(None), de.decode_step_host(None)
+        assert torch.equal(pe.logits(), de.logits()), f"decode step {s}"
+        assert np.array_equal(ip, idd)
+    kp, vp = pe.kv_caches()
+    kd, vd = de.kv_caches()
+    for b, n in enumerate(lens):
+        assert torch.equal(kp[:, b, :, :n + steps], kd[:, b, :, :n + steps]) and torch.equal(vp[:, b, :, :n + steps], vd[:, b, :, :n + steps])
+    assert pe.kv_pages_total - pe.kv_pages_free == sum((n + steps + P - 1) // P for n in lens)
+    pe.close(), de.close()
