@@ -81,10 +81,10 @@ enum {
                                 * {1,2,4,8}. Bit-identical results to the dense cache on the same launch order
                                 * (tests/test_kv_paged_gpu.py). With KV_FP8 as well: fp8 pages + scale pools
                                 * (head_num / kv_head_num in {1,2,4}), bit-identical to the dense fp8 cache. Decode runs the reference launch order
-                                * with b200_decode_attention_paged; a prompt pass attends over a dense scratch slice and
-                                * scatters its rows into pages (FIRST prompt pass of a sequence only). Pages are taken
-                                * when a sequence grows into them, returned by reset / a new prompt pass /
-                                * b200_engine_release_finished; an empty pool fails the call with B200_ENOMEM. */
+                                * with b200_decode_attention_paged; a prompt pass scatters its rows into the pages behind
+                                * the history and attends with b200_context_attention_paged (fp8 pages: first prompt
+                                * pass of a sequence only). Pages are taken when a sequence grows into them, returned by
+                                * reset / b200_engine_release_finished; an empty pool fails the call with B200_ENOMEM. */
 
 /* mode flags for b200_engine_set_mode */
 #define B200_ENGINE_FUSED 1u   /* fused GEMV prologues/epilogues (default)                    */

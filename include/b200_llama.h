@@ -309,6 +309,12 @@ int b200_decode_attention_paged(const void* qkv, void* k_pool_layer, void* v_poo
                                 int max_pages, void* out, void* workspace, size_t workspace_bytes, int batch,
                                 int head_num, int kv_head_num, int head_size, int max_step, const int* seq_steps_dev,
                                 int step_stride, int append_kv, void* stream);
+/* b200_context_attention over a paged cache: a page is exactly one 128-key tile of the kernel (one list lookup per tile in
+ * the TMA producer). Every page the context touches must be in the list and hold this pass's rows already. */
+int b200_context_attention_paged(const void* q, const void* k_pool_layer, const void* v_pool_layer, const int* page_table,
+                                 int max_pages, int n_pages, void* out, const int* padding_offset, const int* input_len,
+                                 const int* history_len, int batch, int seq_len, int token_num, int head_num, int kv_head_num,
+                                 int head_size, int dtype, void* stream);
 int b200_kv_scatter_pages(const void* src, void* pool, const int* page_table, int max_pages, const int* n_rows,
                           const int* dst_row0, int batch, int kv_head_num, int src_seq, int head_size, int elem_bytes,
                           int max_rows, void* stream);

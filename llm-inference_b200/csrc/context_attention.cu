@@ -66,6 +66,10 @@ struct CtxParams {
     int batch, seq_len, head_num, kv_head_num, max_seq_len, q_tiles;
     float scale_log2;         // 1/sqrt(d) * log2(e)
     unsigned long long* trace;   // debug (b200_context_attention_set_trace): %globaltimer stamps of CTA 0
+    // paged cache (b200_context_attention_paged): K / V are page pools [n_pages, hk, 128, d]; key tile j of sequence b is
+    // page page_table[b * max_pages + j] - a page IS one 128-key tile, so the only change is the TMA row coordinate
+    const int* page_table;
+    int max_pages;
 };
 
 // MN-major operand with the 128B swizzle (canonical layout ((8,n),(8,k)):((1,LBO),(8,SBO)) in 16-byte
@@ -217,6 +221,10 @@ context_attn_tcgen05_kernel(const __grid_constant__ CUtensorMap map_q, const __g
         // ================= TMA producer =================
         const int qrow = (b * p.head_num + head) * p.seq_len + q0;
         const int krow = (b * p.kv_head_num + kvh) * p.max_seq_len;
+        const int* pages = p.page_table ? p.page_table + (size_t)b * p.max_pages : nullptr;
+        auto tile_row = [&](int j) {   // first row of key tile j in the K / V tensor map
+            return pages ? (__ldg(pages + j) * p.kv_head_num + kvh) * kCtxTile : krow + j * kCtxTile;
+        };
         if (lane == 0) {
             mbar_expect_tx(q_full, kTileBytes);
             tma_load_2d(smem + kOffQ, &map_q, 0, qrow, q_full);
@@ -229,15 +237,15 @@ context_attn_tcgen05_kernel(const __grid_constant__ CUtensorMap map_q, const __g
             if (lane == 0) {
                 unsigned char* dst = smem + kOffK + (uint32_t)s * kTileBytes;
                 mbar_expect_tx(&k_full[s], kTileBytes);
-                tma_load_2d(dst, &map_k, 0, krow + j * kCtxTile, &k_full[s]);
-                tma_load_2d(dst + kBoxBytes, &map_k, 64, krow + j * kCtxTile, &k_full[s]);
+                tma_load_2d(dst, &map_k, 0, tile_row(j), &k_full[s]);
+                tma_load_2d(dst + kBoxBytes, &map_k, 64, tile_row(j), &k_full[s]);
             }
             ctx_wait(&v_empty[s], ph ^ 1u);
             if (lane == 0) {
                 unsigned char* dst = smem + kOffV + (uint32_t)s * kTileBytes;
                 mbar_expect_tx(&v_full[s], kTileBytes);
-                tma_load_2d(dst, &map_v, 0, krow + j * kCtxTile, &v_full[s]);
-                tma_load_2d(dst + kBoxBytes, &map_v, 64, krow + j * kCtxTile, &v_full[s]);
+                tma_load_2d(dst, &map_v, 0, tile_row(j), &v_full[s]);
+                tma_load_2d(dst + kBoxBytes, &map_v, 64, tile_row(j), &v_full[s]);
             }
             __syncwarp();
         }
@@ -460,11 +468,11 @@ static unsigned long long* g_ctx_trace = nullptr;
  * key tile j at [8j + 0..5] = S_j issued, P_j V_j issued, S_j visible, maxima exchanged, P_j published, O_{j-1} folded */
 extern "C" void b200_context_attention_set_trace(void* dev_buf) { g_ctx_trace = (unsigned long long*)dev_buf; }
 
-extern "C" int b200_context_attention(const void* q, const void* k_cache_layer, const void* v_cache_layer,
-                                      void* out, const int* padding_offset, const int* input_len,
-                                      const int* history_len, int batch, int seq_len, int token_num,
-                                      int head_num, int kv_head_num, int head_size, int max_seq_len,
-                                      int dtype, void* stream) {
+static int context_attention_impl(const void* q, const void* k_cache_layer, const void* v_cache_layer,
+                                  void* out, const int* padding_offset, const int* input_len,
+                                  const int* history_len, int batch, int seq_len, int token_num,
+                                  int head_num, int kv_head_num, int head_size, int max_seq_len,
+                                  int dtype, const int* page_table, int max_pages, long long n_pages, void* stream) {
     (void)padding_offset;   // the packed token index is the prefix sum of input_len (cal_paddingoffset.cu:51-72)
     if (!q || !k_cache_layer || !v_cache_layer || !out || !input_len || !history_len) return B200_EINVAL;
     if (batch < 1 || seq_len < 1 || token_num < 0 || head_num < 1 || kv_head_num < 1 || head_num % kv_head_num ||
@@ -481,7 +489,7 @@ extern "C" int b200_context_attention(const void* q, const void* k_cache_layer, 
     }
     if (disabled) return B200_EUNSUPPORTED;
     const long long q_rows = (long long)batch * head_num * seq_len;
-    const long long kv_rows = (long long)batch * kv_head_num * max_seq_len;
+    const long long kv_rows = page_table ? n_pages * kv_head_num * kCtxTile : (long long)batch * kv_head_num * max_seq_len;
     if (q_rows + kCtxTile >= (1ll << 31) || kv_rows + kCtxTile >= (1ll << 31)) return B200_EUNSUPPORTED;
     if (token_num == 0) return 0;
     CUtensorMap mq, mk, mv;
@@ -497,6 +505,8 @@ extern "C" int b200_context_attention(const void* q, const void* k_cache_layer, 
     p.q_tiles = (seq_len + kCtxTile - 1) / kCtxTile;
     p.scale_log2 = (1.0f / sqrtf((float)head_size)) * 1.4426950408889634f;
     p.trace = g_ctx_trace;
+    p.page_table = page_table;
+    p.max_pages = max_pages;
     static unsigned long long attr_done = 0;   // one bit per device
     {
         cudaError_t e = ensure_max_dynamic_smem(reinterpret_cast<const void*>(context_attn_tcgen05_kernel), (int)kCtxSmem, attr_done);
@@ -508,4 +518,27 @@ extern "C" int b200_context_attention(const void* q, const void* k_cache_layer, 
                              (cudaStream_t)stream, true, mq, mk, mv, p);
     count_launch();
     return (int)e;
+}
+
+extern "C" int b200_context_attention(const void* q, const void* k_cache_layer, const void* v_cache_layer,
+                                      void* out, const int* padding_offset, const int* input_len,
+                                      const int* history_len, int batch, int seq_len, int token_num,
+                                      int head_num, int kv_head_num, int head_size, int max_seq_len,
+                                      int dtype, void* stream) {
+    return context_attention_impl(q, k_cache_layer, v_cache_layer, out, padding_offset, input_len, history_len, batch, seq_len,
+                                  token_num, head_num, kv_head_num, head_size, max_seq_len, dtype, nullptr, 0, 0, stream);
+}
+
+/* the same over a paged cache: K / V page pools [n_pages, kv_heads, 128, d] and the sequences' page lists (DEVICE int
+ * [batch, max_pages]); a page is exactly one 128-key tile of the kernel, so a tile costs one list lookup in the TMA producer.
+ * Every page a sequence's context touches (history + this pass) must be in its list and hold this pass's rows already. */
+extern "C" int b200_context_attention_paged(const void* q, const void* k_pool_layer, const void* v_pool_layer, const int* page_table,
+                                            int max_pages, int n_pages, void* out, const int* padding_offset, const int* input_len,
+                                            const int* history_len, int batch, int seq_len, int token_num, int head_num,
+                                            int kv_head_num, int head_size, int dtype, void* stream) {
+    if (!page_table || max_pages < 1 || n_pages < 1) return B200_EINVAL;
+    static_assert(kCtxTile == B200_KV_PAGE_ROWS, "a page must be one key tile");
+    return context_attention_impl(q, k_pool_layer, v_pool_layer, out, padding_offset, input_len, history_len, batch, seq_len,
+                                  token_num, head_num, kv_head_num, head_size, max_pages * kCtxTile, dtype, page_table, max_pages,
+                                  n_pages, stream);
 }

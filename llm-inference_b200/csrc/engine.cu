@@ -1298,20 +1298,14 @@ static int prefill_impl(b200_engine* e, const int* ids_host, const int* lens_hos
     if (e->kv_paged) {
         if (!flash) return fail("paged KV cache: the prompt pass needs the flash context attention", B200_EUNSUPPORTED);
         for (int b = 0; b < B; ++b)
-            if (hist_b[b] != 0)
-                return fail("paged KV cache: a prompt pass over an existing history is not supported (first pass only)",
-                            B200_EUNSUPPORTED);
-        // every sequence starts afresh: its old pages go back, then it takes the pages of its prompt
-        CU(cudaStreamSynchronize(s));
-        for (int b = 0; b < B; ++b) release_pages(e, b);
-        e->seq_released.assign(B, 0);
+            if (e->seq_released[b])
+                return fail("paged KV cache: a retired sequence gave its pages back - reset the engine before a new prompt pass");
+        // the pages of history + prompt (fp16 pages: the context attention reads the history through the page lists; fp8
+        // pages are first-pass only, checked above)
         for (int b = 0; b < B; ++b) {
-            const int r = ensure_pages(e, b, len_b[b]);
-            if (r < 0) {   // the pool cannot hold these prompts: leave an empty, consistent engine behind
-                const std::string why = g_err;
-                set_step(e, 0);
-                return fail(why, r);
-            }
+            const int r = ensure_pages(e, b, hist_b[b] + len_b[b]);
+            if (r < 0) return r;   // the pool cannot hold these prompts: nothing launched, cached rows and lengths untouched (lists
+                                   // that grew before the failure keep their pages: the sequences grow into them, reset returns them)
         }
         RC(upload_pages(e));
     }
@@ -1398,15 +1392,17 @@ static int prefill_impl(b200_engine* e, const int* ids_host, const int* lens_hos
                                     len, e->cfg.max_seq_len, e->d, len, s));
             }
         } else if (e->kv_paged) {
-            // paged cache: k, v of this pass go to a dense scratch slice [B, hk, len, d] (history is empty, checked above), the
-            // flash kernel attends over it, and the rows are scattered into the sequences' pages
-            RC(b200_qkv_bias_rope_to_cache(q, k, v, qkv, nullptr, pad, hists, B, len, Nt, e->h, e->hk, e->d, len,
-                                           e->cfg.rotary_dim, e->cfg.rotary_base, dt, s));
-            RC(b200_context_attention(q, k, v, att, pad, lens, hists, B, len, Nt, e->h, e->hk, e->d, len, dt, s));
+            // paged cache: k, v of this pass are rotated into a padded scratch slice [B, hk, len, d] (launchAddFusedQKVBias-
+            // TransposeAndRoPE's own output layout), scattered into the sequences' pages behind their history (= launchConcat-
+            // KVCache), and the flash kernel attends over the pages: a page is one of its 128-key tiles
+            RC(b200_qkv_bias_rope_transpose(q, k, v, qkv, nullptr, pad, hists, lens, B, len, Nt, e->h, e->hk, e->d,
+                                            e->cfg.rotary_dim, e->cfg.rotary_base, dt, s));
             RC(b200_kv_scatter_pages(k, e->k_cache + layer_off * es, e->page_table, e->max_pages, lens, hists, B, e->hk, len,
                                      e->d, (int)es, len, s));
             RC(b200_kv_scatter_pages(v, e->v_cache + layer_off * es, e->page_table, e->max_pages, lens, hists, B, e->hk, len,
                                      e->d, (int)es, len, s));
+            RC(b200_context_attention_paged(q, e->k_cache + layer_off * es, e->v_cache + layer_off * es, e->page_table, e->max_pages,
+                                            e->n_pages, att, pad, lens, hists, B, len, Nt, e->h, e->hk, e->d, dt, s));
         } else {
         // bias/RoPE/transpose with ConcatKV folded in: k, v land in the cache rows directly
         RC(b200_qkv_bias_rope_to_cache(q, e->k_cache + layer_off * es, e->v_cache + layer_off * es, qkv, nullptr, pad, hists,

@@ -6,8 +6,7 @@ The paged cache keeps the same rows in pages [n_pages, hk, 128, d] named by one 
 the strongest one available: NOTHING about the arithmetic changes, so on the same launch order the paged path must
 be BIT-IDENTICAL to the dense path (attention output, appended rows, logits, greedy ids) - and the dense path is pinned
 to the oracle (tests/test_decode_gpu.py, test_engine_gpu.py, test_7b_shapes_gpu.py); the kernel-level test also checks
-the oracle directly. On top: the allocator (pages taken as sequences grow, returned by reset / a new prompt pass /
-retirement, a clean B200_ENOMEM when the pool is empty) and a pool smaller than the dense cache serving a ragged batch."""
+the oracle directly. On top: the allocator (pages taken as sequences grow, returned by reset / retirement, a clean B200_ENOMEM when the pool is empty) and a pool smaller than the dense cache serving a ragged batch."""
 import ctypes as C
 
 import numpy as np
@@ -148,9 +147,14 @@ def test_engine_paged_equals_dense_prefill_then_decode(pkg, B, lens):
         assert np.array_equal(ip, idd)
     _same_rows(pe, de, [n + steps for n in lens])
     assert pe.kv_pages_total - pe.kv_pages_free == sum((n + steps + P - 1) // P for n in lens)
-    # a second prompt pass over the existing history is refused loudly, not run on the wrong rows
-    with pytest.raises(RuntimeError, match="first pass only"):
-        pe.prefill_ragged([p[:3] for p in prompts])
+    # a second prompt pass appends behind the history: the context attention reads the history rows through the page lists
+    more = [rng.integers(0, SMALL["vocab_size"], 3 + 10 * b).astype(np.int32) for b in range(B)]
+    assert np.array_equal(pe.prefill_ragged(more), de.prefill_ragged(more))
+    assert torch.equal(pe.logits(), de.logits()), "second prompt pass over a paged history"
+    _same_rows(pe, de, [n + steps + len(m) for n, m in zip(lens, more)])
+    for s in range(2):
+        assert np.array_equal(pe.decode_step_host(None), de.decode_step_host(None))
+        assert torch.equal(pe.logits(), de.logits()), f"decode step {s} after the second prompt pass"
     pe.close(), de.close()
 
 
@@ -187,7 +191,9 @@ def test_small_pool_serves_a_ragged_batch_and_fails_cleanly_when_empty(pkg):
     pe.reset()
     with pytest.raises(RuntimeError, match="page pool exhausted"):
         pe.prefill(rng.integers(0, SMALL["vocab_size"], (B, 400)).astype(np.int32))
-    assert pe.kv_pages_free == 10 and pe.step == 0
+    assert pe.step == 0   # nothing ran; the pages the first sequences took before the failure go back with a reset
+    pe.reset()
+    assert pe.kv_pages_free == 10
     de.reset()
     assert np.array_equal(pe.prefill_ragged(prompts), de.prefill_ragged(prompts))
     assert torch.equal(pe.logits(), de.logits())
