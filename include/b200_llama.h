@@ -309,6 +309,11 @@ int b200_decode_attention_paged(const void* qkv, void* k_pool_layer, void* v_poo
                                 int max_pages, void* out, void* workspace, size_t workspace_bytes, int batch,
                                 int head_num, int kv_head_num, int head_size, int max_step, const int* seq_steps_dev,
                                 int step_stride, int append_kv, void* stream);
+/* b200_qkv_bias_rope_to_cache into a paged cache: k, v of token t of sequence b -> row history_len[b] + t of its pages */
+int b200_qkv_bias_rope_to_pages(void* q, void* k_pool_layer, void* v_pool_layer, const int* page_table, int max_pages,
+                                const void* qkv, const void* bias, const int* padding_offset, const int* history_len,
+                                int batch, int seq_len, int token_num, int head_num, int kv_head_num, int head_size,
+                                int rotary_dim, float rotary_base, int dtype, void* stream);
 /* b200_context_attention over a paged cache: a page is exactly one 128-key tile of the kernel (one list lookup per tile in
  * the TMA producer). Every page the context touches must be in the list and hold this pass's rows already. */
 int b200_context_attention_paged(const void* q, const void* k_pool_layer, const void* v_pool_layer, const int* page_table,

@@ -64,6 +64,7 @@ PROTOTYPES = {
     "b200_kv_quantize_fp8": (_i, [_vp] * 5 + [_i] * 6 + [_vp]),
     "b200_kv_dequant_fp8": (_i, [_vp, _vp, _vp, _sz, _i, _vp]),
     "b200_decode_attention_paged": (_i, [_vp] * 4 + [_i] + [_vp, _vp, _sz] + [_i] * 5 + [_vp, _i, _i, _vp]),
+    "b200_qkv_bias_rope_to_pages": (_i, [_vp] * 4 + [_i] + [_vp] * 4 + [_i] * 7 + [C.c_float, _i, _vp]),
     "b200_context_attention_paged": (_i, [_vp] * 4 + [_i, _i] + [_vp] * 4 + [_i] * 7 + [_vp]),
     "b200_kv_scatter_pages": (_i, [_vp] * 3 + [_i] + [_vp, _vp] + [_i] * 6 + [_vp]),
     "b200_kv_gather_pages": (_i, [_vp] * 3 + [_i] + [_vp] + [_i] * 6 + [_vp]),

@@ -1392,15 +1392,12 @@ static int prefill_impl(b200_engine* e, const int* ids_host, const int* lens_hos
                                     len, e->cfg.max_seq_len, e->d, len, s));
             }
         } else if (e->kv_paged) {
-            // paged cache: k, v of this pass are rotated into a padded scratch slice [B, hk, len, d] (launchAddFusedQKVBias-
-            // TransposeAndRoPE's own output layout), scattered into the sequences' pages behind their history (= launchConcat-
-            // KVCache), and the flash kernel attends over the pages: a page is one of its 128-key tiles
-            RC(b200_qkv_bias_rope_transpose(q, k, v, qkv, nullptr, pad, hists, lens, B, len, Nt, e->h, e->hk, e->d,
-                                            e->cfg.rotary_dim, e->cfg.rotary_base, dt, s));
-            RC(b200_kv_scatter_pages(k, e->k_cache + layer_off * es, e->page_table, e->max_pages, lens, hists, B, e->hk, len,
-                                     e->d, (int)es, len, s));
-            RC(b200_kv_scatter_pages(v, e->v_cache + layer_off * es, e->page_table, e->max_pages, lens, hists, B, e->hk, len,
-                                     e->d, (int)es, len, s));
+            // paged cache: the RoPE kernel writes the rotated k and the v rows straight into the sequences' pages behind their
+            // history (launchAddFusedQKVBiasTransposeAndRoPE + launchConcatKVCache in one pass, as for the dense cache), and the
+            // flash kernel attends over the pages: a page is one of its 128-key tiles
+            RC(b200_qkv_bias_rope_to_pages(q, e->k_cache + layer_off * es, e->v_cache + layer_off * es, e->page_table, e->max_pages,
+                                           qkv, nullptr, pad, hists, B, len, Nt, e->h, e->hk, e->d, e->cfg.rotary_dim,
+                                           e->cfg.rotary_base, dt, s));
             RC(b200_context_attention_paged(q, e->k_cache + layer_off * es, e->v_cache + layer_off * es, e->page_table, e->max_pages,
                                             e->n_pages, att, pad, lens, hists, B, len, Nt, e->h, e->hk, e->d, dt, s));
         } else {

@@ -82,7 +82,8 @@ qkv_rope_transpose_kernel(T* __restrict__ q, T* __restrict__ k, T* __restrict__ 
                           const T* __restrict__ qkv, const T* __restrict__ bias,
                           const int* __restrict__ padding_offset,
                           const int* __restrict__ history_len, int seq_len, int head_num,
-                          int kv_head_num, int head_size, int rot_dim, float base, int kv_rows, int to_cache) {
+                          int kv_head_num, int head_size, int rot_dim, float base, int kv_rows, int to_cache,
+                          const int* __restrict__ page_table, int max_pages) {
     constexpr int E = DT<T>::kPer16B;
     extern __shared__ float2 cs[];  // [head_size/2]; identity beyond rot_dim/2
     pdl_wait();
@@ -98,6 +99,13 @@ qkv_rope_transpose_kernel(T* __restrict__ q, T* __restrict__ k, T* __restrict__ 
     // to_cache: a row beyond the cache slice (history + length > max_seq_len, a caller error the launcher cannot see:
     // the lengths live on the device) is dropped, never written outside the slice
     const bool kv_ok = kv_local >= 0 && kv_local < kv_rows;
+    // paged cache (page_table != NULL, to_cache): k / v are page pools [n_pages, hk, 128, d]; the row lives in the page the
+    // sequence's list names for it. kv_head_row(h) = index of (kv head h, this token's row) among the rows of k / v.
+    const int page = (page_table != nullptr && kv_ok) ? page_table[(size_t)b * max_pages + kv_local / B200_KV_PAGE_ROWS] : 0;
+    auto kv_head_row = [&](int h) -> size_t {
+        if (page_table != nullptr) return ((size_t)page * kv_head_num + h) * B200_KV_PAGE_ROWS + (size_t)(kv_local % B200_KV_PAGE_ROWS);
+        return ((size_t)b * kv_head_num + h) * kv_rows + (size_t)kv_local;
+    };
     const int half_d = head_size >> 1, half_rot = rot_dim >> 1;
     for (int i = threadIdx.x; i < half_d; i += blockDim.x)
         cs[i] = (i < half_rot) ? rope_cos_sin(i, rot_dim, base, (float)pos) : make_float2(1.f, 0.f);
@@ -134,7 +142,7 @@ qkv_rope_transpose_kernel(T* __restrict__ q, T* __restrict__ k, T* __restrict__ 
             if (head < head_num)
                 d = q + (((size_t)b * head_num + head) * seq_len + local) * head_size + p * E;
             else if (kv_ok)
-                d = k + (((size_t)b * kv_head_num + (head - head_num)) * kv_rows + kv_local) * head_size + p * E;
+                d = k + kv_head_row(head - head_num) * head_size + p * E;
             else
                 continue;
             st16(d, Unpack<T>::put(lo));
@@ -153,7 +161,7 @@ qkv_rope_transpose_kernel(T* __restrict__ q, T* __restrict__ k, T* __restrict__ 
                 for (int i = 0; i < E; ++i) f[i] += bf[i];
                 val = Unpack<T>::put(f);
             }
-            if (kv_ok) st16(v + (((size_t)b * kv_head_num + head) * kv_rows + kv_local) * head_size + p * E, val);
+            if (kv_ok) st16(v + kv_head_row(head) * head_size + p * E, val);
         }
     }
     pdl_launch_dependents();
@@ -174,7 +182,8 @@ template <typename T>
 static int qkv_rope_impl(void* q, void* k, void* v, const void* qkv, const void* bias,
                          const int* padding_offset, const int* history_len, int seq_len,
                          int token_num, int head_num, int kv_head_num, int head_size, int rot_dim,
-                         float base, cudaStream_t s, int kv_rows = 0, int to_cache = 0) {
+                         float base, cudaStream_t s, int kv_rows = 0, int to_cache = 0, const int* page_table = nullptr,
+                         int max_pages = 0) {
     constexpr int E = DT<T>::kPer16B;
     if (!to_cache) kv_rows = seq_len;
     B200_RETURN_IF((head_size / 2) % E != 0, B200_EUNSUPPORTED);
@@ -183,11 +192,11 @@ static int qkv_rope_impl(void* q, void* k, void* v, const void* qkv, const void*
     if (bias)
         e = launch_k(qkv_rope_transpose_kernel<T, true>, dim3(token_num), dim3(256), smem, s, true,
                      (T*)q, (T*)k, (T*)v, (const T*)qkv, (const T*)bias, padding_offset,
-                     history_len, seq_len, head_num, kv_head_num, head_size, rot_dim, base, kv_rows, to_cache);
+                     history_len, seq_len, head_num, kv_head_num, head_size, rot_dim, base, kv_rows, to_cache, page_table, max_pages);
     else
         e = launch_k(qkv_rope_transpose_kernel<T, false>, dim3(token_num), dim3(256), smem, s,
                      true, (T*)q, (T*)k, (T*)v, (const T*)qkv, (const T*)nullptr, padding_offset,
-                     history_len, seq_len, head_num, kv_head_num, head_size, rot_dim, base, kv_rows, to_cache);
+                     history_len, seq_len, head_num, kv_head_num, head_size, rot_dim, base, kv_rows, to_cache, page_table, max_pages);
     count_launch();
     return (int)e;
 }
@@ -297,5 +306,32 @@ extern "C" int b200_qkv_bias_rope_to_cache(void* q, void* k_cache_layer, void* v
         return b200::qkv_rope_impl<__half>(q, k_cache_layer, v_cache_layer, qkv, bias, padding_offset, history_len,
                                            seq_len, token_num, head_num, kv_head_num, head_size, rotary_dim,
                                            rotary_base, s, max_seq_len, 1);
+    return B200_EINVAL;
+}
+
+/* b200_qkv_bias_rope_to_cache into a PAGED cache (kv_paged.cu): the rotated keys and the values of token t of sequence b go
+ * to row history_len[b] + t of the sequence's pages (pools [n_pages, kv_head_num, 128, head_size], page lists DEVICE int
+ * [batch, max_pages]); fp16 / fp32. The pages must already be in the lists. */
+extern "C" int b200_qkv_bias_rope_to_pages(void* q, void* k_pool_layer, void* v_pool_layer, const int* page_table, int max_pages,
+                                           const void* qkv, const void* bias, const int* padding_offset,
+                                           const int* history_len, int batch, int seq_len, int token_num, int head_num,
+                                           int kv_head_num, int head_size, int rotary_dim, float rotary_base, int dtype,
+                                           void* stream) {
+    B200_RETURN_IF(!q || !k_pool_layer || !v_pool_layer || !page_table || !qkv || !padding_offset || !history_len, B200_EINVAL);
+    B200_RETURN_IF(batch <= 0 || seq_len <= 0 || token_num < 0 || head_num <= 0 || kv_head_num <= 0 || head_size <= 0 ||
+                       max_pages <= 0,
+                   B200_EINVAL);
+    B200_RETURN_IF(rotary_dim <= 0 || rotary_dim > head_size || (rotary_dim & 1), B200_EINVAL);
+    if (token_num == 0) return B200_OK;
+    cudaStream_t s = (cudaStream_t)stream;
+    const int rows = max_pages * B200_KV_PAGE_ROWS;
+    if (dtype == B200_F32)
+        return b200::qkv_rope_impl<float>(q, k_pool_layer, v_pool_layer, qkv, bias, padding_offset, history_len, seq_len,
+                                          token_num, head_num, kv_head_num, head_size, rotary_dim, rotary_base, s, rows, 1,
+                                          page_table, max_pages);
+    if (dtype == B200_F16)
+        return b200::qkv_rope_impl<__half>(q, k_pool_layer, v_pool_layer, qkv, bias, padding_offset, history_len, seq_len,
+                                           token_num, head_num, kv_head_num, head_size, rotary_dim, rotary_base, s, rows, 1,
+                                           page_table, max_pages);
     return B200_EINVAL;
 }
