@@ -135,6 +135,11 @@ b200_engine* b200_engine_create_ex(const b200_model_config* cfg, int batch, unsi
  * Flags are cleared by reset / fill_kv_random / every prompt pass. */
 int b200_engine_set_eos(b200_engine* e, int eos_id);
 int b200_engine_get_finished(b200_engine* e, unsigned char* flags_host /* [batch] */);
+/* Continuous batching, data-path half: one sequence slot back to "nothing cached" (flag cleared, pages returned) while the
+ * others keep their caches and positions; then b200_engine_prefill_ragged with length 0 for the slots that sit the pass out
+ * (they keep the token they were about to decode). The scheduler that decides WHEN is the caller's. No reference
+ * counterpart: llama.cpp:319-361 runs a fixed batch to the end. */
+int b200_engine_reset_slot(b200_engine* e, int slot);
 /* create_ex with the size of each layer's page pool (B200_ENGINE_KV_PAGED; 0 = batch * ceil(max_seq_len / 128)) */
 b200_engine* b200_engine_create_paged(const b200_model_config* cfg, int batch, unsigned flags, int n_pages);
 int b200_engine_kv_is_paged(const b200_engine* e);

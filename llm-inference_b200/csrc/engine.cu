@@ -821,6 +821,30 @@ static int set_step(b200_engine* e, int n) {
 
 extern "C" int b200_engine_reset(b200_engine* e) { return e ? set_step(e, 0) : B200_EINVAL; }
 
+/* One sequence slot back to "nothing cached" while the others keep their caches and positions (the data-path half of
+ * continuous batching: a retired sequence's slot takes the next request; the reference's loop, llama.cpp:319-361, only
+ * ever runs a fixed batch to the end). Clears the slot's `finished` flag, returns its pages (paged cache) and puts the
+ * engine into the per-sequence (ragged) step form. Follow with b200_engine_prefill_ragged, length 0 for the other slots. */
+extern "C" int b200_engine_reset_slot(b200_engine* e, int b) {
+    if (!e || b < 0 || b >= e->batch) return fail("reset_slot: bad slot");
+    CU(cudaStreamSynchronize(e->stream));
+    if (!e->ragged) {   // the per-sequence step array takes over from the shared step
+        std::vector<int> steps(e->batch);
+        for (int i = 0; i < e->batch; ++i) steps[i] = e->seq_cached[i] + 1;
+        CU(cudaMemcpy(e->seq_steps, steps.data(), sizeof(int) * e->batch, cudaMemcpyHostToDevice));
+        e->ragged = true;
+    }
+    const int one = 1;
+    CU(cudaMemcpy(e->seq_steps + b, &one, sizeof(int), cudaMemcpyHostToDevice));
+    CU(cudaMemset(e->finished + b, 0, 1));
+    e->seq_cached[b] = 0;
+    if (e->kv_paged) {
+        release_pages(e, b);
+        e->seq_released[b] = 0;
+    }
+    return B200_OK;
+}
+
 /* eos_id >= 0 switches sequence retirement on (sampling.cu:81-83: finished[b] = (id == end_id)); -1 off. The flags are
  * cleared by reset / fill_kv / every prompt pass. The persistent whole-step kernel does not look at them (its default use
  * is batch 1, where the generation loop simply stops): engines with retirement on run the multi-kernel orders. */
@@ -1237,9 +1261,14 @@ extern "C" int b200_engine_decode_step_host(b200_engine* e, const int* ids_in_ho
 // (fp32, head size != 128) the reference-order GPU sequence runs instead.
 // ------------------------------------------------------------------------------------------
 namespace b200 {
-__global__ void set_ids_step_kernel(int* ids_cur, const int* ids_next, int* step, int batch, int ref_step) {
+// after a prompt pass: the token each sequence decodes next. A sequence that took no tokens in this pass (lens[b] == 0: the
+// others were being (re)filled around it) keeps the token it was about to decode, mirrored into ids_next for the readers.
+__global__ void set_ids_step_kernel(int* ids_cur, int* ids_next, int* step, int batch, int ref_step, const int* lens) {
     pdl_wait();
-    if (threadIdx.x < batch) ids_cur[threadIdx.x] = ids_next[threadIdx.x];
+    if (threadIdx.x < batch) {
+        if (lens != nullptr && lens[threadIdx.x] == 0) ids_next[threadIdx.x] = ids_cur[threadIdx.x];
+        else ids_cur[threadIdx.x] = ids_next[threadIdx.x];
+    }
     if (threadIdx.x == 0) *step = ref_step;
 }
 }  // namespace b200
@@ -1252,16 +1281,21 @@ static int prefill_impl(b200_engine* e, const int* ids_host, const int* lens_hos
     long long total = 0;
     int len = 0, ctx = 0;   // longest prompt / longest context of this call: the padded extents
     std::vector<int> len_b(B), hist_b(B), cum_b(B + 1, 0);
+    bool any_zero = false;
     for (int b = 0; b < B; ++b) {
         len_b[b] = lens_host ? lens_host[b] : uniform_len;
         hist_b[b] = e->seq_cached[b];
-        if (len_b[b] < 1) return fail("prefill: every sequence needs at least one prompt token");
+        // ragged form only: a sequence may sit a pass out (0 tokens) while others are (re)filled - it keeps its cache, its
+        // position, its `finished` flag and the token it decodes next (continuous batching: b200_engine_reset_slot + this)
+        if (len_b[b] < (lens_host ? 0 : 1)) return fail("prefill: a prompt length is negative (or 0 in the uniform form)");
+        any_zero |= len_b[b] == 0;
         if (hist_b[b] + len_b[b] > e->cfg.max_seq_len - 1) return fail("prefill: prompt does not fit the KV cache");
         total += len_b[b];
         cum_b[b + 1] = (int)total;
         len = std::max(len, len_b[b]);
         ctx = std::max(ctx, hist_b[b] + len_b[b]);
     }
+    if (total < 1) return fail("prefill: no prompt tokens at all");
     if ((long long)B * len >= (1ll << 24)) return fail("prefill: too many tokens");
     const int Nt = (int)total;
     const size_t Np = (size_t)B * len;   // rows of the re-padded [B, h, len, d] buffers
@@ -1288,18 +1322,20 @@ static int prefill_impl(b200_engine* e, const int* ids_host, const int* lens_hos
     }
     const size_t o_lws = take(lin_ws + 256);
     const bool flash = dt == B200_F16 && e->d == 128 && !(getenv("B200_NO_TCGEN05") && getenv("B200_NO_TCGEN05")[0] == '1');
+    if (any_zero && !flash)
+        return fail("prefill: sequences that sit a pass out need the flash context attention (fp16, head size 128)", B200_EUNSUPPORTED);
     if (e->kv_fp8) {
         if (!flash) return fail("fp8 KV cache: the prompt pass needs the flash context attention", B200_EUNSUPPORTED);
         for (int b = 0; b < B; ++b)
-            if (hist_b[b] != 0)
+            if (hist_b[b] != 0 && len_b[b] > 0)
                 return fail("fp8 KV cache: a prompt pass over an existing history is not supported (first pass only)",
                             B200_EUNSUPPORTED);
     }
     if (e->kv_paged) {
         if (!flash) return fail("paged KV cache: the prompt pass needs the flash context attention", B200_EUNSUPPORTED);
         for (int b = 0; b < B; ++b)
-            if (e->seq_released[b])
-                return fail("paged KV cache: a retired sequence gave its pages back - reset the engine before a new prompt pass");
+            if (e->seq_released[b] && len_b[b] > 0)
+                return fail("paged KV cache: a retired sequence gave its pages back - b200_engine_reset_slot before its next prompt");
         // the pages of history + prompt (fp16 pages: the context attention reads the history through the page lists; fp8
         // pages are first-pass only, checked above)
         for (int b = 0; b < B; ++b) {
@@ -1356,7 +1392,12 @@ static int prefill_impl(b200_engine* e, const int* ids_host, const int* lens_hos
     CU(cudaMemcpyAsync(ctxs, e->pf_pinned + Nt + 2 * B, (size_t)B * sizeof(int), cudaMemcpyHostToDevice, s));
     CU(cudaMemcpyAsync(e->seq_steps, e->pf_pinned + Nt + 3 * B, (size_t)B * sizeof(int), cudaMemcpyHostToDevice, s));
     CU(cudaEventRecord(e->pf_copied, s));
-    CU(cudaMemsetAsync(e->finished, 0, B, s));   // a prompt pass starts every sequence afresh
+    if (!any_zero) {
+        CU(cudaMemsetAsync(e->finished, 0, B, s));   // a prompt pass starts every sequence afresh
+    } else {
+        for (int b = 0; b < B; ++b)
+            if (len_b[b] > 0) CU(cudaMemsetAsync(e->finished + b, 0, 1, s));   // ... every sequence that takes part in it
+    }
     auto linear = [&](const void* in, const void* W, void* out, int N, int K) {
         return b200_linear(in, W, nullptr, out, Nt, N, K, 1, dt, lws, lin_ws + 256, s);
     };
@@ -1442,15 +1483,16 @@ static int prefill_impl(b200_engine* e, const int* ids_host, const int* lens_hos
                              (size_t)H * es, (size_t)B, cudaMemcpyDeviceToDevice, s));
     } else {
         for (int b = 0; b < B; ++b)
-            CU(cudaMemcpyAsync((char*)e->hidden + (size_t)b * H * es, (const char*)x + (size_t)(cum_b[b + 1] - 1) * H * es,
-                               (size_t)H * es, cudaMemcpyDeviceToDevice, s));
+            if (len_b[b] > 0)   // (a sequence that sat the pass out keeps its stale row: its logits are not used)
+                CU(cudaMemcpyAsync((char*)e->hidden + (size_t)b * H * es, (const char*)x + (size_t)(cum_b[b + 1] - 1) * H * es,
+                                   (size_t)H * es, cudaMemcpyDeviceToDevice, s));
     }
     CU(cudaMemcpyAsync(e->partial, e->hidden, (size_t)B * H * es, cudaMemcpyDeviceToDevice, s));
     RC(b200_rmsnorm(e->partial, nullptr, e->final_norm, B, H, e->cfg.rms_eps, dt, s));
     RC(b200_linear(e->partial, e->lm_head, nullptr, e->logits, B, e->V, H, 1, dt, e->lin_ws, e->lin_ws_bytes, s));
     RC(b200_argmax(e->logits, e->ids_next, B, e->V, dt, s));
-    CU(launch_k(set_ids_step_kernel, dim3(1), dim3(1024), 0, s, false, e->ids_cur, (const int*)e->ids_next, e->step_dev, B,
-                ctx + 1));
+    CU(launch_k(set_ids_step_kernel, dim3(1), dim3(1024), 0, s, false, e->ids_cur, e->ids_next, e->step_dev, B, ctx + 1,
+                any_zero ? (const int*)lens : (const int*)nullptr));
     count_launch();
     e->step = ctx;
     for (int b = 0; b < B; ++b) e->seq_cached[b] = hist_b[b] + len_b[b];

@@ -27,6 +27,7 @@ ENGINE_PROTOTYPES = {
     "b200_engine_create": (_vp, [C.POINTER(ModelConfig), _i]),
     "b200_engine_create_ex": (_vp, [C.POINTER(ModelConfig), _i, C.c_uint]),
     "b200_engine_create_paged": (_vp, [C.POINTER(ModelConfig), _i, C.c_uint, _i]),
+    "b200_engine_reset_slot": (_i, [_vp, _i]),
     "b200_engine_kv_is_paged": (_i, [_vp]),
     "b200_engine_kv_pages_total": (_i, [_vp]),
     "b200_engine_kv_pages_free": (_i, [_vp]),
@@ -374,6 +375,10 @@ class Engine:
         dt = torch.uint8 if self.kv_fp8 else torch.float16   # fp8 pages: raw e4m3 bytes (scales are not exposed here)
         return (self._view(self.lib.b200_engine_k_cache(self.h), shape, dt),
                 self._view(self.lib.b200_engine_v_cache(self.h), shape, dt))
+
+    def reset_slot(self, slot):
+        """one sequence slot back to 'nothing cached' while the others keep theirs (then prefill_ragged with [] for the others)"""
+        self._ck(self.lib.b200_engine_reset_slot(self.h, int(slot)), "reset_slot")
 
     def release_finished(self):
         """pages of the sequences the device has retired go back to the pool; returns the number released"""

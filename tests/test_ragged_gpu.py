@@ -146,8 +146,12 @@ def test_reset_returns_to_one_step(pkg):
     assert list(eng.seq_steps) == [5, 9] and eng.step == 9
     eng.reset()
     assert list(eng.seq_steps) == [0, 0] and eng.step == 0
+    # a zero-length entry sits the pass out (continuous batching, tests/test_slot_refill_gpu.py); no tokens at all is an error
+    eng.prefill_ragged([np.arange(5, dtype=np.int32), np.zeros(0, np.int32)])
+    assert list(eng.seq_steps) == [5, 0]
+    eng.reset()
     with pytest.raises(RuntimeError):
-        eng.prefill_ragged([np.arange(5, dtype=np.int32), np.zeros(0, np.int32)])
+        eng.prefill_ragged([np.zeros(0, np.int32), np.zeros(0, np.int32)])
     with pytest.raises(RuntimeError):
         eng.prefill_ragged([np.arange(5, dtype=np.int32), np.arange(64, dtype=np.int32)])
     eng.close()
