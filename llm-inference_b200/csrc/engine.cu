@@ -753,7 +753,7 @@ extern "C" int b200_engine_set_p2p(b200_engine* e, b200_p2p* comm) {
         e->program = nullptr;
         cudaFree(e->down_t); cudaFree(e->ffn_acc); cudaFree(e->o_packed); cudaFree(e->o_acc);
         e->down_t = nullptr; e->ffn_acc = nullptr; e->o_packed = nullptr; e->o_acc = nullptr;
-        if (!e->kv_fp8) build_program(e);
+        if (!e->kv_fp8 && !e->kv_paged) build_program(e);
     }
     return B200_OK;
 }
