@@ -342,6 +342,10 @@ class Engine:
         if self.kv_paged:   # gathered COPIES laid out as the dense cache; rows beyond a sequence's length are zero
             k = torch.zeros(shape, dtype=td, device="cuda")
             v = torch.zeros(shape, dtype=td, device="cuda")
+            # the zero fill runs on torch's stream, the gather on the engine's (non-blocking) stream: without this the fill can
+            # land on top of rows the gather has already written (seen in the full test suite, where the block comes out of
+            # torch's cache and the fill is still queued when the gather starts)
+            torch.cuda.synchronize()
             self._ck(self.lib.b200_engine_kv_gather(self.h, C.c_void_p(k.data_ptr()), C.c_void_p(v.data_ptr())), "kv_gather")
             return k, v
         if self.kv_fp8:
