@@ -233,6 +233,7 @@ def test_cfg4_shape_paged_equals_dense(pkg):
     # copy the paged engine's rows into the dense cache (the two fills draw different rows)
     kp, vp = pe.kv_caches()
     kd, vd = de.kv_caches()
+    torch.cuda.synchronize()
     kd.copy_(kp), vd.copy_(vp)
     torch.cuda.synchronize()   # torch's stream, not the engines': the copies must have landed before the first step
     del kp, vp
